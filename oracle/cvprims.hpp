@@ -12,6 +12,7 @@
 // explicit byte stride.
 #pragma once
 #include <cfloat>
+#include <cstddef>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>

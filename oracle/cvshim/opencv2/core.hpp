@@ -1,0 +1,224 @@
+// oracle/cvshim/opencv2/core.hpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+//
+// A minimal stand-in for the slice of the OpenCV C++ API that the reference's
+// src/ORBextractor.cc touches, so that file can be compiled UNMODIFIED from
+// /root/reference into oracle/_ref/ (OpenCV C++ is not installed in this image).
+// The five image primitives forward to oracle/cvprims.hpp, whose arithmetic is pinned
+// against cv2 4.13.0.  Nothing here is shipped or linked into the product library.
+#pragma once
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../cvprims.hpp"
+
+typedef unsigned char uchar;
+#define CV_8U 0
+#define CV_8UC1 0
+#define CV_32F 5
+#define CV_PI 3.1415926535897932384626433832795
+
+static inline int cvRound(double v) { return cvprims::cv_round(v); }
+static inline int cvRound(float v) { return cvprims::cv_round(v); }
+static inline int cvRound(int v) { return v; }
+static inline int cvFloor(double v) { return cvprims::cv_floor(v); }
+static inline int cvCeil(double v) { return cvprims::cv_ceil(v); }
+
+namespace cv {
+
+template <typename T>
+struct Point_ {
+  T x, y;
+  Point_() : x(0), y(0) {}
+  Point_(T _x, T _y) : x(_x), y(_y) {}
+  template <typename U>
+  Point_& operator*=(U s) {
+    x = (T)(x * s);
+    y = (T)(y * s);
+    return *this;
+  }
+};
+typedef Point_<int> Point2i;
+typedef Point_<int> Point;
+typedef Point_<float> Point2f;
+
+struct Size {
+  int width, height;
+  Size() : width(0), height(0) {}
+  Size(int w, int h) : width(w), height(h) {}
+};
+struct Rect {
+  int x, y, width, height;
+  Rect(int _x, int _y, int w, int h) : x(_x), y(_y), width(w), height(h) {}
+};
+
+struct KeyPoint {
+  Point2f pt;
+  float size, angle, response;
+  int octave, class_id;
+  KeyPoint() : size(0), angle(-1), response(0), octave(0), class_id(-1) {}
+  KeyPoint(float x, float y, float _size, float _angle = -1, float _response = 0, int _octave = 0,
+           int _class_id = -1)
+      : pt(x, y), size(_size), angle(_angle), response(_response), octave(_octave), class_id(_class_id) {}
+};
+
+struct MatZeros {
+  int rows, cols, type;
+};
+
+// u8 single-channel matrix with a malloc'd, reference-counted buffer (malloc on purpose:
+// the parity harness replaces operator new with a monotonic arena that is reset per call).
+class Mat {
+  struct Block {
+    int refs;
+  };
+  Block* blk_;
+
+  void retain() {
+    if (blk_) ++blk_->refs;
+  }
+  void drop() {
+    if (blk_ && --blk_->refs == 0) free(blk_);
+    blk_ = nullptr;
+  }
+
+ public:
+  uchar* data;
+  int rows, cols;
+  size_t step;
+
+  Mat() : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) {}
+  Mat(int r, int c, int type) : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) { create(r, c, type); }
+  Mat(Size s, int type) : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) { create(s.height, s.width, type); }
+  Mat(const MatZeros& z) : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) { *this = z; }
+  // wrap caller-owned memory
+  Mat(int r, int c, int, void* ext, size_t st) : blk_(nullptr), data((uchar*)ext), rows(r), cols(c), step(st) {}
+  Mat(const Mat& o) : blk_(o.blk_), data(o.data), rows(o.rows), cols(o.cols), step(o.step) { retain(); }
+  Mat& operator=(const Mat& o) {
+    if (this != &o) {
+      Block* nb = o.blk_;
+      if (nb) ++nb->refs;
+      drop();
+      blk_ = nb;
+      data = o.data; rows = o.rows; cols = o.cols; step = o.step;
+    }
+    return *this;
+  }
+  Mat& operator=(const MatZeros& z) {
+    create(z.rows, z.cols, z.type);
+    for (int y = 0; y < rows; ++y) memset(data + (size_t)y * step, 0, (size_t)cols);
+    return *this;
+  }
+  ~Mat() { drop(); }
+
+  void create(int r, int c, int type) {
+    assert(type == CV_8U);
+    (void)type;
+    if (data && r == rows && c == cols) return;
+    drop();
+    rows = r; cols = c; step = (size_t)c;
+    size_t bytes = sizeof(Block) + 64 + (size_t)r * c;
+    blk_ = (Block*)malloc(bytes);
+    blk_->refs = 1;
+    data = (uchar*)blk_ + 64;
+  }
+  void create(Size s, int type) { create(s.height, s.width, type); }
+  void release() {
+    drop();
+    data = nullptr; rows = cols = 0; step = 0;
+  }
+  static MatZeros zeros(int r, int c, int type) { return MatZeros{r, c, type}; }
+
+  Mat operator()(const Rect& r) const {
+    Mat m(*this);
+    m.data = data + (size_t)r.y * step + r.x;
+    m.rows = r.height; m.cols = r.width;
+    return m;
+  }
+  Mat rowRange(int a, int b) const { return (*this)(Rect(0, a, cols, b - a)); }
+  Mat colRange(int a, int b) const { return (*this)(Rect(a, 0, b - a, rows)); }
+  Mat clone() const {
+    Mat m(rows, cols, CV_8U);
+    for (int y = 0; y < rows; ++y) memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols);
+    return m;
+  }
+  template <typename T> T& at(int y, int x) { return *(T*)(data + (size_t)y * step + x * sizeof(T)); }
+  template <typename T> const T& at(int y, int x) const { return *(const T*)(data + (size_t)y * step + x * sizeof(T)); }
+  uchar* ptr(int y = 0) { return data + (size_t)y * step; }
+  const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
+  template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
+  template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step); }
+  int type() const { return CV_8U; }
+  bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+  size_t step1() const { return step; }
+  Size size() const { return Size(cols, rows); }
+};
+
+class _InputArray {
+  const Mat* m_;
+ public:
+  _InputArray(const Mat& m) : m_(&m) {}
+  bool empty() const { return m_->empty(); }
+  Mat getMat() const { return *m_; }
+};
+class _OutputArray {
+  Mat* m_;
+ public:
+  _OutputArray(Mat& m) : m_(&m) {}
+  void create(int r, int c, int type) const { m_->create(r, c, type); }
+  void release() const { m_->release(); }
+  Mat getMat() const { return *m_; }
+  bool empty() const { return m_->empty(); }
+};
+typedef const _InputArray& InputArray;
+typedef const _OutputArray& OutputArray;
+
+enum { INTER_LINEAR = 1 };
+enum { BORDER_REFLECT_101 = 4, BORDER_ISOLATED = 16 };
+
+inline float fastAtan2(float y, float x) { return cvprims::fast_atan2_deg(y, x); }
+
+inline void resize(const Mat& src, Mat& dst, Size sz, double, double, int interp) {
+  assert(interp == INTER_LINEAR);
+  (void)interp;
+  dst.create(sz, CV_8U);
+  cvprims::resize_linear_u8(src.data, src.cols, src.rows, src.step, dst.data, dst.cols, dst.rows, dst.step);
+}
+
+inline void copyMakeBorder(const Mat& src, Mat& dst, int top, int bottom, int left, int right, int type) {
+  assert((type & ~BORDER_ISOLATED) == BORDER_REFLECT_101 && top == bottom && top == left && top == right);
+  (void)bottom; (void)left; (void)right; (void)type;
+  dst.create(src.rows + 2 * top, src.cols + 2 * top, CV_8U);
+  cvprims::make_border_reflect101(src.data, src.cols, src.rows, src.step, dst.data, dst.step, top);
+}
+
+inline void GaussianBlur(const Mat& src, Mat& dst, Size k, double sx, double sy, int border) {
+  assert(k.width == 7 && k.height == 7 && sx == 2 && sy == 2 && border == BORDER_REFLECT_101);
+  (void)k; (void)sx; (void)sy; (void)border;
+  Mat s = src;  // keeps the buffer alive when dst aliases src
+  dst.create(s.rows, s.cols, CV_8U);
+  cvprims::gaussian_blur7_u8(s.data, s.cols, s.rows, s.step, dst.data, dst.step);
+}
+
+inline void FAST(const Mat& img, std::vector<KeyPoint>& kps, int threshold, bool nonmax) {
+  assert(nonmax);
+  (void)nonmax;
+  std::vector<cvprims::FastKp> f;
+  cvprims::fast9_16(img.data, img.cols, img.rows, img.step, threshold, f);
+  kps.clear();
+  for (const auto& k : f) kps.push_back(KeyPoint((float)k.x, (float)k.y, 7.f, -1.f, (float)k.score));
+}
+
+struct KeyPointsFilter {  // only reached from the reference's unused ComputeKeyPointsOld
+  static void retainBest(std::vector<KeyPoint>& k, int n) {
+    if (n >= 0 && (int)k.size() > n) {
+      std::stable_sort(k.begin(), k.end(), [](const KeyPoint& a, const KeyPoint& b) { return a.response > b.response; });
+      k.resize(n);
+    }
+  }
+};
+
+}  // namespace cv

@@ -1,0 +1,202 @@
+// oracle/match_port.hpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+//
+// CPU restatement of the reference's descriptor-search paths on flat arrays.
+// src/ORBmatcher.cc cannot be compiled here (it pulls Frame/KeyFrame/MapPoint -> Eigen,
+// DBoW2, g2o; none installed), so this follows it line by line instead:
+//   hamming256          ORBmatcher.cc:1848-1864 (DescriptorDistance)
+//   top2 update         ORBmatcher.cc:417-426
+//   search_bow_kf_frame ORBmatcher.cc:360-489
+//   search_bow_kf_kf    ORBmatcher.cc:723-856
+//   three_maxima        ORBmatcher.cc:1802-1843
+//   stereo_search       Frame.cc:527-610 (descriptor part of ComputeStereoMatches)
+// Parity status: unpinned by the reference (it ships no tests); pinned here by
+// known-answer vectors in tests/test_oracle_match.py (numpy popcount cross-check).
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+namespace matchport {
+
+static const int TH_HIGH = 95, TH_LOW = 45, HISTO_LENGTH = 30;  // ORBmatcher.cc:37-40
+
+// The SWAR bit count of the reference, on eight 32-bit words.
+static inline int hamming256(const uint8_t* a, const uint8_t* b) {
+  int dist = 0;
+  for (int i = 0; i < 8; ++i) {
+    uint32_t x, y;
+    memcpy(&x, a + 4 * i, 4);
+    memcpy(&y, b + 4 * i, 4);
+    uint32_t v = x ^ y;
+    v = v - ((v >> 1) & 0x55555555u);
+    v = (v & 0x33333333u) + ((v >> 2) & 0x33333333u);
+    dist += (int)((((v + (v >> 4)) & 0x0F0F0F0Fu) * 0x01010101u) >> 24);
+  }
+  return dist;
+}
+
+struct Top2 {
+  int best1 = 256, best2 = 256;
+  long long idx = -1;
+  inline void feed(int d, long long j) {
+    if (d < best1) { best2 = best1; best1 = d; idx = j; }
+    else if (d < best2) best2 = d;
+  }
+};
+
+// accept rule: ORBmatcher.cc:429-431 (<= th) and :799-801 (strict <)
+static inline bool accept(int best1, int best2, float ratio, int th, bool strict) {
+  if (strict ? !(best1 < th) : !(best1 <= th)) return false;
+  return (float)best1 < ratio * (float)best2;
+}
+
+// Brute-force top-2 of every query against rows [0,nd) of db.
+static inline void top2_bruteforce(const uint8_t* q, int nq, const uint8_t* db, long long nd,
+                                   int* d1, long long* i1, int* d2) {
+  for (int i = 0; i < nq; ++i) {
+    Top2 t;
+    for (long long j = 0; j < nd; ++j) t.feed(hamming256(q + 32 * (size_t)i, db + 32 * (size_t)j), j);
+    d1[i] = t.best1; i1[i] = t.idx; d2[i] = t.best2;
+  }
+}
+
+static inline void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  for (int i = 0; i < L; ++i) {
+    const int s = (int)histo[i].size();
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
+  }
+  if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if (max3 < 0.1f * (float)max1) ind3 = -1;
+}
+
+static inline int rot_bin(float a1, float a2) {
+  const float factor = 1.0f / HISTO_LENGTH;
+  float rot = a1 - a2;
+  if (rot < 0.0) rot += 360.0f;
+  int bin = (int)round(rot * factor);
+  if (bin == HISTO_LENGTH) bin = 0;
+  return bin;
+}
+
+// A DBoW2::FeatureVector flattened: node ids ascending (std::map order), CSR offsets,
+// feature indices in insertion order.
+struct FeatVec {
+  const uint32_t* node; const int* off; const uint32_t* idx; int n_nodes;
+};
+static inline int lower_bound_node(const FeatVec& f, int from, uint32_t id) {
+  int lo = from, hi = f.n_nodes;
+  while (lo < hi) { int m = (lo + hi) / 2; if (f.node[m] < id) lo = m + 1; else hi = m; }
+  return lo;
+}
+
+// Shared body of both SearchByBoW overloads.
+//   side 1 = KeyFrame (its features drive the outer loop), side 2 = Frame / KeyFrame 2.
+//   valid1[i]: feature i of side 1 has a good MapPoint.  valid2 == nullptr (KF-Frame) or
+//   flags for side 2 (KF-KF).  KF-Frame: match2[f] = index on side 1 claiming frame feature
+//   f, and `claimed` is match2 itself; KF-KF: match1[i1] = idx2, claimed = vbMatched2.
+static inline int search_bow(const uint8_t* desc1, int n1, const uint8_t* desc2, int n2,
+                             const FeatVec& fv1, const FeatVec& fv2, const uint8_t* valid1,
+                             const uint8_t* valid2, const float* ang1, const float* ang2,
+                             float ratio, int check_ori, bool kf_kf, int* out) {
+  const int n_out = kf_kf ? n1 : n2;
+  for (int i = 0; i < n_out; ++i) out[i] = -1;
+  std::vector<uint8_t> claimed2((size_t)n2, 0);
+  std::vector<int> hist[HISTO_LENGTH];
+  int nmatches = 0;
+  int a = 0, b = 0;
+  while (a < fv1.n_nodes && b < fv2.n_nodes) {
+    if (fv1.node[a] == fv2.node[b]) {
+      for (int p = fv1.off[a]; p < fv1.off[a + 1]; ++p) {
+        const int i1 = (int)fv1.idx[p];
+        if (!valid1[i1]) continue;
+        Top2 t;
+        for (int r = fv2.off[b]; r < fv2.off[b + 1]; ++r) {
+          const int i2 = (int)fv2.idx[r];
+          if (claimed2[i2]) continue;
+          if (valid2 && !valid2[i2]) continue;
+          t.feed(hamming256(desc1 + 32 * (size_t)i1, desc2 + 32 * (size_t)i2), i2);
+        }
+        if (accept(t.best1, t.best2, ratio, TH_LOW, kf_kf)) {
+          const int i2 = (int)t.idx;
+          claimed2[i2] = 1;
+          if (kf_kf) out[i1] = i2; else out[i2] = i1;
+          if (check_ori) hist[rot_bin(ang1[i1], ang2[i2])].push_back(kf_kf ? i1 : i2);
+          ++nmatches;
+        }
+      }
+      ++a; ++b;
+    } else if (fv1.node[a] < fv2.node[b]) {
+      a = lower_bound_node(fv1, a, fv2.node[b]);
+    } else {
+      b = lower_bound_node(fv2, b, fv1.node[a]);
+    }
+  }
+  if (check_ori) {
+    int i1 = -1, i2 = -1, i3 = -1;
+    three_maxima(hist, HISTO_LENGTH, i1, i2, i3);
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      if (i == i1 || i == i2 || i == i3) continue;
+      for (int j : hist[i]) { out[j] = -1; --nmatches; }
+    }
+  }
+  return nmatches;
+}
+
+// Frame.cc:537-610.  kp arrays are (x, y, octave); out best_idx/best_dist per left keypoint
+// (best_dist == TH_HIGH and best_idx == 0 when nothing beat the initial bound; best_dist == -1
+// when the keypoint was skipped before the scan).
+static inline void stereo_search(const float* lx, const float* ly, const int* loct, const uint8_t* ldesc, int nl,
+                                 const float* rx, const float* ry, const int* roct, const uint8_t* rdesc, int nr,
+                                 const float* scale_factors, int n_rows, float min_d, float max_d,
+                                 int* best_idx, int* best_dist) {
+  std::vector<std::vector<int>> rows((size_t)n_rows);
+  for (int i = 0; i < nr; ++i) {
+    const float r = 2.0f * scale_factors[roct[i]];
+    const int maxr = (int)ceil(ry[i] + r), minr = (int)floor(ry[i] - r);
+    for (int y = minr; y <= maxr; ++y)
+      if (y >= 0 && y < n_rows) rows[y].push_back(i);  // the reference indexes unchecked
+  }
+  for (int i = 0; i < nl; ++i) {
+    best_idx[i] = 0;
+    best_dist[i] = -1;
+    const int row = (int)ly[i];
+    if (row < 0 || row >= n_rows) continue;
+    const std::vector<int>& cand = rows[row];
+    if (cand.empty()) continue;
+    const float minU = lx[i] - max_d, maxU = lx[i] - min_d;
+    if (maxU < 0) continue;
+    int bd = TH_HIGH, bi = 0;
+    for (int c : cand) {
+      if (roct[c] < loct[i] - 1 || roct[c] > loct[i] + 1) continue;
+      if (rx[c] >= minU && rx[c] <= maxU) {
+        const int d = hamming256(ldesc + 32 * (size_t)i, rdesc + 32 * (size_t)c);
+        if (d < bd) { bd = d; bi = c; }
+      }
+    }
+    best_idx[i] = bi;
+    best_dist[i] = bd;
+  }
+}
+
+// Merge of per-shard top-2 results into the result of one sequential scan over the
+// concatenated shards.  Shards are ordered by increasing global row index.
+static inline void merge_top2(const int* d1, const long long* i1, const int* d2, int n_shards, int nq,
+                              int* od1, long long* oi1, int* od2) {
+  for (int q = 0; q < nq; ++q) {
+    Top2 t;
+    for (int s = 0; s < n_shards; ++s) {
+      const size_t k = (size_t)s * nq + q;
+      // feeding (best1, then best2) of each shard in order reproduces the sequential rule:
+      // best1 keeps the lowest global index on ties, best2 is the multiset second minimum.
+      if (i1[k] >= 0) t.feed(d1[k], i1[k]);
+      if (d2[k] < 256) t.feed(d2[k], -2);
+    }
+    od1[q] = t.best1; oi1[q] = t.idx; od2[q] = t.best2;
+  }
+}
+
+}  // namespace matchport

@@ -1,0 +1,142 @@
+"""Deterministic synthetic inputs for the ORB front end.
+
+Frames and descriptor sets are pure functions of an integer seed (numpy PCG64), so the
+tests, the bench and the CPU baseline all see identical bytes.  No dataset exists in the
+reference repo (its drivers read TUM/KITTI/Hamlyn sequences from disk), so every workload
+here is synthetic and says so.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def _rng(seed: int) -> np.random.Generator:
+    return np.random.Generator(np.random.PCG64(int(seed)))
+
+
+def _upsample_bilinear(grid: np.ndarray, h: int, w: int) -> np.ndarray:
+    gh, gw = grid.shape
+    ys = np.linspace(0.0, gh - 1.0, h)
+    xs = np.linspace(0.0, gw - 1.0, w)
+    y0 = np.minimum(ys.astype(np.int64), gh - 2)
+    x0 = np.minimum(xs.astype(np.int64), gw - 2)
+    fy = (ys - y0)[:, None]
+    fx = (xs - x0)[None, :]
+    # smoothstep makes the field C1 so corners come from the fine octaves, not grid seams
+    fy = fy * fy * (3 - 2 * fy)
+    fx = fx * fx * (3 - 2 * fx)
+    a = grid[y0][:, x0]
+    b = grid[y0][:, x0 + 1]
+    c = grid[y0 + 1][:, x0]
+    d = grid[y0 + 1][:, x0 + 1]
+    return (a * (1 - fx) + b * fx) * (1 - fy) + (c * (1 - fx) + d * fx) * fy
+
+
+def _value_noise(h: int, w: int, rng: np.random.Generator, octaves: int = 6, base_cell: int = 64,
+                 gain: float = 0.8) -> np.ndarray:
+    img = np.zeros((h, w), np.float64)
+    for o in range(octaves):
+        cell = max(base_cell >> o, 2)
+        grid = rng.random((h // cell + 3, w // cell + 3))
+        img += (gain ** o) * _upsample_bilinear(grid, h, w)
+    return img
+
+
+def textured_frame(h: int, w: int, seed: int) -> np.ndarray:
+    """Strongly textured u8 frame: every pyramid level yields more FAST corners than its quota."""
+    rng = _rng(seed)
+    f = _value_noise(h, w, rng)
+    f = (f - f.min()) / (f.max() - f.min())
+    return np.round(f * 255.0).astype(np.uint8)
+
+
+def endoscopy_frame(h: int, w: int, seed: int) -> np.ndarray:
+    """Low-texture frame (Hamlyn-style): weak texture under a vignette, specular discs, noise.
+
+    Exercises the minThFAST fallback cells and the under-quota quadtree exit.
+    """
+    rng = _rng(seed)
+    f = _value_noise(h, w, rng, octaves=5, base_cell=96, gain=0.6)
+    f = (f - f.min()) / (f.max() - f.min())
+    img = 110.0 + 0.35 * 255.0 * (f - 0.5)
+    yy, xx = np.mgrid[0:h, 0:w]
+    r2 = ((yy - h / 2) / (h / 2)) ** 2 + ((xx - w / 2) / (w / 2)) ** 2
+    img *= np.clip(1.15 - 0.75 * r2, 0.05, 1.0)
+    for _ in range(40):
+        cy, cx = rng.integers(0, h), rng.integers(0, w)
+        rad = rng.integers(3, 13)
+        img[(yy - cy) ** 2 + (xx - cx) ** 2 <= rad * rad] = 255.0
+    img += rng.normal(0.0, 2.0, (h, w))
+    return np.clip(np.round(img), 0, 255).astype(np.uint8)
+
+
+def stereo_pair(h: int, w: int, seed: int, max_disp: float = 60.0):
+    """(left, right): right is left warped by a smooth horizontal disparity field plus noise."""
+    rng = _rng(seed)
+    left = textured_frame(h, w, seed)
+    disp = max_disp * _upsample_bilinear(rng.random((4, 6)), h, w)
+    xs = np.arange(w)[None, :] + disp  # right(x) = left(x + d)
+    x0 = np.clip(np.floor(xs).astype(np.int64), 0, w - 2)
+    fx = np.clip(xs - x0, 0.0, 1.0)
+    rows = np.arange(h)[:, None]
+    lf = left.astype(np.float64)
+    right = lf[rows, x0] * (1 - fx) + lf[rows, x0 + 1] * fx + rng.normal(0.0, 1.5, (h, w))
+    return left, np.clip(np.round(right), 0, 255).astype(np.uint8)
+
+
+def frame_batch(kind: str, n: int, h: int, w: int, seed: int, distinct: int | None = None) -> np.ndarray:
+    """(n,h,w) u8 batch.  `distinct` < n generates that many frames and tiles them (each copy
+    is still processed independently; used to keep host-side generation time bounded)."""
+    gen = {"textured": textured_frame, "endoscopy": endoscopy_frame}[kind]
+    m = n if distinct is None else min(distinct, n)
+    base = np.stack([gen(h, w, seed * 1000 + i) for i in range(m)])
+    if m == n:
+        return base
+    reps = (n + m - 1) // m
+    return np.ascontiguousarray(np.tile(base, (reps, 1, 1))[:n])
+
+
+def random_descriptors(n: int, seed: int) -> np.ndarray:
+    """(n,32) u8: 256 iid fair bits per row."""
+    return _rng(seed).integers(0, 256, (n, 32), dtype=np.uint8)
+
+
+def flip_bits(desc: np.ndarray, nbits: int, rng: np.random.Generator) -> np.ndarray:
+    out = desc.copy()
+    pos = rng.choice(256, size=nbits, replace=False)
+    for p in pos:
+        out[p >> 3] ^= np.uint8(1 << (p & 7))
+    return out
+
+
+def reloc_workload(n_db: int, n_q: int, seed: int, n_shards: int = 8):
+    """Database + queries for the brute-force relocalization search (config 4).
+
+    Queries get 0-2 planted near neighbours (distance 5..60) at random rows, plus forced
+    edge cases: a plant at row 0, at row n_db-1, on every shard boundary, an exact
+    duplicate best in two shards (index tie-break) and best == second (ratio fail).
+    """
+    rng = _rng(seed)
+    db = random_descriptors(n_db, seed + 1)
+    q = random_descriptors(n_q, seed + 2)
+    bounds = [(n_db * s) // n_shards for s in range(1, n_shards)]
+    forced_rows = [0, n_db - 1] + bounds + [b - 1 for b in bounds]
+    for i in range(n_q):
+        if i < len(forced_rows):
+            rows = [forced_rows[i]]
+        else:
+            rows = list(rng.integers(0, n_db, size=rng.integers(0, 3)))
+        for r in rows:
+            db[r] = flip_bits(q[i], int(rng.integers(5, 61)), rng)
+    k = len(forced_rows)
+    if n_q > k + 2 and n_db >= 4:
+        # duplicate best in two different shards: the lower global row must win
+        d = flip_bits(q[k], 7, rng)
+        lo, hi = n_db // 4, (3 * n_db) // 4
+        db[lo] = d
+        db[hi] = d
+        # best == second at distance 3 (ratio test must fail: 3 < 0.75*3 is false)
+        d2 = flip_bits(q[k + 1], 3, rng)
+        db[n_db // 3] = d2
+        db[n_db // 3 + 1] = flip_bits(q[k + 1], 3, rng)
+    return db, q
