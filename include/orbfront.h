@@ -1,0 +1,194 @@
+/* orbfront.h -- C ABI of the B200-native ORB front end (liborbfront.so).
+ *
+ * This is the drop-in boundary for the reference's data-parallel front end.  The reference
+ * exposes it as two C++ classes inside libORB_SLAM2_E.so (there is no FFI in the reference);
+ * each entry point below names the reference interface it replaces.  The source-compatible
+ * C++ classes (include/ORBextractor.h, include/ORBmatcher.h) are thin wrappers over this ABI.
+ *
+ * Conventions: plain C types only; every function returns ORB_OK (0) or a negative ORB_E_*
+ * code and records a thread-local message readable through orb_last_error().  No function
+ * falls back to a CPU implementation: without a CUDA device they fail with ORB_E_NO_DEVICE.
+ * Handles are not thread-safe but independent (one CUDA stream each), matching the reference,
+ * which never shares an ORBextractor between threads (Frame.cc:78-81) and constructs a stack
+ * ORBmatcher per call site (Tracking.cc:1750).
+ */
+#ifndef ORBFRONT_H_
+#define ORBFRONT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  ORB_OK = 0,
+  ORB_E_INVALID = -1,    /* bad argument */
+  ORB_E_NO_DEVICE = -2,  /* no usable CUDA device */
+  ORB_E_CUDA = -3,       /* CUDA runtime error (message has the detail) */
+  ORB_E_CAPACITY = -4,   /* caller buffer too small; *n_out holds the needed count */
+  ORB_E_STATE = -5       /* call order violated (e.g. reading results before extracting) */
+};
+
+const char* orb_last_error(void);
+/* Number of CUDA devices visible (0 when none); never fails. */
+int orb_device_count(void);
+/* Kernel launches issued by this library in the calling process so far (for bench accounting). */
+long long orb_launch_count(void);
+
+/* ------------------------------------------------------------------ extractor ---------- */
+
+typedef struct orbx_handle orbx_handle;
+
+/* ORBextractor::ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
+ * int minThFAST) -- reference: include/ORBextractor.h:53-54, src/ORBextractor.cc:410-470.
+ * device/max_* size the device buffers once; frames larger than max_* are rejected. */
+typedef struct {
+  int nfeatures;
+  float scale_factor;
+  int nlevels;
+  int ini_th_fast;
+  int min_th_fast;
+  int device;     /* CUDA ordinal */
+  int max_width;  /* largest frame accepted */
+  int max_height;
+  int max_batch;  /* frames per orbx_extract_batch call */
+} orbx_config;
+
+/* Same field order and size (28 bytes) as cv::KeyPoint, so a std::vector<cv::KeyPoint>'s
+ * storage can be passed directly. */
+typedef struct {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} orbx_keypoint;
+
+int orbx_create(const orbx_config* cfg, orbx_handle** out);
+int orbx_destroy(orbx_handle* h);
+
+/* Scale tables the reference's inline getters return (ORBextractor.h:64-84) and the
+ * per-level quota (mnFeaturesPerLevel).  which: 0 scale, 1 inverse scale, 2 sigma^2,
+ * 3 inverse sigma^2. */
+int orbx_get_scale_table(const orbx_handle* h, int which, float* out /* nlevels */);
+int orbx_get_level_quota(const orbx_handle* h, int* out /* nlevels */);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors) -- reference:
+ * include/ORBextractor.h:60-62, src/ORBextractor.cc:1051-1113.  img is a HOST CV_8UC1 buffer
+ * with `stride` bytes per row; the mask argument of the reference is ignored there
+ * (ORBextractor.h:59) and has no counterpart here.  Writes up to cap keypoints / cap*32
+ * descriptor bytes in the reference's output order and sets *n_out.  An empty image
+ * (w or h <= 0, or img NULL) returns ORB_OK with *n_out = 0, as :1054-1055 does. */
+int orbx_extract(orbx_handle* h, const uint8_t* img, int w, int ht, size_t stride,
+                 orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
+
+/* Batched form (frames are independent): n frames of identical size, frame f at
+ * imgs + f*frame_stride.  memory = 0: imgs is host memory (pinned or pageable), copied inside
+ * the call.  memory = 1: imgs is device memory on the handle's device.  Results stay on the
+ * device until read. */
+int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int w, int ht, size_t stride,
+                       size_t frame_stride, int memory);
+/* Blocks until the batch is done; counts[f] = keypoints of frame f. */
+int orbx_batch_counts(orbx_handle* h, int* counts /* n */);
+/* Copies frame f's results (reference output order) to host buffers. */
+int orbx_batch_read(orbx_handle* h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
+/* Copies every frame's results in one transfer: frame f occupies rows [f*cap_per_frame, ...). */
+int orbx_batch_read_all(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts);
+/* Wait for the handle's stream. */
+int orbx_sync(orbx_handle* h);
+
+/* mvImagePyramid[level] (public member read by Frame.cc:534,624-641): size and pixels of
+ * the level computed by the last extract call, for `frame` of the batch.  with_border != 0
+ * copies the (h+38)x(w+38) buffer including the 19-px BORDER_REFLECT_101 frame
+ * (src/ORBextractor.cc:1115-1140). */
+int orbx_level_size(const orbx_handle* h, int level, int* w, int* ht);
+int orbx_get_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border);
+
+/* Stage outputs for parity tests: FAST candidates of (frame, level) as (x,y,score) int
+ * triples in border-relative coordinates (vToDistributeKeys, src/ORBextractor.cc:789-837);
+ * order is unspecified (the reference's order is a function of (x,y)). */
+int orbx_get_candidates(orbx_handle* h, int frame, int level, int32_t* xys, int cap, int* n_out);
+
+/* Elapsed device milliseconds of the last orbx_extract_batch (CUDA events on the handle's
+ * stream, all kernels of the batch), and the number of kernel launches it issued. */
+int orbx_last_batch_ms(orbx_handle* h, float* ms, int* launches);
+
+/* ------------------------------------------------------------------ matcher ------------ */
+
+enum { ORBM_TH_HIGH = 95, ORBM_TH_LOW = 45, ORBM_HISTO_LENGTH = 30 }; /* ORBmatcher.cc:37-40 */
+
+/* static int ORBmatcher::DescriptorDistance(const cv::Mat&, const cv::Mat&) -- reference:
+ * src/ORBmatcher.cc:1848-1864.  Single pair on the host (a kernel launch for 32 bytes would be
+ * absurd); bulk distances go through the device entry points below. */
+int orbm_hamming(const uint8_t* a /* 32 B */, const uint8_t* b /* 32 B */);
+
+/* Row-wise distances of n pairs on the device: out[i] = Hamming(a[i], b[i]).  Host buffers. */
+int orbm_hamming_pairs(int device, const uint8_t* a, const uint8_t* b, int n, int32_t* out);
+
+/* Result of the top-2 scan of src/ORBmatcher.cc:417-426 for one query: best1 = smallest
+ * distance (lowest row index on ties), best2 = second smallest as a multiset, idx = global row
+ * of best1 (-1 when the database is empty; then best1 = best2 = 256). */
+typedef struct {
+  int32_t best1;
+  int32_t best2;
+  int64_t idx;
+} orbm_top2;
+
+/* A shard of the relocalization descriptor database resident on one GPU:
+ * rows are 32-byte descriptors (cv::Mat N x 32 CV_8U, row-major).  row_base is the global
+ * index of the shard's first row; shards are contiguous ranges in increasing global order. */
+typedef struct orbm_db orbm_db;
+int orbm_db_create(int device, int64_t row_base, orbm_db** out);
+int orbm_db_append(orbm_db* db, const uint8_t* rows, int64_t n, int memory /* 0 host, 1 device */);
+int orbm_db_size(const orbm_db* db, int64_t* n);
+int orbm_db_destroy(orbm_db* db);
+
+/* Brute-force top-2 of nq queries against the shard.  memory = 0: q and out are host buffers
+ * (copies inside the call); memory = 1: both are device buffers on db's device and the call is
+ * asynchronous on the db's stream (orbm_db_sync to wait). */
+int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int memory);
+int orbm_db_sync(orbm_db* db);
+int orbm_db_last_ms(orbm_db* db, float* ms, int* launches);
+
+/* Exact merge of per-shard results (shard-major: shards[s*nq + q], shards ordered by row_base)
+ * into the result of one sequential scan, then the acceptance rule of ORBmatcher.cc:429-431:
+ * accept[q] = best1 <= th && (float)best1 < ratio*(float)best2.  Host arrays (n_shards*nq*16 B). */
+int orbm_merge_top2(const orbm_top2* shards, int n_shards, int nq, float ratio, int th,
+                    orbm_top2* out, uint8_t* accept /* may be NULL */);
+
+/* A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) flattened to CSR: node ids
+ * ascending, off[n_nodes+1], feature indices in insertion order. */
+typedef struct {
+  const uint32_t* node;
+  const int32_t* off;
+  const uint32_t* idx;
+  int32_t n_nodes;
+} orbm_featvec;
+
+/* int ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) -- src/ORBmatcher.cc:360-489
+ * (kf_kf = 0) and SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) -- :723-856 (kf_kf = 1).
+ * valid1[i] / valid2[i]: the feature has a non-bad MapPoint (valid2 may be NULL for kf_kf = 0).
+ * out has n2 entries for kf_kf = 0 (index on side 1 matched to frame feature, or -1) and n1
+ * entries for kf_kf = 1 (index on side 2, or -1).  *n_matches = return value of the reference.
+ * All pointers are host memory. */
+int orbm_search_bow(int device, const uint8_t* desc1, int n1, const uint8_t* desc2, int n2,
+                    const orbm_featvec* fv1, const orbm_featvec* fv2, const uint8_t* valid1,
+                    const uint8_t* valid2, const float* angle1, const float* angle2, float nnratio,
+                    int check_orientation, int kf_kf, int32_t* out, int* n_matches);
+
+/* Descriptor part of Frame::ComputeStereoMatches -- src/Frame.cc:527-610: per left keypoint the
+ * best right keypoint on its row band (octave within +-1, uR in [uL-max_d, uL-min_d]) with
+ * initial bound TH_HIGH.  best_dist = -1 for keypoints the reference skips before the scan.
+ * Host memory. */
+int orbm_stereo_search(int device, const orbx_keypoint* left, const uint8_t* ldesc, int nl,
+                       const orbx_keypoint* right, const uint8_t* rdesc, int nr,
+                       const float* scale_factors, int n_levels, int n_rows, float min_d, float max_d,
+                       int32_t* best_idx, int32_t* best_dist);
+
+/* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
+ * denominator of the matching roofline.  Returns 32-bit POPC per second. */
+int orbm_popc_peak(int device, double* popc_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBFRONT_H_ */

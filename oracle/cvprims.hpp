@@ -212,7 +212,19 @@ static inline void fast9_16(const uint8_t* img, int w, int h, size_t step, int t
   std::vector<uint8_t> sc((size_t)w * h, 0);
   for (int y = 3; y < h - 3; ++y)
     for (int x = 3; x < w - 3; ++x) {
-      int s = fast_strength(img + (size_t)y * step + x, step);
+      // cheap necessary condition (every nine-long arc holds one pixel of each opposite
+      // pair), then the exact strength; identical result, ~10x less work on the CPU
+      const uint8_t* p = img + (size_t)y * step + x;
+      const int v = p[0];
+      bool dark = true, bright = true;
+      for (int k = 0; k < 8 && (dark || bright); k += 2) {
+        const int a = v - p[(ptrdiff_t)kRingDy[k] * (ptrdiff_t)step + kRingDx[k]];
+        const int b = v - p[(ptrdiff_t)kRingDy[k + 8] * (ptrdiff_t)step + kRingDx[k + 8]];
+        dark = dark && (a > threshold || b > threshold);
+        bright = bright && (a < -threshold || b < -threshold);
+      }
+      if (!dark && !bright) continue;
+      int s = fast_strength(p, step);
       if (s >= threshold) sc[(size_t)y * w + x] = (uint8_t)s;
     }
   for (int y = 3; y < h - 3; ++y)

@@ -1,0 +1,106 @@
+"""ctypes binding of liborbfront.so (include/orbfront.h).  Fails loudly when the library is
+missing or a call reports an error; there is no CPU fallback anywhere in this package."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+ORB_OK, ORB_E_INVALID, ORB_E_NO_DEVICE, ORB_E_CUDA, ORB_E_CAPACITY, ORB_E_STATE = 0, -1, -2, -3, -4, -5
+
+KEYPOINT_DTYPE = np.dtype([("x", "f4"), ("y", "f4"), ("size", "f4"), ("angle", "f4"), ("response", "f4"),
+                           ("octave", "i4"), ("class_id", "i4")])
+TOP2_DTYPE = np.dtype([("best1", "i4"), ("best2", "i4"), ("idx", "i8")])
+
+
+class OrbFrontError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"liborbfront error {code}: {msg}")
+        self.code = code
+
+
+class OrbxConfig(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("scale_factor", C.c_float), ("nlevels", C.c_int),
+                ("ini_th_fast", C.c_int), ("min_th_fast", C.c_int), ("device", C.c_int),
+                ("max_width", C.c_int), ("max_height", C.c_int), ("max_batch", C.c_int)]
+
+
+class FeatVec(C.Structure):
+    _fields_ = [("node", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p), ("n_nodes", C.c_int32)]
+
+
+_lib = None
+
+_vp, _i, _f, _sz, _i64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64
+_ip = C.POINTER(C.c_int)
+
+# name -> (restype, argtypes); every symbol include/orbfront.h declares
+SIGNATURES = {
+    "orb_last_error": (C.c_char_p, []),
+    "orb_device_count": (_i, []),
+    "orb_launch_count": (C.c_longlong, []),
+    "orbx_create": (_i, [C.POINTER(OrbxConfig), C.POINTER(_vp)]),
+    "orbx_destroy": (_i, [_vp]),
+    "orbx_get_scale_table": (_i, [_vp, _i, _vp]),
+    "orbx_get_level_quota": (_i, [_vp, _vp]),
+    "orbx_extract": (_i, [_vp, _vp, _i, _i, _sz, _vp, _vp, _i, _ip]),
+    "orbx_extract_batch": (_i, [_vp, _vp, _i, _i, _i, _sz, _sz, _i]),
+    "orbx_batch_counts": (_i, [_vp, _vp]),
+    "orbx_batch_read": (_i, [_vp, _i, _vp, _vp, _i, _ip]),
+    "orbx_batch_read_all": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "orbx_sync": (_i, [_vp]),
+    "orbx_level_size": (_i, [_vp, _i, _ip, _ip]),
+    "orbx_get_level": (_i, [_vp, _i, _i, _vp, _sz, _i]),
+    "orbx_get_candidates": (_i, [_vp, _i, _i, _vp, _i, _ip]),
+    "orbx_last_batch_ms": (_i, [_vp, C.POINTER(_f), _ip]),
+    "orbm_hamming": (_i, [_vp, _vp]),
+    "orbm_hamming_pairs": (_i, [_i, _vp, _vp, _i, _vp]),
+    "orbm_db_create": (_i, [_i, _i64, C.POINTER(_vp)]),
+    "orbm_db_append": (_i, [_vp, _vp, _i64, _i]),
+    "orbm_db_size": (_i, [_vp, C.POINTER(_i64)]),
+    "orbm_db_destroy": (_i, [_vp]),
+    "orbm_top2_search": (_i, [_vp, _vp, _i, _vp, _i]),
+    "orbm_db_sync": (_i, [_vp]),
+    "orbm_db_last_ms": (_i, [_vp, C.POINTER(_f), _ip]),
+    "orbm_merge_top2": (_i, [_vp, _i, _i, _f, _i, _vp, _vp]),
+    "orbm_search_bow": (_i, [_i, _vp, _i, _vp, _i, C.POINTER(FeatVec), C.POINTER(FeatVec), _vp, _vp, _vp, _vp, _f,
+                             _i, _i, _vp, _ip]),
+    "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),
+    "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),
+}
+
+
+def lib_path() -> str:
+    return _build.LIB
+
+
+def load():
+    """Loads (building first if sources are newer) the C-ABI library."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if _build.needs_build():
+        if os.path.exists(_build.NVCC):
+            _build.build()
+        elif not os.path.exists(path):
+            raise OrbFrontError(ORB_E_NO_DEVICE, f"{path} is missing and nvcc is unavailable to build it")
+    L = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def check(rc: int):
+    if rc != ORB_OK:
+        raise OrbFrontError(rc, load().orb_last_error().decode(errors="replace"))
+
+
+def ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)

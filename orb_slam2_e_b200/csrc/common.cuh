@@ -1,0 +1,90 @@
+// Shared host/device helpers for liborbfront.so (error reporting, launch accounting,
+// mbarrier / TMA bulk-copy wrappers for sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+
+#include "../../include/orbfront.h"
+
+namespace orbfront {
+
+int set_error(int code, const char* fmt, ...);
+extern std::atomic<long long> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define ORB_CUDA_TRY(expr)                                                                    \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess)                                                                    \
+      return ::orbfront::set_error(ORB_E_CUDA, "%s failed: %s (%s:%d)", #expr,                \
+                                   cudaGetErrorString(_e), __FILE__, __LINE__);               \
+  } while (0)
+
+#define ORB_LAUNCH_CHECK()                                                                    \
+  do {                                                                                        \
+    ::orbfront::count_launch();                                                               \
+    cudaError_t _e = cudaGetLastError();                                                      \
+    if (_e != cudaSuccess)                                                                    \
+      return ::orbfront::set_error(ORB_E_CUDA, "kernel launch failed: %s (%s:%d)",            \
+                                   cudaGetErrorString(_e), __FILE__, __LINE__);               \
+  } while (0)
+
+// Selects the device; ORB_E_NO_DEVICE when there is none (no CPU fallback anywhere).
+int use_device(int device);
+
+#ifdef __CUDACC__
+#define ORB_HD __host__ __device__
+#else
+#define ORB_HD
+#endif
+template <typename T>
+ORB_HD inline T div_up(T a, T b) { return (a + b - 1) / b; }
+template <typename T>
+ORB_HD inline T align_up(T a, T b) { return div_up(a, b) * b; }
+
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion counted in bytes on an mbarrier.
+// dst/src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+#endif
+
+}  // namespace orbfront

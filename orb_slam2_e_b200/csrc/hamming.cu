@@ -1,0 +1,635 @@
+// 256-bit Hamming descriptor search for sm_100a: brute-force top-2 against a resident
+// database shard, BoW-node search, stereo row-band search, pairwise distances.
+//
+// Replaces the scalar loops of the reference (all CPU):
+//   ORBmatcher::DescriptorDistance   src/ORBmatcher.cc:1848-1864
+//   top-2 scan + ratio test          src/ORBmatcher.cc:417-431
+//   SearchByBoW (KF,Frame)/(KF,KF)   src/ORBmatcher.cc:360-489, 723-856
+//   ComputeStereoMatches (search)    src/Frame.cc:527-610
+//
+// Bound: integer POPC issue rate (each database byte is reused by every query, so HBM
+// traffic is ~nq times below the popc time).  Tensor cores are not used: XOR+POPC is not a
+// multiply-accumulate contraction.
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "common.cuh"
+
+namespace orbfront {
+
+// ------------------------------------------------------------------------------------
+// top-2 scan.  One CTA = 8 warps x 32 lanes x QPL queries held in registers = 1024 queries;
+// every lane walks the same database rows, which arrive in shared memory through a 4-stage
+// 1-D TMA bulk pipeline and are read as broadcast LDS.128.  Per pair: 8 LOP3 (xor) + 8 POPC +
+// 4 IADD3, then the reference's two-best update on packed keys (distance << 20 | local row):
+// the smallest key is best1 with the lowest row on ties, the second smallest key carries the
+// multiset second-best distance.
+constexpr int kQPL = 4;                 // queries per lane
+constexpr int kTopWarps = 8;
+constexpr int kTopThreads = kTopWarps * 32;
+constexpr int kQPerCta = kTopThreads * kQPL;  // 1024
+constexpr int kTileRows = 256;          // 8 KB per stage
+constexpr int kStages = 4;
+constexpr int kRowBits = 20;            // local row index bits inside a key
+constexpr uint32_t kKeyNone = 256u << kRowBits;  // "no row yet": distance 256 (ORBmatcher.cc:402-404)
+
+__device__ __forceinline__ int hamming8(const uint32_t (&q)[8], const uint4& a, const uint4& b) {
+  int s0 = __popc(q[0] ^ a.x) + __popc(q[1] ^ a.y) + __popc(q[2] ^ a.z);
+  int s1 = __popc(q[3] ^ a.w) + __popc(q[4] ^ b.x) + __popc(q[5] ^ b.y);
+  return s0 + s1 + __popc(q[6] ^ b.z) + __popc(q[7] ^ b.w);
+}
+
+__global__ void __launch_bounds__(kTopThreads)
+top2_scan_kernel(const uint4* __restrict__ db, long long n_rows, int rows_per_cta,
+                 const uint32_t* __restrict__ queries, int nq, int nq_pad, uint2* __restrict__ partial) {
+  __shared__ __align__(128) uint4 tile[kStages][kTileRows * 2];
+  __shared__ __align__(8) uint64_t full[kStages];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long row0 = (long long)blockIdx.x * rows_per_cta;
+  const int my_rows = (int)min((long long)rows_per_cta, n_rows - row0);
+  const int n_tiles = (my_rows + kTileRows - 1) / kTileRows;
+
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) mbar_init(&full[s], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  auto issue = [&](int t) {
+    const int rows = min(kTileRows, my_rows - t * kTileRows);
+    const uint32_t bytes = (uint32_t)rows * 32u;
+    mbar_expect_tx(&full[t % kStages], bytes);
+    tma_load_1d(&tile[t % kStages][0], db + (row0 + (long long)t * kTileRows) * 2, bytes, &full[t % kStages]);
+  };
+  if (tid == 0)
+    for (int t = 0; t < kStages - 1 && t < n_tiles; ++t) issue(t);
+
+  // queries -> registers (zero rows beyond nq; their results are never read)
+  uint32_t q[kQPL][8];
+  uint32_t k1[kQPL], k2[kQPL];
+  const int qbase = blockIdx.y * kQPerCta + warp * (32 * kQPL);
+#pragma unroll
+  for (int r = 0; r < kQPL; ++r) {
+    const int qi = qbase + r * 32 + lane;
+    const uint4* src = reinterpret_cast<const uint4*>(queries + (size_t)qi * 8);
+    uint4 a = make_uint4(0, 0, 0, 0), b = a;
+    if (qi < nq) { a = __ldg(src); b = __ldg(src + 1); }
+    q[r][0] = a.x; q[r][1] = a.y; q[r][2] = a.z; q[r][3] = a.w;
+    q[r][4] = b.x; q[r][5] = b.y; q[r][6] = b.z; q[r][7] = b.w;
+    k1[r] = kKeyNone; k2[r] = kKeyNone;
+  }
+
+  for (int t = 0; t < n_tiles; ++t) {
+    if (tid == 0 && t + kStages - 1 < n_tiles) issue(t + kStages - 1);
+    mbar_wait(&full[t % kStages], (uint32_t)((t / kStages) & 1));
+    const uint4* rows = &tile[t % kStages][0];
+    const int n = min(kTileRows, my_rows - t * kTileRows);
+    const uint32_t jbase = (uint32_t)(t * kTileRows);
+#pragma unroll 2
+    for (int j = 0; j < n; ++j) {
+      const uint4 a = rows[2 * j], b = rows[2 * j + 1];
+#pragma unroll
+      for (int r = 0; r < kQPL; ++r) {
+        const uint32_t key = ((uint32_t)hamming8(q[r], a, b) << kRowBits) | (jbase + j);
+        const uint32_t hi = max(key, k1[r]);
+        k1[r] = min(key, k1[r]);
+        k2[r] = min(k2[r], hi);
+      }
+    }
+    __syncthreads();  // everyone is done with this stage before it is refilled
+  }
+
+#pragma unroll
+  for (int r = 0; r < kQPL; ++r) {
+    const int qi = qbase + r * 32 + lane;
+    if (qi < nq_pad) partial[(size_t)blockIdx.x * nq_pad + qi] = make_uint2(k1[r], k2[r]);
+  }
+}
+
+// Folds the per-CTA partials (in increasing row order) into one orbm_top2 per query.
+__global__ void top2_reduce_kernel(const uint2* __restrict__ partial, int n_chunks, int rows_per_cta, int nq,
+                                   int nq_pad, long long row_base, orbm_top2* __restrict__ out) {
+  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= nq) return;
+  int b1 = 256, b2 = 256;
+  long long idx = -1;
+  for (int c = 0; c < n_chunks; ++c) {
+    const uint2 p = partial[(size_t)c * nq_pad + qi];
+    const int d1 = (int)(p.x >> kRowBits), d2 = (int)(p.y >> kRowBits);
+    if (d1 < b1) {  // strict: earlier chunk (lower rows) wins ties, as the sequential scan does
+      b2 = b1; b1 = d1;
+      idx = row_base + (long long)c * rows_per_cta + (long long)(p.x & ((1u << kRowBits) - 1));
+    } else if (d1 < b2) {
+      b2 = d1;
+    }
+    if (d2 < b2) b2 = d2;
+  }
+  orbm_top2 r;
+  r.best1 = b1; r.best2 = b2; r.idx = idx;
+  out[qi] = r;
+}
+
+__global__ void hamming_pairs_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n,
+                                     int* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 a0 = a[2 * i], a1 = a[2 * i + 1], b0 = b[2 * i], b1 = b[2 * i + 1];
+  out[i] = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// POPC issue-rate probe: 8 independent chains per thread, 2 alu ops per POPC (below the
+// alu pipe's 4x higher rate), result stored so nothing is eliminated.
+__global__ void __launch_bounds__(256) popc_probe_kernel(uint32_t seed, int iters, uint32_t* out) {
+  uint32_t x[8], acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { x[i] = seed + threadIdx.x * 8 + i + blockIdx.x * 2048; acc[i] = 0; }
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { acc[i] += __popc(x[i]); x[i] += 0x9E3779B9u; }
+  }
+  uint32_t s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += acc[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+
+// ------------------------------------------------------------------------------------
+// SearchByBoW.  The distance work is data-parallel but the reference's greedy claim
+// (ORBmatcher.cc:410 / :777,804: a side-2 feature taken by an earlier side-1 feature is
+// skipped) makes the result depend on scan order, so one warp replays the reference order:
+// side-1 features sequentially, their node's side-2 candidates across the lanes, then a
+// warp top-2 merge on packed keys (distance << 16 | list position).
+struct BowPair { int o1, l1, o2, l2; };  // common node: ranges in idx1 / idx2
+
+__device__ __forceinline__ void warp_top2_merge(uint32_t& k1, uint32_t& k2) {
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    const uint32_t o1 = __shfl_xor_sync(0xffffffffu, k1, s), o2 = __shfl_xor_sync(0xffffffffu, k2, s);
+    const uint32_t hi = max(k1, o1);
+    k1 = min(k1, o1);
+    k2 = min(min(k2, o2), hi);
+  }
+}
+
+__global__ void __launch_bounds__(32)
+bow_search_kernel(const uint4* __restrict__ desc1, const uint4* __restrict__ desc2, const BowPair* __restrict__ pairs,
+                  int n_pairs, const uint32_t* __restrict__ idx1, const uint32_t* __restrict__ idx2,
+                  const uint8_t* __restrict__ valid1, const uint8_t* __restrict__ valid2,
+                  const float* __restrict__ ang1, const float* __restrict__ ang2, float ratio, int check_ori,
+                  int kf_kf, int n_out, uint8_t* __restrict__ claimed2, int* __restrict__ out,
+                  uint8_t* __restrict__ bin_of, int* __restrict__ n_matches) {
+  const int lane = threadIdx.x;
+  __shared__ int hist[ORBM_HISTO_LENGTH];
+  for (int i = lane; i < ORBM_HISTO_LENGTH; i += 32) hist[i] = 0;
+  for (int i = lane; i < n_out; i += 32) out[i] = -1;
+  __syncwarp();
+  int nm = 0;
+  for (int p = 0; p < n_pairs; ++p) {
+    const BowPair pr = pairs[p];
+    for (int a = 0; a < pr.l1; ++a) {
+      const int i1 = (int)idx1[pr.o1 + a];
+      if (!valid1[i1]) continue;
+      const uint4 qa = desc1[2 * i1], qb = desc1[2 * i1 + 1];
+      const uint32_t q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+      uint32_t k1 = 256u << 16, k2 = 256u << 16;
+      for (int b = lane; b < pr.l2; b += 32) {
+        const int i2 = (int)idx2[pr.o2 + b];
+        if (claimed2[i2]) continue;
+        if (valid2 && !valid2[i2]) continue;
+        const uint32_t key = ((uint32_t)hamming8(q, desc2[2 * i2], desc2[2 * i2 + 1]) << 16) | (uint32_t)b;
+        const uint32_t hi = max(key, k1);
+        k1 = min(key, k1);
+        k2 = min(k2, hi);
+      }
+      warp_top2_merge(k1, k2);
+      const int best1 = (int)(k1 >> 16), best2 = min((int)(k2 >> 16), 256);
+      const bool th_ok = kf_kf ? (best1 < ORBM_TH_LOW) : (best1 <= ORBM_TH_LOW);
+      if (best1 < 256 && th_ok && (float)best1 < ratio * (float)best2) {  // uniform across the warp
+        const int i2 = (int)idx2[pr.o2 + (int)(k1 & 0xffffu)];
+        if (lane == 0) {
+          claimed2[i2] = 1;
+          const int slot = kf_kf ? i1 : i2;
+          out[slot] = kf_kf ? i2 : i1;
+          if (check_ori) {
+            float rot = ang1[i1] - ang2[i2];
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * (1.0f / ORBM_HISTO_LENGTH));
+            if (bin == ORBM_HISTO_LENGTH) bin = 0;
+            bin_of[slot] = (uint8_t)bin;
+            hist[bin] += 1;
+          }
+        }
+        ++nm;
+        __syncwarp();
+      }
+    }
+  }
+  __syncwarp();
+  if (check_ori) {
+    // ComputeThreeMaxima, ORBmatcher.cc:1802-1843
+    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+    for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
+      const int s = hist[i];
+      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+      else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < 0.1f * (float)max1) ind3 = -1;
+    int dropped = 0;
+    for (int i = lane; i < n_out; i += 32) {
+      if (out[i] < 0) continue;
+      const int b = bin_of[i];
+      if (b != ind1 && b != ind2 && b != ind3) { out[i] = -1; ++dropped; }
+    }
+    for (int s = 16; s > 0; s >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, s);
+    nm -= dropped;
+  }
+  if (lane == 0) *n_matches = nm;
+}
+
+// ------------------------------------------------------------------------------------
+// Stereo row-band search (Frame.cc:537-610): one warp per left keypoint; the reference's
+// per-row candidate lists are replaced by evaluating the band predicate directly, which
+// visits the same candidates in the same (increasing iR) order.
+__global__ void __launch_bounds__(128)
+stereo_search_kernel(const orbx_keypoint* __restrict__ L, const uint4* __restrict__ ldesc, int nl,
+                     const orbx_keypoint* __restrict__ R, const uint4* __restrict__ rdesc, int nr,
+                     const float* __restrict__ scale, int n_rows, float min_d, float max_d,
+                     int* __restrict__ best_idx, int* __restrict__ best_dist) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= nl) return;
+  const orbx_keypoint kl = L[i];
+  const int row = (int)kl.y;
+  const float minU = kl.x - max_d, maxU = kl.x - min_d;
+  const uint4 qa = ldesc[2 * i], qb = ldesc[2 * i + 1];
+  const uint32_t q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+  uint32_t best = (uint32_t)ORBM_TH_HIGH << kRowBits;
+  int in_band = 0;
+  if (row >= 0 && row < n_rows) {
+    for (int c = lane; c < nr; c += 32) {
+      const orbx_keypoint kr = R[c];
+      const float r = 2.0f * scale[kr.octave];
+      const int maxr = (int)ceilf(kr.y + r), minr = (int)floorf(kr.y - r);
+      if (row < minr || row > maxr) continue;
+      in_band = 1;
+      if (kr.octave < kl.octave - 1 || kr.octave > kl.octave + 1) continue;
+      if (kr.x >= minU && kr.x <= maxU) {
+        const uint32_t key = ((uint32_t)hamming8(q, rdesc[2 * c], rdesc[2 * c + 1]) << kRowBits) | (uint32_t)c;
+        best = min(best, key);
+      }
+    }
+  }
+  in_band = __any_sync(0xffffffffu, in_band);
+  for (int s = 16; s > 0; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
+  if (lane == 0) {
+    if (!in_band || maxU < 0) { best_idx[i] = 0; best_dist[i] = -1; }
+    else {
+      const int d = (int)(best >> kRowBits);
+      best_dist[i] = d;
+      best_idx[i] = d < ORBM_TH_HIGH ? (int)(best & ((1u << kRowBits) - 1)) : 0;
+    }
+  }
+}
+
+}  // namespace orbfront
+
+// ====================================================================================
+// C ABI
+using namespace orbfront;
+
+namespace {
+template <typename T>
+struct DevBuf {  // grow-only device array
+  T* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return ORB_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    ORB_CUDA_TRY(cudaMalloc(&p, n * sizeof(T)));
+    cap = n;
+    return ORB_OK;
+  }
+  ~DevBuf() { if (p) cudaFree(p); }
+};
+}  // namespace
+
+struct orbm_db {
+  int device = 0;
+  int64_t row_base = 0, n = 0, cap = 0;
+  uint4* rows = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  DevBuf<uint2> partial;
+  DevBuf<uint32_t> dq;
+  DevBuf<orbm_top2> dout;
+  int last_launches = 0;
+  bool timed = false;
+};
+
+extern "C" {
+
+int orbm_hamming(const uint8_t* a, const uint8_t* b) {
+  int d = 0;
+  for (int i = 0; i < 4; ++i) {
+    uint64_t x, y;
+    memcpy(&x, a + 8 * i, 8);
+    memcpy(&y, b + 8 * i, 8);
+    d += __builtin_popcountll(x ^ y);
+  }
+  return d;
+}
+
+int orbm_hamming_pairs(int device, const uint8_t* a, const uint8_t* b, int n, int32_t* out) {
+  if (n < 0 || (n > 0 && (!a || !b || !out))) return set_error(ORB_E_INVALID, "orbm_hamming_pairs: bad argument");
+  if (n == 0) return ORB_OK;
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevBuf<uint4> da, db;
+  DevBuf<int> dout;
+  if ((rc = da.reserve((size_t)n * 2)) || (rc = db.reserve((size_t)n * 2)) || (rc = dout.reserve(n))) return rc;
+  ORB_CUDA_TRY(cudaMemcpy(da.p, a, (size_t)n * 32, cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice));
+  hamming_pairs_kernel<<<div_up(n, 256), 256>>>(da.p, db.p, n, dout.p);
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpy(out, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  return ORB_OK;
+}
+
+int orbm_db_create(int device, int64_t row_base, orbm_db** out) {
+  if (!out || row_base < 0) return set_error(ORB_E_INVALID, "orbm_db_create: bad argument");
+  int rc = use_device(device);
+  if (rc) return rc;
+  orbm_db* db = new orbm_db();
+  db->device = device;
+  db->row_base = row_base;
+  cudaError_t e = cudaStreamCreateWithFlags(&db->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&db->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&db->ev1);
+  if (e != cudaSuccess) {
+    delete db;
+    return set_error(ORB_E_CUDA, "orbm_db_create: %s", cudaGetErrorString(e));
+  }
+  *out = db;
+  return ORB_OK;
+}
+
+int orbm_db_append(orbm_db* db, const uint8_t* rows, int64_t n, int memory) {
+  if (!db || n < 0 || (n > 0 && !rows)) return set_error(ORB_E_INVALID, "orbm_db_append: bad argument");
+  if (n == 0) return ORB_OK;
+  int rc = use_device(db->device);
+  if (rc) return rc;
+  if (db->n + n > db->cap) {
+    int64_t ncap = std::max<int64_t>(db->n + n, db->cap + db->cap / 2);
+    uint4* np = nullptr;
+    ORB_CUDA_TRY(cudaMalloc(&np, (size_t)ncap * 32));
+    if (db->n) ORB_CUDA_TRY(cudaMemcpyAsync(np, db->rows, (size_t)db->n * 32, cudaMemcpyDeviceToDevice, db->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+    if (db->rows) cudaFree(db->rows);
+    db->rows = np;
+    db->cap = ncap;
+  }
+  ORB_CUDA_TRY(cudaMemcpyAsync(db->rows + db->n * 2, rows, (size_t)n * 32,
+                               memory ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, db->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+  db->n += n;
+  return ORB_OK;
+}
+
+int orbm_db_size(const orbm_db* db, int64_t* n) {
+  if (!db || !n) return set_error(ORB_E_INVALID, "orbm_db_size: bad argument");
+  *n = db->n;
+  return ORB_OK;
+}
+
+int orbm_db_destroy(orbm_db* db) {
+  if (!db) return ORB_OK;
+  cudaSetDevice(db->device);
+  if (db->rows) cudaFree(db->rows);
+  if (db->ev0) cudaEventDestroy(db->ev0);
+  if (db->ev1) cudaEventDestroy(db->ev1);
+  if (db->stream) cudaStreamDestroy(db->stream);
+  delete db;
+  return ORB_OK;
+}
+
+int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int memory) {
+  if (!db || nq < 0 || (nq > 0 && (!q || !out))) return set_error(ORB_E_INVALID, "orbm_top2_search: bad argument");
+  if (nq == 0) return ORB_OK;
+  int rc = use_device(db->device);
+  if (rc) return rc;
+  const int nq_pad = align_up(nq, kQPerCta);
+  // chunking: ~2 CTAs per SM, whole tiles, and local row indices must fit kRowBits
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
+  const int qblocks = nq_pad / kQPerCta;
+  long long want = std::max(1, (2 * sms) / qblocks);
+  long long rows_per_cta = align_up<long long>(std::max<long long>(div_up<long long>(std::max<int64_t>(db->n, 1), want), 1), kTileRows);
+  rows_per_cta = std::min<long long>(rows_per_cta, 1ll << kRowBits);
+  const int n_chunks = (int)std::max<long long>(div_up<long long>(db->n, rows_per_cta), 0);
+  const uint32_t* dq = nullptr;
+  orbm_top2* dout = nullptr;
+  if (memory == 0) {
+    if ((rc = db->dq.reserve((size_t)nq * 8)) || (rc = db->dout.reserve(nq))) return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(db->dq.p, q, (size_t)nq * 32, cudaMemcpyHostToDevice, db->stream));
+    dq = db->dq.p;
+    dout = db->dout.p;
+  } else {
+    dq = reinterpret_cast<const uint32_t*>(q);
+    dout = out;
+  }
+  if ((rc = db->partial.reserve((size_t)std::max(n_chunks, 1) * nq_pad))) return rc;
+  ORB_CUDA_TRY(cudaEventRecord(db->ev0, db->stream));
+  db->last_launches = 0;
+  if (n_chunks > 0) {
+    top2_scan_kernel<<<dim3(n_chunks, qblocks), kTopThreads, 0, db->stream>>>(db->rows, db->n, (int)rows_per_cta, dq, nq,
+                                                                            nq_pad, db->partial.p);
+    ORB_LAUNCH_CHECK();
+    ++db->last_launches;
+  }
+  top2_reduce_kernel<<<div_up(nq, 128), 128, 0, db->stream>>>(db->partial.p, n_chunks, (int)rows_per_cta, nq, nq_pad,
+                                                               db->row_base, dout);
+  ORB_LAUNCH_CHECK();
+  ++db->last_launches;
+  ORB_CUDA_TRY(cudaEventRecord(db->ev1, db->stream));
+  db->timed = true;
+  if (memory == 0) {
+    ORB_CUDA_TRY(cudaMemcpyAsync(out, dout, (size_t)nq * sizeof(orbm_top2), cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+  }
+  return ORB_OK;
+}
+
+int orbm_db_sync(orbm_db* db) {
+  if (!db) return set_error(ORB_E_INVALID, "orbm_db_sync: null");
+  int rc = use_device(db->device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+  return ORB_OK;
+}
+
+int orbm_db_last_ms(orbm_db* db, float* ms, int* launches) {
+  if (!db || !db->timed) return set_error(ORB_E_STATE, "orbm_db_last_ms: no search has run");
+  int rc = use_device(db->device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaEventSynchronize(db->ev1));
+  if (ms) ORB_CUDA_TRY(cudaEventElapsedTime(ms, db->ev0, db->ev1));
+  if (launches) *launches = db->last_launches;
+  return ORB_OK;
+}
+
+int orbm_merge_top2(const orbm_top2* shards, int n_shards, int nq, float ratio, int th, orbm_top2* out,
+                    uint8_t* accept) {
+  if (!shards || !out || n_shards < 1 || nq < 0) return set_error(ORB_E_INVALID, "orbm_merge_top2: bad argument");
+  for (int q = 0; q < nq; ++q) {
+    int b1 = 256, b2 = 256;
+    int64_t idx = -1;
+    for (int s = 0; s < n_shards; ++s) {  // shards in increasing row order: strict < keeps the lowest row
+      const orbm_top2& p = shards[(size_t)s * nq + q];
+      if (p.idx >= 0 && p.best1 < b1) { b2 = b1; b1 = p.best1; idx = p.idx; }
+      else if (p.idx >= 0 && p.best1 < b2) b2 = p.best1;
+      if (p.best2 < b2) b2 = p.best2;
+    }
+    out[q].best1 = b1; out[q].best2 = b2; out[q].idx = idx;
+    if (accept) accept[q] = (b1 <= th) && ((float)b1 < ratio * (float)b2);
+  }
+  return ORB_OK;
+}
+
+int orbm_popc_peak(int device, double* popc_per_s) {
+  if (!popc_per_s) return set_error(ORB_E_INVALID, "orbm_popc_peak: null");
+  int rc = use_device(device);
+  if (rc) return rc;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const int blocks = sms * 8, iters = 4096;
+  DevBuf<uint32_t> out;
+  if ((rc = out.reserve((size_t)blocks * 256))) return rc;
+  cudaEvent_t e0, e1;
+  ORB_CUDA_TRY(cudaEventCreate(&e0));
+  ORB_CUDA_TRY(cudaEventCreate(&e1));
+  double best = 0;
+  for (int rep = 0; rep < 6; ++rep) {
+    ORB_CUDA_TRY(cudaEventRecord(e0));
+    popc_probe_kernel<<<blocks, 256>>>(rep * 7919u + 1u, iters, out.p);
+    ORB_LAUNCH_CHECK();
+    ORB_CUDA_TRY(cudaEventRecord(e1));
+    ORB_CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    ORB_CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    const double rate = (double)blocks * 256.0 * 8.0 * iters / (ms * 1e-3);
+    if (rep >= 2 && rate > best) best = rate;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *popc_per_s = best;
+  return ORB_OK;
+}
+
+
+int orbm_search_bow(int device, const uint8_t* desc1, int n1, const uint8_t* desc2, int n2,
+                    const orbm_featvec* fv1, const orbm_featvec* fv2, const uint8_t* valid1,
+                    const uint8_t* valid2, const float* angle1, const float* angle2, float nnratio,
+                    int check_orientation, int kf_kf, int32_t* out, int* n_matches) {
+  if (n1 < 0 || n2 < 0 || !fv1 || !fv2 || !out || !n_matches || (n1 > 0 && (!desc1 || !valid1)) ||
+      (n2 > 0 && !desc2) || (check_orientation && (!angle1 || !angle2)) || (kf_kf && !valid2))
+    return set_error(ORB_E_INVALID, "orbm_search_bow: bad argument");
+  const int n_out = kf_kf ? n1 : n2;
+  *n_matches = 0;
+  for (int i = 0; i < n_out; ++i) out[i] = -1;
+  // ordered-map merge of the two node lists (ORBmatcher.cc:381-465) -> common-node ranges
+  std::vector<BowPair> pairs;
+  int a = 0, b = 0;
+  while (a < fv1->n_nodes && b < fv2->n_nodes) {
+    if (fv1->node[a] == fv2->node[b]) {
+      BowPair p{fv1->off[a], fv1->off[a + 1] - fv1->off[a], fv2->off[b], fv2->off[b + 1] - fv2->off[b]};
+      if (p.l2 > 65535) return set_error(ORB_E_INVALID, "orbm_search_bow: node with more than 65535 features");
+      pairs.push_back(p);
+      ++a; ++b;
+    } else if (fv1->node[a] < fv2->node[b]) {
+      a = (int)(std::lower_bound(fv1->node + a, fv1->node + fv1->n_nodes, fv2->node[b]) - fv1->node);
+    } else {
+      b = (int)(std::lower_bound(fv2->node + b, fv2->node + fv2->n_nodes, fv1->node[a]) - fv2->node);
+    }
+  }
+  if (pairs.empty() || n1 == 0 || n2 == 0) return ORB_OK;
+  int rc = use_device(device);
+  if (rc) return rc;
+  const int ni1 = fv1->off[fv1->n_nodes], ni2 = fv2->off[fv2->n_nodes];
+  // one packed upload
+  size_t o = 0;
+  auto place = [&](size_t bytes) { size_t at = o; o = align_up<size_t>(o + bytes, 256); return at; };
+  const size_t o_d1 = place((size_t)n1 * 32), o_d2 = place((size_t)n2 * 32), o_pairs = place(pairs.size() * sizeof(BowPair)),
+               o_i1 = place((size_t)ni1 * 4), o_i2 = place((size_t)ni2 * 4), o_v1 = place(n1), o_v2 = place(n2),
+               o_a1 = place((size_t)n1 * 4), o_a2 = place((size_t)n2 * 4), o_claim = place(n2), o_out = place((size_t)n_out * 4),
+               o_bin = place(n_out), o_nm = place(4);
+  std::vector<uint8_t> host(o, 0);
+  memcpy(&host[o_d1], desc1, (size_t)n1 * 32);
+  memcpy(&host[o_d2], desc2, (size_t)n2 * 32);
+  memcpy(&host[o_pairs], pairs.data(), pairs.size() * sizeof(BowPair));
+  memcpy(&host[o_i1], fv1->idx, (size_t)ni1 * 4);
+  memcpy(&host[o_i2], fv2->idx, (size_t)ni2 * 4);
+  memcpy(&host[o_v1], valid1, n1);
+  if (valid2) memcpy(&host[o_v2], valid2, n2);
+  if (angle1) memcpy(&host[o_a1], angle1, (size_t)n1 * 4);
+  if (angle2) memcpy(&host[o_a2], angle2, (size_t)n2 * 4);
+  for (int i = 0; i < ni1; ++i)
+    if (fv1->idx[i] >= (uint32_t)n1) return set_error(ORB_E_INVALID, "orbm_search_bow: feature index out of range");
+  for (int i = 0; i < ni2; ++i)
+    if (fv2->idx[i] >= (uint32_t)n2) return set_error(ORB_E_INVALID, "orbm_search_bow: feature index out of range");
+  DevBuf<uint8_t> dev;
+  if ((rc = dev.reserve(o))) return rc;
+  uint8_t* d = dev.p;
+  ORB_CUDA_TRY(cudaMemcpy(d, host.data(), o, cudaMemcpyHostToDevice));
+  bow_search_kernel<<<1, 32>>>((const uint4*)(d + o_d1), (const uint4*)(d + o_d2), (const BowPair*)(d + o_pairs),
+                               (int)pairs.size(), (const uint32_t*)(d + o_i1), (const uint32_t*)(d + o_i2), d + o_v1,
+                               valid2 ? d + o_v2 : nullptr, (const float*)(d + o_a1), (const float*)(d + o_a2), nnratio,
+                               check_orientation, kf_kf, n_out, d + o_claim, (int*)(d + o_out), d + o_bin, (int*)(d + o_nm));
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpy(out, d + o_out, (size_t)n_out * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(n_matches, d + o_nm, 4, cudaMemcpyDeviceToHost));
+  return ORB_OK;
+}
+
+int orbm_stereo_search(int device, const orbx_keypoint* left, const uint8_t* ldesc, int nl,
+                       const orbx_keypoint* right, const uint8_t* rdesc, int nr,
+                       const float* scale_factors, int n_levels, int n_rows, float min_d, float max_d,
+                       int32_t* best_idx, int32_t* best_dist) {
+  if (nl < 0 || nr < 0 || n_levels < 1 || !scale_factors || (nl > 0 && (!left || !ldesc || !best_idx || !best_dist)) ||
+      (nr > 0 && (!right || !rdesc)) || nr >= (1 << kRowBits))
+    return set_error(ORB_E_INVALID, "orbm_stereo_search: bad argument");
+  if (nl == 0) return ORB_OK;
+  for (int i = 0; i < nr; ++i)
+    if (right[i].octave < 0 || right[i].octave >= n_levels)
+      return set_error(ORB_E_INVALID, "orbm_stereo_search: right keypoint %d has octave %d", i, right[i].octave);
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevBuf<orbx_keypoint> dl, dr;
+  DevBuf<uint4> ddl, ddr;
+  DevBuf<float> ds;
+  DevBuf<int> dres;
+  if ((rc = dl.reserve(nl)) || (rc = dr.reserve(std::max(nr, 1))) || (rc = ddl.reserve((size_t)nl * 2)) ||
+      (rc = ddr.reserve((size_t)std::max(nr, 1) * 2)) || (rc = ds.reserve(n_levels)) || (rc = dres.reserve((size_t)nl * 2)))
+    return rc;
+  ORB_CUDA_TRY(cudaMemcpy(dl.p, left, (size_t)nl * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+  ORB_CUDA_TRY(cudaMemcpy(ddl.p, ldesc, (size_t)nl * 32, cudaMemcpyHostToDevice));
+  if (nr) {
+    ORB_CUDA_TRY(cudaMemcpy(dr.p, right, (size_t)nr * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+    ORB_CUDA_TRY(cudaMemcpy(ddr.p, rdesc, (size_t)nr * 32, cudaMemcpyHostToDevice));
+  }
+  ORB_CUDA_TRY(cudaMemcpy(ds.p, scale_factors, (size_t)n_levels * 4, cudaMemcpyHostToDevice));
+  stereo_search_kernel<<<div_up(nl, 4), 128>>>(dl.p, ddl.p, nl, dr.p, ddr.p, nr, ds.p, n_rows, min_d, max_d, dres.p,
+                                               dres.p + nl);
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpy(best_idx, dres.p, (size_t)nl * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpy(best_dist, dres.p + nl, (size_t)nl * 4, cudaMemcpyDeviceToHost));
+  return ORB_OK;
+}
+
+}  // extern "C"

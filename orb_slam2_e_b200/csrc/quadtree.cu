@@ -1,0 +1,287 @@
+// Deterministic quadtree keypoint selection (sm_100a): one CTA per (frame, level).
+//
+// Replaces ORBextractor::DistributeOctTree + ExtractorNode::DivideNode
+// (src/ORBextractor.cc:481-763), a sequential std::list algorithm, by an equivalent
+// level-synchronous formulation on SORTED PATH CODES (derivation in DESIGN.md "Quadtree"):
+//   * every candidate carries its root strip and the 2-bit quadrant digit of each split it
+//     would undergo (quadtree_path_code); sorting by that code makes every tree node, at every
+//     depth, a contiguous run, and b[i] = depth at which sorted neighbours i-1 and i separate;
+//   * the list's node count after each breadth-first pass is cnt[d] = #{i : b[i] <= d}, the
+//     number of still-divisible nodes is nexp[d]; the reference's stop rules (:669, :673) are
+//     replayed on those two tables;
+//   * the final "expand the biggest nodes first until N" passes (:676-737) sort the divisible
+//     nodes by (key count, creation order) -- creation order being the reference's pointer
+//     tie-break under a monotonic allocator -- and a prefix sum finds where the loop breaks (:730);
+//   * each leaf keeps its max-response key, first candidate winning ties (:744-760), and
+//     leaves are emitted in the std::list's final order (newest pass first, reverse creation
+//     order inside a pass, single-key roots last in ascending order).
+// Integer/byte work, latency-bound inside a CTA; parallelism comes from the batch:
+// n_frames x n_levels independent CTAs.
+#include "extract.cuh"
+
+namespace orbfront {
+
+constexpr int kQtThreads = 256;
+constexpr uint32_t kSeqMark = 0x8000u;  // "head of a child created by the final partial pass"
+
+struct QtCtl {  // control block in shared memory
+  int hist[kMaxDepth + 3], dlt[kMaxDepth + 3], cnt[kMaxDepth + 3], nexp[kMaxDepth + 3];
+  int d, size, mode, d_bfs, partial, counter, mstar, scan_tmp[kQtThreads / 32], scan_total, run_base;
+};
+enum { kModeFull = 0, kModeOrdered = 1 };
+
+// In-place ascending bitonic sort of np (power of two) 64-bit keys with optional 32-bit values.
+__device__ void bitonic_sort(unsigned long long* a, uint32_t* v, int np) {
+  for (int k = 2; k <= np; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < np; i += kQtThreads) {
+        const int x = i ^ j;
+        if (x > i) {
+          const unsigned long long ai = a[i], ax = a[x];
+          if ((ai > ax) == ((i & k) == 0)) {
+            a[i] = ax; a[x] = ai;
+            if (v) { const uint32_t t = v[i]; v[i] = v[x]; v[x] = t; }
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// Inclusive scan of one int per thread across the CTA; returns the thread's inclusive prefix.
+__device__ int block_inclusive_scan(int v, QtCtl& C) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int s = 1; s < 32; s <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, v, s);
+    if (lane >= s) v += o;
+  }
+  if (lane == 31) C.scan_tmp[warp] = v;
+  __syncthreads();
+  int base = 0;
+  for (int w = 0; w < warp; ++w) base += C.scan_tmp[w];
+  if (threadIdx.x == kQtThreads - 1) C.scan_total = base + v;
+  __syncthreads();
+  return base + v;
+}
+
+// Creation-order key of a depth-k node made by breadth-first passes only: the path prefix with
+// every second digit (counting back from the last) complemented, the root strip complemented when k
+// is even.  Ascending key == order of creation within pass k.
+__device__ __forceinline__ uint32_t bfs_creation_key(uint32_t code, int k, int dmax) {
+  const uint32_t prefix = code >> (2 * (dmax - k));
+  const uint32_t low = (1u << (2 * k)) - 1u;
+  uint32_t mask = 0xCCCCCCCCu & low;
+  if ((k & 1) == 0) mask |= ((1u << kRootBits) - 1u) << (2 * k);
+  return prefix ^ mask;
+}
+
+__global__ void __launch_bounds__(kQtThreads)
+quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+  const LevelGeom& G = P.lv[l];
+  const int N = G.quota, dmax = G.dmax;
+
+  // shared-memory carve-up
+  unsigned long long* s_keys = reinterpret_cast<unsigned long long*>(smem);
+  unsigned long long* nkey = s_keys + S;
+  uint32_t* nval = reinterpret_cast<uint32_t*>(nkey + NP);
+  uint32_t* nhead = nval + NP;
+  uint16_t* s_seq = reinterpret_cast<uint16_t*>(nhead + NP);
+  uint8_t* ngain = reinterpret_cast<uint8_t*>(s_seq + S);
+  uint8_t* s_b = ngain + NP;
+  QtCtl& C = *reinterpret_cast<QtCtl*>(smem + align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16));
+
+  int n = P.cand_count[f * P.nlevels + l];
+  n = min(n, G.cand_cap);
+  uint32_t* kept = P.kept + (size_t)f * P.kept_frame + G.kept_off;
+  if (n == 0) {
+    if (tid == 0) P.kept_count[f * P.nlevels + l] = 0;
+    return;
+  }
+  unsigned long long* gkeys = P.cand + (size_t)f * P.cand_frame + G.cand_off;
+  int np = 1;
+  while (np < n) np <<= 1;
+  const bool in_smem = np <= S;
+  unsigned long long* keys = in_smem ? s_keys : gkeys;
+  uint8_t* b = in_smem ? s_b : P.qt_b + ((size_t)f * (P.cand_frame + kMaxLevels) + G.cand_off + l);
+  // sequence numbers: 16-bit in shared memory, or the same width in the global scratch
+  uint16_t* seq = in_smem ? s_seq : reinterpret_cast<uint16_t*>(P.qt_seq + (size_t)f * P.cand_frame + G.cand_off);
+
+  for (int i = tid; i < np; i += kQtThreads) {
+    const unsigned long long k = i < n ? gkeys[i] : ~0ull;
+    keys[i] = k;  // (pads the global buffer in place when not in shared memory)
+  }
+  __syncthreads();
+  bitonic_sort(keys, nullptr, np);
+
+  // boundary depths b[0..n], tables cnt[] / nexp[]
+  for (int i = tid; i < kMaxDepth + 3; i += kQtThreads) { C.hist[i] = 0; C.dlt[i] = 0; }
+  for (int i = tid; i <= n; i += kQtThreads) {
+    int v = 0;
+    if (i > 0 && i < n) {
+      const uint32_t x = (uint32_t)(keys[i - 1] >> 32) ^ (uint32_t)(keys[i] >> 32);
+      if (x == 0) v = dmax + 1;  // duplicate position: never separates (cannot happen for FAST output)
+      else { const int msb = 31 - __clz(x); v = msb >= 2 * dmax ? 0 : dmax - (msb >> 1); }
+    }
+    b[i] = (uint8_t)v;
+    if (i < n) seq[i] = 0;
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += kQtThreads) {
+    const int a = b[i], e = b[i + 1];
+    atomicAdd(&C.hist[a], 1);
+    if (a < e) { atomicAdd(&C.dlt[a], 1); atomicAdd(&C.dlt[e], -1); }
+  }
+  __syncthreads();
+
+  // replay of the reference's pass loop (ORBextractor.cc:593-739) on the tables
+  if (tid == 0) {
+    int acc = 0, acc2 = 0;
+    for (int d = 0; d <= dmax + 1; ++d) {
+      acc += C.hist[d]; acc2 += C.dlt[d];
+      C.cnt[d] = d <= dmax ? acc : C.cnt[dmax];
+      C.nexp[d] = d <= dmax ? acc2 : 0;
+    }
+    int d = 0, size = C.cnt[0], mode = kModeFull;
+    while (true) {
+      const int prev = size;
+      if (d < dmax) { ++d; size = C.cnt[d]; }     // one breadth-first pass: split every divisible node
+      if (size >= N || size == prev) break;        // :669
+      if (size + 3 * C.nexp[d] > N) { mode = kModeOrdered; break; }  // :673
+    }
+    C.d = d; C.size = size; C.mode = mode; C.d_bfs = d; C.partial = 0;
+  }
+  __syncthreads();
+
+  // ordered passes: biggest nodes first, stop as soon as the list holds N nodes (:676-737)
+  bool first_ordered = true;
+  while (C.mode == kModeOrdered) {
+    const int d = C.d, size = C.size;
+    if (tid == 0) { C.counter = 0; C.mstar = 0x7fffffff; }
+    __syncthreads();
+    for (int i = tid; i < n; i += kQtThreads)
+      if (b[i] <= d && b[i + 1] > d) nhead[atomicAdd(&C.counter, 1)] = (uint32_t)i;
+    __syncthreads();
+    const int M = C.counter;
+    int mp = 1;
+    while (mp < M) mp <<= 1;
+    for (int m = tid; m < mp; m += kQtThreads) {
+      if (m >= M) { nkey[m] = ~0ull; nval[m] = 0; continue; }
+      const int h = (int)nhead[m];
+      int e = h + 1, children = 1;
+      while (b[e] > d) { children += b[e] == d + 1; ++e; }
+      ngain[m] = (uint8_t)(children - 1);
+      const uint32_t code = (uint32_t)(keys[h] >> 32);
+      const uint32_t rank = first_ordered ? bfs_creation_key(code, d, dmax) : (uint32_t)seq[h];
+      nkey[m] = ~(((unsigned long long)(e - h) << 32) | rank);  // ascending ~key == (count, rank) descending
+      nval[m] = (uint32_t)m;
+    }
+    __syncthreads();
+    bitonic_sort(nkey, nval, mp);
+    // where does the running node count reach N?
+    int carried = 0;
+    for (int base = 0; base < M; base += kQtThreads) {
+      const int j = base + tid;
+      const int g = j < M ? ngain[nval[j]] : 0;
+      const int incl = block_inclusive_scan(g, C) + carried;
+      if (j < M && size + incl >= N) atomicMin(&C.mstar, j);
+      carried += C.scan_total;
+      __syncthreads();
+    }
+    const bool stops = C.mstar != 0x7fffffff;
+    const int n_split = stops ? C.mstar + 1 : M;
+    // the split nodes' children get their creation sequence (parent's place in the order, quadrant)
+    for (int j = tid; j < n_split; j += kQtThreads) {
+      const int h = (int)nhead[nval[j]];
+      int p = h;
+      do {
+        if (p == h || b[p] == d + 1) {
+          const uint32_t q = ((uint32_t)(keys[p] >> 32) >> (2 * (dmax - d - 1))) & 3u;
+          seq[p] = (uint16_t)(((uint32_t)j << 2 | q) | (stops ? kSeqMark : 0u));
+        }
+        ++p;
+      } while (b[p] > d);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (stops) { C.partial = 1; C.mode = kModeFull; }
+      else {
+        const int nsize = C.cnt[d + 1];
+        C.d = d + 1; C.size = nsize;
+        if (nsize >= N || nsize == size || d + 1 >= dmax) C.mode = kModeFull;  // :735
+      }
+    }
+    first_ordered = false;
+    __syncthreads();
+  }
+
+  // leaves: runs at depth dfin, plus the children of the nodes split by the final partial pass
+  const int dfin = C.d, partial = C.partial, d_bfs = C.d_bfs;
+  if (tid == 0) C.counter = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += kQtThreads)
+    if (b[i] <= dfin || (partial && (seq[i] & kSeqMark))) nhead[atomicAdd(&C.counter, 1)] = (uint32_t)i;
+  __syncthreads();
+  const int L = min(C.counter, G.kept_cap);
+  int lp = 1;
+  while (lp < L) lp <<= 1;
+  for (int m = tid; m < lp; m += kQtThreads) {
+    if (m >= L) { nkey[m] = ~0ull; nval[m] = 0; continue; }
+    const int p = (int)nhead[m];
+    const bool child = partial && (seq[p] & kSeqMark);
+    const int leaf_d = child ? dfin + 1 : dfin;
+    // best key of the run: highest response, then earliest candidate in the reference's
+    // (cell row, cell col, y, x) detection order
+    int e = p;
+    unsigned long long best = 0;
+    uint32_t best_pay = 0;
+    do {
+      const uint32_t pay = (uint32_t)keys[e];
+      const int x = pay & 0xfff, y = (pay >> 12) & 0xfff;
+      const unsigned long long cell = (unsigned long long)((y - 3) / G.hCell * G.nCols + (x - 3) / G.wCell);
+      const unsigned long long order = (cell << 24) | (unsigned long long)(pay & 0xffffffu);
+      const unsigned long long cmp = ((unsigned long long)(pay >> 24) << 48) | (0xffffffffffffull - order);
+      if (cmp > best || e == p) { best = cmp; best_pay = pay; }
+      ++e;
+    } while (e < n && !(b[e] <= dfin || (partial && (seq[e] & kSeqMark))));
+    const int created = (e - p == 1) ? max((int)b[p], (int)b[p + 1]) : leaf_d;
+    const uint32_t code = (uint32_t)(keys[p] >> 32);
+    unsigned long long within;
+    if (created == 0) within = code >> (2 * dmax);  // single-key roots keep their push_back order
+    else if (created <= d_bfs) within = 0xffffffffull - bfs_creation_key(code, created, dmax);
+    else within = 0xffffffffull - (uint32_t)(seq[p] & ~kSeqMark);
+    nkey[m] = ((unsigned long long)(31 - created) << 40) | within;
+    nval[m] = best_pay;
+  }
+  __syncthreads();
+  bitonic_sort(nkey, nval, lp);
+  for (int m = tid; m < L; m += kQtThreads) kept[m] = nval[m];
+  if (tid == 0) P.kept_count[f * P.nlevels + l] = L;
+}
+
+int quadtree_smem_bytes(int S, int NP) {
+  return (int)(align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16) + sizeof(QtCtl));
+}
+
+int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
+  int nmax = 1;
+  for (int l = 0; l < P.nlevels; ++l) nmax = std::max(nmax, P.lv[l].kept_cap);
+  int NP = 1;
+  while (NP < nmax) NP <<= 1;
+  int S = 4096;
+  if (const char* e = getenv("ORBX_QT_SMEM_KEYS")) S = std::max(256, atoi(e));
+  while (S & (S - 1)) S &= S - 1;  // power of two
+  S = std::max(S, NP);             // node arrays alias nothing, but n_nodes <= n keys
+  const int smem = quadtree_smem_bytes(S, NP);
+  if (smem > 227 * 1024) return set_error(ORB_E_INVALID, "quadtree: %d bytes of shared memory needed (nfeatures too large)", smem);
+  ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  quadtree_select_kernel<<<dim3(P.nlevels, P.n_frames), kQtThreads, smem, s>>>(P, S, NP);
+  ORB_LAUNCH_CHECK();
+  ++*launches;
+  return ORB_OK;
+}
+
+}  // namespace orbfront

@@ -1,0 +1,191 @@
+"""Host-side mirror of ORB_SLAM2::ORBmatcher's descriptor-search interface over the C ABI.
+
+Names and argument meaning follow the reference (include/ORBmatcher.h:37-111); object graphs
+(KeyFrame*, Frame&, MapPoint*) are replaced by the flat arrays they are read from: descriptor
+matrices (N x 32 u8), DBoW2 FeatureVectors as {node_id: [feature indices]}, MapPoint validity
+flags and keypoint angles.  Everything runs in liborbfront.so on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import FeatVec, TOP2_DTYPE, check, ptr
+
+TH_HIGH, TH_LOW, HISTO_LENGTH = 95, 45, 30  # ORBmatcher.cc:37-40
+
+
+def _desc(a) -> np.ndarray:
+    a = np.ascontiguousarray(a, np.uint8)
+    if a.ndim == 1:
+        a = a.reshape(1, -1)
+    if a.ndim != 2 or a.shape[1] != 32:
+        raise ValueError("descriptors must be N x 32 uint8 (cv::Mat CV_8U rows)")
+    return a
+
+
+class _FlatFeatVec:
+    """DBoW2::FeatureVector flattened to CSR with ascending node ids (std::map order)."""
+
+    def __init__(self, fv):
+        if isinstance(fv, dict):
+            nodes = sorted(fv)
+            lists = [np.asarray(fv[k], np.uint32) for k in nodes]
+        else:  # (node_ids, offsets, indices) already flat
+            nodes, off, idx = fv
+            self.node = np.ascontiguousarray(nodes, np.uint32)
+            self.off = np.ascontiguousarray(off, np.int32)
+            self.idx = np.ascontiguousarray(idx, np.uint32)
+            if np.any(np.diff(self.node.astype(np.int64)) <= 0):
+                raise ValueError("node ids must be strictly ascending")
+            self._mk()
+            return
+        self.node = np.asarray(nodes, np.uint32)
+        self.off = np.zeros(len(nodes) + 1, np.int32)
+        if lists:
+            self.off[1:] = np.cumsum([len(x) for x in lists])
+        self.idx = np.concatenate(lists).astype(np.uint32) if lists else np.zeros(0, np.uint32)
+        self._mk()
+
+    def _mk(self):
+        self.c = FeatVec(self.node.ctypes.data, self.off.ctypes.data, self.idx.ctypes.data, len(self.node))
+
+
+class ORBmatcher:
+    """ORBmatcher(nnratio=0.6, checkOri=True) -- include/ORBmatcher.h:41."""
+
+    TH_LOW, TH_HIGH, HISTO_LENGTH = TH_LOW, TH_HIGH, HISTO_LENGTH
+
+    def __init__(self, nnratio: float = 0.6, checkOri: bool = True, device: int = 0):
+        self.mfNNratio = float(np.float32(nnratio))
+        self.mbCheckOrientation = bool(checkOri)
+        self.device = device
+
+    @staticmethod
+    def DescriptorDistance(a, b) -> int:
+        """static int DescriptorDistance(const cv::Mat&, const cv::Mat&) -- ORBmatcher.cc:1848."""
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1)
+        b = np.ascontiguousarray(b, np.uint8).reshape(-1)
+        if a.size != 32 or b.size != 32:
+            raise ValueError("descriptors are 32 bytes")
+        return _lib.load().orbm_hamming(ptr(a), ptr(b))
+
+    def DescriptorDistances(self, a, b) -> np.ndarray:
+        """Row-wise distances of two N x 32 matrices (device)."""
+        a, b = _desc(a), _desc(b)
+        if a.shape != b.shape:
+            raise ValueError("shape mismatch")
+        out = np.zeros(len(a), np.int32)
+        check(_lib.load().orbm_hamming_pairs(self.device, ptr(a), ptr(b), len(a), ptr(out)))
+        return out
+
+    def SearchByBoW(self, desc1, featvec1, valid1, desc2, featvec2, valid2=None, angles1=None, angles2=None,
+                    kf_kf: bool = False):
+        """Both SearchByBoW overloads (ORBmatcher.cc:360-489 KF-Frame, :723-856 KF-KF).
+
+        Returns (nmatches, matches): KF-Frame: matches[f] = KeyFrame feature matched to frame
+        feature f (the reference stores that feature's MapPoint*), or -1.  KF-KF: matches[i1] =
+        feature of KF2, or -1.
+        """
+        d1, d2 = _desc(desc1) if len(desc1) else np.zeros((0, 32), np.uint8), \
+            _desc(desc2) if len(desc2) else np.zeros((0, 32), np.uint8)
+        f1, f2 = _FlatFeatVec(featvec1), _FlatFeatVec(featvec2)
+        v1 = np.ascontiguousarray(valid1, np.uint8)
+        v2 = None if valid2 is None else np.ascontiguousarray(valid2, np.uint8)
+        if kf_kf and v2 is None:
+            raise ValueError("KF-KF search needs valid2")
+        a1 = None if angles1 is None else np.ascontiguousarray(angles1, np.float32)
+        a2 = None if angles2 is None else np.ascontiguousarray(angles2, np.float32)
+        if self.mbCheckOrientation and (a1 is None or a2 is None):
+            raise ValueError("orientation check needs keypoint angles")
+        out = np.zeros(len(d1) if kf_kf else len(d2), np.int32)
+        nm = C.c_int(0)
+        check(_lib.load().orbm_search_bow(
+            self.device, ptr(d1), len(d1), ptr(d2), len(d2), C.byref(f1.c), C.byref(f2.c), ptr(v1),
+            None if v2 is None else ptr(v2), None if a1 is None else ptr(a1), None if a2 is None else ptr(a2),
+            self.mfNNratio, int(self.mbCheckOrientation), int(kf_kf), ptr(out), C.byref(nm)))
+        return nm.value, out
+
+    def StereoSearch(self, kps_left, desc_left, kps_right, desc_right, scale_factors, n_rows, min_d, max_d):
+        """Descriptor part of Frame::ComputeStereoMatches (Frame.cc:527-610): (bestIdxR, bestDist)."""
+        kl = np.ascontiguousarray(kps_left, _lib.KEYPOINT_DTYPE)
+        kr = np.ascontiguousarray(kps_right, _lib.KEYPOINT_DTYPE)
+        dl = _desc(desc_left) if len(kl) else np.zeros((0, 32), np.uint8)
+        dr = _desc(desc_right) if len(kr) else np.zeros((0, 32), np.uint8)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        bi = np.zeros(len(kl), np.int32)
+        bd = np.zeros(len(kl), np.int32)
+        check(_lib.load().orbm_stereo_search(self.device, ptr(kl), ptr(dl), len(kl), ptr(kr), ptr(dr), len(kr), ptr(sf),
+                                             len(sf), int(n_rows), float(min_d), float(max_d), ptr(bi), ptr(bd)))
+        return bi, bd
+
+
+class DescriptorDB:
+    """One GPU-resident shard of the relocalization descriptor database:
+    rows [row_base, row_base + n) of the global N x 32 matrix."""
+
+    def __init__(self, device: int = 0, row_base: int = 0):
+        self._h = C.c_void_p()
+        self.device, self.row_base = device, row_base
+        check(_lib.load().orbm_db_create(device, row_base, C.byref(self._h)))
+
+    def append(self, rows):
+        rows = _desc(rows)
+        check(_lib.load().orbm_db_append(self._h, ptr(rows), len(rows), 0))
+
+    def append_device(self, dev_ptr: int, n: int):
+        check(_lib.load().orbm_db_append(self._h, C.c_void_p(dev_ptr), n, 1))
+
+    def __len__(self):
+        n = C.c_int64()
+        check(_lib.load().orbm_db_size(self._h, C.byref(n)))
+        return n.value
+
+    def top2(self, queries) -> np.ndarray:
+        """Brute-force scan (ORBmatcher.cc:417-426 rule): structured array (best1, best2, idx)."""
+        q = _desc(queries)
+        out = np.zeros(len(q), TOP2_DTYPE)
+        check(_lib.load().orbm_top2_search(self._h, ptr(q), len(q), ptr(out), 0))
+        return out
+
+    def top2_device(self, q_ptr: int, nq: int, out_ptr: int):
+        """Asynchronous scan with device-resident queries/results (on the shard's own stream)."""
+        check(_lib.load().orbm_top2_search(self._h, C.c_void_p(q_ptr), nq, C.c_void_p(out_ptr), 1))
+
+    def sync(self):
+        check(_lib.load().orbm_db_sync(self._h))
+
+    def last_ms(self):
+        ms, n = C.c_float(), C.c_int()
+        check(_lib.load().orbm_db_last_ms(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def close(self):
+        if self._h:
+            _lib.load().orbm_db_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def merge_top2(shard_results, ratio: float = 0.75, th: int = TH_LOW):
+    """Exact merge of per-shard top-2 results (shards ordered by row_base) + acceptance rule
+    (ORBmatcher.cc:429-431).  Returns (merged structured array, accept flags)."""
+    arr = np.ascontiguousarray(np.stack([np.ascontiguousarray(s, TOP2_DTYPE) for s in shard_results]))
+    n_shards, nq = arr.shape
+    out = np.zeros(nq, TOP2_DTYPE)
+    acc = np.zeros(nq, np.uint8)
+    check(_lib.load().orbm_merge_top2(ptr(arr), n_shards, nq, float(ratio), int(th), ptr(out), ptr(acc)))
+    return out, acc.astype(bool)
+
+
+def popc_peak(device: int = 0) -> float:
+    v = C.c_double()
+    check(_lib.load().orbm_popc_peak(device, C.byref(v)))
+    return v.value

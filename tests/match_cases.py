@@ -1,0 +1,91 @@
+"""Seeded inputs for the matcher parity tests (shared by the CPU-oracle and the GPU tests)."""
+import numpy as np
+from orb_slam2_e_b200 import synth
+
+
+def bow_case(seed, n1=300, n2=320, n_nodes=40, shared=0.7, dup_frac=0.5, valid_frac=0.8):
+    """Two feature sets with planted correspondences, random vocabulary-node assignment,
+    validity flags and angles.  Returns dict of flat arrays + FeatureVector dicts."""
+    rng = np.random.default_rng(seed)
+    d1 = synth.random_descriptors(n1, seed * 3 + 1)
+    d2 = synth.random_descriptors(n2, seed * 3 + 2)
+    node1 = rng.integers(0, n_nodes, n1)
+    node2 = rng.integers(0, n_nodes, n2)
+    ang1 = rng.uniform(0, 360, n1).astype(np.float32)
+    ang2 = rng.uniform(0, 360, n2).astype(np.float32)
+    # plant matches: d2[j] = noisy copy of d1[i], same node, coherent rotation (+ outliers)
+    m = int(min(n1, n2) * dup_frac)
+    src = rng.choice(n1, m, replace=False)
+    dst = rng.choice(n2, m, replace=False)
+    for i, j in zip(src, dst):
+        d2[j] = synth.flip_bits(d1[i], int(rng.integers(0, 50)), rng)
+        if rng.random() < shared:
+            node2[j] = node1[i]
+        ang2[j] = np.float32((ang1[i] - (25.0 if rng.random() < 0.8 else rng.uniform(0, 360)) + rng.normal(0, 3)) % 360)
+    # near-ties: a second copy of some d1 rows in the same node (ratio test / claim order)
+    for i in src[: m // 5]:
+        j = int(rng.integers(0, n2))
+        d2[j] = synth.flip_bits(d1[i], int(rng.integers(0, 50)), rng)
+        node2[j] = node1[i]
+    fv1, fv2 = {}, {}
+    for i in rng.permutation(n1):  # insertion order inside a node is arbitrary
+        fv1.setdefault(int(node1[i]) * 7 + 3, []).append(int(i))
+    for j in rng.permutation(n2):
+        fv2.setdefault(int(node2[j]) * 7 + 3, []).append(int(j))
+    # some nodes exist on one side only
+    for k in list(fv1)[:3]:
+        fv1[k + 1] = fv1.pop(k)
+    v1 = (rng.random(n1) < valid_frac).astype(np.uint8)
+    v2 = (rng.random(n2) < valid_frac).astype(np.uint8)
+    return dict(d1=d1, d2=d2, fv1=fv1, fv2=fv2, v1=v1, v2=v2, a1=ang1, a2=ang2)
+
+
+def flat_fv(fv):
+    nodes = sorted(fv)
+    off = np.zeros(len(nodes) + 1, np.int32)
+    off[1:] = np.cumsum([len(fv[k]) for k in nodes])
+    idx = np.concatenate([np.asarray(fv[k], np.uint32) for k in nodes]) if nodes else np.zeros(0, np.uint32)
+    return np.asarray(nodes, np.uint32), off, idx.astype(np.uint32)
+
+
+def oracle_bow(L, case, ratio, check_ori, kf_kf):
+    n1, off1, i1 = flat_fv(case["fv1"])
+    n2, off2, i2 = flat_fv(case["fv2"])
+    out = np.zeros(len(case["d1"]) if kf_kf else len(case["d2"]), np.int32)
+    v2 = case["v2"].ctypes.data if kf_kf else None
+    nm = L.orc_search_bow(case["d1"], len(case["d1"]), case["d2"], len(case["d2"]), n1, off1, i1, len(n1),
+                          n2, off2, i2, len(n2), case["v1"], v2, case["a1"], case["a2"], ratio, int(check_ori),
+                          int(kf_kf), out)
+    return nm, out
+
+
+def stereo_case(seed, nl=400, nr=420, n_rows=376, width=1241, n_levels=8):
+    rng = np.random.default_rng(seed)
+    from orb_slam2_e_b200._lib import KEYPOINT_DTYPE
+    scale = (1.2 ** np.arange(n_levels)).astype(np.float32)
+    kl = np.zeros(nl, KEYPOINT_DTYPE)
+    kr = np.zeros(nr, KEYPOINT_DTYPE)
+    for k, n in ((kl, nl), (kr, nr)):
+        k["octave"] = rng.integers(0, n_levels, n)
+        k["x"] = (rng.integers(19, width - 19, n) * 1.0).astype(np.float32) * 1.0
+        k["y"] = rng.uniform(0, n_rows - 1, n).astype(np.float32)
+    dl = synth.random_descriptors(nl, seed + 5)
+    dr = synth.random_descriptors(nr, seed + 6)
+    m = min(nl, nr) // 2
+    for i, j in zip(rng.choice(nl, m, replace=False), rng.choice(nr, m, replace=False)):
+        dr[j] = synth.flip_bits(dl[i], int(rng.integers(0, 110)), rng)
+        kr["y"][j] = kl["y"][i] + np.float32(rng.normal(0, 1.0))
+        kr["x"][j] = kl["x"][i] - np.float32(rng.uniform(-5, 90))
+        kr["octave"][j] = np.clip(kl["octave"][i] + rng.integers(-2, 3), 0, n_levels - 1)
+    kr["y"] = np.clip(kr["y"], 0, n_rows - 1)
+    kl["x"][:3] = np.float32(-1.0)  # maxU < 0 case with min_d = 0
+    return kl, dl, kr, dr, scale, n_rows
+
+
+def oracle_stereo(L, kl, dl, kr, dr, scale, n_rows, min_d, max_d):
+    bi = np.zeros(len(kl), np.int32)
+    bd = np.zeros(len(kl), np.int32)
+    c = np.ascontiguousarray
+    L.orc_stereo_search(c(kl["x"]), c(kl["y"]), c(kl["octave"]), dl, len(kl), c(kr["x"]), c(kr["y"]), c(kr["octave"]),
+                        dr, len(kr), scale, n_rows, min_d, max_d, bi, bd)
+    return bi, bd
