@@ -1,0 +1,149 @@
+// Orientation (intensity centroid) + steered rBRIEF descriptor + output assembly (sm_100a).
+// One warp per selected keypoint.
+//
+//   IC_Angle              src/ORBextractor.cc:77-104   integer moments over the radius-15 disc of the
+//                                                      UN-blurred level, cv::fastAtan2 in degrees
+//   computeOrbDescriptor  src/ORBextractor.cc:107-147  256 tests on the BLURRED level at pattern points
+//                                                      rotated by the keypoint angle (cvRound'ed)
+//   operator() tail       src/ORBextractor.cc:1101-1111 pt *= mvScaleFactor[level], level-ascending output
+// The moments are exact integers (warp-shuffle reduction); fastAtan2 and the rotation use
+// individually rounded float ops (__f*_rn, no FMA contraction) to match the host arithmetic.
+#include "extract.cuh"
+
+namespace orbfront {
+
+__device__ const int8_t g_pattern[1024] = {
+#include "orb_pattern.inc"
+};
+
+// circular patch row half-widths (umax), ORBextractor.cc:452-469 evaluated for HALF_PATCH_SIZE = 15
+__device__ __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+  constexpr float scale = (float)(180.0 / 3.14159265358979323846);
+  constexpr float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale,
+                  p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
+  constexpr float eps = 2.2204460492503131e-16f;  // (float)DBL_EPSILON
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a, c, c2;
+  if (ax >= ay) {
+    c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+  }
+  if (x < 0) a = __fsub_rn(180.f, a);
+  if (y < 0) a = __fsub_rn(360.f, a);
+  return a;
+}
+
+constexpr int kDescWarps = 8;
+
+// grid: (ceil(kept slots per frame / 8), frames)
+__global__ void __launch_bounds__(kDescWarps * 32)
+orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_frame) {
+  __shared__ int8_t pat[1024];
+  for (int i = threadIdx.x; i < 256; i += kDescWarps * 32)
+    reinterpret_cast<uint32_t*>(pat)[i] = reinterpret_cast<const uint32_t*>(g_pattern)[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int g = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+  const int f = blockIdx.y;
+  if (g >= slots_per_frame) return;
+  int l = 0;
+  while (l + 1 < P.nlevels && g >= P.lv[l + 1].kept_off) ++l;
+  const LevelGeom& G = P.lv[l];
+  const int k = g - G.kept_off;
+  const int* counts = P.kept_count + f * P.nlevels;
+  int before = 0, total = 0;
+  for (int i = 0; i < P.nlevels; ++i) {
+    const int c = counts[i];
+    if (i < l) before += c;
+    total += c;
+  }
+  if (g == 0 && lane == 0) P.out_count[f] = min(total, P.out_cap);
+  if (k >= counts[l]) return;
+  const int at = before + k;
+  if (at >= P.out_cap) return;
+
+  const uint32_t pay = P.kept[(size_t)f * P.kept_frame + G.kept_off + k];
+  const int x = (int)(pay & 0xfff) + (kEdge - 3), y = (int)((pay >> 12) & 0xfff) + (kEdge - 3);  // level coords
+  const int score = (int)(pay >> 24);
+
+  // --- orientation: lane <-> column u = lane-15
+  const int sp = level_pitch(P, l);
+  const uint8_t* c0 = level_ptr(P, l, f) + (size_t)y * sp + x;
+  const int u = lane - kHalfPatch;
+  int m10 = 0, m01 = 0;
+  if (lane < 31) {
+    const int au = u < 0 ? -u : u;
+#pragma unroll
+    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+      if (au <= c_umax[v < 0 ? -v : v]) {
+        const int val = c0[v * sp + u];
+        m10 += u * val;
+        m01 += v * val;
+      }
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    m10 += __shfl_xor_sync(0xffffffffu, m10, s);
+    m01 += __shfl_xor_sync(0xffffffffu, m01, s);
+  }
+  const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+  // --- steered rBRIEF on the blurred level: lane <-> descriptor byte
+  float ca = 0.f, sa = 0.f;
+  if (lane == 0) {
+    constexpr float factorPI = (float)(3.14159265358979323846 / 180.0);
+    const float rad = __fmul_rn(angle, factorPI);
+    double ds, dc;
+    sincos((double)rad, &ds, &dc);  // correctly rounded to float in all but vanishingly rare cases
+    ca = (float)dc;
+    sa = (float)ds;
+  }
+  ca = __shfl_sync(0xffffffffu, ca, 0);
+  sa = __shfl_sync(0xffffffffu, sa, 0);
+  const uint8_t* bc = P.blur + (size_t)f * P.blur_frame + G.off + (size_t)y * G.pitch + x;
+  const int8_t* pp = pat + 32 * lane;  // 8 tests x 2 points x (x,y)
+  uint32_t byte = 0;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    int val[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const float px = (float)pp[4 * t + 2 * e], py = (float)pp[4 * t + 2 * e + 1];
+      const int yy = __float2int_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)));
+      const int xx = __float2int_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)));
+      val[e] = bc[yy * G.pitch + xx];
+    }
+    byte |= (uint32_t)(val[0] < val[1]) << t;
+  }
+  P.out_desc[((size_t)f * P.out_cap + at) * 32 + lane] = (uint8_t)byte;
+  if (lane == 0) {
+    orbx_keypoint kp;
+    kp.x = (float)x; kp.y = (float)y;
+    if (l != 0) { kp.x = __fmul_rn(kp.x, G.scale); kp.y = __fmul_rn(kp.y, G.scale); }
+    kp.size = G.patch;
+    kp.angle = angle;
+    kp.response = (float)score;
+    kp.octave = l;
+    kp.class_id = -1;
+    P.out_kp[(size_t)f * P.out_cap + at] = kp;
+  }
+}
+
+int launch_describe(const ExtractParams& P, cudaStream_t s, int* launches) {
+  const LevelGeom& last = P.lv[P.nlevels - 1];
+  const int slots = last.kept_off + last.kept_cap;
+  orient_describe_kernel<<<dim3(div_up(slots, kDescWarps), P.n_frames), kDescWarps * 32, 0, s>>>(P, slots);
+  ORB_LAUNCH_CHECK();
+  ++*launches;
+  return ORB_OK;
+}
+
+}  // namespace orbfront

@@ -1,0 +1,439 @@
+// Host side of the extractor: handle, geometry/tables (the reference constructor and the
+// per-level constants of ComputePyramid / ComputeKeyPointsOctTree), device buffers, stream
+// orchestration and the orbx_* C ABI (include/orbfront.h).
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+#include "extract.cuh"
+
+using namespace orbfront;
+
+namespace {
+
+inline int cv_round(double v) { return (int)lrint(v); }
+inline int cv_round(float v) { return (int)lrintf(v); }
+inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+template <typename T>
+struct Dev {  // grow-only device allocation
+  T* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return ORB_OK;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+    if (e != cudaSuccess) return set_error(ORB_E_CUDA, "cudaMalloc(%zu bytes): %s", n * sizeof(T), cudaGetErrorString(e));
+    cap = n;
+    return ORB_OK;
+  }
+  ~Dev() { if (p) cudaFree(p); }
+};
+
+}  // namespace
+
+struct orbx_handle {
+  orbx_config cfg;
+  // reference constructor state (ORBextractor.cc:410-446)
+  std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+  std::vector<int> quota;
+  // geometry for the current frame size
+  int w = 0, h = 0;
+  ExtractParams P;
+  size_t l0_pitch = 0, l0_frame = 0;
+  int slots = 0;
+  // device state
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  Dev<uint8_t> l0, pyr, blur, qt_b, out_desc;
+  Dev<unsigned long long> cand;
+  Dev<uint32_t> kept, qt_seq;
+  Dev<int> cand_count, kept_count, out_count;
+  Dev<int4> rtab;
+  Dev<int> blur_tiles;
+  Dev<orbx_keypoint> out_kp;
+  Dev<uint8_t> border_tmp;
+  int n_frames = 0;       // frames of the last batch (0: nothing extracted yet)
+  int last_launches = 0;
+  std::vector<int> host_counts;
+  bool counts_valid = false;
+};
+
+namespace {
+
+// Constructor arithmetic of the reference, expression types included (scaleFactor is stored as
+// double, ORBextractor.h:99).
+void init_tables(orbx_handle* H) {
+  const orbx_config& c = H->cfg;
+  const int nl = c.nlevels;
+  const double sf = (double)c.scale_factor;
+  H->scale.assign(nl, 1.f); H->sigma2.assign(nl, 1.f); H->inv_scale.assign(nl, 1.f); H->inv_sigma2.assign(nl, 1.f);
+  for (int i = 1; i < nl; ++i) {
+    H->scale[i] = (float)(H->scale[i - 1] * sf);
+    H->sigma2[i] = H->scale[i] * H->scale[i];
+  }
+  for (int i = 0; i < nl; ++i) { H->inv_scale[i] = 1.0f / H->scale[i]; H->inv_sigma2[i] = 1.0f / H->sigma2[i]; }
+  H->quota.assign(nl, 0);
+  const float factor = (float)(1.0f / sf);
+  float want = c.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+  int sum = 0;
+  for (int l = 0; l < nl - 1; ++l) {
+    H->quota[l] = cv_round(want);
+    sum += H->quota[l];
+    want *= factor;
+  }
+  H->quota[nl - 1] = std::max(c.nfeatures - sum, 0);
+}
+
+// cv::resize(INTER_LINEAR) taps of one axis (11-bit weights); x axis clamps the fraction with
+// the index, y axis keeps the fraction and clamps rows (see oracle/cvprims.hpp, pinned to cv2).
+void axis_taps(int src_n, int dst_n, bool clamp_frac, int4* out) {
+  const double scale = (double)src_n / dst_n;
+  for (int d = 0; d < dst_n; ++d) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= s;
+    if (clamp_frac) {
+      if (s < 0) { f = 0; s = 0; }
+      if (s >= src_n - 1) { f = 0; s = src_n - 1; }
+    }
+    const int c0 = (short)cv_round((1.f - f) * 2048.f), c1 = (short)cv_round(f * 2048.f);
+    const int s0 = std::min(std::max(s, 0), src_n - 1), s1 = std::min(std::max(s + 1, 0), src_n - 1);
+    out[d] = make_int4(s0, c0, c1, s1);
+  }
+}
+
+int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
+  const orbx_config& c = H->cfg;
+  const int nl = c.nlevels;
+  ExtractParams& P = H->P;
+  const bool geom_changed = (w != H->w || h != H->h);
+  if (geom_changed) {
+    memset(&P, 0, sizeof(P));
+    P.nlevels = nl;
+    P.ini_th = c.ini_th_fast;
+    P.min_th = c.min_th_fast;
+    size_t off = 0;
+    int cell_base = 0, cand_off = 0, kept_off = 0, tab = 0, tiles = 0;
+    std::vector<int> blur_tiles(nl + 1, 0);
+    for (int l = 0; l < nl; ++l) {
+      LevelGeom& G = P.lv[l];
+      G.w = cv_round((float)w * H->inv_scale[l]);
+      G.h = cv_round((float)h * H->inv_scale[l]);
+      const int minB = kEdge - 3, maxBX = G.w - kEdge + 3, maxBY = G.h - kEdge + 3;
+      const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+      if (width < 30.f || height < 30.f)
+        return set_error(ORB_E_INVALID, "level %d is %dx%d: too small for the 30-px FAST cell grid (reference divides by zero)", l, G.w, G.h);
+      G.pitch = (int)align_up<size_t>((size_t)G.w + 4, 64);
+      G.off = off;
+      off += align_up<size_t>((size_t)G.pitch * G.h, 256);
+      G.nCols = (int)(width / 30.f);
+      G.nRows = (int)(height / 30.f);
+      G.wCell = (int)ceilf(width / G.nCols);
+      G.hCell = (int)ceilf(height / G.nRows);
+      G.cell_base = cell_base;
+      cell_base += G.nCols * G.nRows;
+      G.boxW = maxBX - minB;
+      G.boxH = maxBY - minB;
+      G.nIni = (int)roundf((float)G.boxW / (float)G.boxH);
+      if (G.nIni < 1 || G.nIni > (1 << kRootBits))
+        return set_error(ORB_E_INVALID, "level %d aspect ratio gives %d quadtree roots (supported 1..%d)", l, G.nIni, 1 << kRootBits);
+      if (G.boxW > kMaxBox || G.boxH > kMaxBox)
+        return set_error(ORB_E_INVALID, "frame %dx%d exceeds the supported %d-px detection box", w, h, kMaxBox);
+      G.hX = (float)G.boxW / G.nIni;
+      G.quota = H->quota[l];
+      int span = std::max((int)ceilf(G.hX) + 1, G.boxH), lg = 0;
+      while ((1 << lg) < span) ++lg;
+      G.dmax = std::min(lg + 2, kMaxDepth);
+      const int vw = G.w - 2 * kEdge, vh = G.h - 2 * kEdge;
+      G.cand_cap = next_pow2(((vw + 1) / 2 + G.nCols) * ((vh + 1) / 2 + G.nRows));
+      G.cand_off = cand_off;
+      cand_off += G.cand_cap;
+      G.kept_cap = std::max(G.quota, 0) + 4 * G.nIni + 3;
+      G.kept_off = kept_off;
+      kept_off += G.kept_cap;
+      G.scale = H->scale[l];
+      G.patch = (float)(int)(31 * H->scale[l]);  // const int scaledPatchSize = PATCH_SIZE*mvScaleFactor[level]
+      G.xtab = tab; tab += G.w;
+      G.ytab = tab; tab += G.h;
+      blur_tiles[l] = tiles;
+      tiles += div_up(G.w, 64) * div_up(G.h, 32);
+    }
+    blur_tiles[nl] = tiles;
+    P.total_cells = cell_base;
+    P.pyr_frame = P.blur_frame = off;
+    P.cand_frame = (size_t)cand_off;
+    P.kept_frame = (size_t)kept_off;
+    P.out_cap = kept_off;
+    H->slots = kept_off;
+    // resize taps (levels >= 1 read level l-1)
+    std::vector<int4> taps((size_t)tab, make_int4(0, 0, 0, 0));
+    for (int l = 1; l < nl; ++l) {
+      axis_taps(P.lv[l - 1].w, P.lv[l].w, true, &taps[P.lv[l].xtab]);
+      axis_taps(P.lv[l - 1].h, P.lv[l].h, false, &taps[P.lv[l].ytab]);
+    }
+    int rc;
+    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(nl + 1))) return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->rtab.p, taps.data(), taps.size() * sizeof(int4), cudaMemcpyHostToDevice, H->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->blur_tiles.p, blur_tiles.data(), (nl + 1) * sizeof(int), cudaMemcpyHostToDevice, H->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));  // host vectors go out of scope
+    H->w = w; H->h = h;
+    H->l0_pitch = align_up<size_t>((size_t)w + 4, 64);
+    H->l0_frame = H->l0_pitch * (size_t)h;  // pitch is a multiple of 64, so frames stay 64-byte aligned
+  }
+  // buffers (grow-only)
+  int rc;
+  const size_t nf = (size_t)n_frames;
+  if ((own_l0 && (rc = H->l0.reserve(nf * H->l0_frame + 256))) || (rc = H->pyr.reserve(nf * P.pyr_frame + 256)) ||
+      (rc = H->blur.reserve(nf * P.blur_frame + 256)) || (rc = H->cand.reserve(nf * P.cand_frame)) ||
+      (rc = H->qt_b.reserve(nf * (P.cand_frame + kMaxLevels) + 16)) || (rc = H->qt_seq.reserve(nf * P.cand_frame)) ||
+      (rc = H->kept.reserve(nf * P.kept_frame)) || (rc = H->cand_count.reserve(nf * nl)) ||
+      (rc = H->kept_count.reserve(nf * nl)) || (rc = H->out_count.reserve(nf)) ||
+      (rc = H->out_kp.reserve(nf * P.out_cap)) || (rc = H->out_desc.reserve(nf * P.out_cap * 32)))
+    return rc;
+  P.n_frames = n_frames;
+  P.pyr = H->pyr.p; P.blur = H->blur.p; P.cand = H->cand.p; P.cand_count = H->cand_count.p;
+  P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p;
+  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p;
+  P.out_kp = H->out_kp.p; P.out_desc = H->out_desc.p; P.out_count = H->out_count.p;
+  return ORB_OK;
+}
+
+}  // namespace
+
+// ====================================================================================
+extern "C" {
+
+int orbx_create(const orbx_config* cfg, orbx_handle** out) {
+  if (!cfg || !out) return set_error(ORB_E_INVALID, "orbx_create: null argument");
+  if (cfg->nlevels < 1 || cfg->nlevels > kMaxLevels || cfg->nfeatures < 0 || !(cfg->scale_factor > 1.0f) ||
+      cfg->min_th_fast < 1 || cfg->ini_th_fast < cfg->min_th_fast || cfg->ini_th_fast > 254)
+    return set_error(ORB_E_INVALID,
+                     "orbx_create: need 1 <= nlevels <= %d, scaleFactor > 1, 1 <= minThFAST <= iniThFAST <= 254", kMaxLevels);
+  int rc = use_device(cfg->device);
+  if (rc) return rc;
+  orbx_handle* H = new orbx_handle();
+  H->cfg = *cfg;
+  init_tables(H);
+  cudaError_t e = cudaStreamCreateWithFlags(&H->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&H->ev0);
+  if (e == cudaSuccess) e = cudaEventCreate(&H->ev1);
+  if (e != cudaSuccess) {
+    delete H;
+    return set_error(ORB_E_CUDA, "orbx_create: %s", cudaGetErrorString(e));
+  }
+  if (cfg->max_width > 0 && cfg->max_height > 0) {  // size everything up front
+    rc = configure(H, cfg->max_width, cfg->max_height, std::max(cfg->max_batch, 1), true);
+    if (rc) { orbx_destroy(H); return rc; }
+  }
+  *out = H;
+  return ORB_OK;
+}
+
+int orbx_destroy(orbx_handle* H) {
+  if (!H) return ORB_OK;
+  cudaSetDevice(H->cfg.device);
+  if (H->stream) cudaStreamSynchronize(H->stream);
+  if (H->ev0) cudaEventDestroy(H->ev0);
+  if (H->ev1) cudaEventDestroy(H->ev1);
+  if (H->stream) cudaStreamDestroy(H->stream);
+  delete H;
+  return ORB_OK;
+}
+
+int orbx_get_scale_table(const orbx_handle* H, int which, float* out) {
+  if (!H || !out || which < 0 || which > 3) return set_error(ORB_E_INVALID, "orbx_get_scale_table: bad argument");
+  const std::vector<float>& v = which == 0 ? H->scale : which == 1 ? H->inv_scale : which == 2 ? H->sigma2 : H->inv_sigma2;
+  memcpy(out, v.data(), v.size() * sizeof(float));
+  return ORB_OK;
+}
+
+int orbx_get_level_quota(const orbx_handle* H, int* out) {
+  if (!H || !out) return set_error(ORB_E_INVALID, "orbx_get_level_quota: bad argument");
+  memcpy(out, H->quota.data(), H->quota.size() * sizeof(int));
+  return ORB_OK;
+}
+
+int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht, size_t stride, size_t frame_stride,
+                       int memory) {
+  if (!H || n < 0 || (memory != 0 && memory != 1)) return set_error(ORB_E_INVALID, "orbx_extract_batch: bad argument");
+  H->counts_valid = false;
+  if (n == 0 || !imgs || w <= 0 || ht <= 0) {  // empty image: nothing to do (ORBextractor.cc:1054-1055)
+    H->n_frames = 0;
+    return ORB_OK;
+  }
+  if (stride < (size_t)w || (n > 1 && frame_stride < stride * (size_t)(ht - 1) + w))
+    return set_error(ORB_E_INVALID, "orbx_extract_batch: stride smaller than a row / frame");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const bool alias = memory == 1 && ((uintptr_t)imgs % 16 == 0) && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
+  if ((rc = configure(H, w, ht, n, !alias))) return rc;
+  ExtractParams& P = H->P;
+  if (alias) {
+    P.l0 = imgs; P.l0_pitch = stride; P.l0_frame = frame_stride;
+  } else {
+    const cudaMemcpyKind kind = memory ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (H->l0_frame == H->l0_pitch * (size_t)ht && frame_stride == stride * (size_t)ht) {
+      ORB_CUDA_TRY(cudaMemcpy2DAsync(H->l0.p, H->l0_pitch, imgs, stride, (size_t)w, (size_t)ht * n, kind, H->stream));
+    } else {
+      for (int f = 0; f < n; ++f)
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(H->l0.p + (size_t)f * H->l0_frame, H->l0_pitch, imgs + (size_t)f * frame_stride, stride,
+                                       (size_t)w, (size_t)ht, kind, H->stream));
+    }
+    P.l0 = H->l0.p; P.l0_pitch = H->l0_pitch; P.l0_frame = H->l0_frame;
+  }
+  int launches = 0;
+  ORB_CUDA_TRY(cudaEventRecord(H->ev0, H->stream));
+  if ((rc = launch_pyramid(P, H->stream, &launches)) || (rc = launch_fast(P, H->stream, &launches)) ||
+      (rc = launch_quadtree(P, H->stream, &launches)) || (rc = launch_blur(P, H->stream, &launches)) ||
+      (rc = launch_describe(P, H->stream, &launches)))
+    return rc;
+  ORB_CUDA_TRY(cudaEventRecord(H->ev1, H->stream));
+  H->n_frames = n;
+  H->last_launches = launches;
+  return ORB_OK;
+}
+
+int orbx_sync(orbx_handle* H) {
+  if (!H) return set_error(ORB_E_INVALID, "orbx_sync: null");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+
+static int fetch_counts(orbx_handle* H) {
+  if (H->counts_valid) return ORB_OK;
+  H->host_counts.assign((size_t)H->n_frames, 0);
+  if (H->n_frames) {
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->host_counts.data(), H->out_count.p, sizeof(int) * (size_t)H->n_frames,
+                                 cudaMemcpyDeviceToHost, H->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  }
+  H->counts_valid = true;
+  return ORB_OK;
+}
+
+int orbx_batch_counts(orbx_handle* H, int* counts) {
+  if (!H || !counts) return set_error(ORB_E_INVALID, "orbx_batch_counts: bad argument");
+  int rc = use_device(H->cfg.device);
+  if (rc || (rc = fetch_counts(H))) return rc;
+  memcpy(counts, H->host_counts.data(), sizeof(int) * (size_t)H->n_frames);
+  return ORB_OK;
+}
+
+int orbx_batch_read(orbx_handle* H, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out) {
+  if (!H || !n_out || cap < 0) return set_error(ORB_E_INVALID, "orbx_batch_read: bad argument");
+  if (H->n_frames == 0) { *n_out = 0; return ORB_OK; }
+  if (frame < 0 || frame >= H->n_frames) return set_error(ORB_E_INVALID, "orbx_batch_read: frame %d out of range", frame);
+  int rc = use_device(H->cfg.device);
+  if (rc || (rc = fetch_counts(H))) return rc;
+  const int n = H->host_counts[frame];
+  *n_out = n;
+  if (n > cap) return set_error(ORB_E_CAPACITY, "orbx_batch_read: %d keypoints, capacity %d", n, cap);
+  if (n == 0) return ORB_OK;
+  if (!kps || !desc) return set_error(ORB_E_INVALID, "orbx_batch_read: null output");
+  const size_t at = (size_t)frame * H->P.out_cap;
+  ORB_CUDA_TRY(cudaMemcpyAsync(kps, H->out_kp.p + at, sizeof(orbx_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(desc, H->out_desc.p + at * 32, (size_t)n * 32, cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+
+int orbx_batch_read_all(orbx_handle* H, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts) {
+  if (!H || !kps || !desc || !counts) return set_error(ORB_E_INVALID, "orbx_batch_read_all: bad argument");
+  if (H->n_frames == 0) return ORB_OK;
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const int oc = H->P.out_cap;
+  if (cap_per_frame < oc)
+    return set_error(ORB_E_CAPACITY, "orbx_batch_read_all: cap_per_frame %d < %d (per-frame output capacity)", cap_per_frame, oc);
+  ORB_CUDA_TRY(cudaMemcpyAsync(counts, H->out_count.p, sizeof(int) * (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaMemcpy2DAsync(kps, sizeof(orbx_keypoint) * (size_t)cap_per_frame, H->out_kp.p, sizeof(orbx_keypoint) * (size_t)oc,
+                                 sizeof(orbx_keypoint) * (size_t)oc, (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaMemcpy2DAsync(desc, 32 * (size_t)cap_per_frame, H->out_desc.p, 32 * (size_t)oc, 32 * (size_t)oc,
+                                 (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+
+int orbx_extract(orbx_handle* H, const uint8_t* img, int w, int ht, size_t stride, orbx_keypoint* kps, uint8_t* desc,
+                 int cap, int* n_out) {
+  if (!H || !n_out) return set_error(ORB_E_INVALID, "orbx_extract: null argument");
+  *n_out = 0;
+  int rc = orbx_extract_batch(H, img, 1, w, ht, stride, stride * (size_t)std::max(ht, 0), 0);
+  if (rc) return rc;
+  return orbx_batch_read(H, 0, kps, desc, cap, n_out);
+}
+
+int orbx_level_size(const orbx_handle* H, int level, int* w, int* ht) {
+  if (!H || !w || !ht || level < 0 || level >= H->cfg.nlevels) return set_error(ORB_E_INVALID, "orbx_level_size: bad argument");
+  if (H->w == 0) return set_error(ORB_E_STATE, "orbx_level_size: no frame size configured yet");
+  *w = H->P.lv[level].w;
+  *ht = H->P.lv[level].h;
+  return ORB_OK;
+}
+
+int orbx_get_level(orbx_handle* H, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border) {
+  if (!H || !dst || level < 0 || level >= H->cfg.nlevels) return set_error(ORB_E_INVALID, "orbx_get_level: bad argument");
+  if (H->n_frames == 0) return set_error(ORB_E_STATE, "orbx_get_level: nothing extracted yet");
+  if (frame < 0 || frame >= H->n_frames) return set_error(ORB_E_INVALID, "orbx_get_level: frame out of range");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const ExtractParams& P = H->P;
+  const LevelGeom& G = P.lv[level];
+  const uint8_t* src = level == 0 ? P.l0 + (size_t)frame * P.l0_frame : P.pyr + (size_t)frame * P.pyr_frame + G.off;
+  const size_t pitch = level == 0 ? P.l0_pitch : (size_t)G.pitch;
+  if (!with_border) {
+    if (dst_stride < (size_t)G.w) return set_error(ORB_E_INVALID, "orbx_get_level: dst_stride too small");
+    ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_stride, src, pitch, (size_t)G.w, (size_t)G.h, cudaMemcpyDeviceToHost, H->stream));
+  } else {
+    const int W = G.w + 2 * kEdge, Hh = G.h + 2 * kEdge;
+    if (dst_stride < (size_t)W) return set_error(ORB_E_INVALID, "orbx_get_level: dst_stride too small");
+    if ((rc = H->border_tmp.reserve((size_t)W * Hh))) return rc;
+    if ((rc = launch_border_copy(src, G.w, G.h, pitch, H->border_tmp.p, H->stream))) return rc;
+    ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_stride, H->border_tmp.p, (size_t)W, (size_t)W, (size_t)Hh, cudaMemcpyDeviceToHost, H->stream));
+  }
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+
+int orbx_get_candidates(orbx_handle* H, int frame, int level, int32_t* xys, int cap, int* n_out) {
+  if (!H || !n_out || level < 0 || level >= H->cfg.nlevels || cap < 0) return set_error(ORB_E_INVALID, "orbx_get_candidates: bad argument");
+  if (H->n_frames == 0) return set_error(ORB_E_STATE, "orbx_get_candidates: nothing extracted yet");
+  if (frame < 0 || frame >= H->n_frames) return set_error(ORB_E_INVALID, "orbx_get_candidates: frame out of range");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const ExtractParams& P = H->P;
+  int n = 0;
+  ORB_CUDA_TRY(cudaMemcpyAsync(&n, P.cand_count + frame * P.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  *n_out = n;
+  if (n > cap) return set_error(ORB_E_CAPACITY, "orbx_get_candidates: %d candidates, capacity %d", n, cap);
+  if (n == 0) return ORB_OK;
+  if (!xys) return set_error(ORB_E_INVALID, "orbx_get_candidates: null output");
+  std::vector<unsigned long long> tmp((size_t)n);
+  ORB_CUDA_TRY(cudaMemcpyAsync(tmp.data(), P.cand + (size_t)frame * P.cand_frame + P.lv[level].cand_off, sizeof(unsigned long long) * (size_t)n,
+                               cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  for (int i = 0; i < n; ++i) {
+    const uint32_t pay = (uint32_t)tmp[i];
+    xys[3 * i] = (int)(pay & 0xfff);
+    xys[3 * i + 1] = (int)((pay >> 12) & 0xfff);
+    xys[3 * i + 2] = (int)(pay >> 24);
+  }
+  return ORB_OK;
+}
+
+int orbx_last_batch_ms(orbx_handle* H, float* ms, int* launches) {
+  if (!H || H->n_frames == 0) return set_error(ORB_E_STATE, "orbx_last_batch_ms: nothing extracted yet");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaEventSynchronize(H->ev1));
+  if (ms) ORB_CUDA_TRY(cudaEventElapsedTime(ms, H->ev0, H->ev1));
+  if (launches) *launches = H->last_launches;
+  return ORB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,121 @@
+"""GPU parity: the CUDA extractor (through the C ABI) vs the CPU oracle on the same frames.
+
+Bar (BASELINE.json north_star): pyramid pixels, candidate sets, kept keypoints (octave, x, y,
+response, size) and their ORDER bit-exact; angles within 1e-3 rad (in practice identical floats);
+descriptors bit-exact up to <= 1e-4 mismatching bits (rounding-boundary samples)."""
+import numpy as np
+import pytest
+
+from oracle_lib import PortExtractor
+from orb_slam2_e_b200 import synth
+from orb_slam2_e_b200.extractor import ORBextractor
+
+pytestmark = pytest.mark.gpu
+
+TUM = (1000, 1.2, 8, 20, 7)
+KITTI = (2000, 1.2, 8, 20, 7)
+HAMLYN = (1200, 1.1, 6, 24, 7)
+
+
+def compare(img, cfg, gpu=None, frame_result=None):
+    port = PortExtractor(*cfg)
+    pk, pd = port.extract(img)
+    if frame_result is None:
+        gpu = gpu or ORBextractor(*cfg)
+        gk, gd = gpu(img)
+        for l in range(cfg[2]):
+            assert np.array_equal(gpu.level(l, 0, False), port.level(l, False)), f"pyramid level {l}"
+            assert np.array_equal(gpu.level(l, 0, True), port.level(l, True)), f"bordered level {l}"
+            got = gpu.candidates(l)
+            want = port.stage(0, l)
+            key = lambda a: a[np.lexsort((a[:, 0], a[:, 1]))]
+            assert len(got) == len(want), f"level {l}: {len(got)} candidates vs {len(want)}"
+            assert np.array_equal(key(got), key(want)), f"candidates level {l}"
+    else:
+        gk, gd = frame_result
+    assert len(gk) == len(pk), (len(gk), len(pk))
+    for name in ("octave", "x", "y", "response", "size", "class_id"):
+        assert np.array_equal(gk[name], pk[name]), name
+    dang = np.abs(np.deg2rad(gk["angle"].astype(np.float64) - pk["angle"].astype(np.float64)))
+    dang = np.minimum(dang, 2 * np.pi - dang)
+    assert dang.max(initial=0) <= 1e-3
+    same_angle = gk["angle"] == pk["angle"]
+    bits = np.unpackbits(gd ^ pd, axis=1)
+    rate = bits.sum() / max(bits.size, 1)
+    assert rate <= 1e-4, f"descriptor bit mismatch rate {rate}"
+    return dict(n=len(pk), angle_equal=float(same_angle.mean()) if len(pk) else 1.0, bit_rate=rate)
+
+
+def test_getters_match_oracle():
+    g = ORBextractor(*TUM)
+    p = PortExtractor(*TUM)
+    assert [p.quota(l) for l in range(8)] == list(g.mnFeaturesPerLevel)
+    assert [p.scale(l) for l in range(8)] == list(g.GetScaleFactors())
+    assert g.GetLevels() == 8 and abs(g.GetScaleFactor() - 1.2) < 1e-6
+    s = g.GetScaleFactors()
+    assert np.array_equal(g.GetInverseScaleFactors(), (np.float32(1) / s).astype(np.float32))
+    assert np.array_equal(g.GetScaleSigmaSquares(), s * s)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_tum_textured(seed):
+    r = compare(synth.textured_frame(480, 640, seed), TUM)
+    assert r["n"] >= 1000
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_hamlyn_low_texture(seed):
+    compare(synth.endoscopy_frame(480, 640, seed), HAMLYN)
+
+
+def test_kitti_stereo_shapes():
+    left, right = synth.stereo_pair(376, 1241, 21)
+    g = ORBextractor(*KITTI)
+    compare(left, KITTI, g)
+    compare(right, KITTI, g)
+
+
+def test_edge_cases():
+    g = ORBextractor(500, 1.2, 3, 20, 7)
+    k, d = g(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    k, d = g(np.full((200, 260), 90, np.uint8))  # flat: no corners anywhere
+    assert len(k) == 0
+    with pytest.raises(AssertionError):
+        g(np.zeros((100, 100, 3), np.uint8))
+    # strided (non-contiguous rows) input, odd sizes, small quota
+    big = synth.textured_frame(300, 420, 9)
+    compare(big[7:251, 11:390], (300, 1.2, 4, 20, 7))
+    compare(synth.textured_frame(123, 157, 5), (150, 1.3, 3, 15, 5))
+    # a level too small for the 30-px cell grid is rejected loudly
+    from orb_slam2_e_b200._lib import OrbFrontError
+    with pytest.raises(OrbFrontError):
+        ORBextractor(500, 1.2, 8, 20, 7)(synth.textured_frame(100, 120, 1))
+
+
+def test_frame_size_change_and_reuse():
+    g = ORBextractor(*TUM)
+    compare(synth.textured_frame(480, 640, 4), TUM, g)
+    compare(synth.textured_frame(360, 480, 5), TUM, g)
+    compare(synth.textured_frame(480, 640, 6), TUM, g)
+
+
+def test_batch_equals_single_frames():
+    frames = np.stack([synth.textured_frame(480, 640, 20), synth.endoscopy_frame(480, 640, 21),
+                       synth.textured_frame(480, 640, 22), np.full((480, 640), 7, np.uint8),
+                       synth.endoscopy_frame(480, 640, 23)])
+    g = ORBextractor(*HAMLYN, max_width=640, max_height=480, max_batch=5)
+    res = g.extract_batch(frames)
+    assert len(res) == 5 and len(res[3][0]) == 0
+    for f in range(5):
+        compare(frames[f], HAMLYN, frame_result=res[f])
+
+
+def test_large_frame_global_sort_path():
+    """1280x720 with a small smem key budget forces the global-memory quadtree path."""
+    import os
+    os.environ["ORBX_QT_SMEM_KEYS"] = "1024"
+    try:
+        compare(synth.textured_frame(720, 1280, 31), (3000, 1.2, 8, 20, 7))
+    finally:
+        del os.environ["ORBX_QT_SMEM_KEYS"]
