@@ -112,6 +112,17 @@ int orbx_get_candidates(orbx_handle* h, int frame, int level, int32_t* xys, int 
  * stream, all kernels of the batch), and the number of kernel launches it issued. */
 int orbx_last_batch_ms(orbx_handle* h, float* ms, int* launches);
 
+/* The handle's CUDA stream (a cudaStream_t), so a caller can order its own work / events
+ * against the extractor's kernels. */
+int orbx_get_stream(orbx_handle* h, void** cuda_stream);
+
+/* Per-stage device timing.  When enabled, every batch records CUDA events between its stages on
+ * the handle's stream; orbx_last_stage_ms then returns the milliseconds of
+ * [0] pyramid (resize) [1] FAST cells [2] quadtree select [3] Gaussian blur [4] orientation+rBRIEF. */
+enum { ORBX_N_STAGES = 5 };
+int orbx_set_stage_timing(orbx_handle* h, int enabled);
+int orbx_last_stage_ms(orbx_handle* h, float* ms /* ORBX_N_STAGES */);
+
 /* ------------------------------------------------------------------ matcher ------------ */
 
 enum { ORBM_TH_HIGH = 95, ORBM_TH_LOW = 45, ORBM_HISTO_LENGTH = 30 }; /* ORBmatcher.cc:37-40 */
@@ -148,6 +159,7 @@ int orbm_db_destroy(orbm_db* db);
 int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int memory);
 int orbm_db_sync(orbm_db* db);
 int orbm_db_last_ms(orbm_db* db, float* ms, int* launches);
+int orbm_db_get_stream(orbm_db* db, void** cuda_stream);
 
 /* Exact merge of per-shard results (shard-major: shards[s*nq + q], shards ordered by row_base)
  * into the result of one sequential scan, then the acceptance rule of ORBmatcher.cc:429-431:

@@ -56,6 +56,10 @@ SIGNATURES = {
     "orbx_get_level": (_i, [_vp, _i, _i, _vp, _sz, _i]),
     "orbx_get_candidates": (_i, [_vp, _i, _i, _vp, _i, _ip]),
     "orbx_last_batch_ms": (_i, [_vp, C.POINTER(_f), _ip]),
+    "orbx_get_stream": (_i, [_vp, C.POINTER(_vp)]),
+    "orbx_set_stage_timing": (_i, [_vp, _i]),
+    "orbx_last_stage_ms": (_i, [_vp, _vp]),
+    "orbm_db_get_stream": (_i, [_vp, C.POINTER(_vp)]),
     "orbm_hamming": (_i, [_vp, _vp]),
     "orbm_hamming_pairs": (_i, [_i, _vp, _vp, _i, _vp]),
     "orbm_db_create": (_i, [_i, _i64, C.POINTER(_vp)]),

@@ -46,6 +46,8 @@ struct orbx_handle {
   // device state
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t stage_ev[ORBX_N_STAGES + 1] = {};
+  bool stage_timing = false, stage_valid = false;
   Dev<uint8_t> l0, pyr, blur, qt_b, out_desc;
   Dev<unsigned long long> cand;
   Dev<uint32_t> kept, qt_seq;
@@ -237,6 +239,8 @@ int orbx_destroy(orbx_handle* H) {
   if (H->stream) cudaStreamSynchronize(H->stream);
   if (H->ev0) cudaEventDestroy(H->ev0);
   if (H->ev1) cudaEventDestroy(H->ev1);
+  for (cudaEvent_t e : H->stage_ev)
+    if (e) cudaEventDestroy(e);
   if (H->stream) cudaStreamDestroy(H->stream);
   delete H;
   return ORB_OK;
@@ -285,10 +289,15 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
   }
   int launches = 0;
   ORB_CUDA_TRY(cudaEventRecord(H->ev0, H->stream));
-  if ((rc = launch_pyramid(P, H->stream, &launches)) || (rc = launch_fast(P, H->stream, &launches)) ||
-      (rc = launch_quadtree(P, H->stream, &launches)) || (rc = launch_blur(P, H->stream, &launches)) ||
-      (rc = launch_describe(P, H->stream, &launches)))
-    return rc;
+  typedef int (*stage_fn)(const ExtractParams&, cudaStream_t, int*);
+  const stage_fn stages[ORBX_N_STAGES] = {launch_pyramid, launch_fast, launch_quadtree, launch_blur, launch_describe};
+  const bool timing = H->stage_timing;
+  if (timing) ORB_CUDA_TRY(cudaEventRecord(H->stage_ev[0], H->stream));
+  for (int s = 0; s < ORBX_N_STAGES; ++s) {
+    if ((rc = stages[s](P, H->stream, &launches))) return rc;
+    if (timing) ORB_CUDA_TRY(cudaEventRecord(H->stage_ev[s + 1], H->stream));
+  }
+  H->stage_valid = timing;
   ORB_CUDA_TRY(cudaEventRecord(H->ev1, H->stream));
   H->n_frames = n;
   H->last_launches = launches;
@@ -433,6 +442,34 @@ int orbx_last_batch_ms(orbx_handle* H, float* ms, int* launches) {
   ORB_CUDA_TRY(cudaEventSynchronize(H->ev1));
   if (ms) ORB_CUDA_TRY(cudaEventElapsedTime(ms, H->ev0, H->ev1));
   if (launches) *launches = H->last_launches;
+  return ORB_OK;
+}
+
+int orbx_get_stream(orbx_handle* H, void** cuda_stream) {
+  if (!H || !cuda_stream) return set_error(ORB_E_INVALID, "orbx_get_stream: bad argument");
+  *cuda_stream = (void*)H->stream;
+  return ORB_OK;
+}
+
+int orbx_set_stage_timing(orbx_handle* H, int enabled) {
+  if (!H) return set_error(ORB_E_INVALID, "orbx_set_stage_timing: null");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  if (enabled)
+    for (cudaEvent_t& e : H->stage_ev)
+      if (!e) ORB_CUDA_TRY(cudaEventCreate(&e));
+  H->stage_timing = enabled != 0;
+  H->stage_valid = false;
+  return ORB_OK;
+}
+
+int orbx_last_stage_ms(orbx_handle* H, float* ms) {
+  if (!H || !ms) return set_error(ORB_E_INVALID, "orbx_last_stage_ms: bad argument");
+  if (!H->stage_valid) return set_error(ORB_E_STATE, "orbx_last_stage_ms: no batch has run with stage timing enabled");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaEventSynchronize(H->stage_ev[ORBX_N_STAGES]));
+  for (int s = 0; s < ORBX_N_STAGES; ++s) ORB_CUDA_TRY(cudaEventElapsedTime(&ms[s], H->stage_ev[s], H->stage_ev[s + 1]));
   return ORB_OK;
 }
 

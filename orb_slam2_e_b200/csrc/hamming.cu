@@ -484,6 +484,12 @@ int orbm_db_last_ms(orbm_db* db, float* ms, int* launches) {
   return ORB_OK;
 }
 
+int orbm_db_get_stream(orbm_db* db, void** cuda_stream) {
+  if (!db || !cuda_stream) return set_error(ORB_E_INVALID, "orbm_db_get_stream: bad argument");
+  *cuda_stream = (void*)db->stream;
+  return ORB_OK;
+}
+
 int orbm_merge_top2(const orbm_top2* shards, int n_shards, int nq, float ratio, int th, orbm_top2* out,
                     uint8_t* accept) {
   if (!shards || !out || n_shards < 1 || nq < 0) return set_error(ORB_E_INVALID, "orbm_merge_top2: bad argument");

@@ -125,6 +125,22 @@ class ORBextractor:
     def sync(self):
         check(self._L.orbx_sync(self._h))
 
+    STAGES = ("pyramid", "fast", "quadtree", "blur", "describe")
+
+    def cuda_stream(self) -> int:
+        """Address of the handle's cudaStream_t (wrap with torch.cuda.ExternalStream to time on it)."""
+        s = C.c_void_p()
+        check(self._L.orbx_get_stream(self._h, C.byref(s)))
+        return s.value or 0
+
+    def set_stage_timing(self, enabled: bool):
+        check(self._L.orbx_set_stage_timing(self._h, int(enabled)))
+
+    def last_stage_ms(self) -> dict:
+        ms = np.zeros(5, np.float32)
+        check(self._L.orbx_last_stage_ms(self._h, ptr(ms)))
+        return dict(zip(self.STAGES, ms.tolist()))
+
     def last_batch_ms(self):
         ms, n = C.c_float(), C.c_int()
         check(self._L.orbx_last_batch_ms(self._h, C.byref(ms), C.byref(n)))

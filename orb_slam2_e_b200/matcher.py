@@ -157,6 +157,11 @@ class DescriptorDB:
     def sync(self):
         check(_lib.load().orbm_db_sync(self._h))
 
+    def cuda_stream(self) -> int:
+        s = C.c_void_p()
+        check(_lib.load().orbm_db_get_stream(self._h, C.byref(s)))
+        return s.value or 0
+
     def last_ms(self):
         ms, n = C.c_float(), C.c_int()
         check(_lib.load().orbm_db_last_ms(self._h, C.byref(ms), C.byref(n)))
