@@ -1,0 +1,250 @@
+#!/usr/bin/env python
+"""bench.py -- ORB front end on B200: frames/s of ORB extraction (640x480, 1000 features, TUM
+settings) and Gmatch/s of the brute-force Hamming top-2 search (1000 queries vs 10 M rows).
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched under torchrun)
+    python bench.py --impl reference ...                     (the reference's CPU path)
+
+One JSON line on stdout (rank 0).  A "step" = one pass of the extractor over one batch of
+synthetic frames per GPU (frames are independent: sharded over ranks with no collective, weak
+scaling), followed -- outside the extraction timing -- by the matching measurement, whose
+database IS sharded across the ranks and merged with one NCCL all-gather (strong scaling).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+TUM = dict(nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7)
+W, H = 640, 480
+SEED = 1000  # seed = 1000*config + index
+
+
+def level_sizes(w, h, scale, nlevels):
+    s = np.float32(1.0)
+    out = []
+    for l in range(nlevels):
+        if l:
+            s = np.float32(np.float64(s) * np.float64(np.float32(scale)))
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
+
+
+def algorithmic_bytes_per_frame(w, h, cfg, n_kp):
+    """every level read once + every derived level written once + 60 B per keypoint."""
+    px = [a * b for a, b in level_sizes(w, h, cfg["scaleFactor"], cfg["nlevels"])]
+    return sum(px) + sum(px[1:]) + 60 * n_kp, sum(px)
+
+
+class ClockSampler:
+    """nvidia-smi SM clock / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def mark(self):
+        return time.time()
+
+    def summary(self, t0, t1):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15 and len(r) >= 7] or [r for _, r in self.rows[-3:] if len(r) >= 7]
+        try:
+            sm = sorted(float(r[0]) for r in rows)
+            reasons = [n for i, n in ((3, "hw_slowdown"), (4, "hw_thermal_slowdown"), (5, "sw_thermal_slowdown"), (6, "sw_power_cap"))
+                       if any(r[i].lower().startswith("active") for r in rows)]
+            return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons, "samples": len(rows)}
+        except Exception as e:  # pragma: no cover
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["parse error: %s" % e]}
+
+    def stop(self):
+        if self.p is not None:
+            self.p.terminate()
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------ CPU reference arm ------
+def _cpu_libs():
+    """(kind, make_extractor): the reference's own ORBextractor.cc build when oracle/_ref
+    travelled with the snapshot, else the restatement ("port").  bench.py only TIMES these."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib
+    if oracle_lib.ref_lib(fast=True) is not None:
+        return "reference", (lambda c: oracle_lib.RefExtractor(c["nfeatures"], c["scaleFactor"], c["nlevels"], c["iniThFAST"],
+                                                               c["minThFAST"], fast=True)), oracle_lib
+    return "port", (lambda c: oracle_lib.PortExtractor(c["nfeatures"], c["scaleFactor"], c["nlevels"], c["iniThFAST"],
+                                                       c["minThFAST"], fast=True)), oracle_lib
+
+
+def cpu_extract_fps(frames, cfg, threads, budget_s=20.0):
+    """Frames/s of the CPU path on `threads` host threads (one extractor object per thread, the
+    way Frame.cc:78-81 uses two).  ctypes releases the GIL during each call."""
+    kind, mk, _ = _cpu_libs()
+    exts = [mk(cfg) for _ in range(threads)]
+    exts[0].extract(frames[0])  # warm
+    done = [0] * threads
+    t_end = time.time() + budget_s
+    n = len(frames)
+
+    def work(t):
+        i = t
+        while i < n and time.time() < t_end:
+            exts[t].extract(frames[i])
+            done[t] += 1
+            i += threads
+
+    t0 = time.time()
+    th = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    [x.start() for x in th]
+    [x.join() for x in th]
+    dt = time.time() - t0
+    return sum(done) / dt, sum(done), kind
+
+
+def cpu_match_rate(db, q, threads):
+    """Gmatch/s of the reference's SWAR DescriptorDistance + top-2 rule on host threads."""
+    _, _, ol = _cpu_libs()
+    L = ol.oracle(fast=True)
+    d1 = np.zeros(len(q), np.int32); i1 = np.zeros(len(q), np.int64); d2 = np.zeros(len(q), np.int32)
+    t0 = time.time()
+    L.orc_top2_mt(q, len(q), db, len(db), d1, i1, d2, threads)
+    dt = time.time() - t0
+    return len(q) * len(db) / dt / 1e9, (d1, d2, i1)
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's CPU extractor on all host cores, same metric/config."""
+    from orb_slam2_e_b200 import synth
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    per_step = max(threads, min(64, 2 * threads))
+    frames = synth.frame_batch("textured", per_step, H, W, SEED, distinct=min(per_step, 16))
+    kind, mk, _ = _cpu_libs()
+    for _ in range(args.warmup):
+        cpu_extract_fps(frames[:threads], TUM, threads, budget_s=60)
+    t0 = time.time()
+    total = 0
+    for _ in range(args.steps):
+        _, n, kind = cpu_extract_fps(frames, TUM, threads, budget_s=600)
+        total += n
+    dt = time.time() - t0
+    fps = total / dt
+    line = {
+        "impl": "reference", "metric": "frames/s ORB extract (640x480, 1k feats)", "value": fps, "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "ORBextractor 640x480 textured frames, nFeatures=1000, 8 levels, scale 1.2, FAST 20/7 (TUM)",
+                   "frames_per_step": per_step},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
+                         "sample": "%d frames per step, one extractor object per host thread" % per_step},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ GPU arm ----------------
+def run_gpu_arm(args):
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    B = sys.modules[__name__]
+    from orb_slam2_e_b200 import bench_gpu, bench_match
+    rank, world, local, dist = bench_gpu._dist_setup()
+    ex = bench_gpu.bench_extract(args, B, rank, world, local, dist)
+    cpu = None
+    if rank == 0 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        sample = ex["host"][: max(threads, min(2 * threads, 64))]
+        fps, n_done, kind = cpu_extract_fps(sample, TUM, threads, budget_s=args.cpu_seconds)
+        cpu = {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
+               "sample": "%d of the step's frames, one extractor object per host thread (%s ORBextractor over the OpenCV-exact shim)"
+                         % (n_done, "reference's own" if kind == "reference" else "restated")}
+    ex.pop("host")
+    ext = ex.pop("ext")
+    ext.close()
+    torch.cuda.empty_cache()
+    match = None
+    if not args.no_match:
+        match = bench_match.bench_match(args, B, rank, world, local, dist, with_cpu=not args.no_cpu)
+    if dist is not None:
+        dist.barrier()
+    if rank == 0:
+        line = {
+            "metric": "frames/s ORB extract (640x480, 1k feats)", "value": ex["fps"], "unit": "frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ex["ms"] / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "ORBextractor 640x480 textured frames, nFeatures=1000, 8 levels, scale 1.2, FAST 20/7 (TUM), "
+                                   "%d frames per GPU per step" % args.frames,
+                       "frames_per_gpu": args.frames, "sharding": "frames block-partitioned over ranks, no collective",
+                       "l2": "inputs larger than L2 (%d MB of frames per step per GPU), no flush" % (args.frames * W * H >> 20),
+                       "keypoints_per_frame": ex["n_kp"], "fast_candidates_per_frame": ex["n_cand"]},
+            "e2e": {"value": ex["e2e"], "unit": "frames/s", "h2d_bytes_per_step": ex["h2d"], "d2h_bytes_per_step": ex["d2h"]},
+            "gpu_launches": ex["launches"] + (match["gpu_launches"] if match else 0),
+            "clocks": ex["clocks"], "roofline": ex["roofline"], "roofline_pipeline": ex["roofline_pipeline"],
+            "cpu_baseline": cpu, "matching": match,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=1024, help="frames per GPU per step")
+    ap.add_argument("--distinct", type=int, default=32, help="distinct synthetic frames generated (tiled to --frames)")
+    ap.add_argument("--db-rows", type=int, default=10_000_000)
+    ap.add_argument("--queries", type=int, default=1000)
+    ap.add_argument("--cpu-db-rows", type=int, default=200_000)
+    ap.add_argument("--cpu-seconds", type=float, default=20.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-match", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        if args.warmup < 3:
+            args.warmup = 3  # timing rule: at least 3 warm-up steps
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,148 @@
+"""GPU arm of bench.py (kept in the package so bench.py stays a thin contract wrapper).
+
+Timing rules followed: W >= 3 warm-up steps; inputs (n x 307 KB frames, 315 MB at n = 1024) are
+larger than the 126 MB L2, so no explicit flush is needed between steps; device time is taken
+with CUDA events recorded on the extractor's own stream (torch ExternalStream), max over ranks;
+SM clocks / throttle reasons are sampled with nvidia-smi during the timed region.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import numpy as np
+
+
+def _dist_setup():
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local, dist
+
+
+def _max_over_ranks(x, dist, local):
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _barrier(dist):
+    import torch
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def stage_algorithmic_bytes(B, cfg, w, h, n_cand, n_kp):
+    """Algorithmic bytes per frame of each stage (what an ideal kernel of that stage must move)."""
+    px = [a * b for a, b in B.level_sizes(w, h, cfg["scaleFactor"], cfg["nlevels"])]
+    return {
+        "pyramid": sum(px[:-1]) + sum(px[1:]),          # read every source level, write every derived level
+        "fast": sum(px) + 8 * n_cand,                   # read every level once, append candidates
+        "quadtree": 8 * n_cand + 4 * n_kp,              # read candidates, write the selection
+        "blur": 2 * sum(px),                            # read + write every level
+        "describe": n_kp * (709 + 512 + 60),            # orientation disc + 512 samples + keypoint/descriptor out
+    }
+
+
+def bench_extract(args, B, rank, world, local, dist):
+    import torch
+    from orb_slam2_e_b200 import synth, _lib
+    from orb_slam2_e_b200.extractor import ORBextractor
+    L = _lib.load()
+    cfg, w, h, n = B.TUM, B.W, B.H, args.frames
+    host = synth.frame_batch("textured", n, h, w, B.SEED + 7 * rank, distinct=min(n, args.distinct))
+    dev = torch.from_numpy(host).cuda(local)
+    ext = ORBextractor(cfg["nfeatures"], cfg["scaleFactor"], cfg["nlevels"], cfg["iniThFAST"], cfg["minThFAST"],
+                       device=local, max_width=w, max_height=h, max_batch=n)
+    stream = torch.cuda.ExternalStream(ext.cuda_stream(), device=local)
+
+    def step_device():
+        ext.extract_batch_device(dev.data_ptr(), n, h, w, w, w * h)
+
+    for _ in range(max(args.warmup, 1)):
+        step_device()
+    ext.sync()
+    counts = ext.counts()
+    n_kp = float(counts.mean())
+    n_cand = float(sum(len(ext.candidates(l, 0)) for l in range(cfg["nlevels"])))
+
+    # ---- device-resident timing (`value`)
+    ext.set_stage_timing(True)
+    sampler = B.ClockSampler(local)
+    time.sleep(0.3)
+    _barrier(dist)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = L.orb_launch_count()
+    t0 = sampler.mark()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    e1.synchronize()
+    _barrier(dist)
+    t1 = sampler.mark()
+    launches = int(L.orb_launch_count() - l0)
+    ms = _max_over_ranks(e0.elapsed_time(e1), dist, local)
+    stages = ext.last_stage_ms()
+    ext.set_stage_timing(False)
+    clocks = sampler.summary(t0, t1)
+    fps = world * n * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the public batch API with pinned HOST buffers (`e2e`)
+    pin_in = torch.from_numpy(host).pin_memory()
+    cap = ext.out_cap
+    pin_kp = torch.empty(n * cap * 28, dtype=torch.uint8).pin_memory()
+    pin_desc = torch.empty(n * cap * 32, dtype=torch.uint8).pin_memory()
+    cnt = np.zeros(n, np.int32)
+
+    def step_e2e():
+        ext.extract_batch_host_ptr(pin_in.data_ptr(), n, h, w, w, w * h)
+        ext.read_batch_into(pin_kp.data_ptr(), pin_desc.data_ptr(), cap, cnt)
+
+    step_e2e()
+    _barrier(dist)
+    tt = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    dt = _max_over_ranks(time.perf_counter() - tt, dist, local)
+    _barrier(dist)
+    e2e_fps = world * n * args.steps / dt
+    assert int(cnt.sum()) == int(counts.sum()), "e2e path returned a different keypoint count"
+    sampler.stop()
+
+    # ---- roofline of the dominant kernel + of the whole pipeline
+    peak, peak_src = B.measured_peaks()
+    alg = stage_algorithmic_bytes(B, cfg, w, h, n_cand, n_kp)
+    dom = max(stages, key=stages.get)
+    n_launch = {"pyramid": cfg["nlevels"] - 1}.get(dom, 1)
+    achieved = alg[dom] * n / (stages[dom] * 1e-3) / 1e9
+    b_alg, _ = B.algorithmic_bytes_per_frame(w, h, cfg, n_kp)
+    traffic = None
+    tpath = os.path.join(B.ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(dom)
+        except Exception:
+            traffic = None
+    roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom] * n / n_launch,
+            "launches_per_step": n_launch, "kernel_ms_per_step": stages[dom], "stage_ms": stages,
+            "stage_algorithmic_bytes_per_frame": alg}
+    pipe = b_alg * world * n * args.steps / (ms * 1e-3) / 1e9 / world
+    roof_pipe = {"bound": "hbm", "achieved": pipe, "peak": peak, "unit": "GB/s", "frac": pipe / peak,
+                 "algorithmic_bytes_per_frame": b_alg, "note": "SURVEY 8d B_alg x frames/s per GPU"}
+    return dict(fps=fps, ms=ms, e2e=e2e_fps, h2d=int(host.nbytes), d2h=int(n * cap * 60 + 4 * n), launches=launches,
+                clocks=clocks, roofline=roof, roofline_pipeline=roof_pipe, n_kp=n_kp, n_cand=n_cand, host=host, ext=ext)
