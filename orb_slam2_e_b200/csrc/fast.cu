@@ -5,36 +5,38 @@
 // (pinned against cv2 4.13 in tests/test_oracle_prims.py):
 //   * corner strength S = max over the 16 nine-long arcs of min(v-ring) and of min(ring-v), minus 1;
 //     a pixel is a corner at threshold T iff S >= T; response = S (threshold independent);
-//   * 3x3 strict non-max suppression inside the cell's valid region only (the cell ROI's outer
-//     3-px ring has no score, so NMS never acts across cell seams);
-//   * a cell with no keypoint at iniThFAST is redone at minThFAST.
-// One warp per cell: stage the cell (+3 px halo) in shared memory, cheap opposite-pair test on
-// every pixel, ballot-compacted survivors get the exact strength through a packed u16x2
-// VIMNMX3 network (dark arcs in the low half, bright arcs in the high half), then NMS and an
-// order-free append to the (frame, level) candidate list together with the quadtree path code.
+//   * 3x3 strict non-max suppression among the corners of the cell's valid region only (the
+//     cell ROI's outer 3-px ring has no score, so NMS never acts across cell seams);
+//   * a cell with no keypoint at iniThFAST is redone at minThFAST (ORBextractor.cc:820-824).
+// One warp per cell, and -- like the reference -- one detection pass at iniThFAST followed by a
+// second at minThFAST only for empty cells.  A pass:
+//   1. packed prefilter, 4 pixels per lane: VABSDIFF4 of the centre word against the eight ring
+//      positions of four opposite pairs; a nine-long arc holds one pixel of every opposite pair,
+//      so a corner needs |centre - ring| > T on at least one side of each pair (conservative:
+//      signs and the bitwise-OR "max" only let extra pixels through);
+//   2. survivors are compacted into a ring queue and get the exact strength, one pixel per lane,
+//      through a packed u16x2 VIMNMX3 network (dark arcs low half, bright arcs high half);
+//   3. NMS on a zero-framed score tile, survivors appended (any order) to the (frame, level)
+//      candidate list together with their quadtree path code.
+#include <algorithm>
+
 #include "extract.cuh"
 
 namespace orbfront {
 
 constexpr int kFastWarps = 4;
 constexpr int kCellMax = 60;                 // wCell,hCell <= 59 (ceil(width/floor(width/30)))
-constexpr int kTilePitch = 68;               // (59+6) rounded up to a multiple of 4
-constexpr int kTileRows = kCellMax + 6;
-constexpr int kScorePitch = 64;
+constexpr int kQueue = 256;                  // ring queue entries (py << 6 | px)
+// Per-warp shared memory: tile[(maxH+6) x PITCH] | score[(maxH+2) x PITCH] | queue[kQueue] u16.
+// PITCH (bytes, multiple of 4, >= widest cell + 8) is a template parameter so the 16 ring offsets
+// stay immediates; tile/score column = px + 4 (word aligned groups of 4 pixels).
 
-struct FastSmem {
-  uint8_t tile[kTileRows * kTilePitch];
-  uint8_t score[kCellMax * kScorePitch];
-  uint32_t flag_ini[(kCellMax * kCellMax + 31) / 32];
-  uint32_t flag_min[(kCellMax * kCellMax + 31) / 32];
-  uint16_t queue[64];
-};
-
-// exact strength of the pixel at tile position p (pointer to the centre byte)
+// exact strength of the pixel whose centre byte is at p (tile pitch kTilePitch)
+template <int kTilePitch>
 __device__ __forceinline__ int fast_strength(const uint8_t* p) {
   // packed lanes: low half = 256 + (v - ring)  (dark arc),  high half = 256 + (ring - v) (bright arc)
   const int v = p[0];
-  const uint32_t base = 0x01000100u + (uint32_t)v * 0xFFFF0001u;  // (256+v) | (256-v)<<16, no borrow: both halves stay in [1,511]
+  const uint32_t base = 0x01000100u + (uint32_t)v * 0xFFFF0001u;  // (256+v) | (256-v)<<16; halves stay in [1,511]
   uint32_t d[16];
 #define RING(k, dx, dy) d[k] = base + (uint32_t)p[(dy) * kTilePitch + (dx)] * 0x0000FFFFu;
   RING(0, 0, 3) RING(1, 1, 3) RING(2, 2, 2) RING(3, 3, 1) RING(4, 3, 0) RING(5, 3, -1) RING(6, 2, -2) RING(7, 1, -3)
@@ -49,15 +51,22 @@ __device__ __forceinline__ int fast_strength(const uint8_t* p) {
     const uint32_t b = __vimin3_u16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]);
     best = __vimax3_u16x2(best, a, b);
   }
-  const int s = (int)max(best & 0xffffu, best >> 16) - 256 - 1;
-  return s;
+  return (int)max(best & 0xffffu, best >> 16) - 256 - 1;
 }
 
+template <int kTilePitch>
 __global__ void __launch_bounds__(kFastWarps * 32)
-fast_cells_kernel(const __grid_constant__ ExtractParams P) {
+fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_bytes) {
+  constexpr int kTileWords = kTilePitch / 4, kScorePitch = kTilePitch;
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  FastSmem& S = reinterpret_cast<FastSmem*>(smem_raw)[threadIdx.x >> 5];
+  uint8_t* tile8 = smem_raw + (threadIdx.x >> 5) * warp_bytes;
+  uint8_t* score8 = tile8 + (max_h + 6) * kTilePitch;
+  struct { uint32_t* tile; uint32_t* score; uint16_t* queue; } S;
+  S.tile = reinterpret_cast<uint32_t*>(tile8);
+  S.score = reinterpret_cast<uint32_t*>(score8);
+  S.queue = reinterpret_cast<uint16_t*>(score8 + (max_h + 2) * kTilePitch);
   const int lane = threadIdx.x & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const int cell = blockIdx.x * kFastWarps + (threadIdx.x >> 5);
   if (cell >= P.total_cells) return;
   const int f = blockIdx.y;
@@ -70,123 +79,144 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P) {
   const int vw = min(G.wCell, G.w - kEdge - vx0), vh = min(G.hCell, G.h - kEdge - vy0);
   if (vw <= 0 || vh <= 0) return;
 
-  // stage (vw+6) x (vh+6) pixels
-  const uint8_t* src = level_ptr(P, l, f) + (size_t)(vy0 - 3) * level_pitch(P, l) + (vx0 - 3);
+  // stage columns [vx0-4, vx0+vw+4) x rows [vy0-3, vy0+vh+3): pixel (px,py) sits at tile (py+3, px+4)
   const int sp = level_pitch(P, l);
-  const int tw = vw + 6, th = vh + 6;
-  for (int r = 0; r < th; ++r) {
-    const uint8_t* s = src + (size_t)r * sp;
-    for (int c = lane; c < tw; c += 32) S.tile[r * kTilePitch + c] = s[c];
+  const uint8_t* src = level_ptr(P, l, f) + (size_t)(vy0 - 3) * sp + (vx0 - 4);
+  const int tw = min(vw + 8, G.w - (vx0 - 4)), th = vh + 6;
+  {
+    const int total = th * tw;
+    const uint32_t mtw = (1u << 20) / (uint32_t)tw + 1u;  // i / tw for i < 4500, tw < 72
+#pragma unroll 8
+    for (int i = lane; i < total; i += 32) {  // independent byte loads: many in flight per lane
+      const int r = (int)(((uint32_t)i * mtw) >> 20), c = i - r * tw;
+      tile8[r * kTilePitch + c] = __ldg(src + (size_t)r * sp + c);
+    }
   }
   __syncwarp();
 
-  // pass 1: opposite-pair rejection on all pixels, exact strength on the survivors
-  const int th_min = P.min_th, th_ini = P.ini_th;
-  const int npix = vw * vh;
-  int qn = 0;  // queue fill (uniform across the warp)
-  auto drain = [&](int count) {
-    if (lane < count) {
-      const int id = S.queue[lane];
-      const int py = id / vw, px = id - py * vw;
-      const int s = fast_strength(&S.tile[(py + 3) * kTilePitch + px + 3]);
-      S.score[py * kScorePitch + px] = (uint8_t)(s >= th_min ? s : 0);
-    }
-  };
-  for (int base = 0; base < npix; base += 32) {
-    const int id = base + lane;
-    bool pass = false;
-    if (id < npix) {
-      const int py = id / vw, px = id - py * vw;
-      const uint8_t* p = &S.tile[(py + 3) * kTilePitch + px + 3];
-      const int v = p[0];
-      // every nine-long arc holds one pixel of each opposite pair
-      bool dark = true, bright = true;
-#define PAIR(dx, dy)                                                         \
-  {                                                                          \
-    const int a = v - (int)p[(dy) * kTilePitch + (dx)];                      \
-    const int b = v - (int)p[-(dy) * kTilePitch - (dx)];                     \
-    dark = dark && (a > th_min || b > th_min);                               \
-    bright = bright && (a < -th_min || b < -th_min);                         \
-  }
-      PAIR(0, 3) PAIR(3, 0) PAIR(2, 2) PAIR(2, -2)
-#undef PAIR
-      pass = dark || bright;
-      if (!pass) S.score[py * kScorePitch + px] = 0;
-    }
-    const uint32_t m = __ballot_sync(0xffffffffu, pass);
-    if (pass) S.queue[qn + __popc(m & ((1u << lane) - 1))] = (uint16_t)id;
-    qn += __popc(m);
+  const int ng = (vw + 3) >> 2, ngroups = ng * vh;
+  const uint32_t magic = (1u << 20) / (uint32_t)ng + 1u;  // gid / ng == (gid * magic) >> 20 (gid < 1024, ng < 16)
+  int* const count = &P.cand_count[f * P.nlevels + l];
+  unsigned long long* const out = P.cand + (size_t)f * P.cand_frame + G.cand_off;
+
+  // One detection pass at threshold T; returns the number of keypoints it appended.
+  auto detect = [&](const int T) -> int {
+    const int score_words = (vh + 2) * (kScorePitch / 4);
+    for (int i = lane; i < score_words; i += 32) S.score[i] = 0;
+    const uint32_t K = 0x01010101u * (uint32_t)(127 - min(T, 126));
+    auto gt = [&](uint32_t x) { return (((x & 0x7f7f7f7fu) + K) | x) & 0x80808080u; };  // per byte: x > T
+    int head = 0, tail = 0;  // ring queue (uniform across the warp)
+    auto drain = [&](int count_) {
+      if (lane < count_) {
+        const int e = S.queue[(head + lane) & (kQueue - 1)];
+        const int py = e >> 6, px = e & 63;
+        const int s = fast_strength<kTilePitch>(&tile8[(py + 3) * kTilePitch + px + 4]);
+        if (s >= T) score8[(py + 1) * kScorePitch + px + 4] = (uint8_t)s;
+      }
+      head += count_;
+    };
     __syncwarp();
-    if (qn >= 32) {
-      drain(32);
+    for (int base = 0; base < ngroups; base += 32) {
+      const int gid = base + lane;
+      uint32_t flags = 0;
+      int py = 0, g = 0;
+      if (gid < ngroups) {
+        py = (int)(((uint32_t)gid * magic) >> 20);
+        g = gid - py * ng;
+        const uint32_t* r0 = &S.tile[(py + 3) * kTileWords + g + 1];  // word holding the 4 centres
+        const uint32_t c = r0[0], lw = r0[-1], rw = r0[1];
+        const uint32_t* um = r0 - 2 * kTileWords;
+        const uint32_t* dm = r0 + 2 * kTileWords;
+        uint32_t fl = gt(__vabsdiffu4(c, r0[-3 * kTileWords]) | __vabsdiffu4(c, r0[3 * kTileWords]));
+        fl &= gt(__vabsdiffu4(c, __funnelshift_r(c, rw, 24)) | __vabsdiffu4(c, __funnelshift_r(lw, c, 8)));
+        fl &= gt(__vabsdiffu4(c, __funnelshift_r(dm[0], dm[1], 16)) | __vabsdiffu4(c, __funnelshift_r(um[-1], um[0], 16)));
+        fl &= gt(__vabsdiffu4(c, __funnelshift_r(um[0], um[1], 16)) | __vabsdiffu4(c, __funnelshift_r(dm[-1], dm[0], 16)));
+        const int nvalid = min(4, vw - 4 * g);  // pixels of this group inside the cell
+        flags = fl & (0xffffffffu >> (32 - 8 * nvalid));
+      }
+      const int n = __popc(flags);
+      int incl = n;
+#pragma unroll
+      for (int s = 1; s < 32; s <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, s);
+        if (lane >= s) incl += o;
+      }
+      int pos = tail + incl - n;
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+        if (flags >> (8 * b + 7) & 1u) S.queue[(pos++) & (kQueue - 1)] = (uint16_t)(py << 6 | (4 * g + b));
+      tail += __shfl_sync(0xffffffffu, incl, 31);
       __syncwarp();
-      if (lane < qn - 32) S.queue[lane] = S.queue[32 + lane];
-      qn -= 32;
-      __syncwarp();
+      while (tail - head >= 32) drain(32);
     }
-  }
-  drain(qn);
-  __syncwarp();
+    drain(tail - head);
+    __syncwarp();
 
-  // pass 2: strict 3x3 non-max suppression inside the valid region; count both thresholds
-  int n_ini = 0, n_min = 0;
-  const int nchunks = (npix + 31) / 32;
-  for (int c = 0; c < nchunks; ++c) {
-    const int id = c * 32 + lane;
-    bool is_max = false;
-    int s = 0;
-    if (id < npix) {
-      const int py = id / vw, px = id - py * vw;
-      s = S.score[py * kScorePitch + px];
-      if (s) {
-        is_max = true;
+    // strict 3x3 non-max suppression (frame and sub-threshold pixels score 0) + append
+    int appended = 0;
+    for (int base = 0; base < ngroups; base += 32) {
+      const int gid = base + lane;
+      uint32_t w = 0;
+      int py = 0, g = 0;
+      if (gid < ngroups) {
+        py = (int)(((uint32_t)gid * magic) >> 20);
+        g = gid - py * ng;
+        w = S.score[(py + 1) * (kScorePitch / 4) + g + 1];
+      }
+      if (!__any_sync(0xffffffffu, w != 0)) continue;
 #pragma unroll
-        for (int dy = -1; dy <= 1; ++dy)
-#pragma unroll
-          for (int dx = -1; dx <= 1; ++dx) {
-            if (dx == 0 && dy == 0) continue;
-            const int qx = px + dx, qy = py + dy;
-            const int o = (qx >= 0 && qx < vw && qy >= 0 && qy < vh) ? S.score[qy * kScorePitch + qx] : 0;
-            is_max = is_max && s > o;
-          }
+      for (int b = 0; b < 4; ++b) {
+        const int s = (w >> (8 * b)) & 0xff;
+        bool is_max = false;
+        const int px = 4 * g + b;
+        if (s) {
+          const uint8_t* q = &score8[(py + 1) * kScorePitch + px + 4];
+          const int n0 = max(max((int)q[-kScorePitch - 1], (int)q[-kScorePitch]), max((int)q[-kScorePitch + 1], (int)q[-1]));
+          const int n1 = max(max((int)q[1], (int)q[kScorePitch - 1]), max((int)q[kScorePitch], (int)q[kScorePitch + 1]));
+          is_max = s > max(n0, n1);
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, is_max);
+        if (m == 0) continue;
+        int slot = 0;
+        if (lane == 0) slot = atomicAdd(count, __popc(m));
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (is_max) {
+          const int x = vx0 + px - (kEdge - 3), y = vy0 + py - (kEdge - 3);  // border-relative (minBorder = 16)
+          const uint32_t pay = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+          const int at = slot + __popc(m & lt_mask);
+          if (at < G.cand_cap) out[at] = ((unsigned long long)quadtree_path_code(x, y, G) << 32) | pay;
+        }
+        appended += __popc(m);
       }
     }
-    const uint32_t mm = __ballot_sync(0xffffffffu, is_max);
-    const uint32_t mi = __ballot_sync(0xffffffffu, is_max && s >= th_ini);
-    if (lane == 0) { S.flag_min[c] = mm; S.flag_ini[c] = mi; }
-    n_min += __popc(mm);
-    n_ini += __popc(mi);
-  }
-  __syncwarp();
-  const bool use_ini = n_ini > 0;  // ORBextractor.cc:820: fall back only when the cell is empty
-  const int total = use_ini ? n_ini : n_min;
-  if (total == 0) return;
-  int slot = 0;
-  if (lane == 0) slot = atomicAdd(&P.cand_count[f * P.nlevels + l], total);
-  slot = __shfl_sync(0xffffffffu, slot, 0);
-  unsigned long long* out = P.cand + (size_t)f * P.cand_frame + G.cand_off;
-  for (int c = 0; c < nchunks; ++c) {
-    const uint32_t m = use_ini ? S.flag_ini[c] : S.flag_min[c];
-    if (m >> lane & 1u) {
-      const int id = c * 32 + lane;
-      const int py = id / vw, px = id - py * vw;
-      const int x = vx0 + px - (kEdge - 3), y = vy0 + py - (kEdge - 3);  // border-relative (minBorder = 16)
-      const uint32_t s = S.score[py * kScorePitch + px];
-      const uint32_t pay = (s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-      const int at = slot + __popc(m & ((1u << lane) - 1));
-      if (at < G.cand_cap) out[at] = ((unsigned long long)quadtree_path_code(x, y, G) << 32) | pay;
-    }
-    slot += __popc(m);
-  }
+    return appended;
+  };
+
+  if (detect(P.ini_th) == 0 && P.min_th < P.ini_th) detect(P.min_th);  // ORBextractor.cc:820: only for empty cells
+}
+
+template <int PITCH>
+static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) {
+  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + kQueue * 2;
+  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * (66+62)*68 + 2 KB < 48 KB
+  dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
+  fast_cells_kernel<PITCH><<<grid, kFastWarps * 32, smem, s>>>(P, max_h, warp_bytes);
+  ORB_LAUNCH_CHECK();
+  return ORB_OK;
 }
 
 int launch_fast(const ExtractParams& P, cudaStream_t s, int* launches) {
-  const size_t smem = sizeof(FastSmem) * kFastWarps;  // < 48 KB: no opt-in attribute needed
-  static_assert(sizeof(FastSmem) * kFastWarps <= 48 * 1024, "fast_cells_kernel shared memory");
+  int max_w = 1, max_h = 1;
+  for (int l = 0; l < P.nlevels; ++l) { max_w = std::max(max_w, P.lv[l].wCell); max_h = std::max(max_h, P.lv[l].hCell); }
+  if (max_w >= kCellMax || max_h >= kCellMax) return set_error(ORB_E_INVALID, "FAST cell %dx%d exceeds %d", max_w, max_h, kCellMax - 1);
   ORB_CUDA_TRY(cudaMemsetAsync(P.cand_count, 0, sizeof(int) * (size_t)P.n_frames * P.nlevels, s));
-  dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
-  fast_cells_kernel<<<grid, kFastWarps * 32, smem, s>>>(P);
-  ORB_LAUNCH_CHECK();
+  const int need = max_w + 8;
+  int rc;
+  if (need <= 40) rc = launch_fast_pitch<40>(P, s, max_h);
+  else if (need <= 48) rc = launch_fast_pitch<48>(P, s, max_h);
+  else if (need <= 56) rc = launch_fast_pitch<56>(P, s, max_h);
+  else rc = launch_fast_pitch<68>(P, s, max_h);
+  if (rc) return rc;
   ++*launches;
   return ORB_OK;
 }
