@@ -65,6 +65,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   S.tile = reinterpret_cast<uint32_t*>(tile8);
   S.score = reinterpret_cast<uint32_t*>(score8);
   S.queue = reinterpret_cast<uint16_t*>(score8 + (max_h + 2) * kTilePitch);
+  uint32_t* kplist = reinterpret_cast<uint32_t*>(S.queue + kQueue);  // NMS survivors of the cell (<= one per 2x2 block)
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const int cell = blockIdx.x * kFastWarps + (threadIdx.x >> 5);
@@ -84,12 +85,18 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   const uint8_t* src = level_ptr(P, l, f) + (size_t)(vy0 - 3) * sp + (vx0 - 4);
   const int tw = min(vw + 8, G.w - (vx0 - 4)), th = vh + 6;
   {
-    const int total = th * tw;
-    const uint32_t mtw = (1u << 20) / (uint32_t)tw + 1u;  // i / tw for i < 4500, tw < 72
-#pragma unroll 8
-    for (int i = lane; i < total; i += 32) {  // independent byte loads: many in flight per lane
-      const int r = (int)(((uint32_t)i * mtw) >> 20), c = i - r * tw;
-      tile8[r * kTilePitch + c] = __ldg(src + (size_t)r * sp + c);
+    // word-wise: every pitch is a multiple of 4, so all rows share the byte misalignment `sh`;
+    // a tile word is the funnel shift of two aligned global words (independent loads, unrolled)
+    const int sh = (int)(reinterpret_cast<uintptr_t>(src) & 3);
+    const uint32_t* asrc = reinterpret_cast<const uint32_t*>(src - sh);
+    const int spw = sp >> 2, nwt = (tw + 3) >> 2, total = th * nwt;
+    const uint32_t mtw = (1u << 20) / (uint32_t)nwt + 1u;  // i / nwt for i < 1200, nwt < 18
+#pragma unroll 4
+    for (int i = lane; i < total; i += 32) {
+      const int r = (int)(((uint32_t)i * mtw) >> 20), j = i - r * nwt;
+      const uint32_t* a = asrc + (size_t)r * spw + j;
+      const uint32_t lo = __ldg(a), hi = sh ? __ldg(a + 1) : 0u;
+      S.tile[r * kTileWords + j] = __funnelshift_r(lo, hi, 8 * sh);
     }
   }
   __syncwarp();
@@ -176,18 +183,22 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
           is_max = s > max(n0, n1);
         }
         const uint32_t m = __ballot_sync(0xffffffffu, is_max);
-        if (m == 0) continue;
-        int slot = 0;
-        if (lane == 0) slot = atomicAdd(count, __popc(m));
-        slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (is_max) {
-          const int x = vx0 + px - (kEdge - 3), y = vy0 + py - (kEdge - 3);  // border-relative (minBorder = 16)
-          const uint32_t pay = ((uint32_t)s << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-          const int at = slot + __popc(m & lt_mask);
-          if (at < G.cand_cap) out[at] = ((unsigned long long)quadtree_path_code(x, y, G) << 32) | pay;
-        }
+        if (is_max) kplist[appended + __popc(m & lt_mask)] = ((uint32_t)s << 16) | (uint32_t)(py << 6 | px);
         appended += __popc(m);
       }
+    }
+    if (appended == 0) return 0;
+    __syncwarp();
+    // dense tail: one keypoint per lane gets its quadtree path code; one atomic per cell
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(count, appended);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    for (int i = lane; i < appended; i += 32) {
+      const uint32_t e = kplist[i];
+      const int px = e & 63, py = (e >> 6) & 63;
+      const int x = vx0 + px - (kEdge - 3), y = vy0 + py - (kEdge - 3);  // border-relative (minBorder = 16)
+      const uint32_t pay = ((e >> 16) << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+      if (slot + i < G.cand_cap) out[slot + i] = ((unsigned long long)quadtree_path_code(x, y, G) << 32) | pay;
     }
     return appended;
   };
@@ -197,8 +208,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
 
 template <int PITCH>
 static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) {
-  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + kQueue * 2;
-  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * (66+62)*68 + 2 KB < 48 KB
+  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + kQueue * 2 + 4 * ((PITCH - 8) / 2 + 1) * (max_h / 2 + 1);
+  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((66+62)*68 + 512 + 3720) < 48 KB
   dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
   fast_cells_kernel<PITCH><<<grid, kFastWarps * 32, smem, s>>>(P, max_h, warp_bytes);
   ORB_LAUNCH_CHECK();
