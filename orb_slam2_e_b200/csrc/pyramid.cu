@@ -89,54 +89,110 @@ __device__ __forceinline__ int reflect101(int p, int n) {
   return p;  // valid for |overshoot| < n, which holds for 3-px taps on levels >= 7 px
 }
 
-constexpr int kBlurTW = 64, kBlurTH = 32;
+// Blur: one warp per 128-column x 32-row tile, each lane owns 4 adjacent columns (one 32-bit
+// word) and marches down the rows.  Horizontal 7 taps = two DP4A per output on byte windows
+// funnel-shifted out of three aligned words; the last 7 horizontal rows live in registers
+// (fully unrolled ring), vertical 7 taps use the kernel's symmetry.  No shared memory.
+constexpr int kBlurTW = 128, kBlurTH = 32, kBlurWarps = 4;
 
-// grid: (tiles of all levels, 1, frames).  Tiles are numbered level by level.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kBlurWarps * 32, 8)
 blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */) {
-  __shared__ uint8_t raw[kBlurTH + 6][kBlurTW + 8];
-  __shared__ uint16_t hor[kBlurTH + 6][kBlurTW];
+  const int lane = threadIdx.x & 31;
+  const int tile = blockIdx.x * kBlurWarps + (threadIdx.x >> 5);
+  if (tile >= tile_base[P.nlevels]) return;
   int l = 0;
-  while (l + 1 < P.nlevels && (int)blockIdx.x >= tile_base[l + 1]) ++l;
+  while (l + 1 < P.nlevels && tile >= tile_base[l + 1]) ++l;
   const LevelGeom& G = P.lv[l];
   const int f = blockIdx.z;
   if (P.kept_count[f * P.nlevels + l] == 0) return;  // reference skips levels without keypoints (:1089)
-  const int t = blockIdx.x - tile_base[l];
+  const int t = tile - tile_base[l];
   const int tiles_x = div_up(G.w, kBlurTW);
-  const int tx = (t % tiles_x) * kBlurTW, ty = (t / tiles_x) * kBlurTH;
+  const int tx0 = (t % tiles_x) * kBlurTW;
+  const int x0 = tx0 + 4 * lane, y0 = (t / tiles_x) * kBlurTH;
   const uint8_t* src = level_ptr(P, l, f);
   const int sp = level_pitch(P, l);
-  for (int i = threadIdx.x; i < (kBlurTH + 6) * (kBlurTW + 6); i += 256) {
-    const int r = i / (kBlurTW + 6), c = i % (kBlurTW + 6);
-    const int sy = reflect101(ty + r - 3, G.h), sx = reflect101(tx + c - 3, G.w);
-    raw[r][c] = src[(size_t)sy * sp + sx];
-  }
-  __syncthreads();
-  for (int i = threadIdx.x; i < (kBlurTH + 6) * kBlurTW; i += 256) {
-    const int r = i / kBlurTW, c = i % kBlurTW;
-    const uint8_t* p = &raw[r][c];
-    hor[r][c] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
-  }
-  __syncthreads();
   uint8_t* dst = P.blur + (size_t)f * P.blur_frame + G.off;
-  for (int i = threadIdx.x; i < kBlurTH * kBlurTW / 4; i += 256) {
-    const int r = i / (kBlurTW / 4), c = (i % (kBlurTW / 4)) * 4;
-    if (ty + r >= G.h || tx + c >= G.w) continue;
+  // lanes whose 12-byte window [x0-4, x0+8) stays inside the row run the word-wise main loop;
+  // the (at most three per row) groups touching the left/right edge are done afterwards, one
+  // ROW per lane, so the main loop has no divergent reflect path
+  const bool interior = x0 >= 4 && x0 + 8 <= G.w;
+  constexpr uint32_t K1 = 18u | 34u << 8 | 48u << 16 | 56u << 24, K2 = 48u | 34u << 8 | 18u << 16;
+
+  uint32_t ring[7][4];
+  // software pipeline: the three words of row yy+kAhead are requested while row yy is filtered
+  constexpr int kAhead = 3;
+  uint32_t pa[kAhead], pb[kAhead], pc[kAhead];
+  auto fetch = [&](int yy, uint32_t& a, uint32_t& b, uint32_t& c) {
+    a = b = c = 0;
+    const int y = y0 + yy - 3;
+    if (interior && y - 3 < G.h) {  // rows past the bottom are never needed
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(src + (size_t)reflect101(y, G.h) * sp + x0);
+      a = __ldg(w - 1); b = __ldg(w); c = __ldg(w + 1);
+    }
+  };
+#pragma unroll
+  for (int k = 0; k < kAhead; ++k) fetch(k, pa[k], pb[k], pc[k]);
+#pragma unroll
+  for (int yy = 0; yy < kBlurTH + 6; ++yy) {
+    const int y = y0 + yy - 3;
+    {
+      const uint32_t a = pa[yy % kAhead], b = pb[yy % kAhead], c = pc[yy % kAhead];
+      if (yy + kAhead < kBlurTH + 6) fetch(yy + kAhead, pa[yy % kAhead], pb[yy % kAhead], pc[yy % kAhead]);
+      uint32_t* h = ring[yy % 7];
+      h[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
+      h[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
+      h[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
+      h[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
+    }
+    if (yy >= 6) {
+      const int oy = y - 3;  // output row whose 7 horizontal rows are now in the ring
+      if (oy < G.h && interior) {
+        uint32_t out = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t acc = 18u * (ring[(yy - 6) % 7][k] + ring[yy % 7][k]) + 34u * (ring[(yy - 5) % 7][k] + ring[(yy - 1) % 7][k]) +
+                               48u * (ring[(yy - 4) % 7][k] + ring[(yy - 2) % 7][k]) + 56u * ring[(yy - 3) % 7][k];
+          out |= ((acc + 32768u) >> 16) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(dst + (size_t)oy * G.pitch + x0) = out;
+      }
+    }
+  }
+
+  // edge groups of this tile: xg = 0 and the multiples of 4 in (w-8, w)
+  const int oy = y0 + lane;
+  for (int xg = tx0; xg < min(tx0 + kBlurTW, G.w); xg += 4) {
+    if (xg >= 4 && xg + 8 <= G.w) {  // interior: jump to the right edge
+      xg = max(xg, ((G.w - 8) & ~3)) ;
+      if (xg >= 4 && xg + 8 <= G.w) continue;
+    }
+    if (oy >= G.h) continue;
+    int xs[10];
+#pragma unroll
+    for (int j = 0; j < 10; ++j) xs[j] = reflect101(xg - 3 + j, G.w);
+    uint32_t acc[4] = {0, 0, 0, 0};
+#pragma unroll 1
+    for (int dy = 0; dy < 7; ++dy) {
+      const uint8_t* row = src + (size_t)reflect101(oy + dy - 3, G.h) * sp;
+      uint32_t v[10];
+#pragma unroll
+      for (int j = 0; j < 10; ++j) v[j] = row[xs[j]];
+      const uint32_t q = dy == 0 || dy == 6 ? 18u : dy == 1 || dy == 5 ? 34u : dy == 2 || dy == 4 ? 48u : 56u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        acc[k] += q * (18u * (v[k] + v[k + 6]) + 34u * (v[k + 1] + v[k + 5]) + 48u * (v[k + 2] + v[k + 4]) + 56u * v[k + 3]);
+    }
     uint32_t out = 0;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const unsigned acc = 18u * (hor[r][c + k] + hor[r + 6][c + k]) + 34u * (hor[r + 1][c + k] + hor[r + 5][c + k]) +
-                           48u * (hor[r + 2][c + k] + hor[r + 4][c + k]) + 56u * hor[r + 3][c + k];
-      out |= ((acc + 32768u) >> 16) << (8 * k);
-    }
-    *reinterpret_cast<uint32_t*>(dst + (size_t)(ty + r) * G.pitch + tx + c) = out;
+    for (int k = 0; k < 4; ++k) out |= ((acc[k] + 32768u) >> 16) << (8 * k);
+    *reinterpret_cast<uint32_t*>(dst + (size_t)oy * G.pitch + xg) = out;  // pitch padding absorbs the tail
   }
 }
 
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches) {
   int total = 0;
   for (int l = 0; l < P.nlevels; ++l) total += div_up(P.lv[l].w, kBlurTW) * div_up(P.lv[l].h, kBlurTH);
-  blur_kernel<<<dim3(total, 1, P.n_frames), 256, 0, s>>>(P, P.blur_tiles);
+  blur_kernel<<<dim3(div_up(total, kBlurWarps), 1, P.n_frames), kBlurWarps * 32, 0, s>>>(P, P.blur_tiles);
   ORB_LAUNCH_CHECK();
   ++*launches;
   return ORB_OK;
