@@ -11,11 +11,11 @@ import numpy as np
 
 def bench_match(args, B, rank, world, local, dist, with_cpu):
     import torch
-    from orb_slam2_e_b200 import matcher, synth, _lib
+    from orb_slam2_e_b200 import matcher, reloc, synth, _lib
     from orb_slam2_e_b200.bench_gpu import _barrier, _max_over_ranks
     L = _lib.load()
     D, Q = args.db_rows, args.queries
-    lo, hi = D * rank // world, D * (rank + 1) // world
+    lo, hi = reloc.shard_range(D, rank, world)
     rows = hi - lo
     g = torch.Generator(device=f"cuda:{local}")
     g.manual_seed(4000 + rank)
@@ -41,7 +41,7 @@ def bench_match(args, B, rank, world, local, dist, with_cpu):
         else:
             res = out_dev.unsqueeze(0)
         shards = res.cpu().numpy().view(_lib.TOP2_DTYPE).reshape(world, Q)
-        return matcher.merge_top2(list(shards), 0.75, 45)
+        return reloc.merge_shards(shards, 0.75, 45)
 
     for _ in range(max(args.warmup, 1)):
         merged, acc = step()

@@ -1,0 +1,155 @@
+// tests/cpp/dropin_harness.cc -- exercises the PRODUCT's C++ host classes (include/ORBextractor.h,
+// include/ORBmatcher.h) exactly the way the reference's callers use them (Frame.cc:265-267,
+// Tracking.cc:1750-1790, LoopClosing.cc:239), behind a small C interface so pytest can compare the
+// results with the oracle.  cv:: types come from oracle/cvshim (headers only -- no oracle code is
+// executed by these entry points), Frame/KeyFrame/MapPoint from tests/cpp/mock.
+#include <cstdint>
+#include <cstring>
+#include <memory>
+
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+
+using namespace ORB_SLAM2;
+
+struct DropKp { float x, y, size, angle, response; int octave, class_id; };
+
+static thread_local std::string g_err;
+
+extern "C" {
+
+const char* dropin_error() { return g_err.c_str(); }
+
+void* dropin_create(int nf, float sf, int nl, int ini, int mn) {
+  try { return new ORBextractor(nf, sf, nl, ini, mn); }
+  catch (const std::exception& e) { g_err = e.what(); return nullptr; }
+}
+void dropin_destroy(void* h) { delete (ORBextractor*)h; }
+
+int dropin_extract(void* h, const uint8_t* img, int w, int h_, size_t stride, DropKp* kps, uint8_t* desc, int cap) {
+  ORBextractor* e = (ORBextractor*)h;
+  try {
+    cv::Mat im(h_, w, CV_8U, (void*)img, stride);
+    std::vector<cv::KeyPoint> k(3);  // stale content must be replaced
+    cv::Mat d;
+    (*e)(im, cv::Mat(), k, d);
+    const int n = (int)k.size();
+    if (n > cap) return -n;
+    if (n == 0 && !d.empty()) { g_err = "descriptors not released for zero keypoints"; return -1000000; }
+    for (int i = 0; i < n; ++i) {
+      kps[i] = DropKp{k[i].pt.x, k[i].pt.y, k[i].size, k[i].angle, k[i].response, k[i].octave, k[i].class_id};
+      memcpy(desc + 32 * (size_t)i, d.ptr(i), 32);
+    }
+    return n;
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
+int dropin_level_size(void* h, int l, int* w, int* h_) {
+  ORBextractor* e = (ORBextractor*)h;
+  if (l < 0 || l >= e->GetLevels() || e->mvImagePyramid[l].empty()) return -1;
+  *w = e->mvImagePyramid[l].cols;
+  *h_ = e->mvImagePyramid[l].rows;
+  return 0;
+}
+
+// reads mvImagePyramid the way Frame::ComputeStereoMatches does: ROI pointer arithmetic incl. the border
+int dropin_get_level(void* h, int l, uint8_t* dst, size_t dstep, int with_border) {
+  ORBextractor* e = (ORBextractor*)h;
+  if (l < 0 || l >= e->GetLevels() || e->mvImagePyramid[l].empty()) return -1;
+  const cv::Mat& m = e->mvImagePyramid[l];
+  const int b = with_border ? 19 : 0;
+  for (int y = -b; y < m.rows + b; ++y)
+    memcpy(dst + (size_t)(y + b) * dstep, m.data + (ptrdiff_t)y * (ptrdiff_t)m.step - b, (size_t)(m.cols + 2 * b));
+  return 0;
+}
+
+float dropin_scale(void* h, int l) { return ((ORBextractor*)h)->GetScaleFactors()[l]; }
+float dropin_table(void* h, int which, int l) {
+  ORBextractor* e = (ORBextractor*)h;
+  return which == 0 ? e->GetScaleFactors()[l] : which == 1 ? e->GetInverseScaleFactors()[l]
+       : which == 2 ? e->GetScaleSigmaSquares()[l] : e->GetInverseScaleSigmaSquares()[l];
+}
+int dropin_levels(void* h) { return ((ORBextractor*)h)->GetLevels(); }
+float dropin_scale_factor(void* h) { return ((ORBextractor*)h)->GetScaleFactor(); }
+
+int dropin_distance(const uint8_t* a, const uint8_t* b) {
+  cv::Mat ma(1, 32, CV_8U, (void*)a, 32), mb(1, 32, CV_8U, (void*)b, 32);
+  return ORBmatcher::DescriptorDistance(ma, mb);
+}
+
+static void fill_fv(DBoW2::FeatureVector& fv, const uint32_t* node, const int32_t* off, const uint32_t* idx, int n_nodes) {
+  for (int i = 0; i < n_nodes; ++i) fv[node[i]] = std::vector<unsigned int>(idx + off[i], idx + off[i + 1]);
+}
+
+// state: 0 = no MapPoint (NULL), 1 = good MapPoint, 2 = bad MapPoint.  out as in orbm_search_bow.
+int dropin_search_bow(const uint8_t* d1, int n1, const uint8_t* d2, int n2, const uint32_t* node1, const int32_t* off1,
+                      const uint32_t* idx1, int nn1, const uint32_t* node2, const int32_t* off2, const uint32_t* idx2, int nn2,
+                      const uint8_t* state1, const uint8_t* state2, const float* a1, const float* a2, float ratio, int check_ori,
+                      int kf_kf, int32_t* out) {
+  try {
+    std::vector<std::unique_ptr<MapPoint> > pool;
+    auto points = [&](const uint8_t* st, int n) {
+      std::vector<MapPoint*> v((size_t)n, nullptr);
+      for (int i = 0; i < n; ++i)
+        if (st[i]) { pool.emplace_back(new MapPoint(st[i] == 2)); v[i] = pool.back().get(); }
+      return v;
+    };
+    auto keys = [&](const float* a, int n) {
+      std::vector<cv::KeyPoint> k((size_t)n);
+      for (int i = 0; i < n; ++i) k[i].angle = a ? a[i] : 0.f;
+      return k;
+    };
+    KeyFrame kf1;
+    kf1.mDescriptors = cv::Mat(n1, 32, CV_8U, (void*)d1, 32);
+    kf1.mvKeysUn = keys(a1, n1);
+    kf1.mvpMapPoints = points(state1, n1);
+    fill_fv(kf1.mFeatVec, node1, off1, idx1, nn1);
+    ORBmatcher matcher(ratio, check_ori != 0);
+    std::vector<MapPoint*> res;
+    int nm;
+    if (!kf_kf) {
+      Frame F;
+      F.N = n2;
+      F.mDescriptors = cv::Mat(n2, 32, CV_8U, (void*)d2, 32);
+      F.mvKeys = keys(a2, n2);
+      fill_fv(F.mFeatVec, node2, off2, idx2, nn2);
+      nm = matcher.SearchByBoW(&kf1, F, res);
+      for (int f = 0; f < n2; ++f) {
+        out[f] = -1;
+        if (res[f])
+          for (int i = 0; i < n1; ++i)
+            if (kf1.mvpMapPoints[i] == res[f]) out[f] = i;
+      }
+    } else {
+      KeyFrame kf2;
+      kf2.mDescriptors = cv::Mat(n2, 32, CV_8U, (void*)d2, 32);
+      kf2.mvKeysUn = keys(a2, n2);
+      kf2.mvpMapPoints = points(state2, n2);
+      fill_fv(kf2.mFeatVec, node2, off2, idx2, nn2);
+      nm = matcher.SearchByBoW(&kf1, &kf2, res);
+      for (int i = 0; i < n1; ++i) {
+        out[i] = -1;
+        if (res[i])
+          for (int j = 0; j < n2; ++j)
+            if (kf2.mvpMapPoints[j] == res[i]) out[i] = j;
+      }
+    }
+    return nm;
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
+int dropin_stereo(const DropKp* kl, const uint8_t* dl, int nl, const DropKp* kr, const uint8_t* dr, int nr, const float* scale,
+                  int n_levels, int n_rows, float min_d, float max_d, int32_t* best_idx, int32_t* best_dist) {
+  try {
+    std::vector<cv::KeyPoint> L((size_t)nl), R((size_t)nr);
+    memcpy((void*)L.data(), kl, sizeof(DropKp) * (size_t)nl);
+    memcpy((void*)R.data(), kr, sizeof(DropKp) * (size_t)nr);
+    std::vector<int> bi, bd;
+    ORBmatcher::StereoSearch(L, cv::Mat(nl, 32, CV_8U, (void*)dl, 32), R, cv::Mat(nr, 32, CV_8U, (void*)dr, 32),
+                             std::vector<float>(scale, scale + n_levels), n_rows, min_d, max_d, bi, bd);
+    for (int i = 0; i < nl; ++i) { best_idx[i] = bi[i]; best_dist[i] = bd[i]; }
+    return 0;
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
+}  // extern "C"
