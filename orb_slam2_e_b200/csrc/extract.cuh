@@ -6,8 +6,9 @@
 //   pyr     [frame][level >= 1][h_l][pitch_l]  u8   resized levels (level 0 aliases the input
 //                                                    or a pitch-aligned upload buffer)
 //   blur    [frame][level][h_l][pitch_l]        u8   7x7 sigma-2 fixed-point Gaussian of each level
-//   cand    [frame][level][cand_cap_l]          u64  FAST candidates: (quadtree path code << 32) |
-//                                                    (score << 24 | y << 12 | x), any order
+//   cand    [frame][level][cand_cap_l]          u64  FAST candidates: score << 24 | y << 12 | x in the low
+//                                                    half, any order; the quadtree kernel puts the path
+//                                                    code in the high half
 //   kept    [frame][level][kept_cap_l]          u32  selected keypoints in the reference's list order
 //   out_kp  [frame][out_cap] orbx_keypoint, out_desc [frame][out_cap][32] u8, counts
 // No 19-px border is materialised on the hot path: FAST, the orientation disc and the rBRIEF

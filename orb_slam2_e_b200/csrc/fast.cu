@@ -57,6 +57,7 @@ __device__ __forceinline__ int fast_strength(const uint8_t* p) {
 template <int kTilePitch>
 __global__ void __launch_bounds__(kFastWarps * 32)
 fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_bytes) {
+  const int wlist_entries = (max_h * ((kTilePitch - 8) / 4) + 1) & ~1;
   constexpr int kTileWords = kTilePitch / 4, kScorePitch = kTilePitch;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   uint8_t* tile8 = smem_raw + (threadIdx.x >> 5) * warp_bytes;
@@ -65,7 +66,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   S.tile = reinterpret_cast<uint32_t*>(tile8);
   S.score = reinterpret_cast<uint32_t*>(score8);
   S.queue = reinterpret_cast<uint16_t*>(score8 + (max_h + 2) * kTilePitch);
-  uint32_t* kplist = reinterpret_cast<uint32_t*>(S.queue + kQueue);  // NMS survivors of the cell (<= one per 2x2 block)
+  uint16_t* wlist = S.queue + kQueue;  // score words holding a corner: (max_h) x (PITCH-8)/4 entries
+  uint32_t* kplist = reinterpret_cast<uint32_t*>(wlist + wlist_entries);  // NMS survivors of the cell (<= one per 2x2 block)
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const int cell = blockIdx.x * kFastWarps + (threadIdx.x >> 5);
@@ -159,8 +161,10 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
     drain(tail - head);
     __syncwarp();
 
-    // strict 3x3 non-max suppression (frame and sub-threshold pixels score 0) + append
-    int appended = 0;
+    // strict 3x3 non-max suppression (frame and sub-threshold pixels score 0).  First list the
+    // score words that hold a corner (the queue is idle now and is reused for the list: at most
+    // one entry per 4-pixel group), then one listed word per lane.
+    int nw = 0;
     for (int base = 0; base < ngroups; base += 32) {
       const int gid = base + lane;
       uint32_t w = 0;
@@ -170,7 +174,20 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
         g = gid - py * ng;
         w = S.score[(py + 1) * (kScorePitch / 4) + g + 1];
       }
-      if (!__any_sync(0xffffffffu, w != 0)) continue;
+      const uint32_t m = __ballot_sync(0xffffffffu, w != 0);
+      if (w != 0) wlist[nw + __popc(m & lt_mask)] = (uint16_t)(py << 4 | g);
+      nw += __popc(m);
+    }
+    __syncwarp();
+    int appended = 0;
+    for (int base = 0; base < nw; base += 32) {
+      uint32_t w = 0;
+      int py = 0, g = 0;
+      if (base + lane < nw) {
+        const int e = wlist[base + lane];
+        py = e >> 4; g = e & 15;
+        w = S.score[(py + 1) * (kScorePitch / 4) + g + 1];
+      }
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
         const int s = (w >> (8 * b)) & 0xff;
@@ -189,7 +206,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
     }
     if (appended == 0) return 0;
     __syncwarp();
-    // dense tail: one keypoint per lane gets its quadtree path code; one atomic per cell
+    // dense tail: one atomic per cell
     int slot = 0;
     if (lane == 0) slot = atomicAdd(count, appended);
     slot = __shfl_sync(0xffffffffu, slot, 0);
@@ -198,7 +215,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
       const int px = e & 63, py = (e >> 6) & 63;
       const int x = vx0 + px - (kEdge - 3), y = vy0 + py - (kEdge - 3);  // border-relative (minBorder = 16)
       const uint32_t pay = ((e >> 16) << 24) | ((uint32_t)y << 12) | (uint32_t)x;
-      if (slot + i < G.cand_cap) out[slot + i] = ((unsigned long long)quadtree_path_code(x, y, G) << 32) | pay;
+      if (slot + i < G.cand_cap) out[slot + i] = pay;  // the quadtree kernel prepends the path code
     }
     return appended;
   };
@@ -208,7 +225,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
 
 template <int PITCH>
 static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) {
-  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + kQueue * 2 + 4 * ((PITCH - 8) / 2 + 1) * (max_h / 2 + 1);
+  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + kQueue * 2 + 2 * ((max_h * ((PITCH - 8) / 4) + 1) & ~1) +
+                         4 * ((PITCH - 8) / 2 + 1) * (max_h / 2 + 1);
   const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((66+62)*68 + 512 + 3720) < 48 KB
   dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
   fast_cells_kernel<PITCH><<<grid, kFastWarps * 32, smem, s>>>(P, max_h, warp_bytes);

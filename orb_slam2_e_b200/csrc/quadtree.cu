@@ -111,7 +111,11 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   uint16_t* seq = in_smem ? s_seq : reinterpret_cast<uint16_t*>(P.qt_seq + (size_t)f * P.cand_frame + G.cand_off);
 
   for (int i = tid; i < np; i += kQtThreads) {
-    const unsigned long long k = i < n ? gkeys[i] : ~0ull;
+    unsigned long long k = ~0ull;
+    if (i < n) {  // FAST stores the payload only; the path code is attached here, all lanes busy
+      const uint32_t pay = (uint32_t)gkeys[i];
+      k = ((unsigned long long)quadtree_path_code((int)(pay & 0xfff), (int)((pay >> 12) & 0xfff), G) << 32) | pay;
+    }
     keys[i] = k;  // (pads the global buffer in place when not in shared memory)
   }
   __syncthreads();
