@@ -41,16 +41,30 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int kDescWarps = 8;
+constexpr int kPatchR = 18;                 // rotated pattern coordinates stay within +-18 (|p| <= 18.38, cvRound)
+constexpr int kPatchRows = 2 * kPatchR + 1; // 37
+constexpr int kPatchWords = 10;             // 37 bytes at any 4-byte misalignment fit 10 aligned words
+constexpr int kPatchPitch = 4 * kPatchWords;
+
+// cvRound for |v| < 2^22 without the XU pipe: adding 1.5 * 2^23 leaves round-half-even(v) in the mantissa
+__device__ __forceinline__ int round_rn_small(float v) {
+  return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
+}
 
 // grid: (ceil(kept slots per frame / 8), frames)
 __global__ void __launch_bounds__(kDescWarps * 32)
 orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_frame) {
-  __shared__ int8_t pat[1024];
-  for (int i = threadIdx.x; i < 256; i += kDescWarps * 32)
-    reinterpret_cast<uint32_t*>(pat)[i] = reinterpret_cast<const uint32_t*>(g_pattern)[i];
+  // pattern as floats, transposed so that lane (= descriptor byte) is the fastest index:
+  // patf[(t * 2 + e) * 32 + lane] = point e of test t of byte `lane`
+  __shared__ float2 patf[16 * 32];
+  __shared__ __align__(16) uint32_t patch_s[kDescWarps][kPatchRows * kPatchWords];
+  for (int i = threadIdx.x; i < 512; i += kDescWarps * 32) {
+    const int ln = i & 31, te = i >> 5;
+    patf[i] = make_float2((float)g_pattern[32 * ln + 2 * te], (float)g_pattern[32 * ln + 2 * te + 1]);
+  }
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int g = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = blockIdx.x * kDescWarps + warp;
   const int f = blockIdx.y;
   if (g >= slots_per_frame) return;
   int l = 0;
@@ -72,6 +86,26 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
   const uint32_t pay = P.kept[(size_t)f * P.kept_frame + G.kept_off + k];
   const int x = (int)(pay & 0xfff) + (kEdge - 3), y = (int)((pay >> 12) & 0xfff) + (kEdge - 3);  // level coords
   const int score = (int)(pay >> 24);
+
+  // --- stage the 37x37 blurred patch around the keypoint as aligned words (coalesced, ~3 rows per
+  // warp load) -- the 512 pattern samples then come from shared memory instead of 16 scattered
+  // 32-sector global gathers.  Keypoints lie in [19, w-19) x [19, h-19), so the patch is inside the
+  // image; the last word may reach into the row padding (pitch >= w + 4), never past it.
+  const int px0 = x - kPatchR, shift = px0 & 3;
+  {
+    const uint32_t* bsrc = reinterpret_cast<const uint32_t*>(P.blur + (size_t)f * P.blur_frame + G.off +
+                                                             (size_t)(y - kPatchR) * G.pitch + (px0 - shift));
+    const int pw = G.pitch >> 2;
+    uint32_t* dstp = patch_s[warp];
+#pragma unroll
+    for (int it = 0; it < (kPatchRows * kPatchWords + 31) / 32; ++it) {
+      const int i = it * 32 + lane;
+      if (i < kPatchRows * kPatchWords) {
+        const int r = (i * 205) >> 11;  // i / 10 for i < 1024
+        dstp[i] = __ldg(bsrc + r * pw + (i - r * kPatchWords));
+      }
+    }
+  }
 
   // --- orientation: lane <-> column u = lane-15
   const int sp = level_pitch(P, l);
@@ -96,7 +130,7 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
   }
   const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-  // --- steered rBRIEF on the blurred level: lane <-> descriptor byte
+  // --- steered rBRIEF on the blurred patch: lane <-> descriptor byte
   float ca = 0.f, sa = 0.f;
   if (lane == 0) {
     constexpr float factorPI = (float)(3.14159265358979323846 / 180.0);
@@ -108,18 +142,18 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
   }
   ca = __shfl_sync(0xffffffffu, ca, 0);
   sa = __shfl_sync(0xffffffffu, sa, 0);
-  const uint8_t* bc = P.blur + (size_t)f * P.blur_frame + G.off + (size_t)y * G.pitch + x;
-  const int8_t* pp = pat + 32 * lane;  // 8 tests x 2 points x (x,y)
+  __syncwarp();  // patch visible to every lane
+  const uint8_t* pc = reinterpret_cast<const uint8_t*>(patch_s[warp]) + kPatchR * kPatchPitch + kPatchR + shift;
   uint32_t byte = 0;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     int val[2];
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
-      const float px = (float)pp[4 * t + 2 * e], py = (float)pp[4 * t + 2 * e + 1];
-      const int yy = __float2int_rn(__fadd_rn(__fmul_rn(px, sa), __fmul_rn(py, ca)));
-      const int xx = __float2int_rn(__fsub_rn(__fmul_rn(px, ca), __fmul_rn(py, sa)));
-      val[e] = bc[yy * G.pitch + xx];
+      const float2 p = patf[(t * 2 + e) * 32 + lane];
+      const int yy = round_rn_small(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)));
+      const int xx = round_rn_small(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)));
+      val[e] = pc[yy * kPatchPitch + xx];
     }
     byte |= (uint32_t)(val[0] < val[1]) << t;
   }

@@ -56,6 +56,7 @@ struct ExtractParams {
   int* kept_count;                     // [frame][level]
   uint8_t* qt_b;                       // global scratch for oversized (frame,level): boundary depths
   uint32_t* qt_seq;                    //   and creation sequence numbers, cand layout
+  unsigned long long* qt_tmp;          //   and the radix sort's second key buffer, cand layout
   const int4* rtab;                    // resize taps: (src index, c0, c1, clamped src index + 1)
   const int* blur_tiles;               // [nlevels+1] first blur tile of each level
   orbx_keypoint* out_kp;  uint8_t* out_desc;  int out_cap;

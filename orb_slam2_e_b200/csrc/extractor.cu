@@ -49,7 +49,7 @@ struct orbx_handle {
   cudaEvent_t stage_ev[ORBX_N_STAGES + 1] = {};
   bool stage_timing = false, stage_valid = false;
   Dev<uint8_t> l0, pyr, blur, qt_b, out_desc;
-  Dev<unsigned long long> cand;
+  Dev<unsigned long long> cand, qt_tmp;
   Dev<uint32_t> kept, qt_seq;
   Dev<int> cand_count, kept_count, out_count;
   Dev<int4> rtab;
@@ -149,7 +149,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       while ((1 << lg) < span) ++lg;
       G.dmax = std::min(lg + 2, kMaxDepth);
       const int vw = G.w - 2 * kEdge, vh = G.h - 2 * kEdge;
-      G.cand_cap = next_pow2(((vw + 1) / 2 + G.nCols) * ((vh + 1) / 2 + G.nRows));
+      G.cand_cap = (int)align_up<size_t>((size_t)((vw + 1) / 2 + G.nCols) * ((vh + 1) / 2 + G.nRows), 4);  // NMS survivors: <= one per 2x2 block of a cell
       G.cand_off = cand_off;
       cand_off += G.cand_cap;
       G.kept_cap = std::max(G.quota, 0) + 4 * G.nIni + 3;
@@ -189,14 +189,14 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
   const size_t nf = (size_t)n_frames;
   if ((own_l0 && (rc = H->l0.reserve(nf * H->l0_frame + 256))) || (rc = H->pyr.reserve(nf * P.pyr_frame + 256)) ||
       (rc = H->blur.reserve(nf * P.blur_frame + 256)) || (rc = H->cand.reserve(nf * P.cand_frame)) ||
-      (rc = H->qt_b.reserve(nf * (P.cand_frame + kMaxLevels) + 16)) || (rc = H->qt_seq.reserve(nf * P.cand_frame)) ||
+      (rc = H->qt_b.reserve(nf * (P.cand_frame + kMaxLevels) + 16)) || (rc = H->qt_seq.reserve(nf * P.cand_frame)) || (rc = H->qt_tmp.reserve(nf * P.cand_frame)) ||
       (rc = H->kept.reserve(nf * P.kept_frame)) || (rc = H->cand_count.reserve(nf * nl)) ||
       (rc = H->kept_count.reserve(nf * nl)) || (rc = H->out_count.reserve(nf)) ||
       (rc = H->out_kp.reserve(nf * P.out_cap)) || (rc = H->out_desc.reserve(nf * P.out_cap * 32)))
     return rc;
   P.n_frames = n_frames;
   P.pyr = H->pyr.p; P.blur = H->blur.p; P.cand = H->cand.p; P.cand_count = H->cand_count.p;
-  P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p;
+  P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p; P.qt_tmp = H->qt_tmp.p;
   P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p;
   P.out_kp = H->out_kp.p; P.out_desc = H->out_desc.p; P.out_count = H->out_count.p;
   return ORB_OK;

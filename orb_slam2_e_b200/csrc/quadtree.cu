@@ -30,18 +30,17 @@ struct QtCtl {  // control block in shared memory
 };
 enum { kModeFull = 0, kModeOrdered = 1 };
 
-// In-place ascending bitonic sort of np (power of two) 64-bit keys with optional 32-bit values.
+// In-place ascending bitonic sort of np (power of two) 64-bit keys with optional 32-bit values
+// (node tables: at most a few hundred entries).  One compare-exchange per thread and step.
 __device__ void bitonic_sort(unsigned long long* a, uint32_t* v, int np) {
   for (int k = 2; k <= np; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < np; i += kQtThreads) {
-        const int x = i ^ j;
-        if (x > i) {
-          const unsigned long long ai = a[i], ax = a[x];
-          if ((ai > ax) == ((i & k) == 0)) {
-            a[i] = ax; a[x] = ai;
-            if (v) { const uint32_t t = v[i]; v[i] = v[x]; v[x] = t; }
-          }
+      for (int t = threadIdx.x; t < (np >> 1); t += kQtThreads) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), x = i | j;
+        const unsigned long long ai = a[i], ax = a[x];
+        if ((ai > ax) == ((i & k) == 0)) {
+          a[i] = ax; a[x] = ai;
+          if (v) { const uint32_t tv = v[i]; v[i] = v[x]; v[x] = tv; }
         }
       }
       __syncthreads();
@@ -64,6 +63,54 @@ __device__ int block_inclusive_scan(int v, QtCtl& C) {
   if (threadIdx.x == kQtThreads - 1) C.scan_total = base + v;
   __syncthreads();
   return base + v;
+}
+
+// Stable LSD radix sort (8-bit digits) of n 64-bit keys on bits [32, 32 + nbits) -- the quadtree
+// path code -- ping-ponging between buffers a and b (shared or global memory).  Each warp owns a
+// contiguous chunk; per-(warp, digit) counters scanned in (digit, warp) order give every key its
+// stable destination: base + rank among the warp's equal digits (__match_any_sync).  O(n) per pass
+// instead of the O(n log^2 n) compare-exchanges of a sorting network.  Returns the sorted buffer.
+__device__ unsigned long long* radix_sort_codes(unsigned long long* a, unsigned long long* b, int n, int nbits,
+                                                uint32_t* whist /* [8][256] */, QtCtl& C) {
+  constexpr int kWarps = kQtThreads / 32;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int per_warp = ((n + kQtThreads - 1) / kQtThreads) * 32;
+  const int lo = min(n, warp * per_warp), hi = min(n, lo + per_warp);
+  for (int shift = 32; shift < 32 + nbits; shift += 8) {
+    for (int i = tid; i < kWarps * 256; i += kQtThreads) whist[i] = 0;
+    __syncthreads();
+    for (int i = lo + lane; i < hi; i += 32) atomicAdd(&whist[warp * 256 + (int)((a[i] >> shift) & 255u)], 1u);
+    __syncthreads();
+    {
+      uint32_t c[kWarps], tot = 0;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) { c[w] = whist[w * 256 + tid]; tot += c[w]; }
+      uint32_t base = (uint32_t)block_inclusive_scan((int)tot, C) - tot;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) { whist[w * 256 + tid] = base; base += c[w]; }
+    }
+    __syncthreads();
+    for (int i0 = lo; i0 < hi; i0 += 32) {
+      const int i = i0 + lane;
+      const bool act = i < hi;
+      const unsigned long long key = act ? a[i] : 0ull;
+      const int d = act ? (int)((key >> shift) & 255u) : 256 + lane;  // idle lanes match nobody
+      const uint32_t peers = __match_any_sync(0xffffffffu, d);
+      const int r = __popc(peers & lt_mask);
+      uint32_t base = 0;
+      if (act) {
+        base = whist[warp * 256 + d];
+        b[base + r] = key;
+      }
+      __syncwarp();
+      if (act && r == 0) whist[warp * 256 + d] = base + __popc(peers);
+      __syncwarp();
+    }
+    __syncthreads();
+    unsigned long long* t = a; a = b; b = t;
+  }
+  return a;
 }
 
 // Creation-order key of a depth-k node made by breadth-first passes only: the path prefix with
@@ -92,7 +139,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   uint16_t* s_seq = reinterpret_cast<uint16_t*>(nhead + NP);
   uint8_t* ngain = reinterpret_cast<uint8_t*>(s_seq + S);
   uint8_t* s_b = ngain + NP;
-  QtCtl& C = *reinterpret_cast<QtCtl*>(smem + align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16));
+  QtCtl& C = *reinterpret_cast<QtCtl*>(smem + align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16));  // NP >= 512: radix counters alias the node tables
 
   int n = P.cand_count[f * P.nlevels + l];
   n = min(n, G.cand_cap);
@@ -102,24 +149,28 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     return;
   }
   unsigned long long* gkeys = P.cand + (size_t)f * P.cand_frame + G.cand_off;
-  int np = 1;
-  while (np < n) np <<= 1;
-  const bool in_smem = np <= S;
-  unsigned long long* keys = in_smem ? s_keys : gkeys;
+  const bool in_smem = n <= S;
   uint8_t* b = in_smem ? s_b : P.qt_b + ((size_t)f * (P.cand_frame + kMaxLevels) + G.cand_off + l);
   // sequence numbers: 16-bit in shared memory, or the same width in the global scratch
   uint16_t* seq = in_smem ? s_seq : reinterpret_cast<uint16_t*>(P.qt_seq + (size_t)f * P.cand_frame + G.cand_off);
 
-  for (int i = tid; i < np; i += kQtThreads) {
-    unsigned long long k = ~0ull;
-    if (i < n) {  // FAST stores the payload only; the path code is attached here, all lanes busy
-      const uint32_t pay = (uint32_t)gkeys[i];
-      k = ((unsigned long long)quadtree_path_code((int)(pay & 0xfff), (int)((pay >> 12) & 0xfff), G) << 32) | pay;
-    }
-    keys[i] = k;  // (pads the global buffer in place when not in shared memory)
+  // FAST stores the payload only; attach the path code (all lanes busy), in place
+  for (int i = tid; i < n; i += kQtThreads) {
+    const uint32_t pay = (uint32_t)gkeys[i];
+    gkeys[i] = ((unsigned long long)quadtree_path_code((int)(pay & 0xfff), (int)((pay >> 12) & 0xfff), G) << 32) | pay;
   }
   __syncthreads();
-  bitonic_sort(keys, nullptr, np);
+  // sort by path code: global <-> shared ping-pong when the level fits, global <-> global scratch else
+  int root_bits = 0;
+  while ((1 << root_bits) < G.nIni) ++root_bits;
+  const int nbits = 2 * dmax + root_bits;
+  unsigned long long* other = in_smem ? s_keys : P.qt_tmp + (size_t)f * P.cand_frame + G.cand_off;
+  unsigned long long* keys = radix_sort_codes(gkeys, other, n, nbits, reinterpret_cast<uint32_t*>(nkey), C);
+  if (in_smem && keys != s_keys) {  // even number of passes: bring the result into shared memory
+    for (int i = tid; i < n; i += kQtThreads) s_keys[i] = keys[i];
+    keys = s_keys;
+    __syncthreads();
+  }
 
   // boundary depths b[0..n], tables cnt[] / nexp[]
   for (int i = tid; i < kMaxDepth + 3; i += kQtThreads) { C.hist[i] = 0; C.dlt[i] = 0; }
@@ -273,9 +324,9 @@ int quadtree_smem_bytes(int S, int NP) {
 int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
   int nmax = 1;
   for (int l = 0; l < P.nlevels; ++l) nmax = std::max(nmax, P.lv[l].kept_cap);
-  int NP = 1;
+  int NP = 512;  // >= 8 KB for the radix counters that alias the node tables (8 warps x 256 x 4 B <= NP x 16)
   while (NP < nmax) NP <<= 1;
-  int S = 4096;
+  int S = 2048;  // levels with more candidates sort through global scratch (L2); occupancy beats residency here
   if (const char* e = getenv("ORBX_QT_SMEM_KEYS")) S = std::max(256, atoi(e));
   while (S & (S - 1)) S &= S - 1;  // power of two
   S = std::max(S, NP);             // node arrays alias nothing, but n_nodes <= n keys
