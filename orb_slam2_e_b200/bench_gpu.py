@@ -78,8 +78,18 @@ def bench_extract(args, B, rank, world, local, dist):
     n_kp = float(counts.mean())
     n_cand = float(sum(len(ext.candidates(l, 0)) for l in range(cfg["nlevels"])))
 
-    # ---- device-resident timing (`value`)
+    # ---- per-stage device times (separate pass: stage events stay out of the timed region)
     ext.set_stage_timing(True)
+    stages = None
+    for _ in range(3):
+        step_device()
+        ext.sync()
+        st = ext.last_stage_ms()
+        if stages is None or sum(st.values()) < sum(stages.values()):
+            stages = st
+    ext.set_stage_timing(False)
+
+    # ---- device-resident timing (`value`)
     sampler = B.ClockSampler(local)
     time.sleep(0.3)
     _barrier(dist)
@@ -95,8 +105,6 @@ def bench_extract(args, B, rank, world, local, dist):
     t1 = sampler.mark()
     launches = int(L.orb_launch_count() - l0)
     ms = _max_over_ranks(e0.elapsed_time(e1), dist, local)
-    stages = ext.last_stage_ms()
-    ext.set_stage_timing(False)
     clocks = sampler.summary(t0, t1)
     fps = world * n * args.steps / (ms * 1e-3)
 

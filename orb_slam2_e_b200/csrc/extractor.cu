@@ -160,7 +160,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       G.xtab = tab; tab += G.w;
       G.ytab = tab; tab += G.h;
       blur_tiles[l] = tiles;
-      tiles += div_up(G.w, 128) * div_up(G.h, 32);  // blur_kernel warp tiles (pyramid.cu kBlurTW x kBlurTH)
+      tiles += div_up(G.w, 128) * div_up(G.h, 36);  // blur_kernel warp tiles (pyramid.cu kBlurTW x kBlurTH)
     }
     blur_tiles[nl] = tiles;
     P.total_cells = cell_base;

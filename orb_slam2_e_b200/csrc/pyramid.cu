@@ -89,11 +89,16 @@ __device__ __forceinline__ int reflect101(int p, int n) {
   return p;  // valid for |overshoot| < n, which holds for 3-px taps on levels >= 7 px
 }
 
-// Blur: one warp per 128-column x 32-row tile, each lane owns 4 adjacent columns (one 32-bit
+// Blur: one warp per 128-column x 36-row tile, each lane owns 4 adjacent columns (one 32-bit
 // word) and marches down the rows.  Horizontal 7 taps = two DP4A per output on byte windows
-// funnel-shifted out of three aligned words; the last 7 horizontal rows live in registers
-// (fully unrolled ring), vertical 7 taps use the kernel's symmetry.  No shared memory.
-constexpr int kBlurTW = 128, kBlurTH = 32, kBlurWarps = 4;
+// funnel-shifted out of three aligned words; the last 7 horizontal rows live in registers (ring),
+// vertical 7 taps use the kernel's symmetry and PRMT packs byte 2 of the four sums.  The 42 input
+// rows run as 2 x 21: 21 is the common period of the 7-row ring and the 3-deep load pipeline, so
+// register indices stay static while the loop body (about 20 KB of SASS) stays inside the 32 KB
+// instruction cache -- the fully unrolled form stalled on instruction fetch.  No shared memory.
+constexpr int kBlurTW = 128, kBlurTH = 36, kBlurWarps = 4;
+constexpr int kBlurRows = kBlurTH + 6, kBlurBody = 21;
+static_assert(kBlurRows % kBlurBody == 0, "row loop must be whole bodies");
 
 __global__ void __launch_bounds__(kBlurWarps * 32, 8)
 blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */) {
@@ -116,76 +121,87 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   // the (at most three per row) groups touching the left/right edge are done afterwards, one
   // ROW per lane, so the main loop has no divergent reflect path
   const bool interior = x0 >= 4 && x0 + 8 <= G.w;
+  // tiles away from the top/bottom border walk a running row pointer; the others reflect per row
+  const bool y_inside = y0 >= 3 && y0 + kBlurTH + 3 <= G.h;
   constexpr uint32_t K1 = 18u | 34u << 8 | 48u << 16 | 56u << 24, K2 = 48u | 34u << 8 | 18u << 16;
 
-  uint32_t ring[7][4];
-  // software pipeline: the three words of row yy+kAhead are requested while row yy is filtered
-  constexpr int kAhead = 3;
-  uint32_t pa[kAhead], pb[kAhead], pc[kAhead];
-  auto fetch = [&](int yy, uint32_t& a, uint32_t& b, uint32_t& c) {
-    a = b = c = 0;
-    const int y = y0 + yy - 3;
-    if (interior && y - 3 < G.h) {  // rows past the bottom are never needed
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(src + (size_t)reflect101(y, G.h) * sp + x0);
+  if (interior) {
+    uint32_t ring[7][4];
+    constexpr int kAhead = 3;  // the three words of row yy+3 are requested while row yy is filtered
+    uint32_t pa[kAhead], pb[kAhead], pc[kAhead];
+    const uint8_t* rowp = src + (size_t)(y_inside ? y0 - 3 : 0) * sp + x0;  // next row to fetch (y_inside)
+    auto fetch = [&](int yy, uint32_t& a, uint32_t& b, uint32_t& c) {
+      const uint8_t* p = rowp;
+      if (y_inside) {
+        rowp += sp;
+      } else {
+        const int y = y0 + yy - 3;
+        p = src + (size_t)reflect101(min(y, G.h + 2), G.h) * sp + x0;  // rows past h+2 are never used
+      }
+      const uint32_t* w = reinterpret_cast<const uint32_t*>(p);
       a = __ldg(w - 1); b = __ldg(w); c = __ldg(w + 1);
-    }
-  };
+    };
 #pragma unroll
-  for (int k = 0; k < kAhead; ++k) fetch(k, pa[k], pb[k], pc[k]);
+    for (int k = 0; k < kAhead; ++k) fetch(k, pa[k], pb[k], pc[k]);
+    uint8_t* outp = dst + (size_t)y0 * G.pitch + x0;  // next output row
+    int rows_left = min(kBlurTH, G.h - y0);
+#pragma unroll 1
+    for (int blk = 0; blk < kBlurRows / kBlurBody; ++blk) {
 #pragma unroll
-  for (int yy = 0; yy < kBlurTH + 6; ++yy) {
-    const int y = y0 + yy - 3;
-    {
-      const uint32_t a = pa[yy % kAhead], b = pb[yy % kAhead], c = pc[yy % kAhead];
-      if (yy + kAhead < kBlurTH + 6) fetch(yy + kAhead, pa[yy % kAhead], pb[yy % kAhead], pc[yy % kAhead]);
-      uint32_t* h = ring[yy % 7];
-      h[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
-      h[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
-      h[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
-      h[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
-    }
-    if (yy >= 6) {
-      const int oy = y - 3;  // output row whose 7 horizontal rows are now in the ring
-      if (oy < G.h && interior) {
-        uint32_t out = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t acc = 18u * (ring[(yy - 6) % 7][k] + ring[yy % 7][k]) + 34u * (ring[(yy - 5) % 7][k] + ring[(yy - 1) % 7][k]) +
-                               48u * (ring[(yy - 4) % 7][k] + ring[(yy - 2) % 7][k]) + 56u * ring[(yy - 3) % 7][k];
-          out |= ((acc + 32768u) >> 16) << (8 * k);
+      for (int r = 0; r < kBlurBody; ++r) {
+        const int yy = blk * kBlurBody + r;
+        {
+          const uint32_t a = pa[r % kAhead], b = pb[r % kAhead], c = pc[r % kAhead];
+          if (yy + kAhead < kBlurRows) fetch(yy + kAhead, pa[r % kAhead], pb[r % kAhead], pc[r % kAhead]);
+          uint32_t* h = ring[r % 7];
+          h[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
+          h[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
+          h[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
+          h[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
         }
-        *reinterpret_cast<uint32_t*>(dst + (size_t)oy * G.pitch + x0) = out;
+        if ((r >= 6 || blk > 0) && rows_left > 0) {  // the ring holds the 7 horizontal rows of the next output row
+          uint32_t acc[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            acc[k] = 18u * (ring[(r + 1) % 7][k] + ring[r % 7][k]) + 34u * (ring[(r + 2) % 7][k] + ring[(r + 6) % 7][k]) +
+                     48u * (ring[(r + 3) % 7][k] + ring[(r + 5) % 7][k]) + (56u * ring[(r + 4) % 7][k] + 32768u);
+          // result bytes are bits 16..23 of each sum
+          *reinterpret_cast<uint32_t*>(outp) =
+              __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
+          outp += G.pitch;
+          --rows_left;
+        }
       }
     }
   }
 
   // edge groups of this tile: xg = 0 and the multiples of 4 in (w-8, w)
-  const int oy = y0 + lane;
-  for (int xg = tx0; xg < min(tx0 + kBlurTW, G.w); xg += 4) {
-    if (xg >= 4 && xg + 8 <= G.w) {  // interior: jump to the right edge
-      xg = max(xg, ((G.w - 8) & ~3)) ;
-      if (xg >= 4 && xg + 8 <= G.w) continue;
-    }
-    if (oy >= G.h) continue;
-    int xs[10];
+  for (int oy = y0 + lane; oy < min(y0 + kBlurTH, G.h); oy += 32) {
+    for (int xg = tx0; xg < min(tx0 + kBlurTW, G.w); xg += 4) {
+      if (xg >= 4 && xg + 8 <= G.w) {  // interior: jump to the right edge
+        xg = max(xg, ((G.w - 8) & ~3));
+        if (xg >= 4 && xg + 8 <= G.w) continue;
+      }
+      int xs[10];
 #pragma unroll
-    for (int j = 0; j < 10; ++j) xs[j] = reflect101(xg - 3 + j, G.w);
-    uint32_t acc[4] = {0, 0, 0, 0};
+      for (int j = 0; j < 10; ++j) xs[j] = reflect101(xg - 3 + j, G.w);
+      uint32_t acc[4] = {0, 0, 0, 0};
 #pragma unroll 1
-    for (int dy = 0; dy < 7; ++dy) {
-      const uint8_t* row = src + (size_t)reflect101(oy + dy - 3, G.h) * sp;
-      uint32_t v[10];
+      for (int dy = 0; dy < 7; ++dy) {
+        const uint8_t* row = src + (size_t)reflect101(oy + dy - 3, G.h) * sp;
+        uint32_t v[10];
 #pragma unroll
-      for (int j = 0; j < 10; ++j) v[j] = row[xs[j]];
-      const uint32_t q = dy == 0 || dy == 6 ? 18u : dy == 1 || dy == 5 ? 34u : dy == 2 || dy == 4 ? 48u : 56u;
+        for (int j = 0; j < 10; ++j) v[j] = row[xs[j]];
+        const uint32_t q = dy == 0 || dy == 6 ? 18u : dy == 1 || dy == 5 ? 34u : dy == 2 || dy == 4 ? 48u : 56u;
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        acc[k] += q * (18u * (v[k] + v[k + 6]) + 34u * (v[k + 1] + v[k + 5]) + 48u * (v[k + 2] + v[k + 4]) + 56u * v[k + 3]);
+        for (int k = 0; k < 4; ++k)
+          acc[k] += q * (18u * (v[k] + v[k + 6]) + 34u * (v[k + 1] + v[k + 5]) + 48u * (v[k + 2] + v[k + 4]) + 56u * v[k + 3]);
+      }
+      uint32_t out = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) out |= ((acc[k] + 32768u) >> 16) << (8 * k);
+      *reinterpret_cast<uint32_t*>(dst + (size_t)oy * G.pitch + xg) = out;  // pitch padding absorbs the tail
     }
-    uint32_t out = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) out |= ((acc[k] + 32768u) >> 16) << (8 * k);
-    *reinterpret_cast<uint32_t*>(dst + (size_t)oy * G.pitch + xg) = out;  // pitch padding absorbs the tail
   }
 }
 

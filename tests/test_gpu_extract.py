@@ -119,3 +119,44 @@ def test_large_frame_global_sort_path():
         compare(synth.textured_frame(720, 1280, 31), (3000, 1.2, 8, 20, 7))
     finally:
         del os.environ["ORBX_QT_SMEM_KEYS"]
+
+
+def test_config5_4k_frame():
+    """BASELINE config 5: 3840x2160, nFeatures=8000, 12 levels (large-image stress of pyramid + quadtree)."""
+    cfg = (8000, 1.2, 12, 20, 7)
+    img = synth.textured_frame(2160, 3840, 51)
+    port = PortExtractor(*cfg)
+    port.cap = 9000
+    pk, pd = port.extract(img)
+    g = ORBextractor(*cfg)
+    gk, gd = g(img)
+    assert len(pk) >= 8000
+    compare(img, cfg, frame_result=(gk, gd))
+    for l in (0, 5, 11):
+        assert np.array_equal(g.level(l, 0, False), port.level(l, False)), f"pyramid level {l}"
+        got, want = g.candidates(l), port.stage(0, l)
+        key = lambda a: a[np.lexsort((a[:, 0], a[:, 1]))]
+        assert np.array_equal(key(got), key(want)), f"candidates level {l}"
+
+
+def test_config2_stereo_extract_then_search():
+    """BASELINE config 2: KITTI-shape pair, 2000 features per image, extraction of both images on the
+    GPU followed by the descriptor search of Frame::ComputeStereoMatches on the GPU's own output."""
+    import match_cases as mc
+    from oracle_lib import oracle
+    from orb_slam2_e_b200 import matcher
+    left, right = synth.stereo_pair(376, 1241, 33)
+    gl, gr = ORBextractor(*KITTI), ORBextractor(*KITTI)  # two extractor objects, as Frame.cc:78-81
+    kl, dl = gl(left)
+    kr, dr = gr(right)
+    pl, pr = PortExtractor(*KITTI), PortExtractor(*KITTI)
+    pl.cap = pr.cap = 2200
+    okl, odl = pl.extract(left)
+    okr, odr = pr.extract(right)
+    assert kl.tobytes() == okl.tobytes() and kr.tobytes() == okr.tobytes()
+    assert np.array_equal(dl, odl) and np.array_equal(dr, odr)
+    scale = gl.GetScaleFactors()
+    bi, bd = mc.oracle_stereo(oracle(), okl, odl, okr, odr, scale, 376, 0.0, 80.0)
+    gi, gd = matcher.ORBmatcher().StereoSearch(kl, dl, kr, dr, scale, 376, 0.0, 80.0)
+    assert np.array_equal(gd, bd) and np.array_equal(gi, bi)
+    assert ((bd >= 0) & (bd < 70)).sum() > 200  # plenty of candidates pass to the SAD refinement
