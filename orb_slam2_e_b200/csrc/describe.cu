@@ -51,130 +51,142 @@ __device__ __forceinline__ int round_rn_small(float v) {
   return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
 }
 
-// grid: (ceil(kept slots per frame / 8), frames)
+constexpr int kKpPerWarp = 4;  // keypoint slots per warp: amortises the per-CTA pattern table fill
+
+// grid: (ceil(kept slots per frame / (8 warps x 4)), frames)
 __global__ void __launch_bounds__(kDescWarps * 32)
 orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_frame) {
   // pattern as floats, transposed so that lane (= descriptor byte) is the fastest index:
   // patf[(t * 2 + e) * 32 + lane] = point e of test t of byte `lane`
   __shared__ float2 patf[16 * 32];
-  __shared__ __align__(16) uint32_t patch_s[kDescWarps][kPatchRows * kPatchWords];
+  __shared__ __align__(16) uint32_t patch_s[kDescWarps][(kPatchRows + 2) * kPatchWords];  // 39 rows: 13 x 3
   for (int i = threadIdx.x; i < 512; i += kDescWarps * 32) {
     const int ln = i & 31, te = i >> 5;
     patf[i] = make_float2((float)g_pattern[32 * ln + 2 * te], (float)g_pattern[32 * ln + 2 * te + 1]);
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int g = blockIdx.x * kDescWarps + warp;
   const int f = blockIdx.y;
-  if (g >= slots_per_frame) return;
-  int l = 0;
-  while (l + 1 < P.nlevels && g >= P.lv[l + 1].kept_off) ++l;
-  const LevelGeom& G = P.lv[l];
-  const int k = g - G.kept_off;
-  const int* counts = P.kept_count + f * P.nlevels;
-  int before = 0, total = 0;
-  for (int i = 0; i < P.nlevels; ++i) {
-    const int c = counts[i];
-    if (i < l) before += c;
-    total += c;
-  }
-  if (g == 0 && lane == 0) P.out_count[f] = min(total, P.out_cap);
-  if (k >= counts[l]) return;
-  const int at = before + k;
-  if (at >= P.out_cap) return;
-
-  const uint32_t pay = P.kept[(size_t)f * P.kept_frame + G.kept_off + k];
-  const int x = (int)(pay & 0xfff) + (kEdge - 3), y = (int)((pay >> 12) & 0xfff) + (kEdge - 3);  // level coords
-  const int score = (int)(pay >> 24);
-
-  // --- stage the 37x37 blurred patch around the keypoint as aligned words (coalesced, ~3 rows per
-  // warp load) -- the 512 pattern samples then come from shared memory instead of 16 scattered
-  // 32-sector global gathers.  Keypoints lie in [19, w-19) x [19, h-19), so the patch is inside the
-  // image; the last word may reach into the row padding (pitch >= w + 4), never past it.
-  const int px0 = x - kPatchR, shift = px0 & 3;
-  {
-    const uint32_t* bsrc = reinterpret_cast<const uint32_t*>(P.blur + (size_t)f * P.blur_frame + G.off +
-                                                             (size_t)(y - kPatchR) * G.pitch + (px0 - shift));
-    const int pw = G.pitch >> 2;
-    uint32_t* dstp = patch_s[warp];
+  // per-level keypoint counts of the frame -> exclusive prefix (output row of a level's first keypoint)
+  int cnt = lane < P.nlevels ? P.kept_count[f * P.nlevels + lane] : 0, incl = cnt;
 #pragma unroll
-    for (int it = 0; it < (kPatchRows * kPatchWords + 31) / 32; ++it) {
-      const int i = it * 32 + lane;
-      if (i < kPatchRows * kPatchWords) {
-        const int r = (i * 205) >> 11;  // i / 10 for i < 1024
-        dstp[i] = __ldg(bsrc + r * pw + (i - r * kPatchWords));
-      }
-    }
+  for (int s = 1; s < kMaxLevels; s <<= 1) {
+    const int o = __shfl_up_sync(0xffffffffu, incl, s);
+    if (lane >= s) incl += o;
   }
+  const int total = __shfl_sync(0xffffffffu, incl, kMaxLevels - 1);
+  if (blockIdx.x == 0 && threadIdx.x == 0) P.out_count[f] = min(total, P.out_cap);
 
-  // --- orientation: lane <-> column u = lane-15
-  const int sp = level_pitch(P, l);
-  const uint8_t* c0 = level_ptr(P, l, f) + (size_t)y * sp + x;
+  // lane constants: orientation column u = lane - 15 with its disc half-height; staging slot
+  // (3 patch rows x 10 words per warp load)
   const int u = lane - kHalfPatch;
-  int m10 = 0, m01 = 0;
-  if (lane < 31) {
-    const int au = u < 0 ? -u : u;
+  const int vlim = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;  // the disc is symmetric: |u| <= umax[|v|] <=> |v| <= umax[|u|]
+  const int srow = lane / kPatchWords, scol = lane - srow * kPatchWords;  // lanes 30, 31 idle while staging
+
+  const int g0 = (blockIdx.x * kDescWarps + warp) * kKpPerWarp;
+#pragma unroll 1
+  for (int g = g0; g < min(g0 + kKpPerWarp, slots_per_frame); ++g) {
+    int l = 0;
+    while (l + 1 < P.nlevels && g >= P.lv[l + 1].kept_off) ++l;
+    const LevelGeom& G = P.lv[l];
+    const int k = g - G.kept_off;
+    const int n_l = __shfl_sync(0xffffffffu, cnt, l), before = __shfl_sync(0xffffffffu, incl, l) - n_l;
+    if (k >= n_l) continue;
+    const int at = before + k;
+    if (at >= P.out_cap) continue;
+
+    const uint32_t pay = P.kept[(size_t)f * P.kept_frame + G.kept_off + k];
+    const int x = (int)(pay & 0xfff) + (kEdge - 3), y = (int)((pay >> 12) & 0xfff) + (kEdge - 3);  // level coords
+    const int score = (int)(pay >> 24);
+
+    // --- stage the 37x37 blurred patch around the keypoint as aligned words (coalesced, 3 rows per
+    // warp load) -- the 512 pattern samples then come from shared memory instead of 16 scattered
+    // 32-sector global gathers.  Keypoints lie in [19, w-19) x [19, h-19), so the patch is inside the
+    // image; the last word may reach into the row padding (pitch >= w + 4), never past it.  Rows
+    // 37 and 38 of the last load are never sampled and are clamped to the image.
+    const int px0 = x - kPatchR, shift = px0 & 3;
+    __syncwarp();  // previous keypoint's samples are done
+    if (lane < 3 * kPatchWords) {
+      const uint8_t* blur_l = P.blur + (size_t)f * P.blur_frame + G.off;
+      const uint32_t* bsrc = reinterpret_cast<const uint32_t*>(blur_l + (size_t)(y - kPatchR + srow) * G.pitch + (px0 - shift)) + scol;
+      const int step = 3 * (G.pitch >> 2);
+      uint32_t* dstp = patch_s[warp] + lane;
+      const int last_ok = (G.h - 1 - (y - kPatchR + srow)) / 3;  // iterations whose row is inside the image
 #pragma unroll
-    for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-      if (au <= c_umax[v < 0 ? -v : v]) {
-        const int val = c0[v * sp + u];
-        m10 += u * val;
-        m01 += v * val;
+      for (int it = 0; it < (kPatchRows + 2) / 3; ++it) {
+        dstp[it * 3 * kPatchWords] = __ldg(bsrc + min(it, last_ok) * step);
       }
     }
-  }
-#pragma unroll
-  for (int s = 16; s > 0; s >>= 1) {
-    m10 += __shfl_xor_sync(0xffffffffu, m10, s);
-    m01 += __shfl_xor_sync(0xffffffffu, m01, s);
-  }
-  const float angle = fast_atan2_deg((float)m01, (float)m10);
 
-  // --- steered rBRIEF on the blurred patch: lane <-> descriptor byte
-  float ca = 0.f, sa = 0.f;
-  if (lane == 0) {
-    constexpr float factorPI = (float)(3.14159265358979323846 / 180.0);
-    const float rad = __fmul_rn(angle, factorPI);
-    double ds, dc;
-    sincos((double)rad, &ds, &dc);  // correctly rounded to float in all but vanishingly rare cases
-    ca = (float)dc;
-    sa = (float)ds;
-  }
-  ca = __shfl_sync(0xffffffffu, ca, 0);
-  sa = __shfl_sync(0xffffffffu, sa, 0);
-  __syncwarp();  // patch visible to every lane
-  const uint8_t* pc = reinterpret_cast<const uint8_t*>(patch_s[warp]) + kPatchR * kPatchPitch + kPatchR + shift;
-  uint32_t byte = 0;
+    // --- orientation: lane <-> column u; m10 = u * (column sum), m01 = sum of v * pixel
+    const int sp = level_pitch(P, l);
+    int colsum = 0, m01 = 0;
+    {
+      const uint8_t* cp = level_ptr(P, l, f) + (size_t)(y - kHalfPatch) * sp + (x + u);
 #pragma unroll
-  for (int t = 0; t < 8; ++t) {
-    int val[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const float2 p = patf[(t * 2 + e) * 32 + lane];
-      const int yy = round_rn_small(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)));
-      const int xx = round_rn_small(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)));
-      val[e] = pc[yy * kPatchPitch + xx];
+      for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
+        if ((v < 0 ? -v : v) <= vlim) {
+          const int val = *cp;
+          colsum += val;
+          m01 += v * val;
+        }
+        cp += sp;
+      }
     }
-    byte |= (uint32_t)(val[0] < val[1]) << t;
-  }
-  P.out_desc[((size_t)f * P.out_cap + at) * 32 + lane] = (uint8_t)byte;
-  if (lane == 0) {
-    orbx_keypoint kp;
-    kp.x = (float)x; kp.y = (float)y;
-    if (l != 0) { kp.x = __fmul_rn(kp.x, G.scale); kp.y = __fmul_rn(kp.y, G.scale); }
-    kp.size = G.patch;
-    kp.angle = angle;
-    kp.response = (float)score;
-    kp.octave = l;
-    kp.class_id = -1;
-    P.out_kp[(size_t)f * P.out_cap + at] = kp;
+    int m10 = u * colsum;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+      m10 += __shfl_xor_sync(0xffffffffu, m10, s);
+      m01 += __shfl_xor_sync(0xffffffffu, m01, s);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // --- steered rBRIEF on the blurred patch: lane <-> descriptor byte
+    float ca = 0.f, sa = 0.f;
+    if (lane == 0) {
+      constexpr float factorPI = (float)(3.14159265358979323846 / 180.0);
+      const float rad = __fmul_rn(angle, factorPI);
+      double ds, dc;
+      sincos((double)rad, &ds, &dc);  // correctly rounded to float in all but vanishingly rare cases
+      ca = (float)dc;
+      sa = (float)ds;
+    }
+    ca = __shfl_sync(0xffffffffu, ca, 0);
+    sa = __shfl_sync(0xffffffffu, sa, 0);
+    __syncwarp();  // patch visible to every lane
+    const uint8_t* pc = reinterpret_cast<const uint8_t*>(patch_s[warp]) + kPatchR * kPatchPitch + kPatchR + shift;
+    uint32_t byte = 0;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      int val[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const float2 p = patf[(t * 2 + e) * 32 + lane];
+        const int yy = round_rn_small(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)));
+        const int xx = round_rn_small(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)));
+        val[e] = pc[yy * kPatchPitch + xx];
+      }
+      byte |= (uint32_t)(val[0] < val[1]) << t;
+    }
+    P.out_desc[((size_t)f * P.out_cap + at) * 32 + lane] = (uint8_t)byte;
+    if (lane == 0) {
+      orbx_keypoint kp;
+      kp.x = (float)x; kp.y = (float)y;
+      if (l != 0) { kp.x = __fmul_rn(kp.x, G.scale); kp.y = __fmul_rn(kp.y, G.scale); }
+      kp.size = G.patch;
+      kp.angle = angle;
+      kp.response = (float)score;
+      kp.octave = l;
+      kp.class_id = -1;
+      P.out_kp[(size_t)f * P.out_cap + at] = kp;
+    }
   }
 }
 
 int launch_describe(const ExtractParams& P, cudaStream_t s, int* launches) {
   const LevelGeom& last = P.lv[P.nlevels - 1];
   const int slots = last.kept_off + last.kept_cap;
-  orient_describe_kernel<<<dim3(div_up(slots, kDescWarps), P.n_frames), kDescWarps * 32, 0, s>>>(P, slots);
+  orient_describe_kernel<<<dim3(div_up(slots, kDescWarps * kKpPerWarp), P.n_frames), kDescWarps * 32, 0, s>>>(P, slots);
   ORB_LAUNCH_CHECK();
   ++*launches;
   return ORB_OK;

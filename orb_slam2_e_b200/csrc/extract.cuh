@@ -39,6 +39,7 @@ struct LevelGeom {
   float scale;              // mvScaleFactor[level]
   float patch;              // (int)(PATCH_SIZE*scale), as float (KeyPoint::size)
   int xtab, ytab;           // offsets into the resize coefficient table
+  int resize_words;         // every 4-px destination group reads a source window of <= 8 bytes: word-wise resize kernel
 };
 
 struct ExtractParams {

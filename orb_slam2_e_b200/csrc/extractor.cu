@@ -174,6 +174,17 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
     for (int l = 1; l < nl; ++l) {
       axis_taps(P.lv[l - 1].w, P.lv[l].w, true, &taps[P.lv[l].xtab]);
       axis_taps(P.lv[l - 1].h, P.lv[l].h, false, &taps[P.lv[l].ytab]);
+      // word-wise kernel precondition: window of a 4-px group (first left tap .. last right tap) <= 8 bytes,
+      // and consecutive destination rows advance the source row by at most 2
+      bool ok = true;
+      const int4* xt = &taps[P.lv[l].xtab];
+      for (int x0 = 0; x0 < P.lv[l].w && ok; x0 += 4) {
+        const int xe = std::min(x0 + 3, P.lv[l].w - 1);
+        for (int x = x0; x <= xe; ++x) ok = ok && xt[x].x >= xt[x0].x && xt[x].w >= xt[x0].x && xt[x].w - xt[x0].x < 8 && xt[x].x - xt[x0].x < 8;
+      }
+      const int4* yt = &taps[P.lv[l].ytab];
+      for (int y = 0; y < P.lv[l].h && ok; ++y) ok = ok && (yt[y].w == yt[y].x || yt[y].w == yt[y].x + 1) && (y == 0 || yt[y].w >= yt[y - 1].w);
+      P.lv[l].resize_words = ok ? 1 : 0;
     }
     int rc;
     if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(nl + 1))) return rc;
