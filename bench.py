@@ -234,6 +234,7 @@ def main():
     ap.add_argument("--queries", type=int, default=1000)
     ap.add_argument("--cpu-db-rows", type=int, default=200_000)
     ap.add_argument("--cpu-seconds", type=float, default=20.0)
+    ap.add_argument("--chunk-frames", type=int, default=0, help="frames per upload|extract|download chunk of the e2e path")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-match", action="store_true")
     args = ap.parse_args()

@@ -93,6 +93,18 @@ int orbx_batch_counts(orbx_handle* h, int* counts /* n */);
 int orbx_batch_read(orbx_handle* h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
 /* Copies every frame's results in one transfer: frame f occupies rows [f*cap_per_frame, ...). */
 int orbx_batch_read_all(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts);
+/* Rows per frame that orbx_batch_read_all / orbx_extract_batch_host need for w x ht frames
+ * (sum over levels of quota + 4 * quadtree roots + 3; the reference's DistributeOctTree may exceed
+ * a level's quota by up to 3). */
+int orbx_frame_capacity(orbx_handle* h, int w, int ht, int* cap);
+/* Host-to-host batch in one call: frames are uploaded, extracted and their results downloaded in
+ * chunks of chunk_frames (<= 0: a growing schedule n/16, n/8, n/4, n/4 ...) on three streams, so PCIe traffic in both directions
+ * overlaps the kernels.  Pinned host buffers give full overlap; pageable ones still work.  Output
+ * layout as orbx_batch_read_all (frame f at row f*cap_per_frame; counts[f] keypoints).  Blocks
+ * until every result is in host memory. */
+int orbx_extract_batch_host(orbx_handle* h, const uint8_t* imgs, int n, int w, int ht, size_t stride,
+                            size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame,
+                            int* counts, int chunk_frames);
 /* Wait for the handle's stream. */
 int orbx_sync(orbx_handle* h);
 

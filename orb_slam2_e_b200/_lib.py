@@ -48,6 +48,8 @@ SIGNATURES = {
     "orbx_get_level_quota": (_i, [_vp, _vp]),
     "orbx_extract": (_i, [_vp, _vp, _i, _i, _sz, _vp, _vp, _i, _ip]),
     "orbx_extract_batch": (_i, [_vp, _vp, _i, _i, _i, _sz, _sz, _i]),
+    "orbx_extract_batch_host": (_i, [_vp, _vp, _i, _i, _i, _sz, _sz, _vp, _vp, _i, _vp, _i]),
+    "orbx_frame_capacity": (_i, [_vp, _i, _i, _ip]),
     "orbx_batch_counts": (_i, [_vp, _vp]),
     "orbx_batch_read": (_i, [_vp, _i, _vp, _vp, _i, _ip]),
     "orbx_batch_read_all": (_i, [_vp, _vp, _vp, _i, _vp]),

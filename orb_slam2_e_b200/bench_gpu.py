@@ -110,14 +110,14 @@ def bench_extract(args, B, rank, world, local, dist):
 
     # ---- end to end through the public batch API with pinned HOST buffers (`e2e`)
     pin_in = torch.from_numpy(host).pin_memory()
-    cap = ext.out_cap
+    cap = ext.frame_capacity(w, h)
     pin_kp = torch.empty(n * cap * 28, dtype=torch.uint8).pin_memory()
     pin_desc = torch.empty(n * cap * 32, dtype=torch.uint8).pin_memory()
     cnt = np.zeros(n, np.int32)
 
     def step_e2e():
-        ext.extract_batch_host_ptr(pin_in.data_ptr(), n, h, w, w, w * h)
-        ext.read_batch_into(pin_kp.data_ptr(), pin_desc.data_ptr(), cap, cnt)
+        ext.extract_batch_host_ptr_into(pin_in.data_ptr(), n, h, w, w, w * h, pin_kp.data_ptr(), pin_desc.data_ptr(), cap, cnt,
+                                        args.chunk_frames)
 
     step_e2e()
     _barrier(dist)

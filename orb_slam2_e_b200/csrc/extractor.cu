@@ -46,6 +46,11 @@ struct orbx_handle {
   // device state
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // copy streams + per-chunk events of orbx_extract_batch_host (upload | extract | download pipeline)
+  cudaStream_t s_up = nullptr, s_down = nullptr;
+  std::vector<cudaEvent_t> ev_up, ev_done;
+  int* pinned_counts = nullptr;  // page-locked staging for per-frame counts (a pageable destination would block the host per chunk)
+  int pinned_counts_cap = 0;
   cudaEvent_t stage_ev[ORBX_N_STAGES + 1] = {};
   bool stage_timing = false, stage_valid = false;
   Dev<uint8_t> l0, pyr, blur, qt_b, out_desc;
@@ -218,6 +223,27 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
 // ====================================================================================
 extern "C" {
 
+// The parameter block of frames [f0, f0 + nf) of the configured batch.
+static ExtractParams frame_range(const ExtractParams& P, int f0, int nf) {
+  ExtractParams Q = P;
+  const size_t f = (size_t)f0;
+  Q.n_frames = nf;
+  Q.l0 += f * P.l0_frame;
+  Q.pyr += f * P.pyr_frame;
+  Q.blur += f * P.blur_frame;
+  Q.cand += f * P.cand_frame;
+  Q.cand_count += f * P.nlevels;
+  Q.kept += f * P.kept_frame;
+  Q.kept_count += f * P.nlevels;
+  Q.qt_b += f * (P.cand_frame + kMaxLevels);
+  Q.qt_seq += f * P.cand_frame;
+  Q.qt_tmp += f * P.cand_frame;
+  Q.out_kp += f * P.out_cap;
+  Q.out_desc += f * (size_t)P.out_cap * 32;
+  Q.out_count += f;
+  return Q;
+}
+
 int orbx_create(const orbx_config* cfg, orbx_handle** out) {
   if (!cfg || !out) return set_error(ORB_E_INVALID, "orbx_create: null argument");
   if (cfg->nlevels < 1 || cfg->nlevels > kMaxLevels || cfg->nfeatures < 0 || !(cfg->scale_factor > 1.0f) ||
@@ -250,6 +276,11 @@ int orbx_destroy(orbx_handle* H) {
   if (H->stream) cudaStreamSynchronize(H->stream);
   if (H->ev0) cudaEventDestroy(H->ev0);
   if (H->ev1) cudaEventDestroy(H->ev1);
+  if (H->s_up) { cudaStreamSynchronize(H->s_up); cudaStreamDestroy(H->s_up); }
+  if (H->s_down) { cudaStreamSynchronize(H->s_down); cudaStreamDestroy(H->s_down); }
+  if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
+  for (cudaEvent_t e : H->ev_up) cudaEventDestroy(e);
+  for (cudaEvent_t e : H->ev_done) cudaEventDestroy(e);
   for (cudaEvent_t e : H->stage_ev)
     if (e) cudaEventDestroy(e);
   if (H->stream) cudaStreamDestroy(H->stream);
@@ -283,10 +314,17 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
   int rc = use_device(H->cfg.device);
   if (rc) return rc;
   const bool alias = memory == 1 && ((uintptr_t)imgs % 16 == 0) && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
-  if ((rc = configure(H, w, ht, n, !alias))) return rc;
+  // host frames with 16-byte-multiple strides are uploaded with one linear copy and read in place
+  const bool linear = memory == 0 && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
+  if ((rc = configure(H, w, ht, n, !alias && !linear))) return rc;
   ExtractParams& P = H->P;
   if (alias) {
     P.l0 = imgs; P.l0_pitch = stride; P.l0_frame = frame_stride;
+  } else if (linear) {
+    if ((rc = H->l0.reserve((size_t)n * frame_stride + 256))) return rc;
+    const size_t bytes = (size_t)(n - 1) * frame_stride + stride * (size_t)(ht - 1) + (size_t)w;
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->l0.p, imgs, bytes, cudaMemcpyHostToDevice, H->stream));
+    P.l0 = H->l0.p; P.l0_pitch = stride; P.l0_frame = frame_stride;
   } else {
     const cudaMemcpyKind kind = memory ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     if (H->l0_frame == H->l0_pitch * (size_t)ht && frame_stride == stride * (size_t)ht) {
@@ -312,6 +350,120 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
   ORB_CUDA_TRY(cudaEventRecord(H->ev1, H->stream));
   H->n_frames = n;
   H->last_launches = launches;
+  return ORB_OK;
+}
+
+int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht, size_t stride, size_t frame_stride,
+                            orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts, int chunk_frames) {
+  if (!H || n < 0 || !counts || (n > 0 && (!kps || !desc))) return set_error(ORB_E_INVALID, "orbx_extract_batch_host: bad argument");
+  H->counts_valid = false;
+  if (n == 0 || !imgs || w <= 0 || ht <= 0) {
+    H->n_frames = 0;
+    for (int f = 0; f < n; ++f) counts[f] = 0;
+    return ORB_OK;
+  }
+  if (stride < (size_t)w || (n > 1 && frame_stride < stride * (size_t)(ht - 1) + w))
+    return set_error(ORB_E_INVALID, "orbx_extract_batch_host: stride smaller than a row / frame");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  // frames whose rows and frame stride are 16-byte multiples are uploaded as they are (one linear
+  // copy per chunk) and read in place; other layouts go through pitched 2-D copies
+  const bool linear = stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
+  if ((rc = configure(H, w, ht, n, !linear))) return rc;
+  ExtractParams& P = H->P;
+  if (cap_per_frame < P.out_cap)
+    return set_error(ORB_E_CAPACITY, "orbx_extract_batch_host: cap_per_frame %d < %d (per-frame output capacity)", cap_per_frame, P.out_cap);
+  if (linear) {
+    if ((rc = H->l0.reserve((size_t)n * frame_stride + 256))) return rc;
+    P.l0 = H->l0.p; P.l0_pitch = stride; P.l0_frame = frame_stride;
+  } else {
+    P.l0 = H->l0.p; P.l0_pitch = H->l0_pitch; P.l0_frame = H->l0_frame;
+  }
+  if (H->pinned_counts_cap < n) {
+    if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
+    H->pinned_counts = nullptr; H->pinned_counts_cap = 0;
+    ORB_CUDA_TRY(cudaMallocHost(&H->pinned_counts, sizeof(int) * (size_t)n));
+    H->pinned_counts_cap = n;
+  }
+  // chunk schedule: fixed size when the caller asks for one; otherwise start small so the first
+  // kernels begin early and grow to n/4 so later chunks run at full-GPU efficiency
+  std::vector<int> chunk_begin;
+  if (chunk_frames > 0) {
+    for (int f0 = 0; f0 < n; f0 += chunk_frames) chunk_begin.push_back(f0);
+  } else {
+    int size = std::max(32, n / 16);
+    for (int f0 = 0; f0 < n; f0 += size, size = std::min(size * 2, std::max(32, n / 4))) chunk_begin.push_back(f0);
+  }
+  chunk_begin.push_back(n);
+  const int n_chunks = (int)chunk_begin.size() - 1;
+  if (!H->s_up) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_up, cudaStreamNonBlocking));
+  if (!H->s_down) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_down, cudaStreamNonBlocking));
+  while ((int)H->ev_up.size() < n_chunks) {
+    cudaEvent_t a = nullptr, b = nullptr;
+    ORB_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+    H->ev_up.push_back(a);
+    ORB_CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+    H->ev_done.push_back(b);
+  }
+  typedef int (*stage_fn)(const ExtractParams&, cudaStream_t, int*);
+  const stage_fn stages[ORBX_N_STAGES] = {launch_pyramid, launch_fast, launch_quadtree, launch_blur, launch_describe};
+  int launches = 0;
+  const int oc = P.out_cap;
+  // the copy streams must not run ahead of work already queued on the handle's stream
+  ORB_CUDA_TRY(cudaEventRecord(H->ev0, H->stream));
+  ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_up, H->ev0, 0));
+  for (int c = 0; c < n_chunks; ++c) {
+    const int f0 = chunk_begin[c], nf = chunk_begin[c + 1] - f0;
+    if (linear) {
+      const size_t bytes = (size_t)(nf - 1) * frame_stride + stride * (size_t)(ht - 1) + (size_t)w;
+      ORB_CUDA_TRY(cudaMemcpyAsync(H->l0.p + (size_t)f0 * frame_stride, imgs + (size_t)f0 * frame_stride, bytes, cudaMemcpyHostToDevice, H->s_up));
+    } else {
+      for (int f = f0; f < f0 + nf; ++f)
+        ORB_CUDA_TRY(cudaMemcpy2DAsync(H->l0.p + (size_t)f * H->l0_frame, H->l0_pitch, imgs + (size_t)f * frame_stride, stride, (size_t)w,
+                                       (size_t)ht, cudaMemcpyHostToDevice, H->s_up));
+    }
+    ORB_CUDA_TRY(cudaEventRecord(H->ev_up[c], H->s_up));
+    ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_up[c], 0));
+    const ExtractParams Q = frame_range(P, f0, nf);
+    for (int s = 0; s < ORBX_N_STAGES; ++s)
+      if ((rc = stages[s](Q, H->stream, &launches))) return rc;
+    ORB_CUDA_TRY(cudaEventRecord(H->ev_done[c], H->stream));
+    ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_down, H->ev_done[c], 0));
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->pinned_counts + f0, H->out_count.p + f0, sizeof(int) * (size_t)nf, cudaMemcpyDeviceToHost, H->s_down));
+    if (cap_per_frame == oc) {  // same row count on both sides: linear copies
+      ORB_CUDA_TRY(cudaMemcpyAsync(kps + (size_t)f0 * oc, H->out_kp.p + (size_t)f0 * oc, sizeof(orbx_keypoint) * (size_t)oc * nf,
+                                   cudaMemcpyDeviceToHost, H->s_down));
+      ORB_CUDA_TRY(cudaMemcpyAsync(desc + (size_t)f0 * oc * 32, H->out_desc.p + (size_t)f0 * oc * 32, 32 * (size_t)oc * nf,
+                                   cudaMemcpyDeviceToHost, H->s_down));
+    } else {
+      ORB_CUDA_TRY(cudaMemcpy2DAsync(kps + (size_t)f0 * cap_per_frame, sizeof(orbx_keypoint) * (size_t)cap_per_frame,
+                                     H->out_kp.p + (size_t)f0 * oc, sizeof(orbx_keypoint) * (size_t)oc, sizeof(orbx_keypoint) * (size_t)oc,
+                                     (size_t)nf, cudaMemcpyDeviceToHost, H->s_down));
+      ORB_CUDA_TRY(cudaMemcpy2DAsync(desc + (size_t)f0 * cap_per_frame * 32, 32 * (size_t)cap_per_frame, H->out_desc.p + (size_t)f0 * oc * 32,
+                                     32 * (size_t)oc, 32 * (size_t)oc, (size_t)nf, cudaMemcpyDeviceToHost, H->s_down));
+    }
+  }
+  ORB_CUDA_TRY(cudaEventRecord(H->ev1, H->stream));
+  H->stage_valid = false;
+  H->n_frames = n;
+  H->last_launches = launches;
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->s_down));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  memcpy(counts, H->pinned_counts, sizeof(int) * (size_t)n);
+  return ORB_OK;
+}
+
+int orbx_frame_capacity(orbx_handle* H, int w, int ht, int* cap) {
+  if (!H || !cap || w <= 0 || ht <= 0) return set_error(ORB_E_INVALID, "orbx_frame_capacity: bad argument");
+  int total = 0;
+  for (int l = 0; l < H->cfg.nlevels; ++l) {  // per level: quota + 4 * roots + 3 (the last split may overshoot by 3)
+    const int lw = cv_round((float)w * H->inv_scale[l]), lh = cv_round((float)ht * H->inv_scale[l]);
+    const int bw = lw - 2 * (kEdge - 3), bh = lh - 2 * (kEdge - 3);
+    if (bw < 30 || bh < 30) return set_error(ORB_E_INVALID, "orbx_frame_capacity: level %d is %dx%d, too small", l, lw, lh);
+    const int nini = std::max(1, (int)roundf((float)bw / (float)bh));
+    total += std::max(H->quota[l], 0) + 4 * nini + 3;
+  }
+  *cap = total;
   return ORB_OK;
 }
 

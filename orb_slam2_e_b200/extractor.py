@@ -103,6 +103,32 @@ class ORBextractor:
         check(self._L.orbx_extract_batch(self._h, C.c_void_p(host_ptr), n, w, h, stride, frame_stride, 0))
         self._n_frames = n
 
+    def frame_capacity(self, w: int, h: int) -> int:
+        """Exact per-frame output rows needed for w x h frames (<= out_cap)."""
+        cap = C.c_int(0)
+        check(self._L.orbx_frame_capacity(self._h, w, h, C.byref(cap)))
+        return cap.value
+
+    def extract_batch_host(self, frames: np.ndarray, chunk_frames: int = 0):
+        """Host batch through the pipelined upload | extract | download path; returns the list of
+        (keypoints, descriptors) per frame like extract_batch."""
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n, h, w = frames.shape
+        cap = self.frame_capacity(w, h)
+        kps = np.zeros((n, cap), KEYPOINT_DTYPE)
+        desc = np.zeros((n, cap, 32), np.uint8)
+        counts = np.zeros(n, np.int32)
+        self.extract_batch_host_ptr_into(frames.ctypes.data, n, h, w, frames.strides[1], frames.strides[0],
+                                         kps.ctypes.data, desc.ctypes.data, cap, counts, chunk_frames)
+        return [(kps[f, :counts[f]].copy(), desc[f, :counts[f]].copy()) for f in range(n)]
+
+    def extract_batch_host_ptr_into(self, host_ptr: int, n: int, h: int, w: int, stride: int, frame_stride: int,
+                                    kps_ptr: int, desc_ptr: int, cap: int, counts: np.ndarray, chunk_frames: int = 0):
+        """orbx_extract_batch_host on raw (ideally pinned) host addresses; blocks until results are on the host."""
+        check(self._L.orbx_extract_batch_host(self._h, C.c_void_p(host_ptr), n, w, h, stride, frame_stride,
+                                              C.c_void_p(kps_ptr), C.c_void_p(desc_ptr), cap, ptr(counts), chunk_frames))
+        self._n_frames = n
+
     def counts(self) -> np.ndarray:
         out = np.zeros(self._n_frames, np.int32)
         if self._n_frames:

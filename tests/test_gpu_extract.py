@@ -160,3 +160,19 @@ def test_config2_stereo_extract_then_search():
     gi, gd = matcher.ORBmatcher().StereoSearch(kl, dl, kr, dr, scale, 376, 0.0, 80.0)
     assert np.array_equal(gd, bd) and np.array_equal(gi, bi)
     assert ((bd >= 0) & (bd < 70)).sum() > 200  # plenty of candidates pass to the SAD refinement
+
+
+def test_pipelined_host_batch_equals_single_frames():
+    """orbx_extract_batch_host (chunked upload | extract | download) == per-frame results, ragged last chunk."""
+    frames = np.stack([synth.textured_frame(240, 320, 40 + i) if i % 3 else synth.endoscopy_frame(240, 320, 40 + i) for i in range(7)])
+    cfg = (400, 1.2, 4, 20, 7)
+    g = ORBextractor(*cfg)
+    assert g.frame_capacity(320, 240) <= g.out_cap
+    for chunk in (3, 64):
+        res = g.extract_batch_host(frames, chunk_frames=chunk)
+        assert len(res) == 7
+        for f in range(7):
+            compare(frames[f], cfg, frame_result=res[f])
+    res2 = g.extract_batch(frames)  # the two-call path still agrees
+    for f in range(7):
+        assert res2[f][0].tobytes() == res[f][0].tobytes() and np.array_equal(res2[f][1], res[f][1])
