@@ -98,7 +98,7 @@ int orbx_batch_read_all(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int c
  * a level's quota by up to 3). */
 int orbx_frame_capacity(orbx_handle* h, int w, int ht, int* cap);
 /* Host-to-host batch in one call: frames are uploaded, extracted and their results downloaded in
- * chunks of chunk_frames (<= 0: a growing schedule n/16, n/8, n/4, n/4 ...) on three streams, so PCIe traffic in both directions
+ * chunks of chunk_frames (<= 0: an eighth of the batch, at least 32) on three streams, so PCIe traffic in both directions
  * overlaps the kernels.  Pinned host buffers give full overlap; pageable ones still work.  Output
  * layout as orbx_batch_read_all (frame f at row f*cap_per_frame; counts[f] keypoints).  Blocks
  * until every result is in host memory. */

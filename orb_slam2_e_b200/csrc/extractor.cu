@@ -2,6 +2,7 @@
 // per-level constants of ComputePyramid / ComputeKeyPointsOctTree), device buffers, stream
 // orchestration and the orbx_* C ABI (include/orbfront.h).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -47,7 +48,7 @@ struct orbx_handle {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // copy streams + per-chunk events of orbx_extract_batch_host (upload | extract | download pipeline)
-  cudaStream_t s_up = nullptr, s_down = nullptr;
+  cudaStream_t s_up = nullptr, s_down = nullptr, s_alt = nullptr;  // s_alt: second compute stream (odd chunks)
   std::vector<cudaEvent_t> ev_up, ev_done;
   int* pinned_counts = nullptr;  // page-locked staging for per-frame counts (a pageable destination would block the host per chunk)
   int pinned_counts_cap = 0;
@@ -278,6 +279,7 @@ int orbx_destroy(orbx_handle* H) {
   if (H->ev1) cudaEventDestroy(H->ev1);
   if (H->s_up) { cudaStreamSynchronize(H->s_up); cudaStreamDestroy(H->s_up); }
   if (H->s_down) { cudaStreamSynchronize(H->s_down); cudaStreamDestroy(H->s_down); }
+  if (H->s_alt) { cudaStreamSynchronize(H->s_alt); cudaStreamDestroy(H->s_alt); }
   if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
   for (cudaEvent_t e : H->ev_up) cudaEventDestroy(e);
   for (cudaEvent_t e : H->ev_done) cudaEventDestroy(e);
@@ -385,19 +387,20 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
     ORB_CUDA_TRY(cudaMallocHost(&H->pinned_counts, sizeof(int) * (size_t)n));
     H->pinned_counts_cap = n;
   }
-  // chunk schedule: fixed size when the caller asks for one; otherwise start small so the first
-  // kernels begin early and grow to n/4 so later chunks run at full-GPU efficiency
+  // chunk schedule: the caller's size, else an eighth of the batch (at least 32 frames)
   std::vector<int> chunk_begin;
   if (chunk_frames > 0) {
     for (int f0 = 0; f0 < n; f0 += chunk_frames) chunk_begin.push_back(f0);
   } else {
-    int size = std::max(32, n / 16);
-    for (int f0 = 0; f0 < n; f0 += size, size = std::min(size * 2, std::max(32, n / 4))) chunk_begin.push_back(f0);
+    const int size = std::max(32, n / 8);  // measured best with two alternating compute streams (1024 frames: 128)
+    for (int f0 = 0; f0 < n; f0 += size) chunk_begin.push_back(f0);
   }
   chunk_begin.push_back(n);
   const int n_chunks = (int)chunk_begin.size() - 1;
   if (!H->s_up) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_up, cudaStreamNonBlocking));
   if (!H->s_down) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_down, cudaStreamNonBlocking));
+  if (!H->s_alt) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_alt, cudaStreamNonBlocking));
+  static const bool two_streams = getenv("ORBX_ONE_COMPUTE_STREAM") == nullptr;
   while ((int)H->ev_up.size() < n_chunks) {
     cudaEvent_t a = nullptr, b = nullptr;
     ORB_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -423,11 +426,15 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
                                        (size_t)ht, cudaMemcpyHostToDevice, H->s_up));
     }
     ORB_CUDA_TRY(cudaEventRecord(H->ev_up[c], H->s_up));
-    ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_up[c], 0));
+    // consecutive chunks alternate between two compute streams: one chunk's tail (few CTAs left,
+    // latency-bound quadtree) overlaps the next chunk's streaming kernels
+    cudaStream_t cs = (two_streams && (c & 1)) ? H->s_alt : H->stream;
+    ORB_CUDA_TRY(cudaStreamWaitEvent(cs, H->ev_up[c], 0));
     const ExtractParams Q = frame_range(P, f0, nf);
     for (int s = 0; s < ORBX_N_STAGES; ++s)
-      if ((rc = stages[s](Q, H->stream, &launches))) return rc;
-    ORB_CUDA_TRY(cudaEventRecord(H->ev_done[c], H->stream));
+      if ((rc = stages[s](Q, cs, &launches))) return rc;
+    ORB_CUDA_TRY(cudaEventRecord(H->ev_done[c], cs));
+    if (cs != H->stream) ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_done[c], 0));  // ev1 / later work on the handle's stream
     ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_down, H->ev_done[c], 0));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->pinned_counts + f0, H->out_count.p + f0, sizeof(int) * (size_t)nf, cudaMemcpyDeviceToHost, H->s_down));
     if (cap_per_frame == oc) {  // same row count on both sides: linear copies
