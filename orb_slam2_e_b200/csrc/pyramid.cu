@@ -104,38 +104,35 @@ resize_level_words_kernel(const __grid_constant__ ExtractParams P, int l) {
   const int sh = (first & 3) * 8;
   const uint32_t* wsrc = reinterpret_cast<const uint32_t*>(src) + (first >> 2);
   const int spw = sp >> 2;
-  // the three-word window must stay inside the source row's pitch; the rare lanes at the right
-  // edge where it does not fall back to byte loads
-  const bool words_ok = (first & ~3) + 12 <= sp;
+  // a window word is loaded only if it starts inside the source row (the taps never select bytes
+  // past the row's last pixel), so no load leaves the row whatever its pitch
+  const int src_w = P.lv[l - 1].w;
+  const bool need1 = (first & ~3) + 4 < src_w, need2 = (first & ~3) + 8 < src_w;
 
   int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};  // horizontally interpolated source rows rowB-1 and rowB, already >> 4
   int rowB = -1;
-  uint32_t w0 = 0, w1 = 0, w2 = 0;
-  auto request = [&](int sy) {
-    if (words_ok) {
-      const uint32_t* p = wsrc + (size_t)sy * spw;
-      w0 = __ldg(p); w1 = __ldg(p + 1); w2 = __ldg(p + 2);
-    } else {
-      const uint8_t* r = src + (size_t)sy * sp;
-      w0 = w1 = w2 = 0;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {  // window bytes first .. first+7, clamped to the pitch
-        const uint32_t v = r[min(first + j, sp - 1)];
-        if (j < 4) w0 |= v << (8 * j); else w1 |= v << (8 * (j - 4));
-      }
-    }
+  // source rows are consumed in order; two are kept in flight so that a destination row that
+  // advances by two source rows does not wait for a load issued a moment ago
+  uint32_t w0 = 0, w1 = 0, w2 = 0, n0 = 0, n1 = 0, n2 = 0;
+  auto request = [&](int sy, uint32_t& a, uint32_t& b, uint32_t& c) {
+    const uint32_t* p = wsrc + (size_t)sy * spw;
+    a = __ldg(p);
+    b = need1 ? __ldg(p + 1) : 0u;
+    c = need2 ? __ldg(p + 2) : 0u;
   };
   const int y1 = min(y0 + kResizeStrip, D.h);
   int next_src = __ldg(&P.rtab[D.ytab + y0]).x;
-  request(next_src);
+  request(next_src, w0, w1, w2);
+  request(min(next_src + 1, src_h - 1), n0, n1, n2);
   for (int y = y0; y < y1; ++y) {
     const int4 t = __ldg(&P.rtab[D.ytab + y]);
     const int sy0 = t.x, sy1 = t.w, b0 = t.y, b1 = t.z;
     while (rowB < sy1) {  // sy1 is non-decreasing and advances by at most 2 per destination row
-      const uint32_t v0 = words_ok ? __funnelshift_r(w0, w1, sh) : w0, v1 = words_ok ? __funnelshift_r(w1, w2, sh) : w1;
+      const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh);
       rowB = next_src;
       next_src = min(next_src + 1, src_h - 1);
-      request(next_src);
+      w0 = n0; w1 = n1; w2 = n2;
+      request(min(next_src + 1, src_h - 1), n0, n1, n2);
       const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
 #pragma unroll
       for (int k = 0; k < 4; ++k) hA[k] = hB[k];
@@ -203,15 +200,31 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   const uint8_t* src = level_ptr(P, l, f);
   const int sp = level_pitch(P, l);
   uint8_t* dst = P.blur + (size_t)f * P.blur_frame + G.off;
-  // lanes whose 12-byte window [x0-4, x0+8) stays inside the row run the word-wise main loop;
-  // the (at most three per row) groups touching the left/right edge are done afterwards, one
-  // ROW per lane, so the main loop has no divergent reflect path
-  const bool interior = x0 >= 4 && x0 + 8 <= G.w;
+  // Row edges without a divergent path: every lane with a pixel in the row runs the word-wise loop on
+  // its 12-byte window [x0-4, x0+8); where the window leaves the row, BORDER_REFLECT_101 is applied
+  // by three PRMTs whose selectors are lane constants (identity for interior lanes).
+  const int e = G.w - x0;  // pixels of this lane's window that exist from x0 on (>= 8: no right edge)
+  const bool active = e > 0;
   // tiles away from the top/bottom border walk a running row pointer; the others reflect per row
   const bool y_inside = y0 >= 3 && y0 + kBlurTH + 3 <= G.h;
   constexpr uint32_t K1 = 18u | 34u << 8 | 48u << 16 | 56u << 24, K2 = 48u | 34u << 8 | 18u << 16;
+  // window byte i (0..11) <-> x0-4+i; byte i >= e+4 mirrors to 2(e+3)-i, byte i < 4 of lane x0 = 0 to 8-i.
+  // a' = PRMT(b, c, selA); b' = PRMT(a, b, selB); c' = PRMT(lo, hi, selC) with (lo, hi) = (a, b) if e <= 4 else (b, c)
+  uint32_t selA = 0x3210u, selB = 0x7654u, selC = 0x7654u;  // identity: a' = a is taken separately
+  const bool left = x0 == 0, c_from_ab = e <= 4;
+  if (e < 8) {
+    selB = 0; selC = 0;
+    for (int j = 0; j < 4; ++j) {
+      const int ib = 4 + j, ic = 8 + j;
+      const int sb = ib >= e + 4 ? 2 * (e + 3) - ib : ib;  // source window byte, inside (a, b)
+      const int sc = max(ic >= e + 4 ? 2 * (e + 3) - ic : ic, 0);  // inside (a, b) when e <= 4, else inside (b, c); bytes past e+6 are never used
+      selB |= (uint32_t)sb << (4 * j);
+      selC |= (uint32_t)(c_from_ab ? sc : sc - 4) << (4 * j);
+    }
+  }
+  if (left) selA = 0x1234u;  // x = -4..-1 <- x = 4, 3, 2, 1 out of (b, c)
 
-  if (interior) {
+  if (active) {
     uint32_t ring[7][4];
     constexpr int kAhead = 3;  // the three words of row yy+3 are requested while row yy is filtered
     uint32_t pa[kAhead], pb[kAhead], pc[kAhead];
@@ -225,7 +238,9 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
         p = src + (size_t)reflect101(min(y, G.h + 2), G.h) * sp + x0;  // rows past h+2 are never used
       }
       const uint32_t* w = reinterpret_cast<const uint32_t*>(p);
-      a = __ldg(w - 1); b = __ldg(w); c = __ldg(w + 1);
+      a = left ? 0u : __ldg(w - 1);
+      b = __ldg(w);
+      c = e > 4 ? __ldg(w + 1) : 0u;  // never read a word that starts past the row
     };
 #pragma unroll
     for (int k = 0; k < kAhead; ++k) fetch(k, pa[k], pb[k], pc[k]);
@@ -237,8 +252,11 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
       for (int r = 0; r < kBlurBody; ++r) {
         const int yy = blk * kBlurBody + r;
         {
-          const uint32_t a = pa[r % kAhead], b = pb[r % kAhead], c = pc[r % kAhead];
+          const uint32_t a0 = pa[r % kAhead], b0 = pb[r % kAhead], c0 = pc[r % kAhead];
           if (yy + kAhead < kBlurRows) fetch(yy + kAhead, pa[r % kAhead], pb[r % kAhead], pc[r % kAhead]);
+          const uint32_t a = left ? __byte_perm(b0, c0, selA) : a0;
+          const uint32_t b = __byte_perm(a0, b0, selB);
+          const uint32_t c = __byte_perm(c_from_ab ? a0 : b0, c_from_ab ? b0 : c0, selC);
           uint32_t* h = ring[r % 7];
           h[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
           h[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
@@ -251,42 +269,13 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
           for (int k = 0; k < 4; ++k)
             acc[k] = 18u * (ring[(r + 1) % 7][k] + ring[r % 7][k]) + 34u * (ring[(r + 2) % 7][k] + ring[(r + 6) % 7][k]) +
                      48u * (ring[(r + 3) % 7][k] + ring[(r + 5) % 7][k]) + (56u * ring[(r + 4) % 7][k] + 32768u);
-          // result bytes are bits 16..23 of each sum
+          // result bytes are bits 16..23 of each sum; pitch padding absorbs the bytes past the row's end
           *reinterpret_cast<uint32_t*>(outp) =
               __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
           outp += G.pitch;
           --rows_left;
         }
       }
-    }
-  }
-
-  // edge groups of this tile: xg = 0 and the multiples of 4 in (w-8, w)
-  for (int oy = y0 + lane; oy < min(y0 + kBlurTH, G.h); oy += 32) {
-    for (int xg = tx0; xg < min(tx0 + kBlurTW, G.w); xg += 4) {
-      if (xg >= 4 && xg + 8 <= G.w) {  // interior: jump to the right edge
-        xg = max(xg, ((G.w - 8) & ~3));
-        if (xg >= 4 && xg + 8 <= G.w) continue;
-      }
-      int xs[10];
-#pragma unroll
-      for (int j = 0; j < 10; ++j) xs[j] = reflect101(xg - 3 + j, G.w);
-      uint32_t acc[4] = {0, 0, 0, 0};
-#pragma unroll 1
-      for (int dy = 0; dy < 7; ++dy) {
-        const uint8_t* row = src + (size_t)reflect101(oy + dy - 3, G.h) * sp;
-        uint32_t v[10];
-#pragma unroll
-        for (int j = 0; j < 10; ++j) v[j] = row[xs[j]];
-        const uint32_t q = dy == 0 || dy == 6 ? 18u : dy == 1 || dy == 5 ? 34u : dy == 2 || dy == 4 ? 48u : 56u;
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          acc[k] += q * (18u * (v[k] + v[k + 6]) + 34u * (v[k + 1] + v[k + 5]) + 48u * (v[k + 2] + v[k + 4]) + 56u * v[k + 3]);
-      }
-      uint32_t out = 0;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) out |= ((acc[k] + 32768u) >> 16) << (8 * k);
-      *reinterpret_cast<uint32_t*>(dst + (size_t)oy * G.pitch + xg) = out;  // pitch padding absorbs the tail
     }
   }
 }
