@@ -108,13 +108,17 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   int* const count = &P.cand_count[f * P.nlevels + l];
   unsigned long long* const out = P.cand + (size_t)f * P.cand_frame + G.cand_off;
 
+  // zero frame of the score tile (rows 0 and vh+1, words 0 and ng+1 of every row): written once per
+  // cell; the interior words are cleared by each pass's prefilter loop as it visits them
+  for (int i = lane; i < kScorePitch / 4; i += 32) { S.score[i] = 0; S.score[(vh + 1) * (kScorePitch / 4) + i] = 0; }
+  for (int r = 1 + lane; r <= vh; r += 32) { S.score[r * (kScorePitch / 4)] = 0; S.score[r * (kScorePitch / 4) + ng + 1] = 0; }
+
   // One detection pass at threshold T; returns the number of keypoints it appended.
   auto detect = [&](const int T) -> int {
-    const int score_words = (vh + 2) * (kScorePitch / 4);
-    for (int i = lane; i < score_words; i += 32) S.score[i] = 0;
     const uint32_t K = 0x01010101u * (uint32_t)(127 - min(T, 126));
-    auto gt = [&](uint32_t x) { return (((x & 0x7f7f7f7fu) + K) | x) & 0x80808080u; };  // per byte: x > T
+    auto gt = [&](uint32_t x) { return ((x & 0x7f7f7f7fu) + K) | x; };  // bit 7 of every byte: x > T
     int head = 0, tail = 0;  // ring queue (uniform across the warp)
+    int nw = 0;              // entries of wlist
     auto drain = [&](int count_) {
       if (lane < count_) {
         const int e = S.queue[(head + lane) & (kQueue - 1)];
@@ -141,7 +145,13 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
         fl &= gt(__vabsdiffu4(c, __funnelshift_r(dm[0], dm[1], 16)) | __vabsdiffu4(c, __funnelshift_r(um[-1], um[0], 16)));
         fl &= gt(__vabsdiffu4(c, __funnelshift_r(um[0], um[1], 16)) | __vabsdiffu4(c, __funnelshift_r(dm[-1], dm[0], 16)));
         const int nvalid = min(4, vw - 4 * g);  // pixels of this group inside the cell
-        flags = fl & (0xffffffffu >> (32 - 8 * nvalid));
+        flags = fl & (0x80808080u >> (32 - 8 * nvalid));
+        S.score[(py + 1) * (kScorePitch / 4) + g + 1] = 0;  // cleared before any of its pixels is scored
+      }
+      {  // groups with a prefilter survivor are the only score words that can hold a corner
+        const uint32_t m = __ballot_sync(0xffffffffu, flags != 0);
+        if (flags != 0) wlist[nw + __popc(m & lt_mask)] = (uint16_t)(py << 4 | g);
+        nw += __popc(m);
       }
       const int n = __popc(flags);
       int incl = n;
@@ -161,24 +171,25 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
     drain(tail - head);
     __syncwarp();
 
-    // strict 3x3 non-max suppression (frame and sub-threshold pixels score 0).  First list the
-    // score words that hold a corner (the queue is idle now and is reused for the list: at most
-    // one entry per 4-pixel group), then one listed word per lane.
-    int nw = 0;
-    for (int base = 0; base < ngroups; base += 32) {
-      const int gid = base + lane;
-      uint32_t w = 0;
-      int py = 0, g = 0;
-      if (gid < ngroups) {
-        py = (int)(((uint32_t)gid * magic) >> 20);
-        g = gid - py * ng;
-        w = S.score[(py + 1) * (kScorePitch / 4) + g + 1];
+    // keep the listed words that really hold a corner (in place: the write index never passes the
+    // read index, and a batch's entries are all read before its ballot)
+    {
+      int kept_w = 0;
+      for (int base = 0; base < nw; base += 32) {
+        uint32_t e = 0, w = 0;
+        if (base + lane < nw) {
+          e = wlist[base + lane];
+          w = S.score[((e >> 4) + 1) * (kScorePitch / 4) + (e & 15) + 1];
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, w != 0);
+        if (w != 0) wlist[kept_w + __popc(m & lt_mask)] = (uint16_t)e;
+        kept_w += __popc(m);
       }
-      const uint32_t m = __ballot_sync(0xffffffffu, w != 0);
-      if (w != 0) wlist[nw + __popc(m & lt_mask)] = (uint16_t)(py << 4 | g);
-      nw += __popc(m);
+      nw = kept_w;
+      __syncwarp();
     }
-    __syncwarp();
+    // strict 3x3 non-max suppression (frame and sub-threshold pixels score 0): one listed score
+    // word per lane
     int appended = 0;
     for (int base = 0; base < nw; base += 32) {
       uint32_t w = 0;
