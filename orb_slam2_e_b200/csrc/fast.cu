@@ -27,7 +27,8 @@ namespace orbfront {
 constexpr int kFastWarps = 4;
 constexpr int kCellMax = 60;                 // wCell,hCell <= 59 (ceil(width/floor(width/30)))
 constexpr int kQueue = 256;                  // ring queue entries (py << 6 | px)
-// Per-warp shared memory: tile[(maxH+6) x PITCH] | score[(maxH+2) x PITCH] | queue[kQueue] u16.
+// Per-warp shared memory: tile[(maxH+6) x PITCH] | score[(maxH+2) x PITCH] | queue[kQueue] u16, later reused
+// for the cell's NMS survivors | wlist (score words with a prefilter survivor).
 // PITCH (bytes, multiple of 4, >= widest cell + 8) is a template parameter so the 16 ring offsets
 // stay immediates; tile/score column = px + 4 (word aligned groups of 4 pixels).
 
@@ -57,7 +58,7 @@ __device__ __forceinline__ int fast_strength(const uint8_t* p) {
 template <int kTilePitch>
 __global__ void __launch_bounds__(kFastWarps * 32)
 fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_bytes) {
-  const int wlist_entries = (max_h * ((kTilePitch - 8) / 4) + 1) & ~1;
+  const int qk_entries = max(kQueue, (((kTilePitch - 8) / 2 + 1) * (max_h / 2 + 1) + 1) & ~1);
   constexpr int kTileWords = kTilePitch / 4, kScorePitch = kTilePitch;
   extern __shared__ __align__(16) uint8_t smem_raw[];
   uint8_t* tile8 = smem_raw + (threadIdx.x >> 5) * warp_bytes;
@@ -66,8 +67,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   S.tile = reinterpret_cast<uint32_t*>(tile8);
   S.score = reinterpret_cast<uint32_t*>(score8);
   S.queue = reinterpret_cast<uint16_t*>(score8 + (max_h + 2) * kTilePitch);
-  uint16_t* wlist = S.queue + kQueue;  // score words holding a corner: (max_h) x (PITCH-8)/4 entries
-  uint32_t* kplist = reinterpret_cast<uint32_t*>(wlist + wlist_entries);  // NMS survivors of the cell (<= one per 2x2 block)
+  uint16_t* kplist = S.queue;  // NMS survivors of the cell (<= one per 2x2 block); the queue is idle by then
+  uint16_t* wlist = S.queue + qk_entries;  // score words holding a corner: (max_h) x (PITCH-8)/4 entries
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const int cell = blockIdx.x * kFastWarps + (threadIdx.x >> 5);
@@ -211,7 +212,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
           is_max = s > max(n0, n1);
         }
         const uint32_t m = __ballot_sync(0xffffffffu, is_max);
-        if (is_max) kplist[appended + __popc(m & lt_mask)] = ((uint32_t)s << 16) | (uint32_t)(py << 6 | px);
+        if (is_max) kplist[appended + __popc(m & lt_mask)] = (uint16_t)(py << 6 | px);
         appended += __popc(m);
       }
     }
@@ -223,9 +224,10 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
     slot = __shfl_sync(0xffffffffu, slot, 0);
     for (int i = lane; i < appended; i += 32) {
       const uint32_t e = kplist[i];
-      const int px = e & 63, py = (e >> 6) & 63;
+      const int px = e & 63, py = e >> 6;
+      const uint32_t score = score8[(py + 1) * kScorePitch + px + 4];
       const int x = vx0 + px - (kEdge - 3), y = vy0 + py - (kEdge - 3);  // border-relative (minBorder = 16)
-      const uint32_t pay = ((e >> 16) << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+      const uint32_t pay = (score << 24) | ((uint32_t)y << 12) | (uint32_t)x;
       if (slot + i < G.cand_cap) out[slot + i] = pay;  // the quadtree kernel prepends the path code
     }
     return appended;
@@ -236,9 +238,9 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
 
 template <int PITCH>
 static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) {
-  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + kQueue * 2 + 2 * ((max_h * ((PITCH - 8) / 4) + 1) & ~1) +
-                         4 * ((PITCH - 8) / 2 + 1) * (max_h / 2 + 1);
-  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((66+62)*68 + 512 + 3720) < 48 KB
+  const int qk_entries = std::max(kQueue, (((PITCH - 8) / 2 + 1) * (max_h / 2 + 1) + 1) & ~1);  // as in the kernel
+  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + 2 * qk_entries + 2 * ((max_h * ((PITCH - 8) / 4) + 1) & ~1);
+  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((66+62)*68 + 1860 + 1770) < 48 KB
   dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
   fast_cells_kernel<PITCH><<<grid, kFastWarps * 32, smem, s>>>(P, max_h, warp_bytes);
   ORB_LAUNCH_CHECK();
