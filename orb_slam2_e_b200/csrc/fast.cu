@@ -56,7 +56,7 @@ __device__ __forceinline__ int fast_strength(const uint8_t* p) {
 }
 
 template <int kTilePitch>
-__global__ void __launch_bounds__(kFastWarps * 32)
+__global__ void __launch_bounds__(kFastWarps * 32, 10)
 fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_bytes) {
   const int qk_entries = max(kQueue, (((kTilePitch - 8) / 2 + 1) * (max_h / 2 + 1) + 1) & ~1);
   constexpr int kTileWords = kTilePitch / 4, kScorePitch = kTilePitch;
