@@ -92,14 +92,21 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
     // a tile word is the funnel shift of two aligned global words (independent loads, unrolled)
     const int sh = (int)(reinterpret_cast<uintptr_t>(src) & 3);
     const uint32_t* asrc = reinterpret_cast<const uint32_t*>(src - sh);
-    const int spw = sp >> 2, nwt = (tw + 3) >> 2, total = th * nwt;
-    const uint32_t mtw = (1u << 20) / (uint32_t)nwt + 1u;  // i / nwt for i < 1200, nwt < 18
+    const int spw = sp >> 2, nwt = (tw + 3) >> 2;
+    // lane <-> (row within a group of rpi rows, word): the addresses then advance by constants
+    const int rpi = 32 / nwt;  // nwt <= 17
+    const int lr = lane / nwt, lc = lane - lr * nwt;
+    if (lr < rpi) {
+      const uint32_t* a = asrc + (size_t)lr * spw + lc;
+      uint32_t* d = S.tile + lr * kTileWords + lc;
+      const int astep = rpi * spw, dstep = rpi * kTileWords;
 #pragma unroll 4
-    for (int i = lane; i < total; i += 32) {
-      const int r = (int)(((uint32_t)i * mtw) >> 20), j = i - r * nwt;
-      const uint32_t* a = asrc + (size_t)r * spw + j;
-      const uint32_t lo = __ldg(a), hi = sh ? __ldg(a + 1) : 0u;
-      S.tile[r * kTileWords + j] = __funnelshift_r(lo, hi, 8 * sh);
+      for (int r = lr; r < th; r += rpi) {
+        const uint32_t lo = __ldg(a), hi = sh ? __ldg(a + 1) : 0u;
+        *d = __funnelshift_r(lo, hi, 8 * sh);
+        a += astep;
+        d += dstep;
+      }
     }
   }
   __syncwarp();
