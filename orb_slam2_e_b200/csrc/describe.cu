@@ -40,6 +40,33 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
+// sin and cos of x in [0, 2*pi] in double (quadrant reduction with a two-part pi/2 and the classic
+// degree-13/14 kernels, error < 1 ulp of double): rounded to float these equal the correctly rounded
+// sinf/cosf the host library returns, except in vanishingly rare double-rounding cases.  About half
+// the instructions of the general-range library sincos.
+__device__ __forceinline__ void sincos_2pi(double x, double* sn, double* cs) {
+  const double q = rint(x * 6.36619772367581382433e-01);
+  double r = __fma_rn(-q, 1.57079632673412561417e+00, x);
+  r = __fma_rn(-q, 6.07710050650619224932e-11, r);
+  const double z = r * r;
+  double ps = __fma_rn(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
+  ps = __fma_rn(z, ps, 2.75573137070700676789e-06);
+  ps = __fma_rn(z, ps, -1.98412698298579493134e-04);
+  ps = __fma_rn(z, ps, 8.33333333332248946124e-03);
+  ps = __fma_rn(z, ps, -1.66666666666666324348e-01);
+  const double sr = __fma_rn(z * r, ps, r);
+  double pc = __fma_rn(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
+  pc = __fma_rn(z, pc, -2.75573143513906633035e-07);
+  pc = __fma_rn(z, pc, 2.48015872894767294178e-05);
+  pc = __fma_rn(z, pc, -1.38888888888741095749e-03);
+  pc = __fma_rn(z, pc, 4.16666666666666019037e-02);
+  const double cr = __fma_rn(z * z, pc, __fma_rn(z, -0.5, 1.0));
+  const int iq = (int)q;
+  const double s0 = (iq & 1) ? cr : sr, c0 = (iq & 1) ? sr : cr;
+  *sn = (iq & 2) ? -s0 : s0;
+  *cs = ((iq + 1) & 2) ? -c0 : c0;
+}
+
 constexpr int kDescWarps = 8;
 constexpr int kPatchR = 18;                 // rotated pattern coordinates stay within +-18 (|p| <= 18.38, cvRound)
 constexpr int kPatchRows = 2 * kPatchR + 1; // 37
@@ -84,10 +111,10 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
   const int srow = lane / kPatchWords, scol = lane - srow * kPatchWords;  // lanes 30, 31 idle while staging
 
   const int g0 = (blockIdx.x * kDescWarps + warp) * kKpPerWarp;
+  int l = 0;
 #pragma unroll 1
   for (int g = g0; g < min(g0 + kKpPerWarp, slots_per_frame); ++g) {
-    int l = 0;
-    while (l + 1 < P.nlevels && g >= P.lv[l + 1].kept_off) ++l;
+    while (l + 1 < P.nlevels && g >= P.lv[l + 1].kept_off) ++l;  // slots ascend, so does their level
     const LevelGeom& G = P.lv[l];
     const int k = g - G.kept_off;
     const int n_l = __shfl_sync(0xffffffffu, cnt, l), before = __shfl_sync(0xffffffffu, incl, l) - n_l;
@@ -111,10 +138,10 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
       const uint32_t* bsrc = reinterpret_cast<const uint32_t*>(blur_l + (size_t)(y - kPatchR + srow) * G.pitch + (px0 - shift)) + scol;
       const int step = 3 * (G.pitch >> 2);
       uint32_t* dstp = patch_s[warp] + lane;
-      const int last_ok = (G.h - 1 - (y - kPatchR + srow)) / 3;  // iterations whose row is inside the image
 #pragma unroll
       for (int it = 0; it < (kPatchRows + 2) / 3; ++it) {
-        dstp[it * 3 * kPatchWords] = __ldg(bsrc + min(it, last_ok) * step);
+        // the last load covers patch rows 36..38; rows 37 and 38 are never sampled and may lie below the image
+        if (it < (kPatchRows + 2) / 3 - 1 || srow == 0) dstp[it * 3 * kPatchWords] = __ldg(bsrc + it * step);
       }
     }
 
@@ -122,15 +149,14 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
     const int sp = level_pitch(P, l);
     int colsum = 0, m01 = 0;
     {
-      const uint8_t* cp = level_ptr(P, l, f) + (size_t)(y - kHalfPatch) * sp + (x + u);
+      const uint8_t* cp = level_ptr(P, l, f) + (size_t)y * sp + (x + u);
 #pragma unroll
       for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
         if ((v < 0 ? -v : v) <= vlim) {
-          const int val = *cp;
+          const int val = cp[v * sp];
           colsum += val;
           m01 += v * val;
         }
-        cp += sp;
       }
     }
     int m10 = u * colsum;
@@ -147,7 +173,7 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
       constexpr float factorPI = (float)(3.14159265358979323846 / 180.0);
       const float rad = __fmul_rn(angle, factorPI);
       double ds, dc;
-      sincos((double)rad, &ds, &dc);  // correctly rounded to float in all but vanishingly rare cases
+      sincos_2pi((double)rad, &ds, &dc);
       ca = (float)dc;
       sa = (float)ds;
     }

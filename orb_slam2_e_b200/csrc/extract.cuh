@@ -39,6 +39,7 @@ struct LevelGeom {
   float scale;              // mvScaleFactor[level]
   float patch;              // (int)(PATCH_SIZE*scale), as float (KeyPoint::size)
   int xtab, ytab;           // offsets into the resize coefficient table
+  int qx, qy;               // offsets of this level's x / y path-code tables in qcode
   int resize_words;         // every 4-px destination group reads a source window of <= 8 bytes: word-wise resize kernel
 };
 
@@ -60,6 +61,7 @@ struct ExtractParams {
   unsigned long long* qt_tmp;          //   and the radix sort's second key buffer, cand layout
   const int4* rtab;                    // resize taps: (src index, c0, c1, clamped src index + 1)
   const int* blur_tiles;               // [nlevels+1] first blur tile of each level
+  const uint32_t* qcode;               // quadtree path-code tables (per level: boxW+1 x entries, boxH+1 y entries)
   orbx_keypoint* out_kp;  uint8_t* out_desc;  int out_cap;
   int* out_count;                      // [frame]
   int total_cells;                     // sum over levels of nCols*nRows
@@ -72,23 +74,11 @@ __device__ __forceinline__ int level_pitch(const ExtractParams& P, int l) {
   return l == 0 ? (int)P.l0_pitch : P.lv[l].pitch;
 }
 
-// Quadtree path code of a candidate at border-relative (x,y): root strip, then one 2-bit
-// quadrant digit per split with the reference's ceil-half boundaries
-// (ExtractorNode::DivideNode, ORBextractor.cc:481-526; root assignment :545-569).
-__device__ __forceinline__ uint32_t quadtree_path_code(int x, int y, const LevelGeom& g) {
-  const int root = (int)__fdiv_rn((float)x, g.hX);
-  int xl = (int)__fmul_rn(g.hX, (float)root), xh = (int)__fmul_rn(g.hX, (float)(root + 1));
-  int yl = 0, yh = g.boxH;
-  uint32_t code = (uint32_t)root;
-  for (int k = 0; k < g.dmax; ++k) {
-    const int mx = xl + ((xh - xl + 1) >> 1), my = yl + ((yh - yl + 1) >> 1);
-    const int bx = x >= mx, by = y >= my;
-    if (bx) xl = mx; else xh = mx;
-    if (by) yl = my; else yh = my;
-    code = (code << 2) | (uint32_t)(by * 2 + bx);
-  }
-  return code;
-}
+// Quadtree path code of a candidate at border-relative (x,y): root strip, then one 2-bit quadrant
+// digit (by * 2 + bx) per split with the reference's ceil-half boundaries (ExtractorNode::DivideNode,
+// ORBextractor.cc:481-526; root assignment :545-569).  The x and y halvings are independent, so the
+// host tabulates them per level (extractor.cu: build_path_tables) with the digits already spread to
+// their bit positions: code = qcode[qx + x] | qcode[qy + y].
 
 // kernel launchers (each returns an ORB_* code)
 int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches);

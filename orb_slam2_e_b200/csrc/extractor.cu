@@ -59,6 +59,7 @@ struct orbx_handle {
   Dev<uint32_t> kept, qt_seq;
   Dev<int> cand_count, kept_count, out_count;
   Dev<int4> rtab;
+  Dev<uint32_t> qcode;
   Dev<int> blur_tiles;
   Dev<orbx_keypoint> out_kp;
   Dev<uint8_t> border_tmp;
@@ -193,7 +194,39 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       P.lv[l].resize_words = ok ? 1 : 0;
     }
     int rc;
-    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(nl + 1))) return rc;
+    // quadtree path-code tables (extract.cuh): per level the digits of the x halvings (bit 2k of
+    // digit k) with the root strip on top, and of the y halvings (bit 2k+1)
+    std::vector<uint32_t> qcode;
+    for (int l = 0; l < nl; ++l) {
+      LevelGeom& G = P.lv[l];
+      G.qx = (int)qcode.size();
+      for (int x = 0; x <= G.boxW; ++x) {
+        const int root = (int)((float)x / G.hX);  // ORBextractor.cc:569, float division
+        int lo = (int)(G.hX * (float)root), hi = (int)(G.hX * (float)(root + 1));
+        uint32_t code = (uint32_t)root;
+        for (int k = 0; k < G.dmax; ++k) {
+          const int mid = lo + ((hi - lo + 1) >> 1);
+          const int b = x >= mid;
+          if (b) lo = mid; else hi = mid;
+          code = (code << 2) | (uint32_t)b;
+        }
+        qcode.push_back(code);
+      }
+      G.qy = (int)qcode.size();
+      for (int y = 0; y <= G.boxH; ++y) {
+        int lo = 0, hi = G.boxH;
+        uint32_t code = 0;
+        for (int k = 0; k < G.dmax; ++k) {
+          const int mid = lo + ((hi - lo + 1) >> 1);
+          const int b = y >= mid;
+          if (b) lo = mid; else hi = mid;
+          code = (code << 2) | (uint32_t)(b * 2);
+        }
+        qcode.push_back(code);
+      }
+    }
+    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(nl + 1)) || (rc = H->qcode.reserve(qcode.size()))) return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->qcode.p, qcode.data(), qcode.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->rtab.p, taps.data(), taps.size() * sizeof(int4), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->blur_tiles.p, blur_tiles.data(), (nl + 1) * sizeof(int), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));  // host vectors go out of scope
@@ -214,7 +247,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
   P.n_frames = n_frames;
   P.pyr = H->pyr.p; P.blur = H->blur.p; P.cand = H->cand.p; P.cand_count = H->cand_count.p;
   P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p; P.qt_tmp = H->qt_tmp.p;
-  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p;
+  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p; P.qcode = H->qcode.p;
   P.out_kp = H->out_kp.p; P.out_desc = H->out_desc.p; P.out_count = H->out_count.p;
   return ORB_OK;
 }

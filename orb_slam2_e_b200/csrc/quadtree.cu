@@ -4,7 +4,7 @@
 // (src/ORBextractor.cc:481-763), a sequential std::list algorithm, by an equivalent
 // level-synchronous formulation on SORTED PATH CODES (derivation in DESIGN.md "Quadtree"):
 //   * every candidate carries its root strip and the 2-bit quadrant digit of each split it
-//     would undergo (quadtree_path_code); sorting by that code makes every tree node, at every
+//     would undergo (tabulated per level, extract.cuh); sorting by that code makes every tree node, at every
 //     depth, a contiguous run, and b[i] = depth at which sorted neighbours i-1 and i separate;
 //   * the list's node count after each breadth-first pass is cnt[d] = #{i : b[i] <= d}, the
 //     number of still-divisible nodes is nexp[d]; the reference's stop rules (:669, :673) are
@@ -157,7 +157,8 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   // FAST stores the payload only; attach the path code (all lanes busy), in place
   for (int i = tid; i < n; i += kQtThreads) {
     const uint32_t pay = (uint32_t)gkeys[i];
-    gkeys[i] = ((unsigned long long)quadtree_path_code((int)(pay & 0xfff), (int)((pay >> 12) & 0xfff), G) << 32) | pay;
+    const uint32_t code = __ldg(&P.qcode[G.qx + (int)(pay & 0xfff)]) | __ldg(&P.qcode[G.qy + (int)((pay >> 12) & 0xfff)]);
+    gkeys[i] = ((unsigned long long)code << 32) | pay;
   }
   __syncthreads();
   // sort by path code: global <-> shared ping-pong when the level fits, global <-> global scratch else
@@ -275,6 +276,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
 
   // leaves: runs at depth dfin, plus the children of the nodes split by the final partial pass
   const int dfin = C.d, partial = C.partial, d_bfs = C.d_bfs;
+  const uint32_t mag_h = (1u << 20) / (uint32_t)G.hCell + 1u, mag_w = (1u << 20) / (uint32_t)G.wCell + 1u;
   if (tid == 0) C.counter = 0;
   __syncthreads();
   for (int i = tid; i < n; i += kQtThreads)
@@ -296,7 +298,8 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     do {
       const uint32_t pay = (uint32_t)keys[e];
       const int x = pay & 0xfff, y = (pay >> 12) & 0xfff;
-      const unsigned long long cell = (unsigned long long)((y - 3) / G.hCell * G.nCols + (x - 3) / G.wCell);
+      // (y-3) / hCell and (x-3) / wCell by multiplication: exact for operands < 4096 and divisors < 64
+      const unsigned long long cell = (unsigned long long)((((uint32_t)(y - 3) * mag_h) >> 20) * (uint32_t)G.nCols + (((uint32_t)(x - 3) * mag_w) >> 20));
       const unsigned long long order = (cell << 24) | (unsigned long long)(pay & 0xffffffu);
       const unsigned long long cmp = ((unsigned long long)(pay >> 24) << 48) | (0xffffffffffffull - order);
       if (cmp > best || e == p) { best = cmp; best_pay = pay; }
