@@ -111,35 +111,45 @@ resize_level_words_kernel(const __grid_constant__ ExtractParams P, int l) {
 
   int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};  // horizontally interpolated source rows rowB-1 and rowB, already >> 4
   int rowB = -1;
-  // source rows are consumed in order; two are kept in flight so that a destination row that
-  // advances by two source rows does not wait for a load issued a moment ago
-  uint32_t w0 = 0, w1 = 0, w2 = 0, n0 = 0, n1 = 0, n2 = 0;
+  // source rows are consumed in order from two register sets that alternate (no moves, which would
+  // wait for the load): the set just consumed is refilled with the row after next, so two rows stay
+  // in flight and a destination row that advances by two source rows does not wait for a fresh load
+  uint32_t wa0 = 0, wa1 = 0, wa2 = 0, wb0 = 0, wb1 = 0, wb2 = 0;
   auto request = [&](int sy, uint32_t& a, uint32_t& b, uint32_t& c) {
-    const uint32_t* p = wsrc + (size_t)sy * spw;
+    const uint32_t* p = wsrc + (size_t)min(sy, src_h - 1) * spw;
     a = __ldg(p);
     b = need1 ? __ldg(p + 1) : 0u;
     c = need2 ? __ldg(p + 2) : 0u;
   };
+  auto consume = [&](uint32_t w0, uint32_t w1, uint32_t w2) {
+    const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh);
+    const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) hA[k] = hB[k];
+    hB[0] = (int)(__dp2a_lo(coef[0], p01, 0u) >> 4);
+    hB[1] = (int)(__dp2a_hi(coef[1], p01, 0u) >> 4);
+    hB[2] = (int)(__dp2a_lo(coef[2], p23, 0u) >> 4);
+    hB[3] = (int)(__dp2a_hi(coef[3], p23, 0u) >> 4);
+  };
   const int y1 = min(y0 + kResizeStrip, D.h);
-  int next_src = __ldg(&P.rtab[D.ytab + y0]).x;
-  request(next_src, w0, w1, w2);
-  request(min(next_src + 1, src_h - 1), n0, n1, n2);
+  int next_src = __ldg(&P.rtab[D.ytab + y0]).x;  // source row held by the set that is consumed next
+  bool use_a = true;
+  request(next_src, wa0, wa1, wa2);
+  request(next_src + 1, wb0, wb1, wb2);
   for (int y = y0; y < y1; ++y) {
     const int4 t = __ldg(&P.rtab[D.ytab + y]);
     const int sy0 = t.x, sy1 = t.w, b0 = t.y, b1 = t.z;
     while (rowB < sy1) {  // sy1 is non-decreasing and advances by at most 2 per destination row
-      const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh);
+      if (use_a) {
+        consume(wa0, wa1, wa2);
+        request(next_src + 2, wa0, wa1, wa2);
+      } else {
+        consume(wb0, wb1, wb2);
+        request(next_src + 2, wb0, wb1, wb2);
+      }
+      use_a = !use_a;
       rowB = next_src;
-      next_src = min(next_src + 1, src_h - 1);
-      w0 = n0; w1 = n1; w2 = n2;
-      request(min(next_src + 1, src_h - 1), n0, n1, n2);
-      const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) hA[k] = hB[k];
-      hB[0] = (int)(__dp2a_lo(coef[0], p01, 0u) >> 4);
-      hB[1] = (int)(__dp2a_hi(coef[1], p01, 0u) >> 4);
-      hB[2] = (int)(__dp2a_lo(coef[2], p23, 0u) >> 4);
-      hB[3] = (int)(__dp2a_hi(coef[3], p23, 0u) >> 4);
+      ++next_src;
     }
     const bool same = sy0 == sy1;  // clamped rows at the top / bottom border
     uint32_t u[4];
