@@ -36,6 +36,28 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 // Selects the device; ORB_E_NO_DEVICE when there is none (no CPU fallback anywhere).
 int use_device(int device);
 
+// Per-thread, per-device scratch of the small host-buffer entry points (SearchByBoW, stereo search,
+// pairwise distances): a grow-only device buffer, a page-locked host mirror of the same size and a
+// stream, so a call is pack -> one H2D -> kernels -> one D2H -> one sync with no cudaMalloc/cudaFree
+// (which cost more than the work itself).  Re-entrant across threads, as the three SLAM threads need.
+struct CallScratch {
+  uint8_t* dev = nullptr;
+  uint8_t* host = nullptr;  // pinned
+  size_t cap = 0;
+  cudaStream_t stream = nullptr;
+};
+// Returns the calling thread's scratch for `device` with at least `bytes` in both buffers.
+int call_scratch(int device, size_t bytes, CallScratch** out);
+// Offsets of 256-byte aligned pieces inside one scratch block.
+struct Layout {
+  size_t bytes = 0;
+  size_t place(size_t n) {
+    const size_t at = bytes;
+    bytes = (bytes + n + 255) & ~(size_t)255;
+    return at;
+  }
+};
+
 #ifdef __CUDACC__
 #define ORB_HD __host__ __device__
 #else

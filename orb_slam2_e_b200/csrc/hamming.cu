@@ -158,11 +158,14 @@ __global__ void __launch_bounds__(256) popc_probe_kernel(uint32_t seed, int iter
 
 
 // ------------------------------------------------------------------------------------
-// SearchByBoW.  The distance work is data-parallel but the reference's greedy claim
-// (ORBmatcher.cc:410 / :777,804: a side-2 feature taken by an earlier side-1 feature is
-// skipped) makes the result depend on scan order, so one warp replays the reference order:
-// side-1 features sequentially, their node's side-2 candidates across the lanes, then a
-// warp top-2 merge on packed keys (distance << 16 | list position).
+// SearchByBoW.  The reference's greedy claim (ORBmatcher.cc:410 / :777,804: a side-2 feature taken
+// by an earlier side-1 feature is skipped) makes results depend on scan order -- but only inside a
+// vocabulary node: a feature belongs to exactly one node of a DBoW2 FeatureVector, so claims never
+// cross nodes.  One warp per common node therefore replays the reference order exactly (side-1
+// features sequentially, the node's side-2 candidates across the lanes, warp top-2 merge on packed
+// keys distance << 16 | list position) while the nodes run in parallel.  If a caller passes lists in
+// which a feature appears in two common nodes, the host launches a single warp that walks the
+// nodes in order instead.  The rotation histogram is global: atomics, then a one-warp finish kernel.
 struct BowPair { int o1, l1, o2, l2; };  // common node: ranges in idx1 / idx2
 
 __device__ __forceinline__ void warp_top2_merge(uint32_t& k1, uint32_t& k2) {
@@ -175,81 +178,87 @@ __device__ __forceinline__ void warp_top2_merge(uint32_t& k1, uint32_t& k2) {
   }
 }
 
-__global__ void __launch_bounds__(32)
-bow_search_kernel(const uint4* __restrict__ desc1, const uint4* __restrict__ desc2, const BowPair* __restrict__ pairs,
-                  int n_pairs, const uint32_t* __restrict__ idx1, const uint32_t* __restrict__ idx2,
-                  const uint8_t* __restrict__ valid1, const uint8_t* __restrict__ valid2,
-                  const float* __restrict__ ang1, const float* __restrict__ ang2, float ratio, int check_ori,
-                  int kf_kf, int n_out, uint8_t* __restrict__ claimed2, int* __restrict__ out,
-                  uint8_t* __restrict__ bin_of, int* __restrict__ n_matches) {
-  const int lane = threadIdx.x;
-  __shared__ int hist[ORBM_HISTO_LENGTH];
-  for (int i = lane; i < ORBM_HISTO_LENGTH; i += 32) hist[i] = 0;
-  for (int i = lane; i < n_out; i += 32) out[i] = -1;
-  __syncwarp();
+struct BowArgs {
+  const uint4* desc1; const uint4* desc2;
+  const BowPair* pairs; int n_pairs;
+  const uint32_t* idx1; const uint32_t* idx2;
+  const uint8_t* valid1; const uint8_t* valid2;  // valid2 may be null
+  const float* ang1; const float* ang2;
+  float ratio; int check_ori, kf_kf, n_out;
+  uint8_t* claimed2; int* out; uint8_t* bin_of;
+  int* hist;       // [ORBM_HISTO_LENGTH]
+  int* n_matches;  // accepted matches (before the orientation filter)
+};
+
+__global__ void __launch_bounds__(128) bow_node_kernel(const BowArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), n_warps = gridDim.x * (blockDim.x >> 5);
   int nm = 0;
-  for (int p = 0; p < n_pairs; ++p) {
-    const BowPair pr = pairs[p];
+  for (int p = warp; p < A.n_pairs; p += n_warps) {
+    const BowPair pr = A.pairs[p];
     for (int a = 0; a < pr.l1; ++a) {
-      const int i1 = (int)idx1[pr.o1 + a];
-      if (!valid1[i1]) continue;
-      const uint4 qa = desc1[2 * i1], qb = desc1[2 * i1 + 1];
+      const int i1 = (int)A.idx1[pr.o1 + a];
+      if (!A.valid1[i1]) continue;
+      const uint4 qa = A.desc1[2 * i1], qb = A.desc1[2 * i1 + 1];
       const uint32_t q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
       uint32_t k1 = 256u << 16, k2 = 256u << 16;
       for (int b = lane; b < pr.l2; b += 32) {
-        const int i2 = (int)idx2[pr.o2 + b];
-        if (claimed2[i2]) continue;
-        if (valid2 && !valid2[i2]) continue;
-        const uint32_t key = ((uint32_t)hamming8(q, desc2[2 * i2], desc2[2 * i2 + 1]) << 16) | (uint32_t)b;
+        const int i2 = (int)A.idx2[pr.o2 + b];
+        if (A.claimed2[i2]) continue;
+        if (A.valid2 && !A.valid2[i2]) continue;
+        const uint32_t key = ((uint32_t)hamming8(q, A.desc2[2 * i2], A.desc2[2 * i2 + 1]) << 16) | (uint32_t)b;
         const uint32_t hi = max(key, k1);
         k1 = min(key, k1);
         k2 = min(k2, hi);
       }
       warp_top2_merge(k1, k2);
       const int best1 = (int)(k1 >> 16), best2 = min((int)(k2 >> 16), 256);
-      const bool th_ok = kf_kf ? (best1 < ORBM_TH_LOW) : (best1 <= ORBM_TH_LOW);
-      if (best1 < 256 && th_ok && (float)best1 < ratio * (float)best2) {  // uniform across the warp
-        const int i2 = (int)idx2[pr.o2 + (int)(k1 & 0xffffu)];
+      const bool th_ok = A.kf_kf ? (best1 < ORBM_TH_LOW) : (best1 <= ORBM_TH_LOW);
+      if (best1 < 256 && th_ok && (float)best1 < A.ratio * (float)best2) {  // uniform across the warp
+        const int i2 = (int)A.idx2[pr.o2 + (int)(k1 & 0xffffu)];
         if (lane == 0) {
-          claimed2[i2] = 1;
-          const int slot = kf_kf ? i1 : i2;
-          out[slot] = kf_kf ? i2 : i1;
-          if (check_ori) {
-            float rot = ang1[i1] - ang2[i2];
+          A.claimed2[i2] = 1;
+          const int slot = A.kf_kf ? i1 : i2;
+          A.out[slot] = A.kf_kf ? i2 : i1;
+          if (A.check_ori) {
+            float rot = A.ang1[i1] - A.ang2[i2];
             if (rot < 0.0f) rot += 360.0f;
             int bin = (int)roundf(rot * (1.0f / ORBM_HISTO_LENGTH));
             if (bin == ORBM_HISTO_LENGTH) bin = 0;
-            bin_of[slot] = (uint8_t)bin;
-            hist[bin] += 1;
+            A.bin_of[slot] = (uint8_t)bin;
+            atomicAdd(&A.hist[bin], 1);
           }
         }
         ++nm;
-        __syncwarp();
+        __syncwarp();  // the claim is visible to the lanes' next candidate scan
       }
     }
   }
-  __syncwarp();
-  if (check_ori) {
-    // ComputeThreeMaxima, ORBmatcher.cc:1802-1843
-    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-    for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
-      const int s = hist[i];
-      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
-      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
-      else if (s > max3) { max3 = s; ind3 = i; }
-    }
-    if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
-    else if ((float)max3 < 0.1f * (float)max1) ind3 = -1;
-    int dropped = 0;
-    for (int i = lane; i < n_out; i += 32) {
-      if (out[i] < 0) continue;
-      const int b = bin_of[i];
-      if (b != ind1 && b != ind2 && b != ind3) { out[i] = -1; ++dropped; }
-    }
-    for (int s = 16; s > 0; s >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, s);
-    nm -= dropped;
+  if (lane == 0 && nm) atomicAdd(A.n_matches, nm);
+}
+
+// ComputeThreeMaxima (ORBmatcher.cc:1802-1843) and the removal of matches outside the three
+// dominant rotation bins (:468-486).  One warp.
+__global__ void __launch_bounds__(32) bow_finish_kernel(const int* __restrict__ hist, int* __restrict__ out,
+                                                        const uint8_t* __restrict__ bin_of, int n_out, int* __restrict__ n_matches) {
+  const int lane = threadIdx.x;
+  int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+  for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
+    const int s = hist[i];
+    if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+    else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+    else if (s > max3) { max3 = s; ind3 = i; }
   }
-  if (lane == 0) *n_matches = nm;
+  if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+  else if ((float)max3 < 0.1f * (float)max1) ind3 = -1;
+  int dropped = 0;
+  for (int i = lane; i < n_out; i += 32) {
+    if (out[i] < 0) continue;
+    const int b = bin_of[i];
+    if (b != ind1 && b != ind2 && b != ind3) { out[i] = -1; ++dropped; }
+  }
+  for (int s = 16; s > 0; s >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, s);
+  if (lane == 0) *n_matches -= dropped;
 }
 
 // ------------------------------------------------------------------------------------
@@ -351,14 +360,20 @@ int orbm_hamming_pairs(int device, const uint8_t* a, const uint8_t* b, int n, in
   if (n == 0) return ORB_OK;
   int rc = use_device(device);
   if (rc) return rc;
-  DevBuf<uint4> da, db;
-  DevBuf<int> dout;
-  if ((rc = da.reserve((size_t)n * 2)) || (rc = db.reserve((size_t)n * 2)) || (rc = dout.reserve(n))) return rc;
-  ORB_CUDA_TRY(cudaMemcpy(da.p, a, (size_t)n * 32, cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(db.p, b, (size_t)n * 32, cudaMemcpyHostToDevice));
-  hamming_pairs_kernel<<<div_up(n, 256), 256>>>(da.p, db.p, n, dout.p);
+  // per-thread scratch: pack -> one upload -> kernel -> one download -> one sync
+  Layout L;
+  const size_t o_a = L.place((size_t)n * 32), o_b = L.place((size_t)n * 32), o_out = L.place((size_t)n * 4);
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  memcpy(S->host + o_a, a, (size_t)n * 32);
+  memcpy(S->host + o_b, b, (size_t)n * 32);
+  ORB_CUDA_TRY(cudaMemcpyAsync(S->dev, S->host, o_out, cudaMemcpyHostToDevice, S->stream));
+  hamming_pairs_kernel<<<div_up(n, 256), 256, 0, S->stream>>>((const uint4*)(S->dev + o_a), (const uint4*)(S->dev + o_b), n,
+                                                             (int*)(S->dev + o_out));
   ORB_LAUNCH_CHECK();
-  ORB_CUDA_TRY(cudaMemcpy(out, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpyAsync(S->host + o_out, S->dev + o_out, (size_t)n * 4, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  memcpy(out, S->host + o_out, (size_t)n * 4);
   return ORB_OK;
 }
 
@@ -549,14 +564,34 @@ int orbm_search_bow(int device, const uint8_t* desc1, int n1, const uint8_t* des
   const int n_out = kf_kf ? n1 : n2;
   *n_matches = 0;
   for (int i = 0; i < n_out; ++i) out[i] = -1;
+  if (n1 == 0 || n2 == 0 || fv1->n_nodes == 0 || fv2->n_nodes == 0) return ORB_OK;
+  const int ni1 = fv1->off[fv1->n_nodes], ni2 = fv2->off[fv2->n_nodes];
+  int rc = use_device(device);
+  if (rc) return rc;
+  Layout L;
+  const int max_pairs = std::min(fv1->n_nodes, fv2->n_nodes);
+  // upload block
+  const size_t o_d1 = L.place((size_t)n1 * 32), o_d2 = L.place((size_t)n2 * 32),
+               o_pairs = L.place((size_t)max_pairs * sizeof(BowPair)), o_i1 = L.place((size_t)ni1 * 4),
+               o_i2 = L.place((size_t)ni2 * 4), o_v1 = L.place(n1), o_v2 = L.place(n2), o_a1 = L.place((size_t)n1 * 4),
+               o_a2 = L.place((size_t)n2 * 4), o_claim = L.place(n2), o_hist = L.place(ORBM_HISTO_LENGTH * 4),
+               o_bin = L.place(n_out);
+  // download block (initialised on the host, so it is uploaded too)
+  const size_t o_out = L.place((size_t)n_out * 4), o_nm = L.place(4), o_end = L.bytes;
+  // host-only flags for the one-node-per-feature check
+  const size_t o_seen = L.place((size_t)std::max(n1, n2));
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  uint8_t* h = S->host;
+
   // ordered-map merge of the two node lists (ORBmatcher.cc:381-465) -> common-node ranges
-  std::vector<BowPair> pairs;
-  int a = 0, b = 0;
-  while (a < fv1->n_nodes && b < fv2->n_nodes) {
+  BowPair* pairs = reinterpret_cast<BowPair*>(h + o_pairs);
+  int n_pairs = 0;
+  for (int a = 0, b = 0; a < fv1->n_nodes && b < fv2->n_nodes;) {
     if (fv1->node[a] == fv2->node[b]) {
-      BowPair p{fv1->off[a], fv1->off[a + 1] - fv1->off[a], fv2->off[b], fv2->off[b + 1] - fv2->off[b]};
+      const BowPair p{fv1->off[a], fv1->off[a + 1] - fv1->off[a], fv2->off[b], fv2->off[b + 1] - fv2->off[b]};
       if (p.l2 > 65535) return set_error(ORB_E_INVALID, "orbm_search_bow: node with more than 65535 features");
-      pairs.push_back(p);
+      pairs[n_pairs++] = p;
       ++a; ++b;
     } else if (fv1->node[a] < fv2->node[b]) {
       a = (int)(std::lower_bound(fv1->node + a, fv1->node + fv1->n_nodes, fv2->node[b]) - fv1->node);
@@ -564,42 +599,65 @@ int orbm_search_bow(int device, const uint8_t* desc1, int n1, const uint8_t* des
       b = (int)(std::lower_bound(fv2->node + b, fv2->node + fv2->n_nodes, fv1->node[a]) - fv2->node);
     }
   }
-  if (pairs.empty() || n1 == 0 || n2 == 0) return ORB_OK;
-  int rc = use_device(device);
-  if (rc) return rc;
-  const int ni1 = fv1->off[fv1->n_nodes], ni2 = fv2->off[fv2->n_nodes];
-  // one packed upload
-  size_t o = 0;
-  auto place = [&](size_t bytes) { size_t at = o; o = align_up<size_t>(o + bytes, 256); return at; };
-  const size_t o_d1 = place((size_t)n1 * 32), o_d2 = place((size_t)n2 * 32), o_pairs = place(pairs.size() * sizeof(BowPair)),
-               o_i1 = place((size_t)ni1 * 4), o_i2 = place((size_t)ni2 * 4), o_v1 = place(n1), o_v2 = place(n2),
-               o_a1 = place((size_t)n1 * 4), o_a2 = place((size_t)n2 * 4), o_claim = place(n2), o_out = place((size_t)n_out * 4),
-               o_bin = place(n_out), o_nm = place(4);
-  std::vector<uint8_t> host(o, 0);
-  memcpy(&host[o_d1], desc1, (size_t)n1 * 32);
-  memcpy(&host[o_d2], desc2, (size_t)n2 * 32);
-  memcpy(&host[o_pairs], pairs.data(), pairs.size() * sizeof(BowPair));
-  memcpy(&host[o_i1], fv1->idx, (size_t)ni1 * 4);
-  memcpy(&host[o_i2], fv2->idx, (size_t)ni2 * 4);
-  memcpy(&host[o_v1], valid1, n1);
-  if (valid2) memcpy(&host[o_v2], valid2, n2);
-  if (angle1) memcpy(&host[o_a1], angle1, (size_t)n1 * 4);
-  if (angle2) memcpy(&host[o_a2], angle2, (size_t)n2 * 4);
+  if (n_pairs == 0) return ORB_OK;
   for (int i = 0; i < ni1; ++i)
     if (fv1->idx[i] >= (uint32_t)n1) return set_error(ORB_E_INVALID, "orbm_search_bow: feature index out of range");
   for (int i = 0; i < ni2; ++i)
     if (fv2->idx[i] >= (uint32_t)n2) return set_error(ORB_E_INVALID, "orbm_search_bow: feature index out of range");
-  DevBuf<uint8_t> dev;
-  if ((rc = dev.reserve(o))) return rc;
-  uint8_t* d = dev.p;
-  ORB_CUDA_TRY(cudaMemcpy(d, host.data(), o, cudaMemcpyHostToDevice));
-  bow_search_kernel<<<1, 32>>>((const uint4*)(d + o_d1), (const uint4*)(d + o_d2), (const BowPair*)(d + o_pairs),
-                               (int)pairs.size(), (const uint32_t*)(d + o_i1), (const uint32_t*)(d + o_i2), d + o_v1,
-                               valid2 ? d + o_v2 : nullptr, (const float*)(d + o_a1), (const float*)(d + o_a2), nnratio,
-                               check_orientation, kf_kf, n_out, d + o_claim, (int*)(d + o_out), d + o_bin, (int*)(d + o_nm));
+  // Nodes may run in parallel only if no feature sits in two common nodes (always true for a DBoW2
+  // FeatureVector; checked because the ABI takes arbitrary lists).
+  bool disjoint = true;
+  for (int side = 0; side < 2 && disjoint; ++side) {
+    const int n = side ? n2 : n1;
+    const uint32_t* idx = side ? fv2->idx : fv1->idx;
+    uint8_t* seen = h + o_seen;
+    memset(seen, 0, (size_t)n);
+    for (int p = 0; p < n_pairs && disjoint; ++p) {
+      const int o = side ? pairs[p].o2 : pairs[p].o1, l = side ? pairs[p].l2 : pairs[p].l1;
+      for (int i = 0; i < l; ++i) {
+        uint8_t& f = seen[idx[o + i]];
+        if (f) { disjoint = false; break; }
+        f = 1;
+      }
+    }
+  }
+
+  memcpy(h + o_d1, desc1, (size_t)n1 * 32);
+  memcpy(h + o_d2, desc2, (size_t)n2 * 32);
+  memcpy(h + o_i1, fv1->idx, (size_t)ni1 * 4);
+  memcpy(h + o_i2, fv2->idx, (size_t)ni2 * 4);
+  memcpy(h + o_v1, valid1, n1);
+  if (valid2) memcpy(h + o_v2, valid2, n2);
+  if (check_orientation) {
+    memcpy(h + o_a1, angle1, (size_t)n1 * 4);
+    memcpy(h + o_a2, angle2, (size_t)n2 * 4);
+  }
+  memset(h + o_claim, 0, (size_t)n2);
+  memset(h + o_hist, 0, ORBM_HISTO_LENGTH * 4);
+  memset(h + o_out, 0xff, (size_t)n_out * 4);  // -1
+  memset(h + o_nm, 0, 4);
+  uint8_t* d = S->dev;
+  ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_end, cudaMemcpyHostToDevice, S->stream));
+  BowArgs A;
+  A.desc1 = (const uint4*)(d + o_d1); A.desc2 = (const uint4*)(d + o_d2);
+  A.pairs = (const BowPair*)(d + o_pairs); A.n_pairs = n_pairs;
+  A.idx1 = (const uint32_t*)(d + o_i1); A.idx2 = (const uint32_t*)(d + o_i2);
+  A.valid1 = d + o_v1; A.valid2 = valid2 ? d + o_v2 : nullptr;
+  A.ang1 = (const float*)(d + o_a1); A.ang2 = (const float*)(d + o_a2);
+  A.ratio = nnratio; A.check_ori = check_orientation; A.kf_kf = kf_kf; A.n_out = n_out;
+  A.claimed2 = d + o_claim; A.out = (int*)(d + o_out); A.bin_of = d + o_bin;
+  A.hist = (int*)(d + o_hist); A.n_matches = (int*)(d + o_nm);
+  if (disjoint) bow_node_kernel<<<div_up(n_pairs, 4), 128, 0, S->stream>>>(A);
+  else bow_node_kernel<<<1, 32, 0, S->stream>>>(A);  // one warp walks the nodes in order
   ORB_LAUNCH_CHECK();
-  ORB_CUDA_TRY(cudaMemcpy(out, d + o_out, (size_t)n_out * 4, cudaMemcpyDeviceToHost));
-  ORB_CUDA_TRY(cudaMemcpy(n_matches, d + o_nm, 4, cudaMemcpyDeviceToHost));
+  if (check_orientation) {
+    bow_finish_kernel<<<1, 32, 0, S->stream>>>(A.hist, A.out, A.bin_of, n_out, A.n_matches);
+    ORB_LAUNCH_CHECK();
+  }
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_out, d + o_out, o_end - o_out, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  memcpy(out, h + o_out, (size_t)n_out * 4);
+  memcpy(n_matches, h + o_nm, 4);
   return ORB_OK;
 }
 
@@ -616,25 +674,30 @@ int orbm_stereo_search(int device, const orbx_keypoint* left, const uint8_t* lde
       return set_error(ORB_E_INVALID, "orbm_stereo_search: right keypoint %d has octave %d", i, right[i].octave);
   int rc = use_device(device);
   if (rc) return rc;
-  DevBuf<orbx_keypoint> dl, dr;
-  DevBuf<uint4> ddl, ddr;
-  DevBuf<float> ds;
-  DevBuf<int> dres;
-  if ((rc = dl.reserve(nl)) || (rc = dr.reserve(std::max(nr, 1))) || (rc = ddl.reserve((size_t)nl * 2)) ||
-      (rc = ddr.reserve((size_t)std::max(nr, 1) * 2)) || (rc = ds.reserve(n_levels)) || (rc = dres.reserve((size_t)nl * 2)))
-    return rc;
-  ORB_CUDA_TRY(cudaMemcpy(dl.p, left, (size_t)nl * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
-  ORB_CUDA_TRY(cudaMemcpy(ddl.p, ldesc, (size_t)nl * 32, cudaMemcpyHostToDevice));
+  Layout L;
+  const size_t o_l = L.place((size_t)nl * sizeof(orbx_keypoint)), o_r = L.place((size_t)nr * sizeof(orbx_keypoint)),
+               o_dl = L.place((size_t)nl * 32), o_dr = L.place((size_t)nr * 32), o_s = L.place((size_t)n_levels * 4),
+               o_res = L.place((size_t)nl * 8);
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  uint8_t *h = S->host, *d = S->dev;
+  memcpy(h + o_l, left, (size_t)nl * sizeof(orbx_keypoint));
+  memcpy(h + o_dl, ldesc, (size_t)nl * 32);
   if (nr) {
-    ORB_CUDA_TRY(cudaMemcpy(dr.p, right, (size_t)nr * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
-    ORB_CUDA_TRY(cudaMemcpy(ddr.p, rdesc, (size_t)nr * 32, cudaMemcpyHostToDevice));
+    memcpy(h + o_r, right, (size_t)nr * sizeof(orbx_keypoint));
+    memcpy(h + o_dr, rdesc, (size_t)nr * 32);
   }
-  ORB_CUDA_TRY(cudaMemcpy(ds.p, scale_factors, (size_t)n_levels * 4, cudaMemcpyHostToDevice));
-  stereo_search_kernel<<<div_up(nl, 4), 128>>>(dl.p, ddl.p, nl, dr.p, ddr.p, nr, ds.p, n_rows, min_d, max_d, dres.p,
-                                               dres.p + nl);
+  memcpy(h + o_s, scale_factors, (size_t)n_levels * 4);
+  ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_res, cudaMemcpyHostToDevice, S->stream));
+  int* res = (int*)(d + o_res);
+  stereo_search_kernel<<<div_up(nl, 4), 128, 0, S->stream>>>((const orbx_keypoint*)(d + o_l), (const uint4*)(d + o_dl), nl,
+                                                             (const orbx_keypoint*)(d + o_r), (const uint4*)(d + o_dr), nr,
+                                                             (const float*)(d + o_s), n_rows, min_d, max_d, res, res + nl);
   ORB_LAUNCH_CHECK();
-  ORB_CUDA_TRY(cudaMemcpy(best_idx, dres.p, (size_t)nl * 4, cudaMemcpyDeviceToHost));
-  ORB_CUDA_TRY(cudaMemcpy(best_dist, dres.p + nl, (size_t)nl * 4, cudaMemcpyDeviceToHost));
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_res, res, (size_t)nl * 8, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  memcpy(best_idx, h + o_res, (size_t)nl * 4);
+  memcpy(best_dist, h + o_res + (size_t)nl * 4, (size_t)nl * 4);
   return ORB_OK;
 }
 

@@ -31,6 +31,39 @@ int use_device(int device) {
   return ORB_OK;
 }
 
+namespace {
+constexpr int kMaxScratchDevices = 16;
+struct ThreadScratch {
+  CallScratch s[kMaxScratchDevices];
+  ~ThreadScratch() {  // thread exit; at process teardown the context may be gone already: ignore errors
+    for (CallScratch& c : s) {
+      if (c.dev) cudaFree(c.dev);
+      if (c.host) cudaFreeHost(c.host);
+      if (c.stream) cudaStreamDestroy(c.stream);
+    }
+    cudaGetLastError();
+  }
+};
+thread_local ThreadScratch t_scratch;
+}  // namespace
+
+int call_scratch(int device, size_t bytes, CallScratch** out) {
+  if (device < 0 || device >= kMaxScratchDevices) return set_error(ORB_E_INVALID, "device %d: at most %d devices", device, kMaxScratchDevices);
+  CallScratch& c = t_scratch.s[device];
+  if (!c.stream) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  if (bytes > c.cap) {
+    const size_t want = align_up<size_t>(bytes + bytes / 2, 1 << 16);
+    if (c.dev) cudaFree(c.dev);
+    if (c.host) cudaFreeHost(c.host);
+    c.dev = nullptr; c.host = nullptr; c.cap = 0;
+    ORB_CUDA_TRY(cudaMalloc(&c.dev, want));
+    ORB_CUDA_TRY(cudaMallocHost(&c.host, want));
+    c.cap = want;
+  }
+  *out = &c;
+  return ORB_OK;
+}
+
 }  // namespace orbfront
 
 extern "C" {
