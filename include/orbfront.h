@@ -208,6 +208,56 @@ int orbm_stereo_search(int device, const orbx_keypoint* left, const uint8_t* lde
                        const float* scale_factors, int n_levels, int n_rows, float min_d, float max_d,
                        int32_t* best_idx, int32_t* best_dist);
 
+/* ---- Windowed projection searches -------------------------------------------
+ * One primitive behind the five ORBmatcher::SearchByProjection overloads (src/ORBmatcher.cc:46-132,
+ * :134-220, :491-604, :1529-1671, :1673-1800): for every projected query, gather the keypoints of
+ * a frame inside a square window through the frame's cell grid (Frame::GetFeaturesInArea,
+ * src/Frame.cc:342-395; KeyFrame::GetFeaturesInArea, src/KeyFrame.cc:613-652), keep the best and
+ * second-best Hamming distance in the reference's scan order, apply its acceptance rule, and
+ * -- as the reference does by writing mvpMapPoints inside the loop -- let an accepted match hide
+ * its keypoint from every LATER query.  The caller projects (pose, camera and MapPoint state stay
+ * on its side) and passes flat queries in the reference's loop order. */
+typedef struct orbm_grid_frame { /* the searched Frame / KeyFrame; all host memory */
+  const float* x;          /* n: mvKeysUn[i].pt.x */
+  const float* y;          /* n: mvKeysUn[i].pt.y */
+  const int32_t* octave;   /* n: mvKeysUn[i].octave */
+  const float* u_right;    /* n: mvuRight[i], or NULL (monocular: treated as -1) */
+  const uint8_t* desc;     /* n x 32: mDescriptors */
+  int32_t n;
+  float min_x, min_y;           /* mnMinX, mnMinY */
+  float width_inv, height_inv;  /* mfGridElementWidthInv, mfGridElementHeightInv */
+  int32_t cols, rows;           /* FRAME_GRID_COLS x FRAME_GRID_ROWS (64 x 48) or mnGridCols x mnGridRows */
+  const int32_t* cell_off;      /* cols*rows + 1: cell (ix, iy) is entries [off[ix*rows+iy], off[ix*rows+iy+1]) */
+  const uint32_t* cell_idx;     /* mGrid[ix][iy] flattened; a keypoint may appear in at most one cell */
+} orbm_grid_frame;
+
+typedef struct orbm_window_query {
+  float x, y, r;        /* GetFeaturesInArea(x, y, r, min_level, max_level) */
+  float u_right;        /* predicted right-image coordinate of the query */
+  float er_max;         /* a keypoint with mvuRight > 0 is skipped when fabs(u_right - mvuRight) > er_max;
+                           negative: no stereo check */
+  int32_t min_level, max_level; /* as GetFeaturesInArea: filter iff min_level > 0 || max_level >= 0 */
+  int32_t blocks;       /* nonzero: once accepted, the matched keypoint is hidden from later queries
+                           (the reference's `mvpMapPoints[idx] && Observations() > 0` test) */
+} orbm_window_query;
+
+typedef struct orbm_window_result {
+  int32_t idx;          /* matched keypoint (index into the frame), or -1 when not accepted */
+  int32_t best_idx;     /* best keypoint of the scan even if rejected, -1 if the window was empty */
+  int32_t best_dist, best_dist2;  /* 256 when absent */
+  int32_t best_level, best_level2; /* -1 when absent */
+} orbm_window_result;
+
+/* claimed: n flags (keypoints hidden from every query, e.g. mvpMapPoints already set) or NULL.
+ * Acceptance: best_dist <= th, and, when ratio > 0, not (best_level == best_level2 &&
+ * best_dist > ratio * best_dist2)  (src/ORBmatcher.cc:119-123).  ratio <= 0: distance test only
+ * (:1622, :1759, :595).  claim = 0: accepted matches never hide keypoints (:180-181, separate
+ * output vector).  out has nq entries; *n_accepted counts idx >= 0; *rounds (may be NULL) reports
+ * how many parallel passes the order-exact resolution took. */
+int orbm_window_search(int device, const orbm_grid_frame* frame, const orbm_window_query* queries,
+                       const uint8_t* query_desc, int nq, const uint8_t* claimed, int th, float ratio,
+                       int claim, orbm_window_result* out, int* n_accepted, int* rounds);
+
 /* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
  * denominator of the matching roofline.  Returns 32-bit POPC per second. */
 int orbm_popc_peak(int device, double* popc_per_s);

@@ -9,9 +9,12 @@
 //   search_bow_kf_kf    ORBmatcher.cc:723-856
 //   three_maxima        ORBmatcher.cc:1802-1843
 //   stereo_search       Frame.cc:527-610 (descriptor part of ComputeStereoMatches)
+//   features_in_area    Frame.cc:342-395 (GetFeaturesInArea)
+//   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
 // Parity status: unpinned by the reference (it ships no tests); pinned here by
 // known-answer vectors in tests/test_oracle_match.py (numpy popcount cross-check).
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -197,6 +200,94 @@ static inline void merge_top2(const int* d1, const long long* i1, const int* d2,
     }
     od1[q] = t.best1; oi1[q] = t.idx; od2[q] = t.best2;
   }
+}
+
+// ---- Windowed projection search ---------------------------------------------
+// Flat-array restatement of the loop shared by the SearchByProjection overloads.  The searched
+// frame is given as the reference holds it: keypoints, mvuRight, descriptors and the cell grid
+// (cell (ix, iy) at ix*rows+iy).
+struct GridFrame {
+  const float* x; const float* y; const int* octave; const float* u_right; const uint8_t* desc; int n;
+  float min_x, min_y, width_inv, height_inv; int cols, rows;
+  const int* cell_off; const uint32_t* cell_idx;
+};
+
+// Frame::GetFeaturesInArea, Frame.cc:342-395 (KeyFrame.cc:613-652 is the same without levels).
+static inline void features_in_area(const GridFrame& F, float x, float y, float r, int minLevel, int maxLevel,
+                                    std::vector<int>& vIndices) {
+  vIndices.clear();
+  const int nMinCellX = std::max(0, (int)floor((x - F.min_x - r) * F.width_inv));
+  if (nMinCellX >= F.cols) return;
+  const int nMaxCellX = std::min(F.cols - 1, (int)ceil((x - F.min_x + r) * F.width_inv));
+  if (nMaxCellX < 0) return;
+  const int nMinCellY = std::max(0, (int)floor((y - F.min_y - r) * F.height_inv));
+  if (nMinCellY >= F.rows) return;
+  const int nMaxCellY = std::min(F.rows - 1, (int)ceil((y - F.min_y + r) * F.height_inv));
+  if (nMaxCellY < 0) return;
+  const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+  for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+    for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+      const int c = ix * F.rows + iy;
+      for (int j = F.cell_off[c]; j < F.cell_off[c + 1]; j++) {
+        const int k = (int)F.cell_idx[j];
+        if (bCheckLevels) {
+          if (F.octave[k] < minLevel) continue;
+          if (maxLevel >= 0)
+            if (F.octave[k] > maxLevel) continue;
+        }
+        const float distx = F.x[k] - x;
+        const float disty = F.y[k] - y;
+        if (fabs(distx) < r && fabs(disty) < r) vIndices.push_back(k);
+      }
+    }
+  }
+}
+
+struct WindowQuery { float x, y, r, u_right, er_max; int min_level, max_level, blocks; };
+struct WindowResult { int idx, best_idx, best_dist, best_dist2, best_level, best_level2; };
+
+// The query loop of ORBmatcher.cc:52-129 (best + second, level-aware ratio rule), which with
+// ratio <= 0 is the best-only loop of :1553-1640, :1687-1775 and :511-601.  `hidden[k]` plays
+// mvpMapPoints[k] (with Observations() > 0): set before the call for keypoints already matched,
+// and set by an accepted query whose MapPoint blocks (claim mode).
+static inline int window_search(const GridFrame& F, const WindowQuery* q, const uint8_t* qdesc, int nq,
+                                const uint8_t* claimed, int th, float ratio, bool claim, WindowResult* out) {
+  std::vector<uint8_t> hidden(F.n, 0);
+  if (claimed) for (int k = 0; k < F.n; ++k) hidden[k] = claimed[k] != 0;
+  std::vector<int> vIndices;
+  int nmatches = 0;
+  for (int i = 0; i < nq; ++i) {
+    const WindowQuery& Q = q[i];
+    features_in_area(F, Q.x, Q.y, Q.r, Q.min_level, Q.max_level, vIndices);
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (size_t v = 0; v < vIndices.size(); ++v) {
+      const int idx = vIndices[v];
+      if (hidden[idx]) continue;  // :81-83
+      if (Q.er_max >= 0 && F.u_right && F.u_right[idx] > 0) {  // :85-90
+        const float er = fabs(Q.u_right - F.u_right[idx]);
+        if (er > Q.er_max) continue;
+      }
+      const int dist = hamming256(qdesc + 32 * (size_t)i, F.desc + 32 * (size_t)idx);
+      if (dist < bestDist) {  // :97-110
+        bestDist2 = bestDist; bestDist = dist;
+        bestLevel2 = bestLevel; bestLevel = F.octave[idx];
+        bestIdx = idx;
+      } else if (dist < bestDist2) {
+        bestLevel2 = F.octave[idx];
+        bestDist2 = dist;
+      }
+    }
+    WindowResult R{-1, bestIdx, bestDist, bestDist2, bestLevel, bestLevel2};
+    if (bestIdx >= 0 && bestDist <= th) {  // :114-126
+      if (!(ratio > 0 && bestLevel == bestLevel2 && bestDist > ratio * bestDist2)) {
+        R.idx = bestIdx;
+        if (claim && Q.blocks) hidden[bestIdx] = 1;
+        nmatches++;
+      }
+    }
+    out[i] = R;
+  }
+  return nmatches;
 }
 
 }  // namespace matchport

@@ -151,4 +151,12 @@ void orc_stereo_search(const float* lx, const float* ly, const int* loct, const 
                        const float* scale_factors, int n_rows, float min_d, float max_d, int* best_idx, int* best_dist) {
   matchport::stereo_search(lx, ly, loct, ldesc, nl, rx, ry, roct, rdesc, nr, scale_factors, n_rows, min_d, max_d, best_idx, best_dist);
 }
+int orc_window_search(const float* x, const float* y, const int* octave, const float* u_right, const uint8_t* desc, int n,
+                      float min_x, float min_y, float width_inv, float height_inv, int cols, int rows,
+                      const int* cell_off, const uint32_t* cell_idx, const void* queries, const uint8_t* qdesc, int nq,
+                      const uint8_t* claimed, int th, float ratio, int claim, void* out) {
+  matchport::GridFrame F{x, y, octave, u_right, desc, n, min_x, min_y, width_inv, height_inv, cols, rows, cell_off, cell_idx};
+  return matchport::window_search(F, (const matchport::WindowQuery*)queries, qdesc, nq, claimed, th, ratio, claim != 0,
+                                  (matchport::WindowResult*)out);
+}
 }

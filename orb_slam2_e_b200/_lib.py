@@ -14,6 +14,10 @@ ORB_OK, ORB_E_INVALID, ORB_E_NO_DEVICE, ORB_E_CUDA, ORB_E_CAPACITY, ORB_E_STATE 
 KEYPOINT_DTYPE = np.dtype([("x", "f4"), ("y", "f4"), ("size", "f4"), ("angle", "f4"), ("response", "f4"),
                            ("octave", "i4"), ("class_id", "i4")])
 TOP2_DTYPE = np.dtype([("best1", "i4"), ("best2", "i4"), ("idx", "i8")])
+WINDOW_QUERY_DTYPE = np.dtype([("x", "f4"), ("y", "f4"), ("r", "f4"), ("u_right", "f4"), ("er_max", "f4"),
+                               ("min_level", "i4"), ("max_level", "i4"), ("blocks", "i4")])
+WINDOW_RESULT_DTYPE = np.dtype([("idx", "i4"), ("best_idx", "i4"), ("best_dist", "i4"), ("best_dist2", "i4"),
+                                ("best_level", "i4"), ("best_level2", "i4")])
 
 
 class OrbFrontError(RuntimeError):
@@ -30,6 +34,13 @@ class OrbxConfig(C.Structure):
 
 class FeatVec(C.Structure):
     _fields_ = [("node", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p), ("n_nodes", C.c_int32)]
+
+
+class GridFrame(C.Structure):  # orbm_grid_frame
+    _fields_ = [("x", C.c_void_p), ("y", C.c_void_p), ("octave", C.c_void_p), ("u_right", C.c_void_p),
+                ("desc", C.c_void_p), ("n", C.c_int32), ("min_x", C.c_float), ("min_y", C.c_float),
+                ("width_inv", C.c_float), ("height_inv", C.c_float), ("cols", C.c_int32), ("rows", C.c_int32),
+                ("cell_off", C.c_void_p), ("cell_idx", C.c_void_p)]
 
 
 _lib = None
@@ -75,6 +86,7 @@ SIGNATURES = {
     "orbm_search_bow": (_i, [_i, _vp, _i, _vp, _i, C.POINTER(FeatVec), C.POINTER(FeatVec), _vp, _vp, _vp, _vp, _f,
                              _i, _i, _vp, _ip]),
     "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),
+    "orbm_window_search": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _i, _f, _i, _vp, _ip, _ip]),
     "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),
 }
 

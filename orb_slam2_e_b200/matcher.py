@@ -12,7 +12,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import FeatVec, TOP2_DTYPE, check, ptr
+from ._lib import FeatVec, GridFrame, TOP2_DTYPE, WINDOW_QUERY_DTYPE, WINDOW_RESULT_DTYPE, check, ptr
 
 TH_HIGH, TH_LOW, HISTO_LENGTH = 95, 45, 30  # ORBmatcher.cc:37-40
 
@@ -120,6 +120,63 @@ class ORBmatcher:
         check(_lib.load().orbm_stereo_search(self.device, ptr(kl), ptr(dl), len(kl), ptr(kr), ptr(dr), len(kr), ptr(sf),
                                              len(sf), int(n_rows), float(min_d), float(max_d), ptr(bi), ptr(bd)))
         return bi, bd
+
+
+class FrameGrid:
+    """The searched side of a projection search as the reference's Frame holds it: undistorted
+    keypoints, mvuRight, descriptors and the 64 x 48 cell grid (Frame::AssignFeaturesToGrid,
+    Frame.cc:245-260, with PosInGrid, :397-410).  `cells` (list of index lists, column-major
+    (ix, iy) -> ix*rows+iy) overrides the assignment, for KeyFrame grids of other sizes."""
+
+    def __init__(self, x, y, octave, desc, u_right=None, min_x=0.0, min_y=0.0, max_x=640.0, max_y=480.0,
+                 cols=64, rows=48, cells=None):
+        self.x = np.ascontiguousarray(x, np.float32)
+        self.y = np.ascontiguousarray(y, np.float32)
+        self.octave = np.ascontiguousarray(octave, np.int32)
+        self.desc = _desc(desc) if len(self.x) else np.zeros((0, 32), np.uint8)
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        self.n = len(self.x)
+        f32 = np.float32
+        self.min_x, self.min_y = f32(min_x), f32(min_y)
+        self.cols, self.rows = int(cols), int(rows)
+        self.width_inv = f32(f32(cols) / (f32(max_x) - self.min_x))    # Frame.cc:106-107
+        self.height_inv = f32(f32(rows) / (f32(max_y) - self.min_y))
+        if cells is None:
+            def rnd(v):  # C round(): half away from zero
+                v = v.astype(np.float64)
+                return np.where(v >= 0, np.floor(v + 0.5), np.ceil(v - 0.5)).astype(np.int64)
+            px = rnd((self.x - self.min_x) * self.width_inv)
+            py = rnd((self.y - self.min_y) * self.height_inv)
+            ok = (px >= 0) & (px < cols) & (py >= 0) & (py < rows)
+            cell = np.where(ok, px * rows + py, cols * rows)
+            order = np.argsort(cell, kind="stable")  # push_back in keypoint order inside a cell
+            order = order[: int(ok.sum())]
+            counts = np.bincount(cell[ok], minlength=cols * rows)
+            self.cell_idx = np.ascontiguousarray(order, np.uint32)
+        else:
+            assert len(cells) == cols * rows
+            counts = np.array([len(c) for c in cells], np.int64)
+            self.cell_idx = np.ascontiguousarray([i for c in cells for i in c], np.uint32)
+        self.cell_off = np.zeros(cols * rows + 1, np.int32)
+        np.cumsum(counts, out=self.cell_off[1:])
+        self.c = GridFrame(ptr(self.x), ptr(self.y), ptr(self.octave), None if self.u_right is None else ptr(self.u_right),
+                           ptr(self.desc), self.n, float(self.min_x), float(self.min_y), float(self.width_inv),
+                           float(self.height_inv), self.cols, self.rows, ptr(self.cell_off), ptr(self.cell_idx))
+
+
+def window_search(frame: FrameGrid, queries, query_desc, claimed=None, th: int = TH_HIGH, ratio: float = 0.0,
+                  claim: bool = True, device: int = 0):
+    """orbm_window_search: the descriptor loop of the SearchByProjection overloads
+    (ORBmatcher.cc:46-132, :134-220, :491-604, :1529-1800).  Returns (results, n_accepted, passes)."""
+    q = np.ascontiguousarray(queries, WINDOW_QUERY_DTYPE)
+    qd = _desc(query_desc) if len(q) else np.zeros((0, 32), np.uint8)
+    assert len(qd) == len(q)
+    cl = None if claimed is None else np.ascontiguousarray(claimed, np.uint8)
+    out = np.zeros(len(q), WINDOW_RESULT_DTYPE)
+    na, rounds = C.c_int(0), C.c_int(0)
+    check(_lib.load().orbm_window_search(device, C.byref(frame.c), ptr(q), ptr(qd), len(q), None if cl is None else ptr(cl),
+                                         int(th), float(ratio), int(bool(claim)), ptr(out), C.byref(na), C.byref(rounds)))
+    return out, na.value, rounds.value
 
 
 class DescriptorDB:

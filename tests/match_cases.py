@@ -89,3 +89,71 @@ def oracle_stereo(L, kl, dl, kr, dr, scale, n_rows, min_d, max_d):
     L.orc_stereo_search(c(kl["x"]), c(kl["y"]), c(kl["octave"]), dl, len(kl), c(kr["x"]), c(kr["y"]), c(kr["octave"]),
                         dr, len(kr), scale, n_rows, min_d, max_d, bi, bd)
     return bi, bd
+
+
+def window_case(seed, n=1500, nq=1200, width=640, height=480, n_levels=8, stereo=False, th_px=7.0, dup=0.6,
+                clump=0.0, claimed_frac=0.1, nonblocking_frac=0.05, free_levels_frac=0.1):
+    """A frame with a cell grid plus projected queries, shaped like Tracking's projection searches:
+    most queries land near a keypoint that carries a noisy copy of their descriptor, several
+    queries compete for the same keypoint (greedy claims), some keypoints are matched already.
+    `clump` > 0 draws that fraction of the queries inside one small patch (long claim chains)."""
+    from orb_slam2_e_b200.matcher import FrameGrid
+    from orb_slam2_e_b200._lib import WINDOW_QUERY_DTYPE
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(-3, width + 3, n).astype(np.float32)      # undistorted points may leave the image
+    y = rng.uniform(-3, height + 3, n).astype(np.float32)
+    octave = rng.integers(0, n_levels, n).astype(np.int32)
+    desc = synth.random_descriptors(n, seed * 5 + 1)
+    u_right = None
+    if stereo:
+        u_right = np.where(rng.random(n) < 0.7, x - rng.uniform(1, 40, n), -1).astype(np.float32)
+    frame = FrameGrid(x, y, octave, desc, u_right, 0.0, 0.0, float(width), float(height))
+    scale = (1.2 ** np.arange(n_levels)).astype(np.float32)
+    q = np.zeros(nq, WINDOW_QUERY_DTYPE)
+    qd = synth.random_descriptors(nq, seed * 5 + 2)
+    target = rng.integers(0, n, nq)
+    n_clump = int(nq * clump)
+    if n_clump:
+        cx, cy = rng.uniform(100, width - 100), rng.uniform(100, height - 100)
+        near = np.argsort((x - cx) ** 2 + (y - cy) ** 2)[:40]
+        target[:n_clump] = rng.choice(near, n_clump)
+        rng.shuffle(target)
+    for i in range(nq):
+        t = int(target[i])
+        lvl = int(np.clip(octave[t] + rng.integers(-1, 2), 0, n_levels - 1))
+        q["x"][i] = x[t] + rng.normal(0, 2.0)
+        q["y"][i] = y[t] + rng.normal(0, 2.0)
+        q["r"][i] = np.float32(th_px) * scale[lvl]
+        if rng.random() < free_levels_frac:
+            q["min_level"][i], q["max_level"][i] = (0, -1) if rng.random() < 0.5 else (lvl, -1)
+        else:
+            q["min_level"][i], q["max_level"][i] = lvl - 1, lvl + int(rng.integers(0, 2))
+        q["blocks"][i] = rng.random() >= nonblocking_frac
+        if stereo and rng.random() < 0.8:
+            q["u_right"][i] = (u_right[t] if u_right[t] > 0 else q["x"][i] - 10) + rng.normal(0, 3.0)
+            q["er_max"][i] = q["r"][i]
+        else:
+            q["er_max"][i] = -1.0
+        if rng.random() < dup:
+            qd[i] = synth.flip_bits(desc[t], int(rng.integers(0, 70)), rng)
+    # exact ties: the same descriptor on two keypoints of one window
+    for i in range(0, nq, 17):
+        t = int(target[i])
+        d2 = (x - x[t]) ** 2 + (y - y[t]) ** 2
+        nb = np.argsort(d2)[1:3]
+        desc[nb[0]] = desc[t]
+        octave[nb[0]] = octave[t]
+    frame = FrameGrid(x, y, octave, desc, u_right, 0.0, 0.0, float(width), float(height))
+    claimed = (rng.random(n) < claimed_frac).astype(np.uint8)
+    return frame, q, qd, claimed
+
+
+def oracle_window(L, frame, q, qd, claimed, th, ratio, claim):
+    from orb_slam2_e_b200._lib import WINDOW_RESULT_DTYPE
+    out = np.zeros(len(q), WINDOW_RESULT_DTYPE)
+    ur = None if frame.u_right is None else frame.u_right.ctypes.data
+    cl = None if claimed is None else claimed.ctypes.data
+    nm = L.orc_window_search(frame.x, frame.y, frame.octave, ur, frame.desc, frame.n, frame.min_x, frame.min_y,
+                             frame.width_inv, frame.height_inv, frame.cols, frame.rows, frame.cell_off, frame.cell_idx,
+                             q.ctypes.data, qd, len(q), cl, th, ratio, int(claim), out.ctypes.data)
+    return nm, out

@@ -68,6 +68,9 @@ def oracle(fast=False):
                                  u8p, C.c_void_p, f32p, f32p, C.c_float, C.c_int, C.c_int, i32p]
     L.orc_stereo_search.argtypes = [f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, i32p, u8p, C.c_int, f32p, C.c_int,
                                     C.c_float, C.c_float, i32p, i32p]
+    L.orc_window_search.argtypes = [f32p, f32p, i32p, C.c_void_p, u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
+                                    C.c_int, C.c_int, i32p, u32p, C.c_void_p, u8p, C.c_int, C.c_void_p, C.c_int, C.c_float,
+                                    C.c_int, C.c_void_p]
     _cache[key] = L
     return L
 
