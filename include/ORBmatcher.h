@@ -9,11 +9,18 @@
  *     DescriptorDistance(const cv::Mat&, const cv::Mat&)  src/ORBmatcher.cc:1848-1864
  *     SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)  src/ORBmatcher.cc:360-489
  *     SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) src/ORBmatcher.cc:723-856
+ *     SearchByProjection(Frame&, const vector<MapPoint*>&, float)          src/ORBmatcher.cc:46-132
+ *     SearchByProjection(Frame&, Map*, double[3][3], double[3], ...)       src/ORBmatcher.cc:134-220
+ *     SearchByProjection(KeyFrame*, cv::Mat Scw, ...)                      src/ORBmatcher.cc:491-604
+ *     SearchByProjection(Frame&, const Frame&, float, bool)                src/ORBmatcher.cc:1529-1671
+ *     SearchByProjection(Frame&, KeyFrame*, const set<MapPoint*>&, ...)    src/ORBmatcher.cc:1673-1800
  * plus the extension StereoSearch() for Frame::ComputeStereoMatches (src/Frame.cc:527-610).
- * The windowed projection searches (SearchByProjection x5, SearchBySim3, Fuse x2,
- * SearchForTriangulation, SearchForInitialization) stay declared and keep their definitions in
- * the reference's ORBmatcher.cc (next); INTEGRATION.md shows the four
- * definitions to delete from that file.
+ * The projection searches keep the pose / camera / MapPoint arithmetic on the host, written with
+ * the includer's cv::Mat exactly as the reference evaluates it, and hand the descriptor work --
+ * grid gather, Hamming top-2, acceptance and the order-dependent hiding of matched keypoints --
+ * to orbm_window_search.  SearchBySim3, Fuse x2, SearchForTriangulation and
+ * SearchForInitialization stay declared and keep their definitions in the reference's
+ * ORBmatcher.cc; INTEGRATION.md lists the definitions to delete from that file.
  *
  * Like the reference header, this one includes MapPoint.h / KeyFrame.h / Frame.h from the
  * includer's path (the reference's own in its build; tests/cpp/mock in this repo's tests).
@@ -21,6 +28,8 @@
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <set>
@@ -134,6 +143,115 @@ class ORBmatcher {
     for (int r = 0; r < m.rows; ++r) memcpy(&tmp[(size_t)r * 32], m.data + (size_t)r * (size_t)m.step, 32);
     return tmp.data();
   }
+
+  // ---- projection searches: flat views for orbm_window_search
+  struct FlatGrid {  // a Frame's or KeyFrame's keypoints + cell grid
+    std::vector<float> x, y;
+    std::vector<int32_t> oct, off;
+    std::vector<uint32_t> idx;
+    std::vector<uint8_t> tmp;
+    orbm_grid_frame c;
+    void Keys(const std::vector<cv::KeyPoint>& k, const std::vector<float>& uright, const cv::Mat& desc) {
+      const size_t n = k.size();
+      x.resize(n); y.resize(n); oct.resize(n);
+      for (size_t i = 0; i < n; ++i) { x[i] = k[i].pt.x; y[i] = k[i].pt.y; oct[i] = k[i].octave; }
+      c.x = x.data(); c.y = y.data(); c.octave = oct.data();
+      c.u_right = uright.size() == n ? uright.data() : NULL;
+      c.desc = Rows(desc, tmp);
+      c.n = (int32_t)n;
+    }
+    // Frame: public mGrid[64][48] and the static bounds (include/Frame.h:189,211-214)
+    explicit FlatGrid(const Frame& F) {
+      Keys(F.mvKeysUn, F.mvuRight, F.mDescriptors);
+      c.min_x = Frame::mnMinX; c.min_y = Frame::mnMinY;
+      c.width_inv = Frame::mfGridElementWidthInv; c.height_inv = Frame::mfGridElementHeightInv;
+      c.cols = FRAME_GRID_COLS; c.rows = FRAME_GRID_ROWS;
+      off.reserve((size_t)c.cols * c.rows + 1);
+      off.push_back(0);
+      for (int ix = 0; ix < FRAME_GRID_COLS; ++ix)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; ++iy) {
+          const std::vector<std::size_t>& cell = F.mGrid[ix][iy];
+          for (size_t j = 0; j < cell.size(); ++j) idx.push_back((uint32_t)cell[j]);
+          off.push_back((int32_t)idx.size());
+        }
+      c.cell_off = off.data(); c.cell_idx = idx.data();
+    }
+    // KeyFrame: its mGrid is protected (include/KeyFrame.h:233) but is a copy of the grid its Frame
+    // built (KeyFrame.cc:55-60) with Frame::PosInGrid (Frame.cc:397-410) over the static float
+    // bounds, keypoints in index order -- rebuilt here the same way.  The window arithmetic of
+    // KeyFrame::GetFeaturesInArea (KeyFrame.cc:618-632) uses the KeyFrame's own (int) bounds.
+    explicit FlatGrid(const KeyFrame& KF) {
+      Keys(KF.mvKeysUn, KF.mvuRight, KF.mDescriptors);
+      c.min_x = KF.mnMinX; c.min_y = KF.mnMinY;
+      c.width_inv = KF.mfGridElementWidthInv; c.height_inv = KF.mfGridElementHeightInv;
+      c.cols = KF.mnGridCols; c.rows = KF.mnGridRows;
+      const size_t n_cells = (size_t)c.cols * c.rows;
+      std::vector<int32_t> cell_of(KF.mvKeysUn.size(), -1);
+      off.assign(n_cells + 1, 0);
+      for (size_t i = 0; i < KF.mvKeysUn.size(); ++i) {
+        const int px = round((KF.mvKeysUn[i].pt.x - Frame::mnMinX) * Frame::mfGridElementWidthInv);
+        const int py = round((KF.mvKeysUn[i].pt.y - Frame::mnMinY) * Frame::mfGridElementHeightInv);
+        if (px < 0 || px >= c.cols || py < 0 || py >= c.rows) continue;
+        cell_of[i] = px * c.rows + py;
+        ++off[(size_t)cell_of[i] + 1];
+      }
+      for (size_t k = 0; k < n_cells; ++k) off[k + 1] += off[k];
+      idx.resize((size_t)off[n_cells]);
+      std::vector<int32_t> fill(off.begin(), off.end() - 1);
+      for (size_t i = 0; i < cell_of.size(); ++i)
+        if (cell_of[i] >= 0) idx[(size_t)fill[(size_t)cell_of[i]]++] = (uint32_t)i;
+      c.cell_off = off.data(); c.cell_idx = idx.data();
+    }
+  };
+  struct WindowQueries {  // the queries of one call, in the reference's loop order
+    std::vector<orbm_window_query> q;
+    std::vector<uint8_t> desc;
+    std::vector<MapPoint*> mp;
+    std::vector<int> src;  // caller-side index of the query (keypoint of the last frame / keyframe)
+    void Add(MapPoint* pMP, const cv::Mat& d, float x, float y, float r, int minLevel, int maxLevel, float uRight, float erMax,
+             bool blocks, int source = -1) {
+      orbm_window_query w;
+      w.x = x; w.y = y; w.r = r; w.u_right = uRight; w.er_max = erMax;
+      w.min_level = minLevel; w.max_level = maxLevel; w.blocks = blocks ? 1 : 0;
+      q.push_back(w);
+      desc.insert(desc.end(), d.data, d.data + 32);
+      mp.push_back(pMP);
+      src.push_back(source);
+    }
+    std::vector<orbm_window_result> Run(const FlatGrid& g, std::vector<uint8_t> hidden, int th, float ratio, bool claim,
+                                        const char* what) const {
+      std::vector<orbm_window_result> res(q.size());
+      int n = 0;
+      hidden.resize((size_t)g.c.n, 0);
+      if (!q.empty())
+        Check(orbm_window_search(Device(), &g.c, q.data(), desc.data(), (int)q.size(), hidden.data(), th, ratio, claim ? 1 : 0,
+                                 res.data(), &n, NULL),
+              what);
+      return res;
+    }
+  };
+  static int RotationBin(float a1, float a2) {  // src/ORBmatcher.cc:1628-1634
+    const float factor = 1.0f / HISTO_LENGTH;
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = round(rot * factor);
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+  }
+  static void ThreeMaxima(const std::vector<int>* histo, int& ind1, int& ind2, int& ind3) {  // src/ORBmatcher.cc:1802-1843
+    int max1 = 0, max2 = 0, max3 = 0;
+    ind1 = ind2 = ind3 = -1;
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      const int s = (int)histo[i].size();
+      if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+      else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) ind3 = -1;
+  }
+  // src/ORBmatcher.cc:262-330 with :222-260 folded in: frustum test of the map-wide search.
+  static bool InFrustumReloc(MapPoint* pMP, const Frame& F, double R[3][3], double t[3], float viewingCosLimit);
 };
 
 inline int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches) {
@@ -172,6 +290,286 @@ inline int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<M
         "ORBmatcher::SearchByBoW");
   for (size_t i = 0; i < vpMatches12.size() && i < (size_t)n1; ++i)
     if (out[i] >= 0) vpMatches12[i] = vpMapPoints2[out[i]];
+  return nmatches;
+}
+
+// ---- projection searches ----------------------------------------------------------------------
+// Each overload walks its MapPoints in the reference's order, keeps the reference's skip tests and
+// its float expressions for the projection, and queues one window query per surviving point; the
+// GPU resolves all queries of the call at once (orbm_window_search), then the matches are applied
+// in query order, which reproduces the reference's writes one for one.
+
+// Local map points into the current frame (Tracking::SearchLocalPoints).  src/ORBmatcher.cc:46-132
+inline int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th) {
+  const bool bFactor = th != 1.0;
+  WindowQueries W;
+  for (size_t iMP = 0; iMP < vpMapPoints.size(); iMP++) {
+    MapPoint* pMP = vpMapPoints[iMP];
+    if (!pMP->mbTrackInView) continue;
+    if (pMP->isBad()) continue;
+    const int& nPredictedLevel = pMP->mnTrackScaleLevel;
+    float r = pMP->mTrackViewCos > 0.998 ? 3.0 : 4.5;  // RadiusByViewingCos, :332-338
+    if (bFactor) r *= th;
+    const float window = r * F.mvScaleFactors[nPredictedLevel];
+    W.Add(pMP, pMP->GetDescriptor(), pMP->mTrackProjX, pMP->mTrackProjY, window, nPredictedLevel - 1, nPredictedLevel,
+          pMP->mTrackProjXR, window, pMP->Observations() > 0);
+  }
+  std::vector<uint8_t> hidden(F.mvpMapPoints.size(), 0);  // :81-83
+  for (size_t i = 0; i < hidden.size(); ++i) hidden[i] = F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0;
+  const FlatGrid grid(F);
+  const std::vector<orbm_window_result> res = W.Run(grid, hidden, TH_HIGH, mfNNratio, true, "ORBmatcher::SearchByProjection");
+  int nmatches = 0;
+  for (size_t k = 0; k < res.size(); ++k) {
+    if (res[k].idx < 0) continue;
+    F.mvpMapPoints[res[k].idx] = W.mp[k];  // :125-127
+    F.mvpMapPointsInFrame[res[k].idx] = W.mp[k];
+    F.fvMapPointSearchRadious[res[k].idx] = W.q[k].r;
+    nmatches++;
+  }
+  return nmatches;
+}
+
+inline bool ORBmatcher::InFrustumReloc(MapPoint* pMP, const Frame& F, double R[3][3], double t[3], float viewingCosLimit) {
+  cv::Mat P = pMP->GetWorldPos();
+  const float ptX = P.at<float>(0), ptY = P.at<float>(1), ptZ = P.at<float>(2);
+  // camera coordinates: double products rounded to float once, :273-275
+  const float PcX = R[0][0] * ptX + R[0][1] * ptY + R[0][2] * ptZ + t[0];
+  const float PcY = R[1][0] * ptX + R[1][1] * ptY + R[1][2] * ptZ + t[1];
+  const float PcZ = R[2][0] * ptX + R[2][1] * ptY + R[2][2] * ptZ + t[2];
+  if (PcZ < 0.0) return false;
+  const float invz = 1.0 / PcZ;
+  const float u = F.fx * PcX * invz + F.cx;
+  const float v = F.fy * PcY * invz + F.cy;
+  // image bounds as ints, like Frame::GetImageBounds (Frame.cc:517-524)
+  const int minX = Frame::mnMinX, maxX = Frame::mnMaxX, minY = Frame::mnMinY, maxY = Frame::mnMaxY;
+  if (u < minX || u > maxX) return false;
+  if (v < minY || v > maxY) return false;
+  const float maxDistance = pMP->GetMaxDistanceInvariance();
+  const float minDistance = pMP->GetMinDistanceInvariance();
+  // PO = P - Ow with Ow = -R^T t, in double (ComputeDistance, :222-260)
+  double PO[3];
+  for (int i = 0; i < 3; ++i) {
+    const double Rtt = (-1) * R[0][i] * t[0] + (-1) * R[1][i] * t[1] + (-1) * R[2][i] * t[2];
+    PO[i] = (double)(i == 0 ? ptX : i == 1 ? ptY : ptZ) - Rtt;
+  }
+  const float dist = sqrt(PO[0] * PO[0] + PO[1] * PO[1] + PO[2] * PO[2]);
+  if (dist < (0.9 * minDistance) || dist > (maxDistance / 0.9)) return false;
+  cv::Mat Pn = pMP->GetNormal();
+  const float pn[] = {Pn.at<float>(0), Pn.at<float>(1), Pn.at<float>(2)};
+  float viewCos = PO[0] * pn[0] + PO[1] * pn[1] + PO[2] * pn[2];
+  viewCos = viewCos / dist;
+  if (viewCos < viewingCosLimit) return false;
+  const float ratio = dist / minDistance;
+  int nPredictedLevel = (int)(std::lower_bound(F.mvScaleFactors.begin(), F.mvScaleFactors.end(), ratio) - F.mvScaleFactors.begin());
+  if (nPredictedLevel >= F.mnScaleLevels) nPredictedLevel = F.mnScaleLevels - 1;
+  pMP->mRelocProjX = u;
+  pMP->mRelocProjY = v;
+  pMP->mnRelocScaleLevel = nPredictedLevel;
+  pMP->mRelocViewCos = viewCos;
+  return true;
+}
+
+// Every map point against a frame under a candidate pose (PnPsolver).  src/ORBmatcher.cc:134-220
+inline int ORBmatcher::SearchByProjection(Frame& F, Map* pMap, double mCamRcw[3][3], double mCamtcw[3],
+                                          vector<MapPoint*>& vMatchedMPs, vector<cv::KeyPoint>& vMatchedKPs,
+                                          vector<bool>& vbMatched, const float th) {
+  const std::vector<MapPoint*> vpAllMapPoints = pMap->GetAllMapPoints();
+  const int nFeatures = (int)F.mvKeysUn.size();
+  vMatchedMPs = vector<MapPoint*>(nFeatures, static_cast<MapPoint*>(NULL));
+  vMatchedKPs.reserve(nFeatures);
+  vbMatched = vector<bool>(nFeatures, false);
+  const bool bFactor = th != 1.0;
+  WindowQueries W;
+  for (size_t iMP = 0; iMP < vpAllMapPoints.size(); iMP++) {
+    MapPoint* pMP = vpAllMapPoints[iMP];
+    if (!InFrustumReloc(pMP, F, mCamRcw, mCamtcw, 0.5)) continue;
+    const int& nPredictedLevel = pMP->mnRelocScaleLevel;
+    float r = pMP->mRelocViewCos > 0.998 ? 3.0 : 4.5;
+    if (bFactor) r *= th;
+    W.Add(pMP, pMP->GetDescriptor(), pMP->mRelocProjX, pMP->mRelocProjY, r * F.mvScaleFactors[nPredictedLevel],
+          nPredictedLevel - 1, nPredictedLevel, 0.f, -1.f, false);
+  }
+  std::vector<uint8_t> hidden(F.mvpMapPoints.size(), 0);  // :181-182
+  for (size_t i = 0; i < hidden.size(); ++i) hidden[i] = F.mvpMapPoints[i] != NULL;
+  const FlatGrid grid(F);
+  // matches go to a separate vector, so no query hides a keypoint from a later one
+  const std::vector<orbm_window_result> res = W.Run(grid, hidden, TH_RELOC, mfNNratio, false, "ORBmatcher::SearchByProjection");
+  int nmatches = 0;
+  for (size_t k = 0; k < res.size(); ++k) {
+    if (res[k].idx < 0) continue;
+    vMatchedMPs[res[k].idx] = W.mp[k];
+    vMatchedKPs.data()[res[k].idx] = F.mvKeys[res[k].idx];  // :211 writes into the reserved storage; size() stays 0
+    vbMatched[res[k].idx] = true;
+    nmatches++;
+  }
+  return nmatches;
+}
+
+// Loop-closure candidates into a keyframe under a Sim3.  src/ORBmatcher.cc:491-604
+inline int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints,
+                                          std::vector<MapPoint*>& vpMatched, int th) {
+  const float &fx = pKF->fx, &fy = pKF->fy, &cx = pKF->cx, &cy = pKF->cy;
+  cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+  const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+  cv::Mat Rcw = sRcw / scw;
+  cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+  cv::Mat Ow = -Rcw.t() * tcw;
+  std::set<MapPoint*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+  spAlreadyFound.erase(static_cast<MapPoint*>(NULL));
+  WindowQueries W;
+  for (int iMP = 0, iendMP = (int)vpPoints.size(); iMP < iendMP; iMP++) {
+    MapPoint* pMP = vpPoints[iMP];
+    if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+    cv::Mat p3Dw = pMP->GetWorldPos();
+    cv::Mat p3Dc = Rcw * p3Dw + tcw;
+    if (p3Dc.at<float>(2) < 0.0) continue;
+    const float invz = 1 / p3Dc.at<float>(2);
+    const float x = p3Dc.at<float>(0) * invz;
+    const float y = p3Dc.at<float>(1) * invz;
+    const float u = fx * x + cx;
+    const float v = fy * y + cy;
+    if (!pKF->IsInImage(u, v)) continue;
+    const float maxDistance = pMP->GetMaxDistanceInvariance();
+    const float minDistance = pMP->GetMinDistanceInvariance();
+    cv::Mat PO = p3Dw - Ow;
+    const float dist = cv::norm(PO);
+    if (dist < minDistance || dist > maxDistance) continue;
+    cv::Mat Pn = pMP->GetNormal();
+    if (PO.dot(Pn) < 0.5 * dist) continue;
+    const int nPredictedLevel = pMP->PredictScale(dist, pKF);
+    const float radius = th * pKF->mvScaleFactors[nPredictedLevel];
+    // the level test sits inside the candidate loop (:575-578); as a window filter it is the same set
+    W.Add(pMP, pMP->GetDescriptor(), u, v, radius, nPredictedLevel - 1, nPredictedLevel, 0.f, -1.f, true);
+  }
+  std::vector<uint8_t> hidden(vpMatched.size(), 0);  // :570-571
+  for (size_t i = 0; i < hidden.size(); ++i) hidden[i] = vpMatched[i] != NULL;
+  const FlatGrid grid(*pKF);
+  const std::vector<orbm_window_result> res = W.Run(grid, hidden, TH_LOW, 0.f, true, "ORBmatcher::SearchByProjection");
+  int nmatches = 0;
+  for (size_t k = 0; k < res.size(); ++k) {
+    if (res[k].idx < 0) continue;
+    vpMatched[res[k].idx] = W.mp[k];
+    nmatches++;
+  }
+  return nmatches;
+}
+
+// Last frame's points into the current frame (Tracking::TrackWithMotionModel).  src/ORBmatcher.cc:1529-1671
+inline int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono) {
+  const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat twc = -Rcw.t() * tcw;
+  const cv::Mat Rlw = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tlw = LastFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat tlc = Rlw * twc + tlw;
+  const bool bForward = tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+  const bool bBackward = -tlc.at<float>(2) > CurrentFrame.mb && !bMono;
+  WindowQueries W;
+  for (int i = 0; i < LastFrame.N; i++) {
+    MapPoint* pMP = LastFrame.mvpMapPoints[i];
+    if (!pMP || LastFrame.mvbOutlier[i]) continue;
+    cv::Mat x3Dw = pMP->GetWorldPos();
+    cv::Mat x3Dc = Rcw * x3Dw + tcw;
+    const float xc = x3Dc.at<float>(0);
+    const float yc = x3Dc.at<float>(1);
+    const float invzc = 1.0 / x3Dc.at<float>(2);
+    if (invzc < 0) continue;
+    const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+    const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+    if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+    if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+    const int nLastOctave = LastFrame.mvKeys[i].octave;
+    const float radius = th * CurrentFrame.mvScaleFactors[nLastOctave];
+    int minLevel, maxLevel;  // :1583-1588
+    if (bForward) { minLevel = nLastOctave; maxLevel = -1; }
+    else if (bBackward) { minLevel = 0; maxLevel = nLastOctave; }
+    else { minLevel = nLastOctave - 1; maxLevel = nLastOctave + 1; }
+    const float ur = u - CurrentFrame.mbf * invzc;  // :1606-1611
+    W.Add(pMP, pMP->GetDescriptor(), u, v, radius, minLevel, maxLevel, ur, radius, pMP->Observations() > 0, i);
+  }
+  std::vector<uint8_t> hidden(CurrentFrame.mvpMapPoints.size(), 0);  // :1601-1603
+  for (size_t i = 0; i < hidden.size(); ++i)
+    hidden[i] = CurrentFrame.mvpMapPoints[i] && CurrentFrame.mvpMapPoints[i]->Observations() > 0;
+  const FlatGrid grid(CurrentFrame);
+  const std::vector<orbm_window_result> res = W.Run(grid, hidden, TH_HIGH, 0.f, true, "ORBmatcher::SearchByProjection");
+  int nmatches = 0;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  for (size_t k = 0; k < res.size(); ++k) {
+    const int bestIdx2 = res[k].idx;
+    if (bestIdx2 < 0) continue;
+    CurrentFrame.mvpMapPoints[bestIdx2] = W.mp[k];
+    nmatches++;
+    if (mbCheckOrientation)
+      rotHist[RotationBin(LastFrame.mvKeysUn[W.src[k]].angle, CurrentFrame.mvKeysUn[bestIdx2].angle)].push_back(bestIdx2);
+  }
+  if (mbCheckOrientation) {  // :1643-1665
+    int ind1, ind2, ind3;
+    ThreeMaxima(rotHist, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (size_t j = 0; j < rotHist[i].size(); j++) {
+        CurrentFrame.mvpMapPoints[rotHist[i][j]] = static_cast<MapPoint*>(NULL);
+        nmatches--;
+      }
+    }
+  }
+  return nmatches;
+}
+
+// A relocalization candidate keyframe's points into the current frame.  src/ORBmatcher.cc:1673-1800
+inline int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound,
+                                          const float th, const int ORBdist) {
+  const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+  const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+  const cv::Mat Ow = -Rcw.t() * tcw;
+  const std::vector<MapPoint*> vpMPs = pKF->GetMapPointMatches();
+  WindowQueries W;
+  for (size_t i = 0, iend = vpMPs.size(); i < iend; i++) {
+    MapPoint* pMP = vpMPs[i];
+    if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+    cv::Mat x3Dw = pMP->GetWorldPos();
+    cv::Mat x3Dc = Rcw * x3Dw + tcw;
+    const float xc = x3Dc.at<float>(0);
+    const float yc = x3Dc.at<float>(1);
+    const float invzc = 1.0 / x3Dc.at<float>(2);
+    const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+    const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+    if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+    if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+    cv::Mat PO = x3Dw - Ow;
+    float dist3D = cv::norm(PO);
+    const float maxDistance = pMP->GetMaxDistanceInvariance();
+    const float minDistance = pMP->GetMinDistanceInvariance();
+    if (dist3D < minDistance || dist3D > maxDistance) continue;
+    const int nPredictedLevel = pMP->PredictScale(dist3D, &CurrentFrame);
+    const float radius = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
+    W.Add(pMP, pMP->GetDescriptor(), u, v, radius, nPredictedLevel - 1, nPredictedLevel + 1, 0.f, -1.f, true, (int)i);
+  }
+  std::vector<uint8_t> hidden(CurrentFrame.mvpMapPoints.size(), 0);  // :1741-1742: any MapPoint hides the keypoint
+  for (size_t i = 0; i < hidden.size(); ++i) hidden[i] = CurrentFrame.mvpMapPoints[i] != NULL;
+  const FlatGrid grid(CurrentFrame);
+  const std::vector<orbm_window_result> res = W.Run(grid, hidden, ORBdist, 0.f, true, "ORBmatcher::SearchByProjection");
+  int nmatches = 0;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  for (size_t k = 0; k < res.size(); ++k) {
+    const int bestIdx2 = res[k].idx;
+    if (bestIdx2 < 0) continue;
+    CurrentFrame.mvpMapPoints[bestIdx2] = W.mp[k];
+    nmatches++;
+    if (mbCheckOrientation)
+      rotHist[RotationBin(pKF->mvKeysUn[W.src[k]].angle, CurrentFrame.mvKeysUn[bestIdx2].angle)].push_back(bestIdx2);
+  }
+  if (mbCheckOrientation) {  // :1779-1797
+    int ind1, ind2, ind3;
+    ThreeMaxima(rotHist, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (size_t j = 0; j < rotHist[i].size(); j++) {
+        CurrentFrame.mvpMapPoints[rotHist[i][j]] = NULL;
+        nmatches--;
+      }
+    }
+  }
   return nmatches;
 }
 

@@ -69,13 +69,15 @@ struct MatZeros {
   int rows, cols, type;
 };
 
-// u8 single-channel matrix with a malloc'd, reference-counted buffer (malloc on purpose:
-// the parity harness replaces operator new with a monotonic arena that is reset per call).
+// Single-channel matrix, u8 (images, descriptors) or f32 (poses, points), with a malloc'd,
+// reference-counted buffer (malloc on purpose: the extractor parity harness replaces operator new
+// with a monotonic arena that is reset per call).
 class Mat {
   struct Block {
     int refs;
   };
   Block* blk_;
+  int type_;
 
   void retain() {
     if (blk_) ++blk_->refs;
@@ -90,37 +92,42 @@ class Mat {
   int rows, cols;
   size_t step;
 
-  Mat() : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) {}
-  Mat(int r, int c, int type) : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) { create(r, c, type); }
-  Mat(Size s, int type) : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) { create(s.height, s.width, type); }
-  Mat(const MatZeros& z) : blk_(nullptr), data(nullptr), rows(0), cols(0), step(0) { *this = z; }
+  static size_t esz(int type) { return type == CV_32F ? 4 : 1; }
+  size_t elemSize() const { return esz(type_); }
+
+  Mat() : blk_(nullptr), type_(CV_8U), data(nullptr), rows(0), cols(0), step(0) {}
+  Mat(int r, int c, int type) : blk_(nullptr), type_(CV_8U), data(nullptr), rows(0), cols(0), step(0) { create(r, c, type); }
+  Mat(Size s, int type) : blk_(nullptr), type_(CV_8U), data(nullptr), rows(0), cols(0), step(0) { create(s.height, s.width, type); }
+  Mat(const MatZeros& z) : blk_(nullptr), type_(CV_8U), data(nullptr), rows(0), cols(0), step(0) { *this = z; }
   // wrap caller-owned memory
-  Mat(int r, int c, int, void* ext, size_t st) : blk_(nullptr), data((uchar*)ext), rows(r), cols(c), step(st) {}
-  Mat(const Mat& o) : blk_(o.blk_), data(o.data), rows(o.rows), cols(o.cols), step(o.step) { retain(); }
+  Mat(int r, int c, int type, void* ext, size_t st = 0)
+      : blk_(nullptr), type_(type), data((uchar*)ext), rows(r), cols(c), step(st ? st : (size_t)c * esz(type)) {}
+  Mat(const Mat& o) : blk_(o.blk_), type_(o.type_), data(o.data), rows(o.rows), cols(o.cols), step(o.step) { retain(); }
   Mat& operator=(const Mat& o) {
     if (this != &o) {
       Block* nb = o.blk_;
       if (nb) ++nb->refs;
       drop();
       blk_ = nb;
+      type_ = o.type_;
       data = o.data; rows = o.rows; cols = o.cols; step = o.step;
     }
     return *this;
   }
   Mat& operator=(const MatZeros& z) {
     create(z.rows, z.cols, z.type);
-    for (int y = 0; y < rows; ++y) memset(data + (size_t)y * step, 0, (size_t)cols);
+    for (int y = 0; y < rows; ++y) memset(data + (size_t)y * step, 0, (size_t)cols * elemSize());
     return *this;
   }
   ~Mat() { drop(); }
 
   void create(int r, int c, int type) {
-    assert(type == CV_8U);
-    (void)type;
-    if (data && r == rows && c == cols) return;
+    assert(type == CV_8U || type == CV_32F);
+    if (data && r == rows && c == cols && type == type_) return;
     drop();
-    rows = r; cols = c; step = (size_t)c;
-    size_t bytes = sizeof(Block) + 64 + (size_t)r * c;
+    type_ = type;
+    rows = r; cols = c; step = (size_t)c * esz(type);
+    size_t bytes = sizeof(Block) + 64 + (size_t)r * step;
     blk_ = (Block*)malloc(bytes);
     blk_->refs = 1;
     data = (uchar*)blk_ + 64;
@@ -134,28 +141,87 @@ class Mat {
 
   Mat operator()(const Rect& r) const {
     Mat m(*this);
-    m.data = data + (size_t)r.y * step + r.x;
+    m.data = data + (size_t)r.y * step + (size_t)r.x * elemSize();
     m.rows = r.height; m.cols = r.width;
     return m;
   }
   Mat rowRange(int a, int b) const { return (*this)(Rect(0, a, cols, b - a)); }
   Mat colRange(int a, int b) const { return (*this)(Rect(a, 0, b - a, rows)); }
+  Mat row(int y) const { return rowRange(y, y + 1); }
+  Mat col(int x) const { return colRange(x, x + 1); }
   Mat clone() const {
-    Mat m(rows, cols, CV_8U);
-    for (int y = 0; y < rows; ++y) memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols);
+    Mat m(rows, cols, type_);
+    for (int y = 0; y < rows; ++y) memcpy(m.data + (size_t)y * m.step, data + (size_t)y * step, (size_t)cols * elemSize());
     return m;
   }
+  void copyTo(Mat& dst) const { dst = clone(); }
   template <typename T> T& at(int y, int x) { return *(T*)(data + (size_t)y * step + x * sizeof(T)); }
   template <typename T> const T& at(int y, int x) const { return *(const T*)(data + (size_t)y * step + x * sizeof(T)); }
+  // one index: element i of a row or column vector
+  template <typename T> T& at(int i) { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
+  template <typename T> const T& at(int i) const { return rows == 1 ? at<T>(0, i) : at<T>(i, 0); }
   uchar* ptr(int y = 0) { return data + (size_t)y * step; }
   const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
   template <typename T> T* ptr(int y = 0) { return (T*)(data + (size_t)y * step); }
   template <typename T> const T* ptr(int y = 0) const { return (const T*)(data + (size_t)y * step); }
-  int type() const { return CV_8U; }
+  int type() const { return type_; }
   bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-  size_t step1() const { return step; }
+  size_t step1() const { return step / elemSize(); }
   Size size() const { return Size(cols, rows); }
+
+  // ---- f32 algebra (poses and points in the matcher).  Plain float arithmetic evaluated eagerly;
+  // NOT bit-pinned to OpenCV's gemm: both sides of every matcher comparison project with this code.
+  Mat t() const {
+    assert(type_ == CV_32F);
+    Mat m(cols, rows, CV_32F);
+    for (int y = 0; y < rows; ++y)
+      for (int x = 0; x < cols; ++x) m.at<float>(x, y) = at<float>(y, x);
+    return m;
+  }
+  double dot(const Mat& o) const {
+    assert(type_ == CV_32F && o.type_ == CV_32F && rows * cols == o.rows * o.cols);
+    double s = 0;
+    const int n = rows * cols;
+    for (int i = 0; i < n; ++i) s += (double)lin(i) * (double)o.lin(i);
+    return s;
+  }
+  float lin(int i) const { return at<float>(i / cols, i % cols); }
 };
+
+inline Mat operator*(const Mat& a, const Mat& b) {
+  assert(a.type() == CV_32F && b.type() == CV_32F && a.cols == b.rows);
+  Mat m(a.rows, b.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y)
+    for (int x = 0; x < b.cols; ++x) {
+      float s = 0.f;
+      for (int k = 0; k < a.cols; ++k) s += a.at<float>(y, k) * b.at<float>(k, x);
+      m.at<float>(y, x) = s;
+    }
+  return m;
+}
+template <typename F>
+inline Mat mat_zip(const Mat& a, const Mat& b, F f) {
+  assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y)
+    for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = f(a.at<float>(y, x), b.at<float>(y, x));
+  return m;
+}
+template <typename F>
+inline Mat mat_map(const Mat& a, F f) {
+  assert(a.type() == CV_32F);
+  Mat m(a.rows, a.cols, CV_32F);
+  for (int y = 0; y < a.rows; ++y)
+    for (int x = 0; x < a.cols; ++x) m.at<float>(y, x) = f(a.at<float>(y, x));
+  return m;
+}
+inline Mat operator+(const Mat& a, const Mat& b) { return mat_zip(a, b, [](float p, float q) { return p + q; }); }
+inline Mat operator-(const Mat& a, const Mat& b) { return mat_zip(a, b, [](float p, float q) { return p - q; }); }
+inline Mat operator-(const Mat& a) { return mat_map(a, [](float p) { return -p; }); }
+inline Mat operator*(double s, const Mat& a) { return mat_map(a, [s](float p) { return (float)(p * s); }); }
+inline Mat operator*(const Mat& a, double s) { return s * a; }
+inline Mat operator/(const Mat& a, double s) { return mat_map(a, [s](float p) { return (float)(p / s); }); }
+inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
 
 class _InputArray {
   const Mat* m_;

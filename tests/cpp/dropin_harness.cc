@@ -72,72 +72,6 @@ float dropin_table(void* h, int which, int l) {
 int dropin_levels(void* h) { return ((ORBextractor*)h)->GetLevels(); }
 float dropin_scale_factor(void* h) { return ((ORBextractor*)h)->GetScaleFactor(); }
 
-int dropin_distance(const uint8_t* a, const uint8_t* b) {
-  cv::Mat ma(1, 32, CV_8U, (void*)a, 32), mb(1, 32, CV_8U, (void*)b, 32);
-  return ORBmatcher::DescriptorDistance(ma, mb);
-}
-
-static void fill_fv(DBoW2::FeatureVector& fv, const uint32_t* node, const int32_t* off, const uint32_t* idx, int n_nodes) {
-  for (int i = 0; i < n_nodes; ++i) fv[node[i]] = std::vector<unsigned int>(idx + off[i], idx + off[i + 1]);
-}
-
-// state: 0 = no MapPoint (NULL), 1 = good MapPoint, 2 = bad MapPoint.  out as in orbm_search_bow.
-int dropin_search_bow(const uint8_t* d1, int n1, const uint8_t* d2, int n2, const uint32_t* node1, const int32_t* off1,
-                      const uint32_t* idx1, int nn1, const uint32_t* node2, const int32_t* off2, const uint32_t* idx2, int nn2,
-                      const uint8_t* state1, const uint8_t* state2, const float* a1, const float* a2, float ratio, int check_ori,
-                      int kf_kf, int32_t* out) {
-  try {
-    std::vector<std::unique_ptr<MapPoint> > pool;
-    auto points = [&](const uint8_t* st, int n) {
-      std::vector<MapPoint*> v((size_t)n, nullptr);
-      for (int i = 0; i < n; ++i)
-        if (st[i]) { pool.emplace_back(new MapPoint(st[i] == 2)); v[i] = pool.back().get(); }
-      return v;
-    };
-    auto keys = [&](const float* a, int n) {
-      std::vector<cv::KeyPoint> k((size_t)n);
-      for (int i = 0; i < n; ++i) k[i].angle = a ? a[i] : 0.f;
-      return k;
-    };
-    KeyFrame kf1;
-    kf1.mDescriptors = cv::Mat(n1, 32, CV_8U, (void*)d1, 32);
-    kf1.mvKeysUn = keys(a1, n1);
-    kf1.mvpMapPoints = points(state1, n1);
-    fill_fv(kf1.mFeatVec, node1, off1, idx1, nn1);
-    ORBmatcher matcher(ratio, check_ori != 0);
-    std::vector<MapPoint*> res;
-    int nm;
-    if (!kf_kf) {
-      Frame F;
-      F.N = n2;
-      F.mDescriptors = cv::Mat(n2, 32, CV_8U, (void*)d2, 32);
-      F.mvKeys = keys(a2, n2);
-      fill_fv(F.mFeatVec, node2, off2, idx2, nn2);
-      nm = matcher.SearchByBoW(&kf1, F, res);
-      for (int f = 0; f < n2; ++f) {
-        out[f] = -1;
-        if (res[f])
-          for (int i = 0; i < n1; ++i)
-            if (kf1.mvpMapPoints[i] == res[f]) out[f] = i;
-      }
-    } else {
-      KeyFrame kf2;
-      kf2.mDescriptors = cv::Mat(n2, 32, CV_8U, (void*)d2, 32);
-      kf2.mvKeysUn = keys(a2, n2);
-      kf2.mvpMapPoints = points(state2, n2);
-      fill_fv(kf2.mFeatVec, node2, off2, idx2, nn2);
-      nm = matcher.SearchByBoW(&kf1, &kf2, res);
-      for (int i = 0; i < n1; ++i) {
-        out[i] = -1;
-        if (res[i])
-          for (int j = 0; j < n2; ++j)
-            if (kf2.mvpMapPoints[j] == res[i]) out[i] = j;
-      }
-    }
-    return nm;
-  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
-}
-
 int dropin_stereo(const DropKp* kl, const uint8_t* dl, int nl, const DropKp* kr, const uint8_t* dr, int nr, const float* scale,
                   int n_levels, int n_rows, float min_d, float max_d, int32_t* best_idx, int32_t* best_dist) {
   try {
@@ -153,3 +87,9 @@ int dropin_stereo(const DropKp* kl, const uint8_t* dl, int nl, const DropKp* kr,
 }
 
 }  // extern "C"
+
+// ---- matcher scenes shared with the reference build (oracle/ref_match_harness.cc)
+float ORB_SLAM2::Frame::mnMinX, ORB_SLAM2::Frame::mnMinY, ORB_SLAM2::Frame::mnMaxX, ORB_SLAM2::Frame::mnMaxY;
+float ORB_SLAM2::Frame::mfGridElementWidthInv, ORB_SLAM2::Frame::mfGridElementHeightInv;
+#define SCN(name) dropin_##name
+#include "matcher_scenes.inc"
