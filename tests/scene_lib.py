@@ -190,6 +190,9 @@ def _declare(L, prefix):
     g("sbp_sim3_kf").argtypes = [fp, _vp, pp, _vp, C.c_int, _vp, C.c_int]
     g("sbp_map").argtypes = [fp, pp, _vp, _vp, _f, _f, _vp, _vp, _vp]
     g("distance").argtypes = [_vp, _vp]
+    g("time_tracking_searches").argtypes = [fp, fp, pp, _vp, C.c_int, _f, _f, C.c_int, C.c_int, C.POINTER(C.c_double),
+                                            C.POINTER(C.c_double)]
+    g("time_tracking_searches").restype = C.c_double
     g("search_bow").argtypes = [_vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp,
                                 _f, C.c_int, C.c_int, _vp]
 
@@ -240,6 +243,17 @@ class Side:
         return dict(n=n, mp=mp, matched=mt, reloc=rel)
 
 
+def time_tracking(side, cur, last, P, order, th_last=15.0, th_local=1.0, mono=True, reps=30):
+    """(us SearchByProjection(cur, last), us SearchByProjection(cur, local points)), medians."""
+    order = np.ascontiguousarray(order, np.int32)
+    a, b = C.c_double(0), C.c_double(0)
+    rc = getattr(side.L, side.prefix + "time_tracking_searches")(C.byref(cur.c), C.byref(last.c), C.byref(P.c), _p(order),
+                                                                 len(order), th_last, th_local, int(mono), reps, C.byref(a), C.byref(b))
+    if rc <= -1000000:
+        raise RuntimeError("timing scene failed")
+    return a.value, b.value
+
+
 def ref_side(fast=False):
     path = REF_FAST_PATH if fast else REF_PATH
     if not os.path.exists(path):
@@ -251,6 +265,12 @@ def dropin_side():
     import dropin_lib
     dropin_lib.load()
     return Side(C.CDLL(dropin_lib.PATH), "dropin_")
+
+
+def port_side():
+    import subprocess
+    subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "cpp"), "_build/libdropin_port.so"], stdout=subprocess.DEVNULL)
+    return Side(C.CDLL(PORT_PATH), "portm_")
 
 
 def assert_same(a, b, what=""):

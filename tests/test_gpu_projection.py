@@ -1,10 +1,11 @@
-"""The five ORBmatcher::SearchByProjection overloads of the PRODUCT header (include/ORBmatcher.h,
-descriptor work on the GPU through orbm_window_search) against the REFERENCE's own
-src/ORBmatcher.cc compiled unmodified (oracle/_ref/libmatchref.so), on identical scenes.
-Every output (match count, mvpMapPoints, search radii, matched flags) must be equal."""
-import numpy as np
+"""The five ORBmatcher::SearchByProjection overloads, both SearchByBoW overloads and DescriptorDistance
+of the PRODUCT header (include/ORBmatcher.h, descriptor work on the GPU through liborbfront.so)
+against the REFERENCE's own src/ORBmatcher.cc compiled unmodified (oracle/_ref/libmatchref.so), on
+identical scenes (tests/projection_cases.py).  Every output (match count, mvpMapPoints, search
+radii, matched flags) must be equal."""
 import pytest
 
+import projection_cases as pc
 import scene_lib as sl
 
 pytestmark = pytest.mark.gpu
@@ -18,126 +19,35 @@ def sides():
     return ref, sl.dropin_side()
 
 
-def frustum_fields(W, T, rng):
-    """What Frame::isInFrustum (Frame.cc:283-340) leaves in the MapPoints before SearchLocalPoints."""
-    u, v, z = W.project(T)
-    Ow = -T[:3, :3].T @ T[:3, 3]
-    dist = np.linalg.norm(W.pos - Ow, axis=1)
-    level = np.clip(np.ceil(np.log(W.max_dist / dist) / np.log(W.scale)), 0, W.n_levels - 1)
-    inside = (z > 0) & (u >= 0) & (u < W.width) & (v >= 0) & (v < W.height)
-    return dict(in_view=inside & (rng.random(len(u)) < 0.9), proj_x=u, proj_y=v, proj_xr=u - W.cam["mbf"] / z, level=level,
-                view_cos=np.where(rng.random(len(u)) < 0.5, 0.9995, rng.uniform(0.5, 0.998, len(u))))
+LOCAL = [(s, th) for s in (False, True) for th in (1.0, 3.0, 5.0)]
+MOTION = [(m, s, th, mo) for (m, s) in ((True, False), (False, True)) for th in (7.0, 15.0, 30.0)
+          for mo in ("still", "forward", "backward")]
 
 
-@pytest.mark.parametrize("stereo", [False, True])
-@pytest.mark.parametrize("th", [1.0, 3.0, 5.0])
+@pytest.mark.parametrize("stereo,th", LOCAL)
 def test_search_local_points(sides, stereo, th):
-    ref, got = sides
-    W = sl.World(21 + int(th), stereo=stereo)
-    rng = np.random.default_rng(5)
-    T = sl.pose(rng)
-    F = W.observe(T, 77, assign=0.15)
-    P = W.points(track=frustum_fields(W, T, rng))
-    order = rng.permutation(P.n)[:1300]
-    a, b = ref.sbp_local(F, P, order, th), got.sbp_local(F, P, order, th)
-    assert a["n"] > 150
-    sl.assert_same(a, b, "SearchByProjection(F, vpMapPoints)")
+    pc.search_local_points(*sides, stereo, th)
 
 
-@pytest.mark.parametrize("mono,stereo", [(True, False), (False, True)])
-@pytest.mark.parametrize("th", [7.0, 15.0, 30.0])
-@pytest.mark.parametrize("motion", ["still", "forward", "backward"])
+@pytest.mark.parametrize("mono,stereo,th,motion", MOTION)
 def test_track_with_motion_model(sides, mono, stereo, th, motion):
-    ref, got = sides
-    W = sl.World(31, stereo=stereo)
-    rng = np.random.default_rng(int(th) + len(motion))
-    Tl = sl.pose(rng)
-    Tc = sl.pose(rng)
-    if motion != "still":  # move along the optical axis by more than the baseline (bForward / bBackward, :1547-1548)
-        Tc = Tl.copy()
-        Tc[2, 3] += -0.5 if motion == "forward" else 0.5
-    last = W.observe(Tl, 101, assign=0.8, outliers=0.05)
-    cur = W.observe(Tc, 102, assign=0.1)
-    P = W.points()
-    a = ref.sbp_last_frame(cur, last, P, th, mono)
-    b = got.sbp_last_frame(cur, last, P, th, mono)
-    assert a["n"] > 100
-    sl.assert_same(a, b, "SearchByProjection(CurrentFrame, LastFrame)")
-    a = ref.sbp_last_frame(cur, last, P, th, mono, check_ori=False)
-    b = got.sbp_last_frame(cur, last, P, th, mono, check_ori=False)
-    sl.assert_same(a, b, "SearchByProjection(CurrentFrame, LastFrame), no orientation check")
+    pc.track_with_motion_model(*sides, mono, stereo, th, motion)
 
 
 @pytest.mark.parametrize("th,orb_dist", [(10.0, 100), (3.0, 64)])
 def test_relocalization_refinement(sides, th, orb_dist):
-    ref, got = sides
-    W = sl.World(41)
-    rng = np.random.default_rng(9)
-    kf = W.observe(sl.pose(rng), 201, assign=0.85)
-    cur = W.observe(sl.pose(rng), 202, assign=0.2)
-    found = rng.choice(W.pos.shape[0], 200, replace=False)
-    P = W.points()
-    a = ref.sbp_reloc_kf(cur, kf, P, found, th, orb_dist)
-    b = got.sbp_reloc_kf(cur, kf, P, found, th, orb_dist)
-    assert a["n"] > 50
-    sl.assert_same(a, b, "SearchByProjection(CurrentFrame, pKF, sAlreadyFound)")
+    pc.relocalization_refinement(*sides, th, orb_dist)
 
 
 @pytest.mark.parametrize("scale", [1.0, 1.25])
 def test_loop_closure_sim3(sides, scale):
-    ref, got = sides
-    W = sl.World(51)
-    rng = np.random.default_rng(3)
-    T = sl.pose(rng)
-    kf = W.observe(T, 301, assign=0.3)
-    S = T.copy()
-    S[:3, :] *= np.float32(scale)  # Scw = [s R | s t]
-    P = W.points()
-    order = rng.permutation(P.n)[:1000]
-    matched = kf.mp.copy()
-    a = ref.sbp_sim3_kf(kf, S, P, order, matched, 10)
-    b = got.sbp_sim3_kf(kf, S, P, order, matched, 10)
-    assert a["n"] > 50
-    sl.assert_same(a, b, "SearchByProjection(pKF, Scw)")
+    pc.loop_closure_sim3(*sides, scale)
 
 
 @pytest.mark.parametrize("th", [1.0, 15.0])
 def test_map_wide_pose_candidate(sides, th):
-    ref, got = sides
-    W = sl.World(61, n_points=2500)
-    rng = np.random.default_rng(4)
-    T = sl.pose(rng)
-    F = W.observe(T, 401, assign=0.1)
-    P = W.points()
-    R, t = T[:3, :3].astype(np.float64), T[:3, 3].astype(np.float64)
-    a, b = ref.sbp_map(F, P, R, t, th), got.sbp_map(F, P, R, t, th)
-    assert a["n"] > 100
-    sl.assert_same(a, b, "SearchByProjection(F, pMap, Rcw, tcw)")
+    pc.map_wide_pose_candidate(*sides, th)
 
 
 def test_bow_and_distance_against_the_reference_source(sides):
-    """SearchByBoW x2 and DescriptorDistance of the product header against the reference's own code."""
-    import ctypes as C
-    import match_cases as mc
-    ref, got = sides
-    rng = np.random.default_rng(8)
-    d = rng.integers(0, 256, (64, 32), dtype=np.uint8)
-    for i in range(0, 64, 2):
-        assert ref.L.refm_distance(d[i].ctypes.data, d[i + 1].ctypes.data) == got.L.dropin_distance(d[i].ctypes.data, d[i + 1].ctypes.data)
-    for kf_kf in (0, 1):
-        for check_ori in (0, 1):
-            case = mc.bow_case(17 + kf_kf, n1=900, n2=950, n_nodes=60)
-            n1, off1, i1 = mc.flat_fv(case["fv1"])
-            n2, off2, i2 = mc.flat_fv(case["fv2"])
-            st1 = np.where(case["v1"] > 0, 1, rng.integers(0, 3, len(case["v1"])) * 2 % 4 // 2 * 2).astype(np.uint8)
-            st2 = np.where(case["v2"] > 0, 1, 0).astype(np.uint8)
-            outs = []
-            for side in (ref, got):
-                out = np.zeros(len(case["d1"]) if kf_kf else len(case["d2"]), np.int32)
-                p = lambda a: a.ctypes.data
-                nm = side._call("search_bow", p(case["d1"]), len(case["d1"]), p(case["d2"]), len(case["d2"]), p(n1), p(off1), p(i1),
-                                len(n1), p(n2), p(off2), p(i2), len(n2), p(st1), p(st2), p(case["a1"]), p(case["a2"]), 0.75,
-                                check_ori, kf_kf, p(out))
-                outs.append((nm, out))
-            assert outs[0][0] == outs[1][0] and outs[0][0] > 50
-            assert np.array_equal(outs[0][1], outs[1][1])
+    pc.bow_and_distance(*sides)

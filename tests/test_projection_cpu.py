@@ -1,0 +1,52 @@
+"""CPU half of the matcher pin: the product header (include/ORBmatcher.h) over the CPU restatement
+(tests/cpp/port_scenes.cc -> oracle/match_port.hpp) against the reference's own src/ORBmatcher.cc
+(oracle/_ref/libmatchref.so) on the scenes of tests/projection_cases.py.  Equality here pins the
+restatement -- window_search, search_bow, hamming256 -- on the reference's code, and checks the
+header's host-side logic without a GPU; tests/test_gpu_window.py and test_gpu_match.py then hold
+the CUDA kernels to the restatement, and tests/test_gpu_projection.py to the reference directly."""
+import pytest
+
+import projection_cases as pc
+import scene_lib as sl
+
+
+@pytest.fixture(scope="module")
+def sides():
+    ref = sl.ref_side()
+    if ref is None:
+        pytest.skip("oracle/_ref/libmatchref.so not built (needs /root/reference at build time)")
+    return ref, sl.port_side()
+
+
+LOCAL = [(s, th) for s in (False, True) for th in (1.0, 3.0, 5.0)]
+MOTION = [(m, s, th, mo) for (m, s) in ((True, False), (False, True)) for th in (7.0, 15.0, 30.0)
+          for mo in ("still", "forward", "backward")]
+
+
+@pytest.mark.parametrize("stereo,th", LOCAL)
+def test_search_local_points(sides, stereo, th):
+    pc.search_local_points(*sides, stereo, th)
+
+
+@pytest.mark.parametrize("mono,stereo,th,motion", MOTION)
+def test_track_with_motion_model(sides, mono, stereo, th, motion):
+    pc.track_with_motion_model(*sides, mono, stereo, th, motion)
+
+
+@pytest.mark.parametrize("th,orb_dist", [(10.0, 100), (3.0, 64)])
+def test_relocalization_refinement(sides, th, orb_dist):
+    pc.relocalization_refinement(*sides, th, orb_dist)
+
+
+@pytest.mark.parametrize("scale", [1.0, 1.25])
+def test_loop_closure_sim3(sides, scale):
+    pc.loop_closure_sim3(*sides, scale)
+
+
+@pytest.mark.parametrize("th", [1.0, 15.0])
+def test_map_wide_pose_candidate(sides, th):
+    pc.map_wide_pose_candidate(*sides, th)
+
+
+def test_bow_and_distance_against_the_reference_source(sides):
+    pc.bow_and_distance(*sides)
