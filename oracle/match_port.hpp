@@ -1,8 +1,7 @@
 // oracle/match_port.hpp -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
 //
 // CPU restatement of the reference's descriptor-search paths on flat arrays.
-// src/ORBmatcher.cc cannot be compiled here (it pulls Frame/KeyFrame/MapPoint -> Eigen,
-// DBoW2, g2o; none installed), so this follows it line by line instead:
+// It follows src/ORBmatcher.cc line by line:
 //   hamming256          ORBmatcher.cc:1848-1864 (DescriptorDistance)
 //   top2 update         ORBmatcher.cc:417-426
 //   search_bow_kf_frame ORBmatcher.cc:360-489
@@ -11,8 +10,12 @@
 //   stereo_search       Frame.cc:527-610 (descriptor part of ComputeStereoMatches)
 //   features_in_area    Frame.cc:342-395 (GetFeaturesInArea)
 //   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
-// Parity status: unpinned by the reference (it ships no tests); pinned here by
-// known-answer vectors in tests/test_oracle_match.py (numpy popcount cross-check).
+// Parity status: hamming256, search_bow (both overloads) and window_search are pinned on the
+// reference's own src/ORBmatcher.cc compiled unmodified over mocks (oracle/_ref/libmatchref.so):
+// tests/test_projection_cpu.py runs the product header over this restatement against it on 31
+// scenes.  top2_bruteforce / merge_top2 (no such function in the reference) and stereo_search
+// (Frame.cc is not compilable here) stay "parity unpinned": known answers + an independent numpy
+// model in tests/test_oracle_match.py.
 #pragma once
 #include <algorithm>
 #include <cmath>
