@@ -18,9 +18,12 @@
  * The projection searches keep the pose / camera / MapPoint arithmetic on the host, written with
  * the includer's cv::Mat exactly as the reference evaluates it, and hand the descriptor work --
  * grid gather, Hamming top-2, acceptance and the order-dependent hiding of matched keypoints --
- * to orbm_window_search.  SearchBySim3, Fuse x2, SearchForTriangulation and
- * SearchForInitialization stay declared and keep their definitions in the reference's
- * ORBmatcher.cc; INTEGRATION.md lists the definitions to delete from that file.
+ * to orbm_window_search.  Same for
+ *     Fuse(KeyFrame*, const vector<MapPoint*>&, float)                     src/ORBmatcher.cc:1026-1176
+ *     Fuse(KeyFrame*, cv::Mat Scw, ..., vector<MapPoint*>& vpReplacePoint) src/ORBmatcher.cc:1178-1301
+ *     SearchBySim3(KeyFrame*, KeyFrame*, ..., s12, R12, t12, th)           src/ORBmatcher.cc:1303-1527
+ * SearchForTriangulation and SearchForInitialization stay declared and keep their definitions
+ * in the reference's ORBmatcher.cc; INTEGRATION.md lists the definitions to delete from that file.
  *
  * Like the reference header, this one includes MapPoint.h / KeyFrame.h / Frame.h from the
  * includer's path (the reference's own in its build; tests/cpp/mock in this repo's tests).
@@ -219,13 +222,17 @@ class ORBmatcher {
       src.push_back(source);
     }
     std::vector<orbm_window_result> Run(const FlatGrid& g, std::vector<uint8_t> hidden, int th, float ratio, bool claim,
-                                        const char* what) const {
+                                        const char* what, const std::vector<float>* invLevelSigma2 = NULL) const {
       std::vector<orbm_window_result> res(q.size());
       int n = 0;
       hidden.resize((size_t)g.c.n, 0);
+      orbm_window_params prm;
+      prm.th = th; prm.ratio = ratio; prm.claim = claim ? 1 : 0;
+      prm.inv_level_sigma2 = invLevelSigma2 ? invLevelSigma2->data() : NULL;
+      prm.n_levels = invLevelSigma2 ? (int32_t)invLevelSigma2->size() : 0;
+      prm.chi2_mono = 5.99; prm.chi2_stereo = 7.8;  // src/ORBmatcher.cc:1131,1143
       if (!q.empty())
-        Check(orbm_window_search(Device(), &g.c, q.data(), desc.data(), (int)q.size(), hidden.data(), th, ratio, claim ? 1 : 0,
-                                 res.data(), &n, NULL),
+        Check(orbm_window_search(Device(), &g.c, q.data(), desc.data(), (int)q.size(), hidden.data(), &prm, res.data(), &n, NULL),
               what);
       return res;
     }
@@ -571,6 +578,197 @@ inline int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, co
     }
   }
   return nmatches;
+}
+
+// Local map points into a neighbouring keyframe (LocalMapping::SearchInNeighbors).
+// src/ORBmatcher.cc:1026-1176.  The search reads only the keyframe's keypoints, so all points are
+// searched at once; the bookkeeping (Replace / AddObservation / AddMapPoint) then runs in the
+// reference's order, re-testing the two skip conditions that earlier iterations can switch on.
+inline int ORBmatcher::Fuse(KeyFrame* pKF, const vector<MapPoint*>& vpMapPoints, const float th) {
+  cv::Mat Rcw = pKF->GetRotation();
+  cv::Mat tcw = pKF->GetTranslation();
+  const float &fx = pKF->fx, &fy = pKF->fy, &cx = pKF->cx, &cy = pKF->cy, &bf = pKF->mbf;
+  cv::Mat Ow = pKF->GetCameraCenter();
+  const int nMPs = (int)vpMapPoints.size();
+  WindowQueries W;
+  for (int i = 0; i < nMPs; i++) {
+    MapPoint* pMP = vpMapPoints[i];
+    if (!pMP) continue;
+    if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;  // both only ever turn on: safe to test early, re-tested below
+    cv::Mat p3Dw = pMP->GetWorldPos();
+    cv::Mat p3Dc = Rcw * p3Dw + tcw;
+    if (p3Dc.at<float>(2) < 0.0f) continue;
+    const float invz = 1 / p3Dc.at<float>(2);
+    const float x = p3Dc.at<float>(0) * invz;
+    const float y = p3Dc.at<float>(1) * invz;
+    const float u = fx * x + cx;
+    const float v = fy * y + cy;
+    if (!pKF->IsInImage(u, v)) continue;
+    const float ur = u - bf * invz;
+    const float maxDistance = pMP->GetMaxDistanceInvariance();
+    const float minDistance = pMP->GetMinDistanceInvariance();
+    cv::Mat PO = p3Dw - Ow;
+    const float dist3D = cv::norm(PO);
+    if (dist3D < minDistance || dist3D > maxDistance) continue;
+    cv::Mat Pn = pMP->GetNormal();
+    if (PO.dot(Pn) < 0.5 * dist3D) continue;
+    const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+    const float radius = th * pKF->mvScaleFactors[nPredictedLevel];
+    W.Add(pMP, pMP->GetDescriptor(), u, v, radius, nPredictedLevel - 1, nPredictedLevel, ur, -1.f, false, i);
+  }
+  const FlatGrid grid(*pKF);
+  const std::vector<orbm_window_result> res =
+      W.Run(grid, std::vector<uint8_t>(), TH_LOW, 0.f, false, "ORBmatcher::Fuse", &pKF->mvInvLevelSigma2);
+  int nFused = 0;
+  for (size_t k = 0; k < res.size(); ++k) {
+    MapPoint* pMP = W.mp[k];
+    if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;  // :1047-1048, as of this iteration
+    const int bestIdx = res[k].idx;
+    if (bestIdx < 0) continue;
+    MapPoint* pMPinKF = pKF->GetMapPoint(bestIdx);  // :1149-1167
+    if (pMPinKF) {
+      if (!pMPinKF->isBad()) {
+        if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+        else pMPinKF->Replace(pMP);
+      }
+    } else {
+      pMP->AddObservation(pKF, bestIdx);
+      pKF->AddMapPoint(pMP, bestIdx);
+    }
+    nFused++;
+  }
+  return nFused;
+}
+
+// Loop-closure points into a keyframe under a corrected Sim3 (LoopClosing::SearchAndFuse).
+// src/ORBmatcher.cc:1178-1301
+inline int ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th,
+                            vector<MapPoint*>& vpReplacePoint) {
+  const float &fx = pKF->fx, &fy = pKF->fy, &cx = pKF->cx, &cy = pKF->cy;
+  cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+  const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+  cv::Mat Rcw = sRcw / scw;
+  cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+  cv::Mat Ow = -Rcw.t() * tcw;
+  const std::set<MapPoint*> spAlreadyFound = pKF->GetMapPoints();
+  const int nPoints = (int)vpPoints.size();
+  WindowQueries W;
+  for (int iMP = 0; iMP < nPoints; iMP++) {
+    MapPoint* pMP = vpPoints[iMP];
+    if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+    cv::Mat p3Dw = pMP->GetWorldPos();
+    cv::Mat p3Dc = Rcw * p3Dw + tcw;
+    if (p3Dc.at<float>(2) < 0.0f) continue;
+    const float invz = 1.0 / p3Dc.at<float>(2);
+    const float x = p3Dc.at<float>(0) * invz;
+    const float y = p3Dc.at<float>(1) * invz;
+    const float u = fx * x + cx;
+    const float v = fy * y + cy;
+    if (!pKF->IsInImage(u, v)) continue;
+    const float maxDistance = pMP->GetMaxDistanceInvariance();
+    const float minDistance = pMP->GetMinDistanceInvariance();
+    cv::Mat PO = p3Dw - Ow;
+    const float dist3D = cv::norm(PO);
+    if (dist3D < minDistance || dist3D > maxDistance) continue;
+    cv::Mat Pn = pMP->GetNormal();
+    if (PO.dot(Pn) < 0.5 * dist3D) continue;
+    const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+    const float radius = th * pKF->mvScaleFactors[nPredictedLevel];
+    W.Add(pMP, pMP->GetDescriptor(), u, v, radius, nPredictedLevel - 1, nPredictedLevel, 0.f, -1.f, false, iMP);
+  }
+  const FlatGrid grid(*pKF);
+  const std::vector<orbm_window_result> res = W.Run(grid, std::vector<uint8_t>(), TH_LOW, 0.f, false, "ORBmatcher::Fuse");
+  int nFused = 0;
+  for (size_t k = 0; k < res.size(); ++k) {
+    const int bestIdx = res[k].idx;
+    if (bestIdx < 0) continue;
+    MapPoint* pMP = W.mp[k];
+    MapPoint* pMPinKF = pKF->GetMapPoint(bestIdx);  // :1281-1292
+    if (pMPinKF) {
+      if (!pMPinKF->isBad()) vpReplacePoint[W.src[k]] = pMPinKF;
+    } else {
+      pMP->AddObservation(pKF, bestIdx);
+      pKF->AddMapPoint(pMP, bestIdx);
+    }
+    nFused++;
+  }
+  return nFused;
+}
+
+// Mutual projection search between two keyframes under a Sim3 (LoopClosing::ComputeSim3).
+// src/ORBmatcher.cc:1303-1527
+inline int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12,
+                                    const cv::Mat& R12, const cv::Mat& t12, const float th) {
+  const float &fx = pKF1->fx, &fy = pKF1->fy, &cx = pKF1->cx, &cy = pKF1->cy;
+  cv::Mat R1w = pKF1->GetRotation();
+  cv::Mat t1w = pKF1->GetTranslation();
+  cv::Mat R2w = pKF2->GetRotation();
+  cv::Mat t2w = pKF2->GetTranslation();
+  cv::Mat sR12 = s12 * R12;
+  cv::Mat sR21 = (1.0 / s12) * R12.t();
+  cv::Mat t21 = -sR21 * t12;
+  const std::vector<MapPoint*> vpMapPoints1 = pKF1->GetMapPointMatches();
+  const int N1 = (int)vpMapPoints1.size();
+  const std::vector<MapPoint*> vpMapPoints2 = pKF2->GetMapPointMatches();
+  const int N2 = (int)vpMapPoints2.size();
+  std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+  for (int i = 0; i < N1; i++) {
+    MapPoint* pMP = vpMatches12[i];
+    if (pMP) {
+      vbAlreadyMatched1[i] = true;
+      const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+      if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+    }
+  }
+  // one direction: points of `from` (already in its camera frame through Rfw, tfw) into `into`
+  struct Direction {
+    static std::vector<int> Search(const std::vector<MapPoint*>& vpMapPoints, const std::vector<bool>& vbAlreadyMatched,
+                                   const cv::Mat& Rfw, const cv::Mat& tfw, const cv::Mat& sR, const cv::Mat& t, KeyFrame* into,
+                                   float fx, float fy, float cx, float cy, float th) {
+      const int N = (int)vpMapPoints.size();
+      WindowQueries W;
+      for (int i = 0; i < N; i++) {
+        MapPoint* pMP = vpMapPoints[i];
+        if (!pMP || vbAlreadyMatched[i]) continue;
+        if (pMP->isBad()) continue;
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dcf = Rfw * p3Dw + tfw;
+        cv::Mat p3Dc = sR * p3Dcf + t;
+        if (p3Dc.at<float>(2) < 0.0) continue;
+        const float invz = 1.0 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz;
+        const float y = p3Dc.at<float>(1) * invz;
+        const float u = fx * x + cx;
+        const float v = fy * y + cy;
+        if (!into->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance();
+        const float minDistance = pMP->GetMinDistanceInvariance();
+        const float dist3D = cv::norm(p3Dc);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const int nPredictedLevel = pMP->PredictScale(dist3D, into);
+        const float radius = th * into->mvScaleFactors[nPredictedLevel];
+        W.Add(pMP, pMP->GetDescriptor(), u, v, radius, nPredictedLevel - 1, nPredictedLevel, 0.f, -1.f, false, i);
+      }
+      const FlatGrid grid(*into);
+      const std::vector<orbm_window_result> res =
+          W.Run(grid, std::vector<uint8_t>(), TH_HIGH, 0.f, false, "ORBmatcher::SearchBySim3");
+      std::vector<int> vnMatch(N, -1);
+      for (size_t k = 0; k < res.size(); ++k)
+        if (res[k].idx >= 0) vnMatch[W.src[k]] = res[k].idx;
+      return vnMatch;
+    }
+  };
+  const std::vector<int> vnMatch1 = Direction::Search(vpMapPoints1, vbAlreadyMatched1, R1w, t1w, sR21, t21, pKF2, fx, fy, cx, cy, th);
+  const std::vector<int> vnMatch2 = Direction::Search(vpMapPoints2, vbAlreadyMatched2, R2w, t2w, sR12, t12, pKF1, fx, fy, cx, cy, th);
+  int nFound = 0;  // :1510-1524: keep what both directions agree on
+  for (int i1 = 0; i1 < N1; i1++) {
+    const int idx2 = vnMatch1[i1];
+    if (idx2 >= 0 && vnMatch2[idx2] == i1) {
+      vpMatches12[i1] = vpMapPoints2[idx2];
+      nFound++;
+    }
+  }
+  return nFound;
 }
 
 inline void ORBmatcher::StereoSearch(const std::vector<cv::KeyPoint>& keysLeft, const cv::Mat& descLeft,

@@ -210,7 +210,8 @@ int orbm_stereo_search(int device, const orbx_keypoint* left, const uint8_t* lde
 
 /* ---- Windowed projection searches -------------------------------------------
  * One primitive behind the five ORBmatcher::SearchByProjection overloads (src/ORBmatcher.cc:46-132,
- * :134-220, :491-604, :1529-1671, :1673-1800): for every projected query, gather the keypoints of
+ * :134-220, :491-604, :1529-1671, :1673-1800), both Fuse overloads (:1026-1176, :1178-1301) and SearchBySim3
+ * (:1303-1527): for every projected query, gather the keypoints of
  * a frame inside a square window through the frame's cell grid (Frame::GetFeaturesInArea,
  * src/Frame.cc:342-395; KeyFrame::GetFeaturesInArea, src/KeyFrame.cc:613-652), keep the best and
  * second-best Hamming distance in the reference's scan order, apply its acceptance rule, and
@@ -248,15 +249,28 @@ typedef struct orbm_window_result {
   int32_t best_level, best_level2; /* -1 when absent */
 } orbm_window_result;
 
+typedef struct orbm_window_params {
+  int32_t th;      /* accept iff best_dist <= th */
+  float ratio;     /* > 0: also reject when best_level == best_level2 && best_dist > ratio * best_dist2
+                      (src/ORBmatcher.cc:119-123); <= 0: distance test only (:1622, :1759, :595) */
+  int32_t claim;   /* nonzero: an accepted query with `blocks` hides its keypoint from later queries;
+                      0: matches never hide keypoints (:180-181, :1148, :1276: separate outputs) */
+  /* Reprojection gate of ORBmatcher::Fuse (src/ORBmatcher.cc:1118-1146), off when inv_level_sigma2
+   * is NULL: a candidate with mvuRight >= 0 is skipped when
+   * ((x-kx)^2 + (y-ky)^2 + (u_right-kr)^2) * inv_level_sigma2[octave] > chi2_stereo, any other when
+   * ((x-kx)^2 + (y-ky)^2) * inv_level_sigma2[octave] > chi2_mono (float products, double compare). */
+  const float* inv_level_sigma2; /* n_levels: mvInvLevelSigma2 */
+  int32_t n_levels;
+  double chi2_mono, chi2_stereo; /* 5.99, 7.8 */
+} orbm_window_params;
+
 /* claimed: n flags (keypoints hidden from every query, e.g. mvpMapPoints already set) or NULL.
- * Acceptance: best_dist <= th, and, when ratio > 0, not (best_level == best_level2 &&
- * best_dist > ratio * best_dist2)  (src/ORBmatcher.cc:119-123).  ratio <= 0: distance test only
- * (:1622, :1759, :595).  claim = 0: accepted matches never hide keypoints (:180-181, separate
- * output vector).  out has nq entries; *n_accepted counts idx >= 0; *rounds (may be NULL) reports
- * how many parallel passes the order-exact resolution took. */
+ * out has nq entries; *n_accepted counts idx >= 0; *rounds (may be NULL) reports how many parallel
+ * passes the order-exact resolution took. */
 int orbm_window_search(int device, const orbm_grid_frame* frame, const orbm_window_query* queries,
-                       const uint8_t* query_desc, int nq, const uint8_t* claimed, int th, float ratio,
-                       int claim, orbm_window_result* out, int* n_accepted, int* rounds);
+                       const uint8_t* query_desc, int nq, const uint8_t* claimed,
+                       const orbm_window_params* params, orbm_window_result* out, int* n_accepted,
+                       int* rounds);
 
 /* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
  * denominator of the matching roofline.  Returns 32-bit POPC per second. */

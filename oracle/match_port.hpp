@@ -253,8 +253,12 @@ struct WindowResult { int idx, best_idx, best_dist, best_dist2, best_level, best
 // ratio <= 0 is the best-only loop of :1553-1640, :1687-1775 and :511-601.  `hidden[k]` plays
 // mvpMapPoints[k] (with Observations() > 0): set before the call for keypoints already matched,
 // and set by an accepted query whose MapPoint blocks (claim mode).
+// Optional reprojection gate: the candidate test of ORBmatcher::Fuse, ORBmatcher.cc:1118-1146.
+struct WindowGate { const float* inv_level_sigma2; double chi2_mono, chi2_stereo; };
+
 static inline int window_search(const GridFrame& F, const WindowQuery* q, const uint8_t* qdesc, int nq,
-                                const uint8_t* claimed, int th, float ratio, bool claim, WindowResult* out) {
+                                const uint8_t* claimed, int th, float ratio, bool claim, WindowResult* out,
+                                const WindowGate* gate = nullptr) {
   std::vector<uint8_t> hidden(F.n, 0);
   if (claimed) for (int k = 0; k < F.n; ++k) hidden[k] = claimed[k] != 0;
   std::vector<int> vIndices;
@@ -269,6 +273,23 @@ static inline int window_search(const GridFrame& F, const WindowQuery* q, const 
       if (Q.er_max >= 0 && F.u_right && F.u_right[idx] > 0) {  // :85-90
         const float er = fabs(Q.u_right - F.u_right[idx]);
         if (er > Q.er_max) continue;
+      }
+      if (gate) {
+        const int kpLevel = F.octave[idx];
+        const float u = Q.x, v = Q.y, ur = Q.u_right;
+        const float kpr = F.u_right ? F.u_right[idx] : -1.0f;
+        if (kpr >= 0) {
+          const float ex = u - F.x[idx];
+          const float ey = v - F.y[idx];
+          const float er = ur - kpr;
+          const float e2 = ex * ex + ey * ey + er * er;
+          if (e2 * gate->inv_level_sigma2[kpLevel] > gate->chi2_stereo) continue;
+        } else {
+          const float ex = u - F.x[idx];
+          const float ey = v - F.y[idx];
+          const float e2 = ex * ex + ey * ey;
+          if (e2 * gate->inv_level_sigma2[kpLevel] > gate->chi2_mono) continue;
+        }
       }
       const int dist = hamming256(qdesc + 32 * (size_t)i, F.desc + 32 * (size_t)idx);
       if (dist < bestDist) {  // :97-110

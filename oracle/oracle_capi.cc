@@ -154,9 +154,11 @@ void orc_stereo_search(const float* lx, const float* ly, const int* loct, const 
 int orc_window_search(const float* x, const float* y, const int* octave, const float* u_right, const uint8_t* desc, int n,
                       float min_x, float min_y, float width_inv, float height_inv, int cols, int rows,
                       const int* cell_off, const uint32_t* cell_idx, const void* queries, const uint8_t* qdesc, int nq,
-                      const uint8_t* claimed, int th, float ratio, int claim, void* out) {
+                      const uint8_t* claimed, int th, float ratio, int claim, void* out, const float* inv_level_sigma2,
+                      double chi2_mono, double chi2_stereo) {
   matchport::GridFrame F{x, y, octave, u_right, desc, n, min_x, min_y, width_inv, height_inv, cols, rows, cell_off, cell_idx};
+  matchport::WindowGate gate{inv_level_sigma2, chi2_mono, chi2_stereo};
   return matchport::window_search(F, (const matchport::WindowQuery*)queries, qdesc, nq, claimed, th, ratio, claim != 0,
-                                  (matchport::WindowResult*)out);
+                                  (matchport::WindowResult*)out, inv_level_sigma2 ? &gate : nullptr);
 }
 }

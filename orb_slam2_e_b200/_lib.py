@@ -43,6 +43,11 @@ class GridFrame(C.Structure):  # orbm_grid_frame
                 ("cell_off", C.c_void_p), ("cell_idx", C.c_void_p)]
 
 
+class WindowParams(C.Structure):  # orbm_window_params
+    _fields_ = [("th", C.c_int32), ("ratio", C.c_float), ("claim", C.c_int32), ("inv_level_sigma2", C.c_void_p),
+                ("n_levels", C.c_int32), ("chi2_mono", C.c_double), ("chi2_stereo", C.c_double)]
+
+
 _lib = None
 
 _vp, _i, _f, _sz, _i64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64
@@ -86,7 +91,7 @@ SIGNATURES = {
     "orbm_search_bow": (_i, [_i, _vp, _i, _vp, _i, C.POINTER(FeatVec), C.POINTER(FeatVec), _vp, _vp, _vp, _vp, _f,
                              _i, _i, _vp, _ip]),
     "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),
-    "orbm_window_search": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _i, _f, _i, _vp, _ip, _ip]),
+    "orbm_window_search": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, C.POINTER(WindowParams), _vp, _ip, _ip]),
     "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),
 }
 

@@ -46,6 +46,8 @@ struct WinArgs {
   int th;
   float ratio;
   int max_rounds;  // 1: no claims, single pass
+  const float* inv_sigma2;  // Fuse's reprojection gate, or null
+  double chi2_mono, chi2_stereo;
 };
 
 __device__ __forceinline__ int hamming256(const uint32_t (&q)[8], const uint4 a, const uint4 b) {
@@ -100,6 +102,17 @@ __global__ void __launch_bounds__(kWinWarps * 32) window_search_kernel(const Win
             if (!(fabsf(r.x - Q.x) < Q.r && fabsf(r.y - Q.y) < Q.r)) continue;                           // :384-388
             if (__ldcg(&cur[pos]) < qi) continue;  // hidden: claimed before the call, or owned by an earlier query
             if (Q.er_max >= 0.0f && r.z > 0.0f && fabsf(Q.u_right - r.z) > Q.er_max) continue;  // ORBmatcher.cc:90-95
+            if (A.inv_sigma2) {  // ORBmatcher.cc:1118-1146
+              const float ex = Q.x - r.x, ey = Q.y - r.y;
+              if (r.z >= 0.0f) {
+                const float er = Q.u_right - r.z;
+                const float e2 = ex * ex + ey * ey + er * er;
+                if ((double)(e2 * __ldg(&A.inv_sigma2[oct])) > A.chi2_stereo) continue;
+              } else {
+                const float e2 = ex * ex + ey * ey;
+                if ((double)(e2 * __ldg(&A.inv_sigma2[oct])) > A.chi2_mono) continue;
+              }
+            }
             const uint32_t key = ((uint32_t)hamming256(qd, __ldg(&A.desc[2 * pos]), __ldg(&A.desc[2 * pos + 1])) << kPosBits) |
                                  (uint32_t)pos;
             const uint32_t hi = max(key, k1);
@@ -170,8 +183,13 @@ __global__ void __launch_bounds__(kWinWarps * 32) window_search_kernel(const Win
 using namespace orbfront;
 
 extern "C" int orbm_window_search(int device, const orbm_grid_frame* F, const orbm_window_query* queries,
-                                  const uint8_t* query_desc, int nq, const uint8_t* claimed, int th, float ratio,
-                                  int claim, orbm_window_result* out, int* n_accepted, int* rounds) {
+                                  const uint8_t* query_desc, int nq, const uint8_t* claimed, const orbm_window_params* prm,
+                                  orbm_window_result* out, int* n_accepted, int* rounds) {
+  if (!prm) return set_error(ORB_E_INVALID, "orbm_window_search: null params");
+  const int th = prm->th, claim = prm->claim;
+  const float ratio = prm->ratio;
+  const bool gate = prm->inv_level_sigma2 != nullptr;
+  if (gate && prm->n_levels < 1) return set_error(ORB_E_INVALID, "orbm_window_search: reprojection gate without levels");
   if (!F || nq < 0 || (nq > 0 && (!queries || !query_desc || !out)) || F->n < 0 || F->cols < 1 || F->rows < 1 ||
       !F->cell_off || (F->n > 0 && (!F->x || !F->y || !F->octave || !F->desc)))
     return set_error(ORB_E_INVALID, "orbm_window_search: bad argument");
@@ -192,7 +210,7 @@ extern "C" int orbm_window_search(int device, const orbm_grid_frame* F, const or
   const size_t o_rec = L.place((size_t)npos * 16), o_desc = L.place((size_t)npos * 32), o_feat = L.place((size_t)npos * 4),
                o_off = L.place((size_t)(n_cells + 1) * 4), o_q = L.place((size_t)nq * sizeof(orbm_window_query)),
                o_qd = L.place((size_t)nq * 32), o_init = L.place((size_t)npos * 4), o_owner = L.place((size_t)npos * 12),
-               o_ctrl = L.place(32);
+               o_ctrl = L.place(32), o_sig = L.place(gate ? (size_t)prm->n_levels * 4 : 0);
   const size_t o_up_end = L.bytes;  // device-only below, then the download block
   const size_t o_keys = L.place((size_t)nq * 8), o_acc = L.place(nq);
   const size_t o_out = L.place((size_t)nq * sizeof(orbm_window_result)), o_end = L.bytes;
@@ -216,6 +234,8 @@ extern "C" int orbm_window_search(int device, const orbm_grid_frame* F, const or
     rec[4 * p + 1] = F->y[f];
     rec[4 * p + 2] = F->u_right ? F->u_right[f] : -1.0f;
     memcpy(&rec[4 * p + 3], &F->octave[f], 4);
+    if (gate && (F->octave[f] < 0 || F->octave[f] >= prm->n_levels))
+      return set_error(ORB_E_INVALID, "orbm_window_search: keypoint %u has octave %d outside the sigma table", f, F->octave[f]);
     memcpy(h + o_desc + (size_t)p * 32, F->desc + (size_t)f * 32, 32);
     feat[p] = (int)f;
     init[p] = (claimed && claimed[f]) ? -1 : INT_MAX;
@@ -225,6 +245,7 @@ extern "C" int orbm_window_search(int device, const orbm_grid_frame* F, const or
   memcpy(h + o_qd, query_desc, (size_t)nq * 32);
   for (int k = 0; k < 3; ++k) memcpy(h + o_owner + (size_t)k * npos * 4, init, (size_t)npos * 4);
   memset(h + o_ctrl, 0, 32);
+  if (gate) memcpy(h + o_sig, prm->inv_level_sigma2, (size_t)prm->n_levels * 4);
   ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_up_end, cudaMemcpyHostToDevice, S->stream));
 
   WinArgs A;
@@ -235,6 +256,8 @@ extern "C" int orbm_window_search(int device, const orbm_grid_frame* F, const or
   A.nq = nq; A.npos = npos; A.cols = F->cols; A.rows = F->rows;
   A.min_x = F->min_x; A.min_y = F->min_y; A.width_inv = F->width_inv; A.height_inv = F->height_inv;
   A.th = th; A.ratio = ratio;
+  A.inv_sigma2 = gate ? (const float*)(d + o_sig) : nullptr;
+  A.chi2_mono = prm->chi2_mono; A.chi2_stereo = prm->chi2_stereo;
   A.max_rounds = claim ? nq + 1 : 1;
   int grid = div_up(nq, kWinWarps);
   if (claim) {  // every CTA must be resident: the passes meet at a grid barrier

@@ -12,7 +12,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import FeatVec, GridFrame, TOP2_DTYPE, WINDOW_QUERY_DTYPE, WINDOW_RESULT_DTYPE, check, ptr
+from ._lib import FeatVec, GridFrame, WindowParams, TOP2_DTYPE, WINDOW_QUERY_DTYPE, WINDOW_RESULT_DTYPE, check, ptr
 
 TH_HIGH, TH_LOW, HISTO_LENGTH = 95, 45, 30  # ORBmatcher.cc:37-40
 
@@ -165,17 +165,21 @@ class FrameGrid:
 
 
 def window_search(frame: FrameGrid, queries, query_desc, claimed=None, th: int = TH_HIGH, ratio: float = 0.0,
-                  claim: bool = True, device: int = 0):
+                  claim: bool = True, device: int = 0, inv_level_sigma2=None, chi2_mono: float = 5.99, chi2_stereo: float = 7.8):
     """orbm_window_search: the descriptor loop of the SearchByProjection overloads
-    (ORBmatcher.cc:46-132, :134-220, :491-604, :1529-1800).  Returns (results, n_accepted, passes)."""
+    (ORBmatcher.cc:46-132, :134-220, :491-604, :1529-1800); with inv_level_sigma2 also the
+    reprojection gate of Fuse (:1118-1146).  Returns (results, n_accepted, passes)."""
     q = np.ascontiguousarray(queries, WINDOW_QUERY_DTYPE)
     qd = _desc(query_desc) if len(q) else np.zeros((0, 32), np.uint8)
     assert len(qd) == len(q)
     cl = None if claimed is None else np.ascontiguousarray(claimed, np.uint8)
     out = np.zeros(len(q), WINDOW_RESULT_DTYPE)
     na, rounds = C.c_int(0), C.c_int(0)
+    sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+    prm = WindowParams(int(th), float(ratio), int(bool(claim)), None if sig is None else ptr(sig), 0 if sig is None else len(sig),
+                       float(chi2_mono), float(chi2_stereo))
     check(_lib.load().orbm_window_search(device, C.byref(frame.c), ptr(q), ptr(qd), len(q), None if cl is None else ptr(cl),
-                                         int(th), float(ratio), int(bool(claim)), ptr(out), C.byref(na), C.byref(rounds)))
+                                         C.byref(prm), ptr(out), C.byref(na), C.byref(rounds)))
     return out, na.value, rounds.value
 
 

@@ -27,13 +27,15 @@ int orbm_search_bow(int, const uint8_t* desc1, int n1, const uint8_t* desc2, int
   return ORB_OK;
 }
 int orbm_window_search(int, const orbm_grid_frame* F, const orbm_window_query* q, const uint8_t* qd, int nq,
-                       const uint8_t* claimed, int th, float ratio, int claim, orbm_window_result* out, int* n_accepted, int* rounds) {
+                       const uint8_t* claimed, const orbm_window_params* prm, orbm_window_result* out, int* n_accepted,
+                       int* rounds) {
   static_assert(sizeof(orbm_window_query) == sizeof(matchport::WindowQuery), "query layout");
   static_assert(sizeof(orbm_window_result) == sizeof(matchport::WindowResult), "result layout");
   matchport::GridFrame G{F->x, F->y, F->octave, F->u_right, F->desc, F->n, F->min_x, F->min_y, F->width_inv, F->height_inv,
                          F->cols, F->rows, F->cell_off, F->cell_idx};
-  const int n = matchport::window_search(G, (const matchport::WindowQuery*)q, qd, nq, claimed, th, ratio, claim != 0,
-                                         (matchport::WindowResult*)out);
+  matchport::WindowGate gate{prm->inv_level_sigma2, prm->chi2_mono, prm->chi2_stereo};
+  const int n = matchport::window_search(G, (const matchport::WindowQuery*)q, qd, nq, claimed, prm->th, prm->ratio, prm->claim != 0,
+                                         (matchport::WindowResult*)out, prm->inv_level_sigma2 ? &gate : nullptr);
   if (n_accepted) *n_accepted = n;
   if (rounds) *rounds = 1;
   return ORB_OK;

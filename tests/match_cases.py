@@ -148,12 +148,13 @@ def window_case(seed, n=1500, nq=1200, width=640, height=480, n_levels=8, stereo
     return frame, q, qd, claimed
 
 
-def oracle_window(L, frame, q, qd, claimed, th, ratio, claim):
+def oracle_window(L, frame, q, qd, claimed, th, ratio, claim, inv_level_sigma2=None, chi2_mono=5.99, chi2_stereo=7.8):
     from orb_slam2_e_b200._lib import WINDOW_RESULT_DTYPE
     out = np.zeros(len(q), WINDOW_RESULT_DTYPE)
     ur = None if frame.u_right is None else frame.u_right.ctypes.data
     cl = None if claimed is None else claimed.ctypes.data
     nm = L.orc_window_search(frame.x, frame.y, frame.octave, ur, frame.desc, frame.n, frame.min_x, frame.min_y,
                              frame.width_inv, frame.height_inv, frame.cols, frame.rows, frame.cell_off, frame.cell_idx,
-                             q.ctypes.data, qd, len(q), cl, th, ratio, int(claim), out.ctypes.data)
+                             q.ctypes.data, qd, len(q), cl, th, ratio, int(claim), out.ctypes.data,
+                             None if inv_level_sigma2 is None else inv_level_sigma2.ctypes.data, chi2_mono, chi2_stereo)
     return nm, out

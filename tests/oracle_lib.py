@@ -70,7 +70,7 @@ def oracle(fast=False):
                                     C.c_float, C.c_float, i32p, i32p]
     L.orc_window_search.argtypes = [f32p, f32p, i32p, C.c_void_p, u8p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                     C.c_int, C.c_int, i32p, u32p, C.c_void_p, u8p, C.c_int, C.c_void_p, C.c_int, C.c_float,
-                                    C.c_int, C.c_void_p]
+                                    C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double]
     _cache[key] = L
     return L
 

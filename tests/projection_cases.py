@@ -114,3 +114,51 @@ def bow_and_distance(ref, got):
                 outs.append((nm, out))
             assert outs[0][0] == outs[1][0] and outs[0][0] > 50
             assert np.array_equal(outs[0][1], outs[1][1])
+
+
+def fuse_neighbors(ref, got, stereo, th):
+    """LocalMapping::SearchInNeighbors: the current keyframe's points into a neighbour (:557, :582)."""
+    W = sl.World(71, stereo=stereo)
+    rng = np.random.default_rng(12)
+    kf = W.observe(sl.pose(rng), 501, assign=0.5)
+    P = W.points()
+    order = rng.permutation(P.n)[:1100]
+    order[rng.random(len(order)) < 0.05] = -1          # NULL entries (:1044-1045)
+    order[10:20] = order[0:10]                         # duplicates: the second visit finds the point in the keyframe
+    a, b = ref.fuse(kf, P, order, th), got.fuse(kf, P, order, th)
+    assert a["n"] > 100 and (a["replaced"] >= 0).sum() > 10
+    sl.assert_same(a, b, "Fuse(pKF, vpMapPoints)")
+
+
+def fuse_loop(ref, got, scale):
+    """LoopClosing::SearchAndFuse (:599)."""
+    W = sl.World(72)
+    rng = np.random.default_rng(13)
+    T = sl.pose(rng)
+    kf = W.observe(T, 502, assign=0.4)
+    S = T.copy()
+    S[:3, :] *= np.float32(scale)
+    P = W.points()
+    order = rng.permutation(P.n)[:1000]
+    a, b = ref.fuse_sim3(kf, S, P, order), got.fuse_sim3(kf, S, P, order)
+    assert a["n"] > 100 and (a["replace"] >= 0).sum() > 10
+    sl.assert_same(a, b, "Fuse(pKF, Scw)")
+
+
+def sim3_mutual(ref, got, s12):
+    """LoopClosing::ComputeSim3 (:323): KF1 and KF2 see the same map from two poses; T12 maps camera 2 to camera 1."""
+    W = sl.World(73)
+    rng = np.random.default_rng(14)
+    T1, T2 = sl.pose(rng, 3.0, 0.2), sl.pose(rng, 3.0, 0.2)
+    kf1 = W.observe(T1, 503, assign=0.8)
+    kf2 = W.observe(T2, 504, assign=0.8)
+    T12 = T1.astype(np.float64) @ np.linalg.inv(T2.astype(np.float64))
+    R12, t12 = T12[:3, :3], T12[:3, 3] * s12
+    P = W.points()
+    m = np.full(kf1.n, -1, np.int32)
+    pre = np.flatnonzero(kf1.mp >= 0)[:40]
+    m[pre] = kf1.mp[pre]                                # already matched (:1336-1346)
+    a = ref.search_by_sim3(kf1, kf2, P, m, s12, R12, t12)
+    b = got.search_by_sim3(kf1, kf2, P, m, s12, R12, t12)
+    assert a["n"] > 50
+    sl.assert_same(a, b, "SearchBySim3")

@@ -190,6 +190,9 @@ def _declare(L, prefix):
     g("sbp_sim3_kf").argtypes = [fp, _vp, pp, _vp, C.c_int, _vp, C.c_int]
     g("sbp_map").argtypes = [fp, pp, _vp, _vp, _f, _f, _vp, _vp, _vp]
     g("distance").argtypes = [_vp, _vp]
+    g("fuse").argtypes = [fp, pp, _vp, C.c_int, _f, _vp, _vp, _vp, _vp]
+    g("fuse_sim3").argtypes = [fp, _vp, pp, _vp, C.c_int, _f, _vp, _vp, _vp]
+    g("search_by_sim3").argtypes = [fp, fp, pp, _vp, _f, _vp, _vp, _f]
     g("time_tracking_searches").argtypes = [fp, fp, pp, _vp, C.c_int, _f, _f, C.c_int, C.c_int, C.POINTER(C.c_double),
                                             C.POINTER(C.c_double)]
     g("time_tracking_searches").restype = C.c_double
@@ -252,6 +255,33 @@ def time_tracking(side, cur, last, P, order, th_last=15.0, th_local=1.0, mono=Tr
     if rc <= -1000000:
         raise RuntimeError("timing scene failed")
     return a.value, b.value
+
+
+def _more_side_methods():
+    def fuse(self, kf, P, order, th=3.0):
+        order = np.ascontiguousarray(order, np.int32)
+        kmp, rep, nobs, bad = np.zeros(kf.n, np.int32), np.zeros(P.n, np.int32), np.zeros(P.n, np.int32), np.zeros(P.n, np.uint8)
+        n = self._call("fuse", C.byref(kf.c), C.byref(P.c), _p(order), len(order), th, _p(kmp), _p(rep), _p(nobs), _p(bad))
+        return dict(n=n, kf_mp=kmp, replaced=rep, n_obs=nobs, bad=bad)
+
+    def fuse_sim3(self, kf, Scw, P, order, th=4.0):
+        order = np.ascontiguousarray(order, np.int32)
+        S = np.ascontiguousarray(Scw, np.float32)
+        kmp, rep, nobs = np.zeros(kf.n, np.int32), np.zeros(len(order), np.int32), np.zeros(P.n, np.int32)
+        n = self._call("fuse_sim3", C.byref(kf.c), _p(S), C.byref(P.c), _p(order), len(order), th, _p(kmp), _p(rep), _p(nobs))
+        return dict(n=n, kf_mp=kmp, replace=rep, n_obs=nobs)
+
+    def search_by_sim3(self, kf1, kf2, P, matches12, s12, R12, t12, th=7.5):
+        m = np.ascontiguousarray(matches12, np.int32).copy()
+        R = np.ascontiguousarray(R12, np.float32)
+        t = np.ascontiguousarray(t12, np.float32)
+        n = self._call("search_by_sim3", C.byref(kf1.c), C.byref(kf2.c), C.byref(P.c), _p(m), s12, _p(R), _p(t), th)
+        return dict(n=n, matches12=m)
+
+    Side.fuse, Side.fuse_sim3, Side.search_by_sim3 = fuse, fuse_sim3, search_by_sim3
+
+
+_more_side_methods()
 
 
 def ref_side(fast=False):

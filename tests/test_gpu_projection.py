@@ -51,3 +51,18 @@ def test_map_wide_pose_candidate(sides, th):
 
 def test_bow_and_distance_against_the_reference_source(sides):
     pc.bow_and_distance(*sides)
+
+
+@pytest.mark.parametrize("stereo,th", [(False, 3.0), (True, 3.0), (True, 6.0)])
+def test_fuse_into_neighbor_keyframe(sides, stereo, th):
+    pc.fuse_neighbors(*sides, stereo, th)
+
+
+@pytest.mark.parametrize("scale", [1.0, 1.2])
+def test_fuse_loop_points(sides, scale):
+    pc.fuse_loop(*sides, scale)
+
+
+@pytest.mark.parametrize("s12", [1.0, 1.15])
+def test_search_by_sim3(sides, s12):
+    pc.sim3_mutual(*sides, s12)

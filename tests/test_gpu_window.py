@@ -14,9 +14,9 @@ pytestmark = pytest.mark.gpu
 FIELDS = ("idx", "best_idx", "best_dist", "best_dist2", "best_level", "best_level2")
 
 
-def _check(frame, q, qd, claimed, th, ratio, claim):
-    want_n, want = mc.oracle_window(oracle(), frame, q, qd, claimed, th, ratio, claim)
-    got, got_n, passes = matcher.window_search(frame, q, qd, claimed, th, ratio, claim)
+def _check(frame, q, qd, claimed, th, ratio, claim, sigma=None):
+    want_n, want = mc.oracle_window(oracle(), frame, q, qd, claimed, th, ratio, claim, sigma)
+    got, got_n, passes = matcher.window_search(frame, q, qd, claimed, th, ratio, claim, inv_level_sigma2=sigma)
     for f in FIELDS:
         bad = np.flatnonzero(got[f] != want[f])
         assert len(bad) == 0, (f, bad[:5], got[bad[:5]], want[bad[:5]])
@@ -80,3 +80,16 @@ def test_rejects_keypoint_in_two_cells():
         f = matcher.FrameGrid(np.ones(2), np.ones(2), np.zeros(2), np.zeros((2, 32), np.uint8), cells=cells)
         q = np.zeros(1, WINDOW_QUERY_DTYPE)
         matcher.window_search(f, q, np.zeros((1, 32), np.uint8))
+
+
+@pytest.mark.parametrize("stereo", [False, True])
+def test_reprojection_gate_of_fuse(stereo):
+    """ORBmatcher.cc:1118-1146: chi-square gate on the reprojection error, per keypoint level."""
+    frame, q, qd, claimed = mc.window_case(13, stereo=stereo, th_px=6.0)
+    sigma = (1.0 / (1.2 ** np.arange(8)) ** 2).astype(np.float32)
+    q["er_max"] = -1.0
+    if stereo:
+        q["u_right"] = q["x"] - 12.0
+    _, n_gate = _check(frame, q, qd, None, matcher.TH_LOW, 0.0, False, sigma)
+    _, n_free = _check(frame, q, qd, None, matcher.TH_LOW, 0.0, False, None)
+    assert 0 < n_gate < n_free
