@@ -22,8 +22,11 @@
  *     Fuse(KeyFrame*, const vector<MapPoint*>&, float)                     src/ORBmatcher.cc:1026-1176
  *     Fuse(KeyFrame*, cv::Mat Scw, ..., vector<MapPoint*>& vpReplacePoint) src/ORBmatcher.cc:1178-1301
  *     SearchBySim3(KeyFrame*, KeyFrame*, ..., s12, R12, t12, th)           src/ORBmatcher.cc:1303-1527
- * SearchForTriangulation and SearchForInitialization stay declared and keep their definitions
- * in the reference's ORBmatcher.cc; INTEGRATION.md lists the definitions to delete from that file.
+ * and, through orbm_search_triangulation (vocabulary nodes + epipolar gate),
+ *     SearchForTriangulation(KeyFrame*, KeyFrame*, cv::Mat F12, ...)       src/ORBmatcher.cc:858-1024
+ * Only SearchForInitialization (monocular start-up, run a handful of times) stays declared and
+ * keeps its definition in the reference's ORBmatcher.cc; INTEGRATION.md lists the definitions to
+ * delete from that file.
  *
  * Like the reference header, this one includes MapPoint.h / KeyFrame.h / Frame.h from the
  * includer's path (the reference's own in its build; tests/cpp/mock in this repo's tests).
@@ -769,6 +772,56 @@ inline int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<
     }
   }
   return nFound;
+}
+
+// Unmatched keypoints of two keyframes under the epipolar constraint (LocalMapping::CreateNewMapPoints).
+// src/ORBmatcher.cc:858-1024
+inline int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
+                                              std::vector<pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo) {
+  // epipole in the second image, :866-872
+  cv::Mat Cw = pKF1->GetCameraCenter();
+  cv::Mat R2w = pKF2->GetRotation();
+  cv::Mat t2w = pKF2->GetTranslation();
+  cv::Mat C2 = R2w * Cw + t2w;
+  const float invz = 1.0f / C2.at<float>(2);
+  const float ex = pKF2->fx * C2.at<float>(0) * invz + pKF2->cx;
+  const float ey = pKF2->fy * C2.at<float>(1) * invz + pKF2->cy;
+  struct Side {
+    std::vector<float> x, y, angle;
+    std::vector<int32_t> oct;
+    std::vector<uint8_t> usable, stereo, tmp;
+    FlatFeatVec fv;
+    orbm_tri_keyframe c;
+    Side(KeyFrame* pKF, bool bOnlyStereo) : fv(pKF->mFeatVec) {
+      const size_t n = pKF->mvKeysUn.size();
+      x.resize(n); y.resize(n); angle.resize(n); oct.resize(n); usable.resize(n); stereo.resize(n);
+      for (size_t i = 0; i < n; ++i) {
+        const cv::KeyPoint& kp = pKF->mvKeysUn[i];
+        x[i] = kp.pt.x; y[i] = kp.pt.y; angle[i] = kp.angle; oct[i] = kp.octave;
+        stereo[i] = i < pKF->mvuRight.size() && pKF->mvuRight[i] >= 0;
+        usable[i] = !pKF->GetMapPoint(i) && (!bOnlyStereo || stereo[i]);  // :897-905, :915-925
+      }
+      c.desc = Rows(pKF->mDescriptors, tmp);
+      c.x = x.data(); c.y = y.data(); c.octave = oct.data(); c.angle = angle.data();
+      c.usable = usable.data(); c.stereo = stereo.data(); c.n = (int32_t)n; c.fv = &fv.c;
+    }
+  };
+  const Side s1(pKF1, bOnlyStereo), s2(pKF2, bOnlyStereo);
+  float F[9];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) F[3 * r + c] = F12.at<float>(r, c);
+  std::vector<int32_t> vMatches12((size_t)s1.c.n, -1);
+  int nmatches = 0;
+  Check(orbm_search_triangulation(Device(), &s1.c, &s2.c, F, ex, ey, pKF2->mvScaleFactors.data(), pKF2->mvLevelSigma2.data(),
+                                  (int)pKF2->mvScaleFactors.size(), mbCheckOrientation ? 1 : 0, vMatches12.data(), &nmatches),
+        "ORBmatcher::SearchForTriangulation");
+  vMatchedPairs.clear();
+  vMatchedPairs.reserve(nmatches);
+  for (size_t i = 0, iend = vMatches12.size(); i < iend; i++) {
+    if (vMatches12[i] < 0) continue;
+    vMatchedPairs.push_back(std::make_pair(i, (size_t)vMatches12[i]));
+  }
+  return nmatches;
 }
 
 inline void ORBmatcher::StereoSearch(const std::vector<cv::KeyPoint>& keysLeft, const cv::Mat& descLeft,

@@ -272,6 +272,32 @@ int orbm_window_search(int device, const orbm_grid_frame* frame, const orbm_wind
                        const orbm_window_params* params, orbm_window_result* out, int* n_accepted,
                        int* rounds);
 
+/* ORBmatcher::SearchForTriangulation -- src/ORBmatcher.cc:858-1024 (LocalMapping::CreateNewMapPoints):
+ * keypoints of two keyframes that have no MapPoint yet, matched inside common vocabulary nodes
+ * under the epipolar constraint of F12.  For every usable side-1 keypoint of a common node the
+ * side-2 keypoint with the smallest distance <= TH_LOW (the LAST one on ties, as `dist > bestDist`
+ * skips only strictly worse candidates) among those that pass the epipole test (:921-927, both
+ * keypoints monocular) and CheckDistEpipolarLine (:341-358); then the rotation-histogram filter.
+ * The reference never sets vbMatched2, so side-1 keypoints are independent.  Host memory. */
+typedef struct orbm_tri_keyframe {
+  const uint8_t* desc;     /* n x 32 */
+  const float* x;          /* n: mvKeysUn[i].pt.x */
+  const float* y;
+  const int32_t* octave;   /* n */
+  const float* angle;      /* n (read when check_orientation) */
+  const uint8_t* usable;   /* n: GetMapPoint(i) == NULL && (!bOnlyStereo || mvuRight[i] >= 0) */
+  const uint8_t* stereo;   /* n: mvuRight[i] >= 0 */
+  int32_t n;
+  const orbm_featvec* fv;  /* mFeatVec */
+} orbm_tri_keyframe;
+/* F12: 9 floats row-major; ex, ey: epipole in image 2 (:868-872); scale_factors2 / level_sigma2_2:
+ * pKF2->mvScaleFactors / mvLevelSigma2.  matches12 has kf1->n entries (index in kf2 or -1);
+ * *n_matches = the reference's return value. */
+int orbm_search_triangulation(int device, const orbm_tri_keyframe* kf1, const orbm_tri_keyframe* kf2,
+                              const float* F12, float ex, float ey, const float* scale_factors2,
+                              const float* level_sigma2_2, int n_levels, int check_orientation,
+                              int32_t* matches12, int* n_matches);
+
 /* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
  * denominator of the matching roofline.  Returns 32-bit POPC per second. */
 int orbm_popc_peak(int device, double* popc_per_s);

@@ -10,8 +10,9 @@
 //   stereo_search       Frame.cc:527-610 (descriptor part of ComputeStereoMatches)
 //   features_in_area    Frame.cc:342-395 (GetFeaturesInArea)
 //   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
+//   search_triangulation ORBmatcher.cc:858-1024 + :341-358
 // Parity status: hamming256, search_bow (both overloads) and window_search are pinned on the
-// reference's own src/ORBmatcher.cc compiled unmodified over mocks (oracle/_ref/libmatchref.so):
+// reference's own src/ORBmatcher.cc (as is search_triangulation) compiled unmodified over mocks (oracle/_ref/libmatchref.so):
 // tests/test_projection_cpu.py runs the product header over this restatement against it on 31
 // scenes.  top2_bruteforce / merge_top2 (no such function in the reference) and stereo_search
 // (Frame.cc is not compilable here) stay "parity unpinned": known answers + an independent numpy
@@ -310,6 +311,82 @@ static inline int window_search(const GridFrame& F, const WindowQuery* q, const 
       }
     }
     out[i] = R;
+  }
+  return nmatches;
+}
+
+// ---- SearchForTriangulation, ORBmatcher.cc:858-1024 (with CheckDistEpipolarLine, :341-358) ------
+struct TriKeyFrame {
+  const uint8_t* desc; const float* x; const float* y; const int* octave; const float* angle;
+  const uint8_t* usable;  // GetMapPoint(i) == NULL && (!bOnlyStereo || mvuRight[i] >= 0)
+  const uint8_t* stereo;  // mvuRight[i] >= 0
+  int n; FeatVec fv;
+};
+
+static inline bool check_dist_epipolar_line(float x1, float y1, float x2, float y2, int octave2, const float* F12,
+                                            const float* level_sigma2) {
+  const float a = x1 * F12[0] + y1 * F12[3] + F12[6];
+  const float b = x1 * F12[1] + y1 * F12[4] + F12[7];
+  const float c = x1 * F12[2] + y1 * F12[5] + F12[8];
+  const float num = a * x2 + b * y2 + c;
+  const float den = a * a + b * b;
+  if (den == 0) return false;
+  const float dsqr = num * num / den;
+  return dsqr < 3.84 * level_sigma2[octave2];
+}
+
+static inline int search_triangulation(const TriKeyFrame& K1, const TriKeyFrame& K2, const float* F12, float ex, float ey,
+                                       const float* scale_factors2, const float* level_sigma2_2, int check_ori, int* vMatches12) {
+  int nmatches = 0;
+  for (int i = 0; i < K1.n; ++i) vMatches12[i] = -1;
+  std::vector<int> rotHist[HISTO_LENGTH];
+  int a = 0, b = 0;
+  while (a < K1.fv.n_nodes && b < K2.fv.n_nodes) {
+    if (K1.fv.node[a] == K2.fv.node[b]) {
+      for (int p = K1.fv.off[a]; p < K1.fv.off[a + 1]; ++p) {
+        const int idx1 = (int)K1.fv.idx[p];
+        if (!K1.usable[idx1]) continue;  // :894-903
+        const bool bStereo1 = K1.stereo[idx1] != 0;
+        int bestDist = TH_LOW, bestIdx2 = -1;
+        for (int r = K2.fv.off[b]; r < K2.fv.off[b + 1]; ++r) {
+          const int idx2 = (int)K2.fv.idx[r];
+          if (!K2.usable[idx2]) continue;  // :913-925 (vbMatched2 is never set by the reference)
+          const bool bStereo2 = K2.stereo[idx2] != 0;
+          const int dist = hamming256(K1.desc + 32 * (size_t)idx1, K2.desc + 32 * (size_t)idx2);
+          if (dist > TH_LOW || dist > bestDist) continue;
+          if (!bStereo1 && !bStereo2) {
+            const float distex = ex - K2.x[idx2];
+            const float distey = ey - K2.y[idx2];
+            if (distex * distex + distey * distey < 100 * scale_factors2[K2.octave[idx2]]) continue;
+          }
+          if (check_dist_epipolar_line(K1.x[idx1], K1.y[idx1], K2.x[idx2], K2.y[idx2], K2.octave[idx2], F12, level_sigma2_2)) {
+            bestIdx2 = idx2;
+            bestDist = dist;
+          }
+        }
+        if (bestIdx2 >= 0) {
+          vMatches12[idx1] = bestIdx2;
+          nmatches++;
+          if (check_ori) rotHist[rot_bin(K1.angle[idx1], K2.angle[bestIdx2])].push_back(idx1);
+        }
+      }
+      ++a; ++b;
+    } else if (K1.fv.node[a] < K2.fv.node[b]) {
+      a = lower_bound_node(K1.fv, a, K2.fv.node[b]);
+    } else {
+      b = lower_bound_node(K2.fv, b, K1.fv.node[a]);
+    }
+  }
+  if (check_ori) {
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (size_t j = 0; j < rotHist[i].size(); j++) {
+        vMatches12[rotHist[i][j]] = -1;
+        nmatches--;
+      }
+    }
   }
   return nmatches;
 }

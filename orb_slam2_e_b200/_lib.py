@@ -43,6 +43,11 @@ class GridFrame(C.Structure):  # orbm_grid_frame
                 ("cell_off", C.c_void_p), ("cell_idx", C.c_void_p)]
 
 
+class TriKeyFrame(C.Structure):  # orbm_tri_keyframe
+    _fields_ = [("desc", C.c_void_p), ("x", C.c_void_p), ("y", C.c_void_p), ("octave", C.c_void_p), ("angle", C.c_void_p),
+                ("usable", C.c_void_p), ("stereo", C.c_void_p), ("n", C.c_int32), ("fv", C.POINTER(FeatVec))]
+
+
 class WindowParams(C.Structure):  # orbm_window_params
     _fields_ = [("th", C.c_int32), ("ratio", C.c_float), ("claim", C.c_int32), ("inv_level_sigma2", C.c_void_p),
                 ("n_levels", C.c_int32), ("chi2_mono", C.c_double), ("chi2_stereo", C.c_double)]
@@ -92,6 +97,7 @@ SIGNATURES = {
                              _i, _i, _vp, _ip]),
     "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_window_search": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, C.POINTER(WindowParams), _vp, _ip, _ip]),
+    "orbm_search_triangulation": (_i, [_i, C.POINTER(TriKeyFrame), C.POINTER(TriKeyFrame), _vp, _f, _f, _vp, _vp, _i, _i, _vp, _ip]),
     "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),
 }
 

@@ -262,6 +262,59 @@ __global__ void __launch_bounds__(32) bow_finish_kernel(const int* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------
+// SearchForTriangulation (ORBmatcher.cc:858-1024).  No claims (vbMatched2 is never set), so one
+// warp per (common node, side-1 keypoint) item; candidates across the lanes.  Key = distance << 16
+// | (65535 - list position): min picks the smallest distance and, on ties, the LAST candidate.
+struct TriItem { int i1, o2, l2; };
+struct TriArgs {
+  const uint4* desc1; const uint4* desc2;
+  const TriItem* items; int n_items;
+  const uint32_t* idx2;
+  const float2* xy1; const float2* xy2; const int* oct2;
+  const uint8_t* usable2; const uint8_t* stereo1; const uint8_t* stereo2;
+  float F[9]; float ex, ey;
+  const float* sf2; const float* sigma2;
+  int* best;  // [n_items] side-2 index or -1
+};
+
+__global__ void __launch_bounds__(128) triangulation_kernel(const TriArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int item = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (item >= A.n_items) return;
+  const TriItem it = A.items[item];
+  const uint4 qa = A.desc1[2 * it.i1], qb = A.desc1[2 * it.i1 + 1];
+  const uint32_t q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+  const float2 p1 = A.xy1[it.i1];
+  const bool st1 = A.stereo1[it.i1] != 0;
+  // epipolar line in image 2, ORBmatcher.cc:344-346
+  const float a = p1.x * A.F[0] + p1.y * A.F[3] + A.F[6];
+  const float b = p1.x * A.F[1] + p1.y * A.F[4] + A.F[7];
+  const float c = p1.x * A.F[2] + p1.y * A.F[5] + A.F[8];
+  const float den = a * a + b * b;
+  uint32_t best = 0xffffffffu;
+  if (den != 0.0f) {
+    for (int k = lane; k < it.l2; k += 32) {
+      const int i2 = (int)A.idx2[it.o2 + k];
+      if (!A.usable2[i2]) continue;
+      const int dist = hamming8(q, A.desc2[2 * i2], A.desc2[2 * i2 + 1]);
+      if (dist > ORBM_TH_LOW) continue;
+      const float2 p2 = A.xy2[i2];
+      const int oc = A.oct2[i2];
+      if (!st1 && !A.stereo2[i2]) {  // too close to the epipole, :921-927
+        const float dx = A.ex - p2.x, dy = A.ey - p2.y;
+        if (dx * dx + dy * dy < 100 * A.sf2[oc]) continue;
+      }
+      const float num = a * p2.x + b * p2.y + c;
+      const float dsqr = num * num / den;
+      if (!((double)dsqr < 3.84 * (double)A.sigma2[oc])) continue;
+      best = min(best, ((uint32_t)dist << 16) | (uint32_t)(65535 - k));
+    }
+  }
+  for (int s = 16; s > 0; s >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, s));
+  if (lane == 0) A.best[item] = best == 0xffffffffu ? -1 : (int)A.idx2[it.o2 + 65535 - (int)(best & 0xffffu)];
+}
+
+// ------------------------------------------------------------------------------------
 // Stereo row-band search (Frame.cc:537-610): one warp per left keypoint; the reference's
 // per-row candidate lists are replaced by evaluating the band predicate directly, which
 // visits the same candidates in the same (increasing iR) order.
@@ -698,6 +751,123 @@ int orbm_stereo_search(int device, const orbx_keypoint* left, const uint8_t* lde
   ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
   memcpy(best_idx, h + o_res, (size_t)nl * 4);
   memcpy(best_dist, h + o_res + (size_t)nl * 4, (size_t)nl * 4);
+  return ORB_OK;
+}
+
+int orbm_search_triangulation(int device, const orbm_tri_keyframe* kf1, const orbm_tri_keyframe* kf2, const float* F12,
+                              float ex, float ey, const float* scale_factors2, const float* level_sigma2_2, int n_levels,
+                              int check_orientation, int32_t* matches12, int* n_matches) {
+  if (!kf1 || !kf2 || !F12 || !scale_factors2 || !level_sigma2_2 || n_levels < 1 || !matches12 || !n_matches || kf1->n < 0 ||
+      kf2->n < 0 || !kf1->fv || !kf2->fv)
+    return set_error(ORB_E_INVALID, "orbm_search_triangulation: bad argument");
+  for (const orbm_tri_keyframe* k : {kf1, kf2})
+    if (k->n > 0 && (!k->desc || !k->x || !k->y || !k->octave || !k->usable || !k->stereo || (check_orientation && !k->angle)))
+      return set_error(ORB_E_INVALID, "orbm_search_triangulation: missing keyframe array");
+  const int n1 = kf1->n, n2 = kf2->n;
+  *n_matches = 0;
+  for (int i = 0; i < n1; ++i) matches12[i] = -1;
+  const orbm_featvec *fv1 = kf1->fv, *fv2 = kf2->fv;
+  if (n1 == 0 || n2 == 0 || fv1->n_nodes == 0 || fv2->n_nodes == 0) return ORB_OK;
+  const int ni1 = fv1->off[fv1->n_nodes], ni2 = fv2->off[fv2->n_nodes];
+  for (int i = 0; i < ni1; ++i)
+    if (fv1->idx[i] >= (uint32_t)n1) return set_error(ORB_E_INVALID, "orbm_search_triangulation: feature index out of range");
+  for (int i = 0; i < ni2; ++i)
+    if (fv2->idx[i] >= (uint32_t)n2) return set_error(ORB_E_INVALID, "orbm_search_triangulation: feature index out of range");
+  for (int i = 0; i < n2; ++i)
+    if (kf2->octave[i] < 0 || kf2->octave[i] >= n_levels)
+      return set_error(ORB_E_INVALID, "orbm_search_triangulation: keypoint %d of keyframe 2 has octave %d", i, kf2->octave[i]);
+  int rc = use_device(device);
+  if (rc) return rc;
+  Layout L;
+  const size_t o_d1 = L.place((size_t)n1 * 32), o_d2 = L.place((size_t)n2 * 32), o_items = L.place((size_t)ni1 * sizeof(TriItem)),
+               o_i2 = L.place((size_t)ni2 * 4), o_xy1 = L.place((size_t)n1 * 8), o_xy2 = L.place((size_t)n2 * 8),
+               o_oct2 = L.place((size_t)n2 * 4), o_us2 = L.place(n2), o_st1 = L.place(n1), o_st2 = L.place(n2),
+               o_sf = L.place((size_t)n_levels * 4), o_sg = L.place((size_t)n_levels * 4);
+  const size_t o_up_end = L.bytes;
+  const size_t o_best = L.place((size_t)ni1 * 4);
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  uint8_t *h = S->host, *d = S->dev;
+  // items: usable side-1 keypoints of the common nodes, in the reference's scan order (:888-978)
+  TriItem* items = reinterpret_cast<TriItem*>(h + o_items);
+  int n_items = 0;
+  for (int a = 0, b = 0; a < fv1->n_nodes && b < fv2->n_nodes;) {
+    if (fv1->node[a] == fv2->node[b]) {
+      const int l2 = fv2->off[b + 1] - fv2->off[b];
+      if (l2 > 65535) return set_error(ORB_E_INVALID, "orbm_search_triangulation: node with more than 65535 features");
+      for (int p = fv1->off[a]; p < fv1->off[a + 1]; ++p) {
+        const int i1 = (int)fv1->idx[p];
+        if (kf1->usable[i1]) items[n_items++] = TriItem{i1, fv2->off[b], l2};
+      }
+      ++a; ++b;
+    } else if (fv1->node[a] < fv2->node[b]) {
+      a = (int)(std::lower_bound(fv1->node + a, fv1->node + fv1->n_nodes, fv2->node[b]) - fv1->node);
+    } else {
+      b = (int)(std::lower_bound(fv2->node + b, fv2->node + fv2->n_nodes, fv1->node[a]) - fv2->node);
+    }
+  }
+  if (n_items == 0) return ORB_OK;
+  memcpy(h + o_d1, kf1->desc, (size_t)n1 * 32);
+  memcpy(h + o_d2, kf2->desc, (size_t)n2 * 32);
+  memcpy(h + o_i2, fv2->idx, (size_t)ni2 * 4);
+  float* xy1 = reinterpret_cast<float*>(h + o_xy1);
+  for (int i = 0; i < n1; ++i) { xy1[2 * i] = kf1->x[i]; xy1[2 * i + 1] = kf1->y[i]; }
+  float* xy2 = reinterpret_cast<float*>(h + o_xy2);
+  for (int i = 0; i < n2; ++i) { xy2[2 * i] = kf2->x[i]; xy2[2 * i + 1] = kf2->y[i]; }
+  memcpy(h + o_oct2, kf2->octave, (size_t)n2 * 4);
+  memcpy(h + o_us2, kf2->usable, n2);
+  memcpy(h + o_st1, kf1->stereo, n1);
+  memcpy(h + o_st2, kf2->stereo, n2);
+  memcpy(h + o_sf, scale_factors2, (size_t)n_levels * 4);
+  memcpy(h + o_sg, level_sigma2_2, (size_t)n_levels * 4);
+  ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_up_end, cudaMemcpyHostToDevice, S->stream));
+  TriArgs A;
+  A.desc1 = (const uint4*)(d + o_d1); A.desc2 = (const uint4*)(d + o_d2);
+  A.items = (const TriItem*)(d + o_items); A.n_items = n_items;
+  A.idx2 = (const uint32_t*)(d + o_i2);
+  A.xy1 = (const float2*)(d + o_xy1); A.xy2 = (const float2*)(d + o_xy2); A.oct2 = (const int*)(d + o_oct2);
+  A.usable2 = d + o_us2; A.stereo1 = d + o_st1; A.stereo2 = d + o_st2;
+  for (int i = 0; i < 9; ++i) A.F[i] = F12[i];
+  A.ex = ex; A.ey = ey;
+  A.sf2 = (const float*)(d + o_sf); A.sigma2 = (const float*)(d + o_sg);
+  A.best = (int*)(d + o_best);
+  triangulation_kernel<<<div_up(n_items, 4), 128, 0, S->stream>>>(A);
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_best, d + o_best, (size_t)n_items * 4, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  // apply in scan order, then the rotation filter (:980-1008)
+  const int* best = reinterpret_cast<const int*>(h + o_best);
+  std::vector<int> rot_hist[ORBM_HISTO_LENGTH];
+  int nm = 0;
+  for (int k = 0; k < n_items; ++k) {
+    if (best[k] < 0) continue;
+    const int i1 = items[k].i1;
+    matches12[i1] = best[k];
+    ++nm;
+    if (check_orientation) {
+      float rot = kf1->angle[i1] - kf2->angle[best[k]];
+      if (rot < 0.0f) rot += 360.0f;
+      int bin = (int)roundf(rot * (1.0f / ORBM_HISTO_LENGTH));
+      if (bin == ORBM_HISTO_LENGTH) bin = 0;
+      rot_hist[bin].push_back(i1);
+    }
+  }
+  if (check_orientation) {
+    int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+    for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
+      const int sz = (int)rot_hist[i].size();
+      if (sz > max1) { max3 = max2; max2 = max1; max1 = sz; ind3 = ind2; ind2 = ind1; ind1 = i; }
+      else if (sz > max2) { max3 = max2; max2 = sz; ind3 = ind2; ind2 = i; }
+      else if (sz > max3) { max3 = sz; ind3 = i; }
+    }
+    if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if ((float)max3 < 0.1f * (float)max1) ind3 = -1;
+    for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (int i1 : rot_hist[i]) { matches12[i1] = -1; --nm; }
+    }
+  }
+  *n_matches = nm;
   return ORB_OK;
 }
 

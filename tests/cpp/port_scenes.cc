@@ -40,6 +40,15 @@ int orbm_window_search(int, const orbm_grid_frame* F, const orbm_window_query* q
   if (rounds) *rounds = 1;
   return ORB_OK;
 }
+int orbm_search_triangulation(int, const orbm_tri_keyframe* k1, const orbm_tri_keyframe* k2, const float* F12, float ex, float ey,
+                              const float* sf2, const float* sg2, int, int check_ori, int32_t* matches12, int* n_matches) {
+  auto side = [](const orbm_tri_keyframe* k) {
+    return matchport::TriKeyFrame{k->desc, k->x, k->y, k->octave, k->angle, k->usable, k->stereo, k->n,
+                                  matchport::FeatVec{k->fv->node, k->fv->off, k->fv->idx, k->fv->n_nodes}};
+  };
+  *n_matches = matchport::search_triangulation(side(k1), side(k2), F12, ex, ey, sf2, sg2, check_ori, matches12);
+  return ORB_OK;
+}
 int orbm_stereo_search(int, const orbx_keypoint*, const uint8_t*, int, const orbx_keypoint*, const uint8_t*, int, const float*, int,
                        int, float, float, int32_t*, int32_t*) {
   return ORB_E_INVALID;  // not exercised by the scenes

@@ -162,3 +162,42 @@ def sim3_mutual(ref, got, s12):
     b = got.search_by_sim3(kf1, kf2, P, m, s12, R12, t12)
     assert a["n"] > 50
     sl.assert_same(a, b, "SearchBySim3")
+
+
+def _feature_vector(truth, rng, n_nodes=90):
+    """DBoW2-like FeatureVector: keypoints of the same map point mostly fall in the same node."""
+    node = np.where(truth >= 0, (truth * 2654435761 % 1000003) % n_nodes, rng.integers(0, n_nodes, len(truth)))
+    flip = rng.random(len(truth)) < 0.1
+    node[flip] = rng.integers(0, n_nodes, int(flip.sum()))
+    node = node * 5 + 2
+    ids = np.unique(node)
+    off, idx = [0], []
+    for i in ids:
+        members = np.flatnonzero(node == i)
+        idx.extend(rng.permutation(members))
+        off.append(len(idx))
+    return np.ascontiguousarray(ids, np.uint32), np.ascontiguousarray(off, np.int32), np.ascontiguousarray(idx, np.uint32)
+
+
+def triangulation(ref, got, stereo, only_stereo, check_ori):
+    """LocalMapping::CreateNewMapPoints (:315): unmatched keypoints of two keyframes, epipolar gate from F12."""
+    W = sl.World(81, stereo=stereo)
+    rng = np.random.default_rng(15)
+    T1, T2 = sl.pose(rng, 2.0, 0.3), sl.pose(rng, 2.0, 0.3)
+    kf1 = W.observe(T1, 601, assign=0.3, bit_noise=40)
+    truth1 = W.last_truth
+    kf2 = W.observe(T2, 602, assign=0.3, bit_noise=40)
+    truth2 = W.last_truth
+    fv1, fv2 = _feature_vector(truth1, rng), _feature_vector(truth2, rng)
+    # LocalMapping::ComputeF12 (LocalMapping.cc:596-614): F12 = K1^-T [t12]x R12 K2^-1
+    R1, t1, R2, t2 = T1[:3, :3].astype(np.float64), T1[:3, 3].astype(np.float64), T2[:3, :3].astype(np.float64), T2[:3, 3].astype(np.float64)
+    R12 = R1 @ R2.T
+    t12 = -R1 @ R2.T @ t2 + t1
+    tx = np.array([[0, -t12[2], t12[1]], [t12[2], 0, -t12[0]], [-t12[1], t12[0], 0]])
+    K = np.array([[W.cam["fx"], 0, W.cam["cx"]], [0, W.cam["fy"], W.cam["cy"]], [0, 0, 1.0]])
+    F12 = np.linalg.inv(K).T @ tx @ R12 @ np.linalg.inv(K)
+    P = W.points()
+    a = ref.search_triangulation(kf1, kf2, P, fv1, fv2, F12, only_stereo, check_ori)
+    b = got.search_triangulation(kf1, kf2, P, fv1, fv2, F12, only_stereo, check_ori)
+    assert a["n"] > 40, a["n"]
+    sl.assert_same(a, b, "SearchForTriangulation")

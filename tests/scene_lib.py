@@ -173,6 +173,7 @@ class World:
         out = None
         if outliers > 0:
             out = (rng.random(n) < outliers).astype(np.uint8)
+        self.last_truth = np.concatenate([seen, np.full(n_cl, -1)])[perm]  # map point behind each keypoint (-1: clutter)
         fr = Frame(x[perm], y[perm], octave[perm], ang[perm], desc[perm], None if ur is None else ur[perm], Tcw, mp[perm],
                    None if out is None else out[perm], self.cam, (0.0, 0.0, float(self.width), float(self.height)),
                    self.n_levels, self.scale)
@@ -193,6 +194,8 @@ def _declare(L, prefix):
     g("fuse").argtypes = [fp, pp, _vp, C.c_int, _f, _vp, _vp, _vp, _vp]
     g("fuse_sim3").argtypes = [fp, _vp, pp, _vp, C.c_int, _f, _vp, _vp, _vp]
     g("search_by_sim3").argtypes = [fp, fp, pp, _vp, _f, _vp, _vp, _f]
+    g("search_triangulation").argtypes = [fp, fp, pp, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, C.c_int, C.c_int,
+                                          _vp, C.c_int]
     g("time_tracking_searches").argtypes = [fp, fp, pp, _vp, C.c_int, _f, _f, C.c_int, C.c_int, C.POINTER(C.c_double),
                                             C.POINTER(C.c_double)]
     g("time_tracking_searches").restype = C.c_double
@@ -278,7 +281,18 @@ def _more_side_methods():
         n = self._call("search_by_sim3", C.byref(kf1.c), C.byref(kf2.c), C.byref(P.c), _p(m), s12, _p(R), _p(t), th)
         return dict(n=n, matches12=m)
 
+    def search_triangulation(self, kf1, kf2, P, fv1, fv2, F12, only_stereo=False, check_ori=True):
+        """fv = (node ids ascending u32, offsets i32, feature indices u32)."""
+        F = np.ascontiguousarray(F12, np.float32)
+        pairs = np.zeros((kf1.n, 2), np.int32)
+        rc = self._call("search_triangulation", C.byref(kf1.c), C.byref(kf2.c), C.byref(P.c), _p(fv1[0]), _p(fv1[1]), _p(fv1[2]),
+                        len(fv1[0]), _p(fv2[0]), _p(fv2[1]), _p(fv2[2]), len(fv2[0]), _p(F), int(only_stereo), int(check_ori),
+                        _p(pairs), kf1.n)
+        n, k = divmod(rc, 100000)
+        return dict(n=n, pairs=pairs[:k].copy())
+
     Side.fuse, Side.fuse_sim3, Side.search_by_sim3 = fuse, fuse_sim3, search_by_sim3
+    Side.search_triangulation = search_triangulation
 
 
 _more_side_methods()
@@ -307,6 +321,7 @@ def assert_same(a, b, what=""):
     assert a.keys() == b.keys()
     for k in a:
         if isinstance(a[k], np.ndarray):
+            assert a[k].shape == b[k].shape, (what, k, a[k].shape, b[k].shape)
             bad = np.flatnonzero(np.asarray(a[k] != b[k]).reshape(len(a[k]), -1).any(1))
             assert len(bad) == 0, (what, k, bad[:8], a[k][bad[:8]], b[k][bad[:8]])
         else:

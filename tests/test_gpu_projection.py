@@ -66,3 +66,9 @@ def test_fuse_loop_points(sides, scale):
 @pytest.mark.parametrize("s12", [1.0, 1.15])
 def test_search_by_sim3(sides, s12):
     pc.sim3_mutual(*sides, s12)
+
+
+@pytest.mark.parametrize("stereo,only_stereo,check_ori", [(False, False, True), (True, False, True), (True, True, True),
+                                                          (False, False, False)])
+def test_search_for_triangulation(sides, stereo, only_stereo, check_ori):
+    pc.triangulation(*sides, stereo, only_stereo, check_ori)
