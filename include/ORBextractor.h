@@ -60,6 +60,21 @@ class ORBextractor {
   void SetPyramidDownload(bool enabled) { download_pyramid_ = enabled; }
   /* Extension: the C-ABI handle, for batch / device-pointer use (orbx_extract_batch). */
   orbx_handle* Handle() { return impl_; }
+  /* Extension: the whole of Frame::ComputeStereoMatches (src/Frame.cc:527-700) on the pyramids the two
+   * extractors still hold on the device after operator() -- row-band descriptor search, 11x11
+   * sliding-window refinement, parabola fit, median rejection.  With it a stereo Frame never reads
+   * mvImagePyramid, so both extractors can SetPyramidDownload(false). */
+  static void ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<cv::KeyPoint>& keysLeft,
+                                   const cv::Mat& descLeft, const std::vector<cv::KeyPoint>& keysRight, const cv::Mat& descRight,
+                                   float mb, float mbf, std::vector<float>& mvuRight, std::vector<float>& mvDepth) {
+    assert((keysLeft.empty() || (size_t)descLeft.step == 32) && (keysRight.empty() || (size_t)descRight.step == 32));
+    mvuRight.assign(keysLeft.size(), -1.0f);
+    mvDepth.assign(keysLeft.size(), -1.0f);
+    Check(orbx_stereo_matches(left.impl_, 0, right.impl_, 0, reinterpret_cast<const orbx_keypoint*>(keysLeft.data()), descLeft.data,
+                              (int)keysLeft.size(), reinterpret_cast<const orbx_keypoint*>(keysRight.data()), descRight.data,
+                              (int)keysRight.size(), mb, mbf, mvuRight.data(), mvDepth.data()),
+          "ORBextractor::ComputeStereoMatches");
+  }
 
  protected:
   std::vector<cv::Point> pattern;  // kept for layout; the pattern lives in the library

@@ -298,6 +298,19 @@ int orbm_search_triangulation(int device, const orbm_tri_keyframe* kf1, const or
                               const float* level_sigma2_2, int n_levels, int check_orientation,
                               int32_t* matches12, int* n_matches);
 
+/* Frame::ComputeStereoMatches, whole -- src/Frame.cc:527-700: the row-band descriptor search
+ * (orbm_stereo_search), the 11x11 sliding-window refinement on the pyramid level of the left
+ * keypoint (:613-653), the parabola fit (:655-684) and the median-based rejection (:687-700).
+ * The pyramids are read where the two extractors left them on the device (frame_left / frame_right
+ * of their last batches; the two may be the same handle holding both images as one batch of two),
+ * so a stereo frame needs no mvImagePyramid download.  Keypoints and descriptors are the outputs
+ * of those extractions (host memory).  mb, mbf: Frame::mb, Frame::mbf.  u_right / depth: mvuRight /
+ * mvDepth, -1 where unmatched. */
+int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, int frame_right,
+                        const orbx_keypoint* keys_left, const uint8_t* desc_left, int n_left,
+                        const orbx_keypoint* keys_right, const uint8_t* desc_right, int n_right,
+                        float mb, float mbf, float* u_right, float* depth);
+
 /* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
  * denominator of the matching roofline.  Returns 32-bit POPC per second. */
 int orbm_popc_peak(int device, double* popc_per_s);

@@ -8,6 +8,7 @@
 //   search_bow_kf_kf    ORBmatcher.cc:723-856
 //   three_maxima        ORBmatcher.cc:1802-1843
 //   stereo_search       Frame.cc:527-610 (descriptor part of ComputeStereoMatches)
+//   compute_stereo_matches Frame.cc:527-700 (whole: + sliding-window refinement, parabola, median filter)
 //   features_in_area    Frame.cc:342-395 (GetFeaturesInArea)
 //   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
 //   search_triangulation ORBmatcher.cc:858-1024 + :341-358
@@ -19,6 +20,7 @@
 // model in tests/test_oracle_match.py.
 #pragma once
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -186,6 +188,97 @@ static inline void stereo_search(const float* lx, const float* ly, const int* lo
     }
     best_idx[i] = bi;
     best_dist[i] = bd;
+  }
+}
+
+// Frame::ComputeStereoMatches, whole: Frame.cc:527-700.  Pyramid levels as the extractor leaves them
+// (mvImagePyramid[l]: pointer to pixel (0,0) of level l, row stride, width, height).
+struct PyrLevel { const uint8_t* px; size_t step; int w, h; };
+
+static inline void compute_stereo_matches(const float* lx, const float* ly, const int* loct, const uint8_t* ldesc, int nl,
+                                          const float* rx, const float* ry, const int* roct, const uint8_t* rdesc, int nr,
+                                          const float* mvScaleFactors, const float* mvInvScaleFactors,
+                                          const PyrLevel* pyrL, const PyrLevel* pyrR, float mb, float mbf,
+                                          float* mvuRight, float* mvDepth) {
+  for (int i = 0; i < nl; ++i) { mvuRight[i] = -1.0f; mvDepth[i] = -1.0f; }
+  const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+  const int nRows = pyrL[0].h;
+  const float minZ = mb;
+  const float minD = 0;
+  const float maxD = mbf / minZ;
+  std::vector<int> best_idx((size_t)nl), best_dist((size_t)nl);
+  stereo_search(lx, ly, loct, ldesc, nl, rx, ry, roct, rdesc, nr, mvScaleFactors, nRows, minD, maxD, best_idx.data(),
+                best_dist.data());
+  std::vector<std::pair<int, int> > vDistIdx;
+  for (int iL = 0; iL < nl; ++iL) {
+    if (best_dist[iL] < 0) continue;  // skipped before the scan
+    const int levelL = loct[iL];
+    const float uL = lx[iL];
+    if (best_dist[iL] < thOrbDist) {  // :613
+      const float uR0 = rx[best_idx[iL]];
+      const float scaleFactor = mvInvScaleFactors[levelL];
+      const float scaleduL = round(lx[iL] * scaleFactor);
+      const float scaledvL = round(ly[iL] * scaleFactor);
+      const float scaleduR0 = round(uR0 * scaleFactor);
+      const int w = 5;
+      const PyrLevel& PL = pyrL[levelL];
+      const PyrLevel& PR = pyrR[levelL];
+      // IL = patch - its centre, as float (:624-626)
+      float IL[11][11];
+      {
+        const int r0 = (int)(scaledvL - w), c0 = (int)(scaleduL - w);
+        const float centre = (float)PL.px[(size_t)(r0 + w) * PL.step + c0 + w];
+        for (int r = 0; r < 2 * w + 1; ++r)
+          for (int c = 0; c < 2 * w + 1; ++c) IL[r][c] = (float)PL.px[(size_t)(r0 + r) * PL.step + c0 + c] - centre;
+      }
+      int bestDist = INT_MAX;
+      int bestincR = 0;
+      const int L = 5;
+      std::vector<float> vDists(2 * L + 1);
+      const float iniu = scaleduR0 + L - w;
+      const float endu = scaleduR0 + L + w + 1;
+      if (iniu < 0 || endu >= PR.w) continue;
+      for (int incR = -L; incR <= +L; incR++) {
+        const int r0 = (int)(scaledvL - w), c0 = (int)(scaleduR0 + incR - w);
+        const float centre = (float)PR.px[(size_t)(r0 + w) * PR.step + c0 + w];
+        double acc = 0;  // cv::norm(IL, IR, NORM_L1)
+        for (int r = 0; r < 2 * w + 1; ++r)
+          for (int c = 0; c < 2 * w + 1; ++c)
+            acc += std::fabs((double)IL[r][c] - (double)((float)PR.px[(size_t)(r0 + r) * PR.step + c0 + c] - centre));
+        const float dist = (float)acc;
+        if (dist < bestDist) {
+          bestDist = (int)dist;
+          bestincR = incR;
+        }
+        vDists[L + incR] = dist;
+      }
+      if (bestincR == -L || bestincR == L) continue;
+      const float dist1 = vDists[L + bestincR - 1];
+      const float dist2 = vDists[L + bestincR];
+      const float dist3 = vDists[L + bestincR + 1];
+      const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+      if (deltaR < -1 || deltaR > 1) continue;
+      float bestuR = mvScaleFactors[levelL] * ((float)scaleduR0 + (float)bestincR + deltaR);
+      float disparity = (uL - bestuR);
+      if (disparity >= minD && disparity < maxD) {
+        if (disparity <= 0) {
+          disparity = 0.01;
+          bestuR = uL - 0.01;
+        }
+        mvDepth[iL] = mbf / disparity;
+        mvuRight[iL] = bestuR;
+        vDistIdx.push_back(std::pair<int, int>(bestDist, iL));
+      }
+    }
+  }
+  if (vDistIdx.empty()) return;  // the reference reads vDistIdx[0] of an empty vector here
+  std::sort(vDistIdx.begin(), vDistIdx.end());
+  const float median = vDistIdx[vDistIdx.size() / 2].first;
+  const float thDist = 1.5f * 1.4f * median;
+  for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+    if (vDistIdx[i].first < thDist) break;
+    mvuRight[vDistIdx[i].second] = -1;
+    mvDepth[vDistIdx[i].second] = -1;
   }
 }
 

@@ -161,4 +161,18 @@ int orc_window_search(const float* x, const float* y, const int* octave, const f
   return matchport::window_search(F, (const matchport::WindowQuery*)queries, qdesc, nq, claimed, th, ratio, claim != 0,
                                   (matchport::WindowResult*)out, inv_level_sigma2 ? &gate : nullptr);
 }
+// pyramids: n_levels entries each of (pointer, step, w, h) passed as parallel arrays
+void orc_compute_stereo_matches(const float* lx, const float* ly, const int* loct, const uint8_t* ldesc, int nl,
+                                const float* rx, const float* ry, const int* roct, const uint8_t* rdesc, int nr,
+                                const float* scale, const float* inv_scale, int n_levels, const uint8_t* const* pxL,
+                                const uint8_t* const* pxR, const int* step, const int* w, const int* h, float mb, float mbf,
+                                float* u_right, float* depth) {
+  std::vector<matchport::PyrLevel> L((size_t)n_levels), R((size_t)n_levels);
+  for (int l = 0; l < n_levels; ++l) {
+    L[l] = matchport::PyrLevel{pxL[l], (size_t)step[l], w[l], h[l]};
+    R[l] = matchport::PyrLevel{pxR[l], (size_t)step[l], w[l], h[l]};
+  }
+  matchport::compute_stereo_matches(lx, ly, loct, ldesc, nl, rx, ry, roct, rdesc, nr, scale, inv_scale, L.data(), R.data(), mb, mbf,
+                                    u_right, depth);
+}
 }

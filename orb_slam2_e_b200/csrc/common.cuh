@@ -58,6 +58,17 @@ struct Layout {
   }
 };
 
+// Device-resident pyramid of one frame of an extractor handle (defined in extractor.cu), for kernels
+// outside the extractor that read mvImagePyramid in place (stereo refinement).
+struct PyramidView {
+  enum { kLevels = 16 };
+  const uint8_t* px[kLevels];
+  int pitch[kLevels], w[kLevels], h[kLevels];
+  float scale[kLevels], inv_scale[kLevels];
+  int n_levels, device;
+};
+int pyramid_view(orbx_handle* h, int frame, PyramidView* out);  // waits for the handle's stream
+
 #ifdef __CUDACC__
 #define ORB_HD __host__ __device__
 #else

@@ -579,6 +579,31 @@ int orbx_extract(orbx_handle* H, const uint8_t* img, int w, int ht, size_t strid
   return orbx_batch_read(H, 0, kps, desc, cap, n_out);
 }
 
+}  // extern "C"
+namespace orbfront {
+int pyramid_view(orbx_handle* H, int frame, PyramidView* out) {
+  if (!H || !out) return set_error(ORB_E_INVALID, "pyramid_view: bad argument");
+  if (H->n_frames == 0) return set_error(ORB_E_STATE, "stereo matching: nothing extracted yet");
+  if (frame < 0 || frame >= H->n_frames) return set_error(ORB_E_INVALID, "stereo matching: frame %d out of range", frame);
+  if (H->cfg.nlevels > PyramidView::kLevels) return set_error(ORB_E_INVALID, "stereo matching: more than %d levels", PyramidView::kLevels);
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const ExtractParams& P = H->P;
+  for (int l = 0; l < H->cfg.nlevels; ++l) {
+    const LevelGeom& G = P.lv[l];
+    out->px[l] = l == 0 ? P.l0 + (size_t)frame * P.l0_frame : P.pyr + (size_t)frame * P.pyr_frame + G.off;
+    out->pitch[l] = l == 0 ? (int)P.l0_pitch : G.pitch;
+    out->w[l] = G.w; out->h[l] = G.h;
+    out->scale[l] = H->scale[l]; out->inv_scale[l] = H->inv_scale[l];
+  }
+  out->n_levels = H->cfg.nlevels;
+  out->device = H->cfg.device;
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+}  // namespace orbfront
+extern "C" {
+
 int orbx_level_size(const orbx_handle* H, int level, int* w, int* ht) {
   if (!H || !w || !ht || level < 0 || level >= H->cfg.nlevels) return set_error(ORB_E_INVALID, "orbx_level_size: bad argument");
   if (H->w == 0) return set_error(ORB_E_STATE, "orbx_level_size: no frame size configured yet");

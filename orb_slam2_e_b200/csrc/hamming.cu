@@ -359,6 +359,90 @@ stereo_search_kernel(const orbx_keypoint* __restrict__ L, const uint4* __restric
   }
 }
 
+// ------------------------------------------------------------------------------------
+// Sub-pixel stereo refinement (Frame.cc:613-684): for a left keypoint whose best right keypoint is
+// closer than thOrbDist, slide an 11x11 patch of the left pyramid level over 11 columns of the
+// right one (L1 distance of the centre-subtracted patches: integer arithmetic, exact), fit a
+// parabola through the best offset and its neighbours, and turn the disparity into uRight / depth.
+// One warp per left keypoint; both pyramids are read where the extractor left them in HBM.
+struct StereoRefineArgs {
+  const orbx_keypoint* L; const orbx_keypoint* R; int nl;
+  const int* best_idx; const int* best_dist;
+  PyramidView pl, pr;
+  float min_d, max_d, mbf;
+  int th_orb;
+  float* u_right; float* depth; int* sad;  // [nl]; sad = -1 where nothing was assigned
+};
+
+__global__ void __launch_bounds__(128) stereo_refine_kernel(const StereoRefineArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= A.nl) return;
+  float out_u = -1.0f, out_z = -1.0f;
+  int out_sad = -1;
+  const int bd = A.best_dist[i];
+  if (bd >= 0 && bd < A.th_orb) {  // warp-uniform
+    const orbx_keypoint kl = A.L[i];
+    const int oct = kl.octave;
+    const float uL = kl.x;
+    const float uR0 = A.R[A.best_idx[i]].x;
+    const float sf = A.pl.inv_scale[oct];
+    const float scaleduL = roundf(kl.x * sf), scaledvL = roundf(kl.y * sf), scaleduR0 = roundf(uR0 * sf);
+    constexpr int w = 5, Ls = 5;
+    const float iniu = scaleduR0 + Ls - w, endu = scaleduR0 + Ls + w + 1;
+    const int x0 = (int)(scaleduL - w), y0 = (int)(scaledvL - w), r0 = (int)(scaleduR0 - Ls - w);
+    const int W = A.pl.w[oct], H = A.pl.h[oct];
+    // the reference's own guard (:636-638), plus staying inside the level (always true for keypoints
+    // the extractor produced: they keep 16 px from every border of their level)
+    const bool ok = !(iniu < 0 || endu >= A.pr.w[oct]) && x0 >= 0 && y0 >= 0 && x0 + 2 * w < W && y0 + 2 * w < H && r0 >= 0 &&
+                    r0 + 2 * (w + Ls) < A.pr.w[oct] && y0 + 2 * w < A.pr.h[oct];
+    if (ok) {
+      const uint8_t* pl = A.pl.px[oct] + (size_t)y0 * A.pl.pitch[oct] + x0;
+      const uint8_t* pr = A.pr.px[oct] + (size_t)y0 * A.pr.pitch[oct] + r0;
+      const int cL = pl[(size_t)w * A.pl.pitch[oct] + w];
+      int sums[2 * Ls + 1];
+#pragma unroll
+      for (int k = 0; k <= 2 * Ls; ++k) sums[k] = 0;
+      for (int p = lane; p < (2 * w + 1) * (2 * w + 1); p += 32) {
+        const int r = p / (2 * w + 1), c = p - r * (2 * w + 1);
+        const int vl = (int)pl[(size_t)r * A.pl.pitch[oct] + c] - cL;
+        const uint8_t* row = pr + (size_t)r * A.pr.pitch[oct] + c;
+        const uint8_t* ctr = pr + (size_t)w * A.pr.pitch[oct] + w;
+#pragma unroll
+        for (int k = 0; k <= 2 * Ls; ++k) sums[k] += abs(vl - ((int)row[k] - (int)ctr[k]));
+      }
+#pragma unroll
+      for (int k = 0; k <= 2 * Ls; ++k)
+        for (int s = 16; s > 0; s >>= 1) sums[k] += __shfl_xor_sync(0xffffffffu, sums[k], s);
+      int best = 0x7fffffff, bestinc = 0;  // :628-653, first minimum
+#pragma unroll
+      for (int k = 0; k <= 2 * Ls; ++k)
+        if (sums[k] < best) { best = sums[k]; bestinc = k - Ls; }
+      if (bestinc != -Ls && bestinc != Ls) {
+        float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+        for (int k = 1; k < 2 * Ls; ++k)
+          if (k == bestinc + Ls) { d1 = (float)sums[k - 1]; d2 = (float)sums[k]; d3 = (float)sums[k + 1]; }
+        const float deltaR = (d1 - d3) / (2.0f * (d1 + d3 - 2.0f * d2));  // :659-663
+        if (!(deltaR < -1 || deltaR > 1)) {
+          float bestuR = A.pl.scale[oct] * ((float)scaleduR0 + (float)bestinc + deltaR);
+          float disparity = uL - bestuR;
+          if (disparity >= A.min_d && disparity < A.max_d) {
+            if (disparity <= 0) {
+              disparity = 0.01;
+              bestuR = (float)((double)uL - 0.01);
+            }
+            out_z = A.mbf / disparity;
+            out_u = bestuR;
+            out_sad = best;
+          }
+        }
+      }
+    }
+  }
+  if (lane == 0) { A.u_right[i] = out_u; A.depth[i] = out_z; A.sad[i] = out_sad; }
+}
+
 }  // namespace orbfront
 
 // ====================================================================================
@@ -868,6 +952,78 @@ int orbm_search_triangulation(int device, const orbm_tri_keyframe* kf1, const or
     }
   }
   *n_matches = nm;
+  return ORB_OK;
+}
+
+int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, int frame_right, const orbx_keypoint* kl,
+                        const uint8_t* dl, int nl, const orbx_keypoint* kr, const uint8_t* dr, int nr, float mb, float mbf,
+                        float* u_right, float* depth) {
+  if (!left || !right || nl < 0 || nr < 0 || (nl > 0 && (!kl || !dl || !u_right || !depth)) || (nr > 0 && (!kr || !dr)) ||
+      nr >= (1 << kRowBits))
+    return set_error(ORB_E_INVALID, "orbx_stereo_matches: bad argument");
+  for (int i = 0; i < nl; ++i) { u_right[i] = -1.0f; depth[i] = -1.0f; }  // Frame.cc:529-530
+  if (nl == 0) return ORB_OK;
+  StereoRefineArgs A;
+  int rc;
+  if ((rc = pyramid_view(left, frame_left, &A.pl)) || (rc = pyramid_view(right, frame_right, &A.pr))) return rc;
+  if (A.pl.device != A.pr.device || A.pl.n_levels != A.pr.n_levels)
+    return set_error(ORB_E_INVALID, "orbx_stereo_matches: the two extractors differ in device or level count");
+  const int n_levels = A.pl.n_levels, device = A.pl.device;
+  for (int l = 0; l < n_levels; ++l)
+    if (A.pl.h[l] != A.pr.h[l]) return set_error(ORB_E_INVALID, "orbx_stereo_matches: left and right level %d differ in height", l);
+  for (int i = 0; i < nl; ++i)
+    if (kl[i].octave < 0 || kl[i].octave >= n_levels) return set_error(ORB_E_INVALID, "orbx_stereo_matches: left keypoint %d has octave %d", i, kl[i].octave);
+  for (int i = 0; i < nr; ++i)
+    if (kr[i].octave < 0 || kr[i].octave >= n_levels) return set_error(ORB_E_INVALID, "orbx_stereo_matches: right keypoint %d has octave %d", i, kr[i].octave);
+  const int n_rows = A.pl.h[0];  // :535
+  const float min_d = 0, max_d = mbf / mb;  // :557-559
+  Layout L;
+  const size_t o_l = L.place((size_t)nl * sizeof(orbx_keypoint)), o_r = L.place((size_t)nr * sizeof(orbx_keypoint)),
+               o_dl = L.place((size_t)nl * 32), o_dr = L.place((size_t)nr * 32), o_s = L.place((size_t)n_levels * 4);
+  const size_t o_up_end = L.bytes;
+  const size_t o_best = L.place((size_t)nl * 8);
+  const size_t o_res = L.place((size_t)nl * 12), o_end = L.bytes;
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  uint8_t *h = S->host, *d = S->dev;
+  memcpy(h + o_l, kl, (size_t)nl * sizeof(orbx_keypoint));
+  memcpy(h + o_dl, dl, (size_t)nl * 32);
+  if (nr) {
+    memcpy(h + o_r, kr, (size_t)nr * sizeof(orbx_keypoint));
+    memcpy(h + o_dr, dr, (size_t)nr * 32);
+  }
+  memcpy(h + o_s, A.pl.scale, (size_t)n_levels * 4);
+  ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_up_end, cudaMemcpyHostToDevice, S->stream));
+  int* best = (int*)(d + o_best);
+  stereo_search_kernel<<<div_up(nl, 4), 128, 0, S->stream>>>((const orbx_keypoint*)(d + o_l), (const uint4*)(d + o_dl), nl,
+                                                             (const orbx_keypoint*)(d + o_r), (const uint4*)(d + o_dr), nr,
+                                                             (const float*)(d + o_s), n_rows, min_d, max_d, best, best + nl);
+  ORB_LAUNCH_CHECK();
+  A.L = (const orbx_keypoint*)(d + o_l); A.R = (const orbx_keypoint*)(d + o_r); A.nl = nl;
+  A.best_idx = best; A.best_dist = best + nl;
+  A.min_d = min_d; A.max_d = max_d; A.mbf = mbf;
+  A.th_orb = (ORBM_TH_HIGH + ORBM_TH_LOW) / 2;  // :532
+  A.u_right = (float*)(d + o_res); A.depth = A.u_right + nl; A.sad = (int*)(A.depth + nl);
+  stereo_refine_kernel<<<div_up(nl, 4), 128, 0, S->stream>>>(A);
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_res, d + o_res, o_end - o_res, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  const float* ur = reinterpret_cast<const float*>(h + o_res);
+  const float* z = ur + nl;
+  const int* sad = reinterpret_cast<const int*>(z + nl);
+  // outlier rejection on the patch distance (:687-700): drop matches at or above 2.1 x the median
+  std::vector<std::pair<int, int> > vDistIdx;
+  for (int i = 0; i < nl; ++i)
+    if (sad[i] >= 0) { u_right[i] = ur[i]; depth[i] = z[i]; vDistIdx.push_back(std::make_pair(sad[i], i)); }
+  if (vDistIdx.empty()) return ORB_OK;  // the reference indexes an empty vector here
+  std::sort(vDistIdx.begin(), vDistIdx.end());
+  const float median = vDistIdx[vDistIdx.size() / 2].first;
+  const float thDist = 1.5f * 1.4f * median;
+  for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+    if (vDistIdx[i].first < thDist) break;
+    u_right[vDistIdx[i].second] = -1;
+    depth[vDistIdx[i].second] = -1;
+  }
   return ORB_OK;
 }
 

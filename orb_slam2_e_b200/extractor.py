@@ -205,3 +205,19 @@ class ORBextractor:
             self.close()
         except Exception:
             pass
+
+
+def stereo_matches(left: "ORBextractor", right: "ORBextractor", keys_left, desc_left, keys_right, desc_right, mb: float,
+                   mbf: float, frame_left: int = 0, frame_right: int = 0):
+    """Frame::ComputeStereoMatches, whole (Frame.cc:527-700), on the pyramids the two extractors hold on
+    the device: returns (mvuRight, mvDepth), -1 where unmatched.  `left` and `right` may be the same
+    extractor holding both images as one batch (frame_left / frame_right)."""
+    kl = np.ascontiguousarray(keys_left, _lib.KEYPOINT_DTYPE)
+    kr = np.ascontiguousarray(keys_right, _lib.KEYPOINT_DTYPE)
+    dl = np.ascontiguousarray(desc_left, np.uint8).reshape(-1, 32)
+    dr = np.ascontiguousarray(desc_right, np.uint8).reshape(-1, 32)
+    ur = np.zeros(len(kl), np.float32)
+    z = np.zeros(len(kl), np.float32)
+    check(_lib.load().orbx_stereo_matches(left._h, frame_left, right._h, frame_right, ptr(kl), ptr(dl), len(kl), ptr(kr), ptr(dr),
+                                          len(kr), float(mb), float(mbf), ptr(ur), ptr(z)))
+    return ur, z

@@ -72,6 +72,31 @@ float dropin_table(void* h, int which, int l) {
 int dropin_levels(void* h) { return ((ORBextractor*)h)->GetLevels(); }
 float dropin_scale_factor(void* h) { return ((ORBextractor*)h)->GetScaleFactor(); }
 
+// Frame::Frame (stereo, Frame.cc:63-99) the drop-in way: two extractors, then the whole stereo matching on the device.
+int dropin_stereo_frame(void* hl, void* hr, const uint8_t* left, const uint8_t* right, int w, int h_, size_t stride, float mb,
+                        float mbf, DropKp* kps, uint8_t* desc, float* u_right, float* depth, int cap) {
+  try {
+    ORBextractor *el = (ORBextractor*)hl, *er = (ORBextractor*)hr;
+    el->SetPyramidDownload(false);
+    er->SetPyramidDownload(false);
+    std::vector<cv::KeyPoint> kl, kr;
+    cv::Mat dl, dr;
+    (*el)(cv::Mat(h_, w, CV_8U, (void*)left, stride), cv::Mat(), kl, dl);
+    (*er)(cv::Mat(h_, w, CV_8U, (void*)right, stride), cv::Mat(), kr, dr);
+    std::vector<float> ur, z;
+    ORBextractor::ComputeStereoMatches(*el, *er, kl, dl, kr, dr, mb, mbf, ur, z);
+    const int n = (int)kl.size();
+    if (n > cap) return -n;
+    for (int i = 0; i < n; ++i) {
+      kps[i] = DropKp{kl[i].pt.x, kl[i].pt.y, kl[i].size, kl[i].angle, kl[i].response, kl[i].octave, kl[i].class_id};
+      memcpy(desc + 32 * (size_t)i, dl.ptr(i), 32);
+      u_right[i] = ur[i];
+      depth[i] = z[i];
+    }
+    return n;
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
 int dropin_stereo(const DropKp* kl, const uint8_t* dl, int nl, const DropKp* kr, const uint8_t* dr, int nr, const float* scale,
                   int n_levels, int n_rows, float min_d, float max_d, int32_t* best_idx, int32_t* best_dist) {
   try {

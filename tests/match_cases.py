@@ -158,3 +158,22 @@ def oracle_window(L, frame, q, qd, claimed, th, ratio, claim, inv_level_sigma2=N
                              q.ctypes.data, qd, len(q), cl, th, ratio, int(claim), out.ctypes.data,
                              None if inv_level_sigma2 is None else inv_level_sigma2.ctypes.data, chi2_mono, chi2_stereo)
     return nm, out
+
+
+def oracle_stereo_matches(L, kl, dl, kr, dr, scale, inv_scale, levels_left, levels_right, mb, mbf):
+    """Whole Frame::ComputeStereoMatches restatement on host pyramids (lists of 2-D u8 arrays)."""
+    import ctypes as C
+    n_levels = len(levels_left)
+    PL = (C.c_void_p * n_levels)(*[a.ctypes.data for a in levels_left])
+    PR = (C.c_void_p * n_levels)(*[a.ctypes.data for a in levels_right])
+    for a, b in zip(levels_left, levels_right):
+        assert a.shape == b.shape and a.strides == b.strides and a.strides[1] == 1
+    step = np.array([a.strides[0] for a in levels_left], np.int32)
+    w = np.array([a.shape[1] for a in levels_left], np.int32)
+    h = np.array([a.shape[0] for a in levels_left], np.int32)
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    ur, z = np.zeros(len(kl), np.float32), np.zeros(len(kl), np.float32)
+    L.orc_compute_stereo_matches(f(kl["x"]), f(kl["y"]), np.ascontiguousarray(kl["octave"], np.int32), dl, len(kl), f(kr["x"]),
+                                 f(kr["y"]), np.ascontiguousarray(kr["octave"], np.int32), dr, len(kr), f(scale), f(inv_scale),
+                                 n_levels, C.cast(PL, C.c_void_p), C.cast(PR, C.c_void_p), step, w, h, mb, mbf, ur, z)
+    return ur, z

@@ -97,3 +97,31 @@ def test_stereo_search_through_cpp_class():
     assert L.dropin_stereo(kl.ctypes.data, dl, len(kl), kr.ctypes.data, dr, len(kr), np.ascontiguousarray(scale, np.float32),
                            len(scale), n_rows, 0.0, 80.0, gi, gd) == 0, L.dropin_error()
     assert np.array_equal(gd, bd) and np.array_equal(gi, bi)
+
+
+def test_stereo_frame_through_cpp_classes_without_pyramid_download():
+    """Two ORBextractor objects + ORBextractor::ComputeStereoMatches (whole Frame.cc:527-700 on the
+    device-resident pyramids; SetPyramidDownload(false) on both) against the CPU restatement."""
+    from orb_slam2_e_b200 import synth
+    from orb_slam2_e_b200._lib import KEYPOINT_DTYPE
+    from oracle_lib import PortExtractor
+    L = dropin_lib.load()
+    cfg = (1200, 1.2, 8, 20, 7)
+    left, right = (np.ascontiguousarray(a) for a in synth.stereo_pair(240, 640, 12, max_disp=40.0))
+    hl, hr = L.dropin_create(*cfg), L.dropin_create(*cfg)
+    cap = 1500
+    kps = np.zeros(cap, KEYPOINT_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+    ur = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32)
+    mbf, mb = 40.0, 0.08
+    n = L.dropin_stereo_frame(hl, hr, left, right, 640, 240, 640, mb, mbf, kps.ctypes.data, desc, ur, z, cap)
+    assert n > 0, L.dropin_error()
+    pl, pr = PortExtractor(*cfg), PortExtractor(*cfg)
+    okl, odl = pl.extract(left)
+    okr, odr = pr.extract(right)
+    assert kps[:n].tobytes() == okl.tobytes()
+    scale = np.array([pl.scale(l) for l in range(cfg[2])], np.float32)
+    our, oz = mc.oracle_stereo_matches(oracle(), okl, odl, okr, odr, scale, (np.float32(1.0) / scale).astype(np.float32),
+                                       [pl.level(l) for l in range(cfg[2])], [pr.level(l) for l in range(cfg[2])], mb, mbf)
+    assert (our >= 0).sum() > 100
+    assert ur[:n].tobytes() == our.tobytes() and z[:n].tobytes() == oz.tobytes()
+    L.dropin_destroy(hl); L.dropin_destroy(hr)

@@ -162,6 +162,43 @@ def test_config2_stereo_extract_then_search():
     assert ((bd >= 0) & (bd < 70)).sum() > 200  # plenty of candidates pass to the SAD refinement
 
 
+@pytest.mark.parametrize("one_handle", [False, True])
+def test_config2_whole_stereo_matching_on_device(one_handle):
+    """BASELINE config 2 end to end: both images extracted on the GPU, then Frame::ComputeStereoMatches
+    (Frame.cc:527-700: row search, 11x11 sliding-window refinement, parabola fit, median rejection)
+    on the pyramids still resident in HBM.  mvuRight / mvDepth must equal the CPU restatement run on
+    the oracle's pyramids bit for bit (integer patch distances, identical float expressions)."""
+    import match_cases as mc
+    from oracle_lib import oracle
+    from orb_slam2_e_b200 import extractor as ex
+    left, right = synth.stereo_pair(376, 1241, 34)
+    mbf, mb = 386.1448, 386.1448 / 718.856  # KITTI 00-02
+    if one_handle:  # one extractor, the pair as a batch of two
+        g = ORBextractor(*KITTI)
+        (kl, dl), (kr, dr) = g.extract_batch(np.stack([left, right]))
+        ur, z = ex.stereo_matches(g, g, kl, dl, kr, dr, mb, mbf, 0, 1)
+    else:           # two extractor objects, as Frame.cc:78-81
+        gl, gr = ORBextractor(*KITTI), ORBextractor(*KITTI)
+        kl, dl = gl(left)
+        kr, dr = gr(right)
+        ur, z = ex.stereo_matches(gl, gr, kl, dl, kr, dr, mb, mbf)
+        g = gl
+    pl, pr = PortExtractor(*KITTI), PortExtractor(*KITTI)
+    pl.cap = pr.cap = 2200
+    okl, odl = pl.extract(left)
+    okr, odr = pr.extract(right)
+    assert kl.tobytes() == okl.tobytes() and kr.tobytes() == okr.tobytes()
+    levels_l = [pl.level(l) for l in range(KITTI[2])]
+    levels_r = [pr.level(l) for l in range(KITTI[2])]
+    our, oz = mc.oracle_stereo_matches(oracle(), okl, odl, okr, odr, g.GetScaleFactors(), g.GetInverseScaleFactors(), levels_l,
+                                       levels_r, mb, mbf)
+    assert (our >= 0).sum() > 150, (our >= 0).sum()
+    assert ur.tobytes() == our.tobytes() and z.tobytes() == oz.tobytes()
+    # disparities of the synthetic pair are 0..60 px: depths follow
+    d = kl["x"][our >= 0] - our[our >= 0]
+    assert d.min() >= 0 and d.max() < 80
+
+
 def test_pipelined_host_batch_equals_single_frames():
     """orbx_extract_batch_host (chunked upload | extract | download) == per-frame results, ragged last chunk."""
     frames = np.stack([synth.textured_frame(240, 320, 40 + i) if i % 3 else synth.endoscopy_frame(240, 320, 40 + i) for i in range(7)])
