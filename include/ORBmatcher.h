@@ -24,9 +24,11 @@
  *     SearchBySim3(KeyFrame*, KeyFrame*, ..., s12, R12, t12, th)           src/ORBmatcher.cc:1303-1527
  * and, through orbm_search_triangulation (vocabulary nodes + epipolar gate),
  *     SearchForTriangulation(KeyFrame*, KeyFrame*, cv::Mat F12, ...)       src/ORBmatcher.cc:858-1024
- * Only SearchForInitialization (monocular start-up, run a handful of times) stays declared and
- * keeps its definition in the reference's ORBmatcher.cc; INTEGRATION.md lists the definitions to
- * delete from that file.
+ * and, through orbm_window_candidates (window gather + all distances; the re-assignment
+ * bookkeeping of :641-668 runs over the lists on the host),
+ *     SearchForInitialization(Frame&, Frame&, vbPrevMatched, vnMatches12, windowSize)  src/ORBmatcher.cc:606-721
+ * With these the header defines every public method of the class: the reference's
+ * src/ORBmatcher.cc leaves the build.
  *
  * Like the reference header, this one includes MapPoint.h / KeyFrame.h / Frame.h from the
  * includer's path (the reference's own in its build; tests/cpp/mock in this repo's tests).
@@ -35,6 +37,7 @@
 #define ORBMATCHER_H
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -821,6 +824,84 @@ inline int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv
     if (vMatches12[i] < 0) continue;
     vMatchedPairs.push_back(std::make_pair(i, (size_t)vMatches12[i]));
   }
+  return nmatches;
+}
+
+// Monocular initialisation: level-0 keypoints of the first frame searched in a window of the second.
+// src/ORBmatcher.cc:606-721.  A keypoint of F2 can be re-assigned to a later query with a smaller
+// distance (:641-642, :661-668), so the acceptance needs every candidate, not the best two: the GPU
+// gathers the windows and computes all distances (orbm_window_candidates); the re-assignment
+// bookkeeping then runs over those lists in the reference's order.
+inline int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
+                                               std::vector<int>& vnMatches12, int windowSize) {
+  int nmatches = 0;
+  vnMatches12 = std::vector<int>(F1.mvKeysUn.size(), -1);
+  std::vector<int> rotHist[HISTO_LENGTH];
+  std::vector<int> vMatchedDistance(F2.mvKeysUn.size(), INT_MAX);
+  std::vector<int> vnMatches21(F2.mvKeysUn.size(), -1);
+  WindowQueries W;
+  for (size_t i1 = 0, iend1 = F1.mvKeysUn.size(); i1 < iend1; i1++) {
+    const int level1 = F1.mvKeysUn[i1].octave;
+    if (level1 > 0) continue;
+    W.Add(NULL, F1.mDescriptors.row((int)i1), vbPrevMatched[i1].x, vbPrevMatched[i1].y, windowSize, level1, level1, 0.f, -1.f, false,
+          (int)i1);
+  }
+  const FlatGrid grid(F2);
+  const int nq = (int)W.q.size();
+  std::vector<int32_t> offset((size_t)nq), count((size_t)nq), candIdx, candDist;
+  if (nq > 0) {
+    int total = 0;
+    candIdx.resize((size_t)nq * 64 + 1024);
+    candDist.resize(candIdx.size());
+    int rc = orbm_window_candidates(Device(), &grid.c, W.q.data(), W.desc.data(), nq, offset.data(), count.data(), candIdx.data(),
+                                    candDist.data(), (int)candIdx.size(), &total);
+    if (rc == ORB_E_CAPACITY) {
+      candIdx.resize((size_t)total);
+      candDist.resize((size_t)total);
+      rc = orbm_window_candidates(Device(), &grid.c, W.q.data(), W.desc.data(), nq, offset.data(), count.data(), candIdx.data(),
+                                  candDist.data(), total, &total);
+    }
+    Check(rc, "ORBmatcher::SearchForInitialization");
+  }
+  for (int k = 0; k < nq; ++k) {
+    const int i1 = W.src[k];
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int c = offset[k]; c < offset[k] + count[k]; ++c) {
+      const int i2 = candIdx[c], dist = candDist[c];
+      if (vMatchedDistance[i2] <= dist) continue;
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) bestDist2 = dist;
+    }
+    if (bestDist <= TH_LOW) {
+      if (bestDist < (float)bestDist2 * mfNNratio) {
+        if (vnMatches21[bestIdx2] >= 0) {
+          vnMatches12[vnMatches21[bestIdx2]] = -1;
+          nmatches--;
+        }
+        vnMatches12[i1] = bestIdx2;
+        vnMatches21[bestIdx2] = i1;
+        vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (mbCheckOrientation) rotHist[RotationBin(F1.mvKeysUn[i1].angle, F2.mvKeysUn[bestIdx2].angle)].push_back(i1);
+      }
+    }
+  }
+  if (mbCheckOrientation) {  // :685-707
+    int ind1, ind2, ind3;
+    ThreeMaxima(rotHist, ind1, ind2, ind3);
+    for (int i = 0; i < HISTO_LENGTH; i++) {
+      if (i == ind1 || i == ind2 || i == ind3) continue;
+      for (size_t j = 0; j < rotHist[i].size(); j++) {
+        const int idx1 = rotHist[i][j];
+        if (vnMatches12[idx1] >= 0) {
+          vnMatches12[idx1] = -1;
+          nmatches--;
+        }
+      }
+    }
+  }
+  for (size_t i1 = 0, iend1 = vnMatches12.size(); i1 < iend1; i1++)  // :710-712
+    if (vnMatches12[i1] >= 0) vbPrevMatched[i1] = F2.mvKeysUn[vnMatches12[i1]].pt;
   return nmatches;
 }
 

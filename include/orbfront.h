@@ -272,6 +272,17 @@ int orbm_window_search(int device, const orbm_grid_frame* frame, const orbm_wind
                        const orbm_window_params* params, orbm_window_result* out, int* n_accepted,
                        int* rounds);
 
+/* Candidate lists of windowed queries, for callers whose acceptance rule needs more than the best
+ * two (ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:606-721, re-assigns a keypoint to a
+ * later query with a smaller distance): for every query the keypoints GetFeaturesInArea returns, in
+ * its order, each with its Hamming distance to the query descriptor.  Query q owns entries
+ * [offset[q], offset[q] + count[q]) of cand_idx / cand_dist (ranges are disjoint, not ordered by q).
+ * cap: capacity of cand_idx / cand_dist; ORB_E_CAPACITY with *n_total = entries needed when too
+ * small.  u_right / er_max / blocks of the queries are ignored. */
+int orbm_window_candidates(int device, const orbm_grid_frame* frame, const orbm_window_query* queries,
+                           const uint8_t* query_desc, int nq, int32_t* offset, int32_t* count,
+                           int32_t* cand_idx, int32_t* cand_dist, int cap, int* n_total);
+
 /* ORBmatcher::SearchForTriangulation -- src/ORBmatcher.cc:858-1024 (LocalMapping::CreateNewMapPoints):
  * keypoints of two keyframes that have no MapPoint yet, matched inside common vocabulary nodes
  * under the epipolar constraint of F12.  For every usable side-1 keypoint of a common node the

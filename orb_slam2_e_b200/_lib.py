@@ -97,6 +97,7 @@ SIGNATURES = {
                              _i, _i, _vp, _ip]),
     "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_window_search": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, C.POINTER(WindowParams), _vp, _ip, _ip]),
+    "orbm_window_candidates": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _ip]),
     "orbm_search_triangulation": (_i, [_i, C.POINTER(TriKeyFrame), C.POINTER(TriKeyFrame), _vp, _f, _f, _vp, _vp, _i, _i, _vp, _ip]),
     "orbx_stereo_matches": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
     "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),

@@ -177,6 +177,65 @@ __global__ void __launch_bounds__(kWinWarps * 32) window_search_kernel(const Win
   if (tid == 0) A.ctrl[4] = round + 1;
 }
 
+// Candidate lists (orbm_window_candidates): same gather, every candidate written out in scan order.
+// pass 0 counts and reserves a range with one atomicAdd per query; pass 1 fills.
+struct CandArgs {
+  const float4* rec; const uint4* desc; const int* feat; const int* cell_off;
+  const orbm_window_query* q; const uint4* qdesc;
+  int nq, cols, rows;
+  float min_x, min_y, width_inv, height_inv;
+  int* offset; int* count; int* cursor;  // [nq], [nq], [1]
+  int2* out; int cap;                    // (keypoint, distance)
+};
+
+template <int kPass>
+__global__ void __launch_bounds__(kWinWarps * 32) window_candidates_kernel(const CandArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int qi = blockIdx.x * kWinWarps + (threadIdx.x >> 5);
+  if (qi >= A.nq) return;
+  const orbm_window_query Q = A.q[qi];
+  const int cx0 = max(0, (int)floorf((Q.x - A.min_x - Q.r) * A.width_inv));
+  const int cx1 = min(A.cols - 1, (int)ceilf((Q.x - A.min_x + Q.r) * A.width_inv));
+  const int cy0 = max(0, (int)floorf((Q.y - A.min_y - Q.r) * A.height_inv));
+  const int cy1 = min(A.rows - 1, (int)ceilf((Q.y - A.min_y + Q.r) * A.height_inv));
+  uint32_t qd[8];
+  int base = 0;
+  if (kPass == 1) {
+    const uint4 qa = __ldg(&A.qdesc[2 * qi]), qb = __ldg(&A.qdesc[2 * qi + 1]);
+    qd[0] = qa.x; qd[1] = qa.y; qd[2] = qa.z; qd[3] = qa.w; qd[4] = qb.x; qd[5] = qb.y; qd[6] = qb.z; qd[7] = qb.w;
+    base = A.offset[qi];
+    if (base + A.count[qi] > A.cap) return;  // the host reports ORB_E_CAPACITY
+  }
+  int n = 0;
+  if (cx0 < A.cols && cx1 >= 0 && cy0 < A.rows && cy1 >= 0) {
+    const bool check_levels = Q.min_level > 0 || Q.max_level >= 0;
+    for (int ix = cx0; ix <= cx1; ++ix) {
+      const int b = __ldg(&A.cell_off[ix * A.rows + cy0]), e = __ldg(&A.cell_off[ix * A.rows + cy1 + 1]);
+      for (int p0 = b; p0 < e; p0 += 32) {  // uniform trip count: the ballot below needs the whole warp
+        const int pos = p0 + lane;
+        bool in = pos < e;
+        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (in) {
+          r = __ldg(&A.rec[pos]);
+          const int oct = __float_as_int(r.w);
+          if (check_levels && (oct < Q.min_level || (Q.max_level >= 0 && oct > Q.max_level))) in = false;
+          if (!(fabsf(r.x - Q.x) < Q.r && fabsf(r.y - Q.y) < Q.r)) in = false;
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, in);
+        if (kPass == 1 && in) {
+          const int slot = base + n + __popc(m & ((1u << lane) - 1));
+          A.out[slot] = make_int2(__ldg(&A.feat[pos]), hamming256(qd, __ldg(&A.desc[2 * pos]), __ldg(&A.desc[2 * pos + 1])));
+        }
+        n += __popc(m);
+      }
+    }
+  }
+  if (kPass == 0 && lane == 0) {
+    A.count[qi] = n;
+    A.offset[qi] = atomicAdd(A.cursor, n);
+  }
+}
+
 }  // namespace
 }  // namespace orbfront
 
@@ -283,5 +342,77 @@ extern "C" int orbm_window_search(int device, const orbm_grid_frame* F, const or
   const int* ctrl = reinterpret_cast<const int*>(h + o_ctrl);
   if (n_accepted) *n_accepted = ctrl[5];
   if (rounds) *rounds = ctrl[4];
+  return ORB_OK;
+}
+
+extern "C" int orbm_window_candidates(int device, const orbm_grid_frame* F, const orbm_window_query* queries,
+                                      const uint8_t* query_desc, int nq, int32_t* offset, int32_t* count, int32_t* cand_idx,
+                                      int32_t* cand_dist, int cap, int* n_total) {
+  if (!F || nq < 0 || cap < 0 || !n_total || (nq > 0 && (!queries || !query_desc || !offset || !count)) || F->n < 0 || F->cols < 1 ||
+      F->rows < 1 || !F->cell_off || (F->n > 0 && (!F->x || !F->y || !F->octave || !F->desc)) || (cap > 0 && (!cand_idx || !cand_dist)))
+    return set_error(ORB_E_INVALID, "orbm_window_candidates: bad argument");
+  *n_total = 0;
+  if (nq == 0) return ORB_OK;
+  const long long n_cells = (long long)F->cols * F->rows;
+  if (n_cells > (1 << 22)) return set_error(ORB_E_INVALID, "orbm_window_candidates: grid of %lld cells", n_cells);
+  const int npos = F->cell_off[n_cells];
+  if (F->cell_off[0] != 0 || npos < 0 || npos >= (1 << kPosBits) || (npos > 0 && !F->cell_idx))
+    return set_error(ORB_E_INVALID, "orbm_window_candidates: bad cell table (%d entries)", npos);
+  for (long long c = 0; c < n_cells; ++c)
+    if (F->cell_off[c + 1] < F->cell_off[c]) return set_error(ORB_E_INVALID, "orbm_window_candidates: cell offsets not ascending");
+  int rc = use_device(device);
+  if (rc) return rc;
+  Layout L;
+  const size_t o_rec = L.place((size_t)npos * 16), o_desc = L.place((size_t)npos * 32), o_feat = L.place((size_t)npos * 4),
+               o_off = L.place((size_t)(n_cells + 1) * 4), o_q = L.place((size_t)nq * sizeof(orbm_window_query)),
+               o_qd = L.place((size_t)nq * 32), o_cur = L.place(4);
+  const size_t o_up_end = L.bytes;
+  const size_t o_oc = L.place((size_t)nq * 8);  // offset[nq], count[nq]
+  const size_t o_out = L.place((size_t)cap * 8), o_end = L.bytes;
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  uint8_t *h = S->host, *d = S->dev;
+  float* rec = reinterpret_cast<float*>(h + o_rec);
+  int* feat = reinterpret_cast<int*>(h + o_feat);
+  for (int p = 0; p < npos; ++p) {
+    const uint32_t f = F->cell_idx[p];
+    if (f >= (uint32_t)F->n) return set_error(ORB_E_INVALID, "orbm_window_candidates: cell entry %u out of range", f);
+    rec[4 * p + 0] = F->x[f];
+    rec[4 * p + 1] = F->y[f];
+    rec[4 * p + 2] = -1.0f;
+    memcpy(&rec[4 * p + 3], &F->octave[f], 4);
+    memcpy(h + o_desc + (size_t)p * 32, F->desc + (size_t)f * 32, 32);
+    feat[p] = (int)f;
+  }
+  memcpy(h + o_off, F->cell_off, (size_t)(n_cells + 1) * 4);
+  memcpy(h + o_q, queries, (size_t)nq * sizeof(orbm_window_query));
+  memcpy(h + o_qd, query_desc, (size_t)nq * 32);
+  memset(h + o_cur, 0, 4);
+  ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_up_end, cudaMemcpyHostToDevice, S->stream));
+  CandArgs A;
+  A.rec = (const float4*)(d + o_rec); A.desc = (const uint4*)(d + o_desc); A.feat = (const int*)(d + o_feat);
+  A.cell_off = (const int*)(d + o_off); A.q = (const orbm_window_query*)(d + o_q); A.qdesc = (const uint4*)(d + o_qd);
+  A.nq = nq; A.cols = F->cols; A.rows = F->rows;
+  A.min_x = F->min_x; A.min_y = F->min_y; A.width_inv = F->width_inv; A.height_inv = F->height_inv;
+  A.offset = (int*)(d + o_oc); A.count = A.offset + nq; A.cursor = (int*)(d + o_cur);
+  A.out = (int2*)(d + o_out); A.cap = cap;
+  const int grid = div_up(nq, kWinWarps);
+  window_candidates_kernel<0><<<grid, kWinWarps * 32, 0, S->stream>>>(A);
+  ORB_LAUNCH_CHECK();
+  window_candidates_kernel<1><<<grid, kWinWarps * 32, 0, S->stream>>>(A);
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_oc, d + o_oc, (size_t)nq * 8, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_cur, d + o_cur, 4, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  const int total = *reinterpret_cast<const int*>(h + o_cur);
+  *n_total = total;
+  memcpy(offset, h + o_oc, (size_t)nq * 4);
+  memcpy(count, h + o_oc + (size_t)nq * 4, (size_t)nq * 4);
+  if (total > cap) return set_error(ORB_E_CAPACITY, "orbm_window_candidates: %d candidates, capacity %d", total, cap);
+  if (total == 0) return ORB_OK;
+  ORB_CUDA_TRY(cudaMemcpyAsync(h + o_out, d + o_out, (size_t)total * 8, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  const int* pairs = reinterpret_cast<const int*>(h + o_out);
+  for (int k = 0; k < total; ++k) { cand_idx[k] = pairs[2 * k]; cand_dist[k] = pairs[2 * k + 1]; }
   return ORB_OK;
 }

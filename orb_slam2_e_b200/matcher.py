@@ -183,6 +183,27 @@ def window_search(frame: FrameGrid, queries, query_desc, claimed=None, th: int =
     return out, na.value, rounds.value
 
 
+def window_candidates(frame: FrameGrid, queries, query_desc, device: int = 0):
+    """orbm_window_candidates: per query the keypoints GetFeaturesInArea returns, in its order, with
+    their Hamming distances.  Returns a list of (keypoint indices, distances) per query."""
+    q = np.ascontiguousarray(queries, WINDOW_QUERY_DTYPE)
+    qd = _desc(query_desc) if len(q) else np.zeros((0, 32), np.uint8)
+    off, cnt = np.zeros(len(q), np.int32), np.zeros(len(q), np.int32)
+    cap = max(1024, 64 * len(q))
+    L = _lib.load()
+    while True:
+        idx, dist = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+        total = C.c_int(0)
+        rc = L.orbm_window_candidates(device, C.byref(frame.c), ptr(q), ptr(qd), len(q), ptr(off), ptr(cnt), ptr(idx), ptr(dist), cap,
+                                      C.byref(total))
+        if rc == -4:  # ORB_E_CAPACITY
+            cap = total.value
+            continue
+        check(rc)
+        break
+    return [(idx[o:o + c].copy(), dist[o:o + c].copy()) for o, c in zip(off, cnt)]
+
+
 class DescriptorDB:
     """One GPU-resident shard of the relocalization descriptor database:
     rows [row_base, row_base + n) of the global N x 32 matrix."""

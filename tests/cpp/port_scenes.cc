@@ -40,6 +40,22 @@ int orbm_window_search(int, const orbm_grid_frame* F, const orbm_window_query* q
   if (rounds) *rounds = 1;
   return ORB_OK;
 }
+int orbm_window_candidates(int, const orbm_grid_frame* F, const orbm_window_query* q, const uint8_t* qd, int nq, int32_t* offset,
+                           int32_t* count, int32_t* cand_idx, int32_t* cand_dist, int cap, int* n_total) {
+  matchport::GridFrame G{F->x, F->y, F->octave, F->u_right, F->desc, F->n, F->min_x, F->min_y, F->width_inv, F->height_inv,
+                         F->cols, F->rows, F->cell_off, F->cell_idx};
+  std::vector<int> v;
+  int total = 0;
+  for (int i = 0; i < nq; ++i) {
+    matchport::features_in_area(G, q[i].x, q[i].y, q[i].r, q[i].min_level, q[i].max_level, v);
+    offset[i] = total;
+    count[i] = (int)v.size();
+    for (size_t k = 0; k < v.size(); ++k, ++total)
+      if (total < cap) { cand_idx[total] = v[k]; cand_dist[total] = matchport::hamming256(qd + 32 * (size_t)i, F->desc + 32 * (size_t)v[k]); }
+  }
+  *n_total = total;
+  return total > cap ? ORB_E_CAPACITY : ORB_OK;
+}
 int orbm_search_triangulation(int, const orbm_tri_keyframe* k1, const orbm_tri_keyframe* k2, const float* F12, float ex, float ey,
                               const float* sf2, const float* sg2, int, int check_ori, int32_t* matches12, int* n_matches) {
   auto side = [](const orbm_tri_keyframe* k) {

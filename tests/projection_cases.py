@@ -201,3 +201,19 @@ def triangulation(ref, got, stereo, only_stereo, check_ori):
     b = got.search_triangulation(kf1, kf2, P, fv1, fv2, F12, only_stereo, check_ori)
     assert a["n"] > 40, a["n"]
     sl.assert_same(a, b, "SearchForTriangulation")
+
+
+def initialization(ref, got, window, ratio, check_ori):
+    """Tracking::MonocularInitialization (Tracking.cc:718,791): level-0 keypoints of the initial frame
+    searched around their previous position in the current frame; later queries steal keypoints."""
+    W = sl.World(91, n_points=2500)
+    rng = np.random.default_rng(16)
+    f1 = W.observe(sl.pose(rng, 1.0, 0.05), 701, clutter=0.5)
+    f2 = W.observe(sl.pose(rng, 1.0, 0.05), 702, clutter=0.5)
+    f1.octave[:] = np.where(rng.random(f1.n) < 0.6, 0, f1.octave)   # plenty of level-0 keypoints on both sides
+    f2.octave[:] = np.where(rng.random(f2.n) < 0.6, 0, f2.octave)
+    prev = np.stack([f1.x, f1.y], 1) + rng.normal(0, 8.0, (f1.n, 2))
+    a = ref.search_for_initialization(f1, f2, prev, window, ratio, check_ori)
+    b = got.search_for_initialization(f1, f2, prev, window, ratio, check_ori)
+    assert a["n"] > 30, a["n"]
+    sl.assert_same(a, b, "SearchForInitialization")

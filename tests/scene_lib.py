@@ -194,6 +194,7 @@ def _declare(L, prefix):
     g("fuse").argtypes = [fp, pp, _vp, C.c_int, _f, _vp, _vp, _vp, _vp]
     g("fuse_sim3").argtypes = [fp, _vp, pp, _vp, C.c_int, _f, _vp, _vp, _vp]
     g("search_by_sim3").argtypes = [fp, fp, pp, _vp, _f, _vp, _vp, _f]
+    g("search_for_initialization").argtypes = [fp, fp, _vp, _vp, C.c_int, _f, C.c_int]
     g("search_triangulation").argtypes = [fp, fp, pp, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, C.c_int, _vp, C.c_int, C.c_int,
                                           _vp, C.c_int]
     g("time_tracking_searches").argtypes = [fp, fp, pp, _vp, C.c_int, _f, _f, C.c_int, C.c_int, C.POINTER(C.c_double),
@@ -292,7 +293,14 @@ def _more_side_methods():
         return dict(n=n, pairs=pairs[:k].copy())
 
     Side.fuse, Side.fuse_sim3, Side.search_by_sim3 = fuse, fuse_sim3, search_by_sim3
+    def search_for_initialization(self, f1, f2, prev, window=100, ratio=0.9, check_ori=True):
+        pv = np.ascontiguousarray(prev, np.float32).copy()
+        m = np.zeros(f1.n, np.int32)
+        n = self._call("search_for_initialization", C.byref(f1.c), C.byref(f2.c), _p(pv), _p(m), int(window), ratio, int(check_ori))
+        return dict(n=n, matches12=m, prev=pv)
+
     Side.search_triangulation = search_triangulation
+    Side.search_for_initialization = search_for_initialization
 
 
 _more_side_methods()

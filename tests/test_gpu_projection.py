@@ -72,3 +72,8 @@ def test_search_by_sim3(sides, s12):
                                                           (False, False, False)])
 def test_search_for_triangulation(sides, stereo, only_stereo, check_ori):
     pc.triangulation(*sides, stereo, only_stereo, check_ori)
+
+
+@pytest.mark.parametrize("window,ratio,check_ori", [(100, 0.9, True), (100, 0.9, False), (30, 0.7, True)])
+def test_search_for_initialization(sides, window, ratio, check_ori):
+    pc.initialization(*sides, window, ratio, check_ori)

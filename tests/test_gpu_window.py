@@ -93,3 +93,39 @@ def test_reprojection_gate_of_fuse(stereo):
     _, n_gate = _check(frame, q, qd, None, matcher.TH_LOW, 0.0, False, sigma)
     _, n_free = _check(frame, q, qd, None, matcher.TH_LOW, 0.0, False, None)
     assert 0 < n_gate < n_free
+
+
+@pytest.mark.parametrize("kw", [dict(th_px=40.0, n=1500, nq=400), dict(n=50, nq=30), dict(th_px=3.0)])
+def test_window_candidates_lists(kw):
+    """orbm_window_candidates: every candidate of every window, in GetFeaturesInArea's order, with its
+    distance -- against a brute-force numpy model of Frame.cc:342-395."""
+    frame, q, qd, _ = mc.window_case(17, **kw)
+    got = matcher.window_candidates(frame, q, qd)
+    pop = np.array([bin(i).count("1") for i in range(256)], np.int32)
+    cell_of = np.full(frame.n, -1)
+    for c in range(frame.cols * frame.rows):
+        cell_of[frame.cell_idx[frame.cell_off[c]:frame.cell_off[c + 1]]] = c
+    pos_of = np.empty(frame.n, np.int64)
+    pos_of[frame.cell_idx] = np.arange(len(frame.cell_idx))
+    total = 0
+    for i in range(len(q)):
+        x, y, r = q["x"][i], q["y"][i], q["r"][i]
+        f32 = np.float32
+        cx0 = max(0, int(np.floor((x - frame.min_x - r) * frame.width_inv)))
+        cx1 = min(frame.cols - 1, int(np.ceil((x - frame.min_x + r) * frame.width_inv)))
+        cy0 = max(0, int(np.floor((y - frame.min_y - r) * frame.height_inv)))
+        cy1 = min(frame.rows - 1, int(np.ceil((y - frame.min_y + r) * frame.height_inv)))
+        ok = (cell_of >= 0) & (cell_of // frame.rows >= cx0) & (cell_of // frame.rows <= cx1) & (cell_of % frame.rows >= cy0) & \
+             (cell_of % frame.rows <= cy1)
+        lo, hi = q["min_level"][i], q["max_level"][i]
+        if lo > 0 or hi >= 0:
+            ok &= frame.octave >= lo
+            if hi >= 0:
+                ok &= frame.octave <= hi
+        ok &= (np.abs(frame.x - x) < r) & (np.abs(frame.y - y) < r)
+        want = np.flatnonzero(ok)
+        want = want[np.argsort(pos_of[want])]
+        assert np.array_equal(got[i][0], want), i
+        assert np.array_equal(got[i][1], pop[frame.desc[want] ^ qd[i]].sum(1))
+        total += len(want)
+    assert total > 0
