@@ -322,6 +322,29 @@ int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, i
                         const orbx_keypoint* keys_right, const uint8_t* desc_right, int n_right,
                         float mb, float mbf, float* u_right, float* depth);
 
+/* ---- Vocabulary tree --------------------------------------------------------
+ * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> as ORB-SLAM2 uses it (include/ORBVocabulary.h):
+ * the k-ary tree stays resident on the device and descriptors are pushed down it in bulk
+ * (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1217-1259, called per feature from :1127-1196 by
+ * Frame::ComputeBoW, src/Frame.cc:410-417, and KeyFrame::ComputeBoW, src/KeyFrame.cc:70-79). */
+typedef struct orbm_vocab orbm_vocab;
+/* Nodes 0..n_nodes-1, node 0 the root; parent[i] < i; children keep ascending node order (the order
+ * loadFromTextFile appends them, :1377-1391).  is_word[i]: node i carries a word; word ids count
+ * those nodes in node order (:1407-1414).  desc: n_nodes x 32; weight: per node (Node::weight). */
+int orbm_vocab_create(int device, int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_word,
+                      const uint8_t* desc, const double* weight, orbm_vocab** out);
+/* Reads the text format of TemplatedVocabulary::loadFromTextFile (:1337-1421; "k L scoring weighting",
+ * then one "parent leaf d0..d31 weight" line per node).  Unlike the reference, an empty last line does
+ * not become a node. */
+int orbm_vocab_load_text(int device, const char* path, orbm_vocab** out);
+int orbm_vocab_info(const orbm_vocab* v, int* k, int* L, int* n_nodes, int* n_words);
+int orbm_vocab_destroy(orbm_vocab* v);
+/* transform(feature, word_id, weight, &nid, levelsup) for n descriptors (host memory): word id and
+ * weight of the leaf each descriptor reaches (first child with the smallest distance at every
+ * level), and the node it passed at level L - levelsup (0 when that is the root or above). */
+int orbm_vocab_transform(orbm_vocab* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id,
+                         int32_t* node_id, double* weight);
+
 /* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
  * denominator of the matching roofline.  Returns 32-bit POPC per second. */
 int orbm_popc_peak(int device, double* popc_per_s);

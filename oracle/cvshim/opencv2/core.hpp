@@ -11,6 +11,8 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <sstream>
+#include <string>
 #include <vector>
 
 #include "../../cvprims.hpp"
@@ -222,6 +224,32 @@ inline Mat operator*(double s, const Mat& a) { return mat_map(a, [s](float p) { 
 inline Mat operator*(const Mat& a, double s) { return s * a; }
 inline Mat operator/(const Mat& a, double s) { return mat_map(a, [s](float p) { return (float)(p / s); }); }
 inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
+
+// cv::FileStorage / cv::FileNode: compile-only stand-ins (DBoW2's TemplatedVocabulary has virtual
+// save/load members over them; the oracle only uses its text loader).  Every read yields "absent".
+class FileNode {
+ public:
+  FileNode operator[](const char*) const { return FileNode(); }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+  FileNode operator[](int) const { return FileNode(); }
+  size_t size() const { return 0; }
+  operator int() const { return 0; }
+  operator float() const { return 0.f; }
+  operator double() const { return 0.0; }
+  operator std::string() const { return std::string(); }
+};
+class FileStorage {
+ public:
+  enum { READ = 0, WRITE = 1 };
+  FileStorage() {}
+  FileStorage(const std::string&, int) {}
+  bool isOpened() const { return false; }
+  void release() {}
+  FileNode operator[](const char*) const { return FileNode(); }
+  FileNode operator[](const std::string&) const { return FileNode(); }
+};
+template <typename T>
+inline FileStorage& operator<<(FileStorage& fs, const T&) { return fs; }
 
 class _InputArray {
   const Mat* m_;

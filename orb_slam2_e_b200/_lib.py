@@ -100,6 +100,11 @@ SIGNATURES = {
     "orbm_window_candidates": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _ip]),
     "orbm_search_triangulation": (_i, [_i, C.POINTER(TriKeyFrame), C.POINTER(TriKeyFrame), _vp, _f, _f, _vp, _vp, _i, _i, _vp, _ip]),
     "orbx_stereo_matches": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
+    "orbm_vocab_create": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, C.POINTER(C.c_void_p)]),
+    "orbm_vocab_load_text": (_i, [_i, C.c_char_p, C.POINTER(C.c_void_p)]),
+    "orbm_vocab_info": (_i, [_vp, _ip, _ip, _ip, _ip]),
+    "orbm_vocab_destroy": (_i, [_vp]),
+    "orbm_vocab_transform": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),
 }
 
