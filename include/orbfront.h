@@ -345,6 +345,23 @@ int orbm_vocab_destroy(orbm_vocab* v);
 int orbm_vocab_transform(orbm_vocab* v, const uint8_t* desc, int n, int levelsup, int32_t* word_id,
                          int32_t* node_id, double* weight);
 
+/* MapPoint::ComputeDistinctiveDescriptors -- src/MapPoint.cc:305-370, batched over map points
+ * (LocalMapping::ProcessNewKeyFrame / CreateNewMapPoints / SearchInNeighbors refresh hundreds per
+ * keyframe): point p owns descriptors [offset[p], offset[p+1]) of desc (the rows of its good
+ * observations, in the reference's std::map iteration order).  best[p] = index inside that range
+ * of the descriptor with the least median distance to the others -- median = element
+ * (int)(0.5*(N-1)) of the sorted row of the N x N distance matrix, diagonal included, first row on
+ * ties -- or -1 for an empty range.  At most 1024 descriptors per point.  Host memory. */
+int orbm_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* offset, int n_points,
+                                 int32_t* best);
+
+/* Descriptor database interchange: a flat little-endian file, 16-byte header
+ * {"ORBD", u32 version = 1, u64 n_rows} followed by n_rows x 32 descriptor bytes; a shard's rows can
+ * be appended straight from / saved straight to it.  orbm_db_load appends rows [first, first+count)
+ * of the file (count < 0: to the end) to db. */
+int orbm_db_save(orbm_db* db, const char* path);
+int orbm_db_load(orbm_db* db, const char* path, int64_t first, int64_t count);
+
 /* Measures the integer POPC issue rate of the device (dependent-free chains on every SM), the
  * denominator of the matching roofline.  Returns 32-bit POPC per second. */
 int orbm_popc_peak(int device, double* popc_per_s);

@@ -12,6 +12,7 @@
 //   features_in_area    Frame.cc:342-395 (GetFeaturesInArea)
 //   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
 //   search_triangulation ORBmatcher.cc:858-1024 + :341-358
+//   distinctive_descriptor MapPoint.cc:333-363 (ComputeDistinctiveDescriptors; restatement only, unpinned)
 // Parity status: hamming256, search_bow (both overloads) and window_search are pinned on the
 // reference's own src/ORBmatcher.cc (as is search_triangulation) compiled unmodified over mocks (oracle/_ref/libmatchref.so):
 // tests/test_projection_cpu.py runs the product header over this restatement against it on 31
@@ -482,6 +483,32 @@ static inline int search_triangulation(const TriKeyFrame& K1, const TriKeyFrame&
     }
   }
   return nmatches;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors, MapPoint.cc:333-363, on the N descriptors of one point.
+static inline int distinctive_descriptor(const uint8_t* desc, int N) {
+  if (N <= 0) return -1;
+  std::vector<float> Distances((size_t)N * N);
+  for (int i = 0; i < N; i++) {
+    Distances[(size_t)i * N + i] = 0;
+    for (int j = i + 1; j < N; j++) {
+      int distij = hamming256(desc + 32 * (size_t)i, desc + 32 * (size_t)j);
+      Distances[(size_t)i * N + j] = distij;
+      Distances[(size_t)j * N + i] = distij;
+    }
+  }
+  int BestMedian = INT_MAX;
+  int BestIdx = 0;
+  for (int i = 0; i < N; i++) {
+    std::vector<int> vDists(Distances.begin() + (size_t)i * N, Distances.begin() + (size_t)(i + 1) * N);
+    std::sort(vDists.begin(), vDists.end());
+    int median = vDists[0.5 * (N - 1)];
+    if (median < BestMedian) {
+      BestMedian = median;
+      BestIdx = i;
+    }
+  }
+  return BestIdx;
 }
 
 }  // namespace matchport

@@ -175,4 +175,7 @@ void orc_compute_stereo_matches(const float* lx, const float* ly, const int* loc
   matchport::compute_stereo_matches(lx, ly, loct, ldesc, nl, rx, ry, roct, rdesc, nr, scale, inv_scale, L.data(), R.data(), mb, mbf,
                                     u_right, depth);
 }
+void orc_distinctive_descriptors(const uint8_t* desc, const int* offset, int n_points, int* best) {
+  for (int p = 0; p < n_points; ++p) best[p] = matchport::distinctive_descriptor(desc + 32 * (size_t)offset[p], offset[p + 1] - offset[p]);
+}
 }

@@ -105,6 +105,9 @@ SIGNATURES = {
     "orbm_vocab_info": (_i, [_vp, _ip, _ip, _ip, _ip]),
     "orbm_vocab_destroy": (_i, [_vp]),
     "orbm_vocab_transform": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "orbm_distinctive_descriptors": (_i, [_i, _vp, _vp, _i, _vp]),
+    "orbm_db_save": (_i, [_vp, C.c_char_p]),
+    "orbm_db_load": (_i, [_vp, C.c_char_p, _i64, _i64]),
     "orbm_popc_peak": (_i, [_i, C.POINTER(C.c_double)]),
 }
 

@@ -443,6 +443,43 @@ __global__ void __launch_bounds__(128) stereo_refine_kernel(const StereoRefineAr
   if (lane == 0) { A.u_right[i] = out_u; A.depth[i] = out_z; A.sad[i] = out_sad; }
 }
 
+// ------------------------------------------------------------------------------------
+// MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:305-370), one warp per map point: for every
+// row of the N x N distance matrix the k-th smallest entry (k = (int)(0.5*(N-1)), diagonal 0
+// included) by bisection on the value range 0..256 with warp-wide counts; smallest median wins,
+// first row on ties.  Rows live in shared memory (N <= 1024).
+constexpr int kDistinctWarps = 4, kDistinctMaxN = 1024;
+
+__global__ void __launch_bounds__(kDistinctWarps * 32) distinctive_kernel(const uint4* __restrict__ desc,
+                                                                          const int* __restrict__ offset, int n_points,
+                                                                          int* __restrict__ best) {
+  __shared__ uint16_t row[kDistinctWarps][kDistinctMaxN];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int p = blockIdx.x * kDistinctWarps + w;
+  if (p >= n_points) return;
+  const int o = offset[p], N = offset[p + 1] - o;
+  if (N <= 0) { if (lane == 0) best[p] = -1; return; }
+  const int k = (int)(0.5 * (N - 1));
+  int best_median = 0x7fffffff, best_idx = 0;
+  for (int i = 0; i < N; ++i) {
+    const uint4 qa = __ldg(&desc[2 * (o + i)]), qb = __ldg(&desc[2 * (o + i) + 1]);
+    const uint32_t q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+    for (int j = lane; j < N; j += 32) row[w][j] = (uint16_t)hamming8(q, __ldg(&desc[2 * (o + j)]), __ldg(&desc[2 * (o + j) + 1]));
+    __syncwarp();
+    int lo = 0, hi = 256;  // smallest v with #(d <= v) >= k + 1
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      int c = 0;
+      for (int j = lane; j < N; j += 32) c += row[w][j] <= mid;
+      for (int s = 16; s > 0; s >>= 1) c += __shfl_xor_sync(0xffffffffu, c, s);
+      if (c >= k + 1) hi = mid; else lo = mid + 1;
+    }
+    if (lo < best_median) { best_median = lo; best_idx = i; }
+    __syncwarp();
+  }
+  if (lane == 0) best[p] = best_idx;
+}
+
 }  // namespace orbfront
 
 // ====================================================================================
@@ -1025,6 +1062,79 @@ int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, i
     depth[vDistIdx[i].second] = -1;
   }
   return ORB_OK;
+}
+
+int orbm_distinctive_descriptors(int device, const uint8_t* desc, const int32_t* offset, int n_points, int32_t* best) {
+  if (n_points < 0 || (n_points > 0 && (!offset || !best))) return set_error(ORB_E_INVALID, "orbm_distinctive_descriptors: bad argument");
+  if (n_points == 0) return ORB_OK;
+  if (offset[0] != 0) return set_error(ORB_E_INVALID, "orbm_distinctive_descriptors: offset[0] must be 0");
+  for (int p = 0; p < n_points; ++p) {
+    const int n = offset[p + 1] - offset[p];
+    if (n < 0 || n > kDistinctMaxN)
+      return set_error(ORB_E_INVALID, "orbm_distinctive_descriptors: point %d has %d descriptors (0..%d supported)", p, n, kDistinctMaxN);
+  }
+  const int total = offset[n_points];
+  if (total > 0 && !desc) return set_error(ORB_E_INVALID, "orbm_distinctive_descriptors: null descriptors");
+  int rc = use_device(device);
+  if (rc) return rc;
+  Layout L;
+  const size_t o_d = L.place((size_t)total * 32), o_off = L.place((size_t)(n_points + 1) * 4);
+  const size_t o_up_end = L.bytes;
+  const size_t o_best = L.place((size_t)n_points * 4);
+  CallScratch* S = nullptr;
+  if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+  if (total) memcpy(S->host + o_d, desc, (size_t)total * 32);
+  memcpy(S->host + o_off, offset, (size_t)(n_points + 1) * 4);
+  ORB_CUDA_TRY(cudaMemcpyAsync(S->dev, S->host, o_up_end, cudaMemcpyHostToDevice, S->stream));
+  distinctive_kernel<<<div_up(n_points, kDistinctWarps), kDistinctWarps * 32, 0, S->stream>>>(
+      (const uint4*)(S->dev + o_d), (const int*)(S->dev + o_off), n_points, (int*)(S->dev + o_best));
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpyAsync(S->host + o_best, S->dev + o_best, (size_t)n_points * 4, cudaMemcpyDeviceToHost, S->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+  memcpy(best, S->host + o_best, (size_t)n_points * 4);
+  return ORB_OK;
+}
+
+namespace {
+struct DbFileHeader { char magic[4]; uint32_t version; uint64_t n_rows; };
+static_assert(sizeof(DbFileHeader) == 16, "16-byte header");
+}  // namespace
+
+int orbm_db_save(orbm_db* db, const char* path) {
+  if (!db || !path) return set_error(ORB_E_INVALID, "orbm_db_save: bad argument");
+  int rc = use_device(db->device);
+  if (rc) return rc;
+  std::vector<uint8_t> rows((size_t)db->n * 32);
+  if (db->n) {
+    ORB_CUDA_TRY(cudaMemcpyAsync(rows.data(), db->rows, rows.size(), cudaMemcpyDeviceToHost, db->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+  }
+  FILE* f = fopen(path, "wb");
+  if (!f) return set_error(ORB_E_INVALID, "orbm_db_save: cannot open %s", path);
+  DbFileHeader h = {{'O', 'R', 'B', 'D'}, 1u, (uint64_t)db->n};
+  const bool ok = fwrite(&h, sizeof(h), 1, f) == 1 && (rows.empty() || fwrite(rows.data(), 1, rows.size(), f) == rows.size());
+  if (fclose(f) != 0 || !ok) return set_error(ORB_E_INVALID, "orbm_db_save: short write to %s", path);
+  return ORB_OK;
+}
+
+int orbm_db_load(orbm_db* db, const char* path, int64_t first, int64_t count) {
+  if (!db || !path || first < 0) return set_error(ORB_E_INVALID, "orbm_db_load: bad argument");
+  FILE* f = fopen(path, "rb");
+  if (!f) return set_error(ORB_E_INVALID, "orbm_db_load: cannot open %s", path);
+  DbFileHeader h;
+  if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, "ORBD", 4) != 0 || h.version != 1) {
+    fclose(f);
+    return set_error(ORB_E_INVALID, "orbm_db_load: %s is not a descriptor database file", path);
+  }
+  if ((uint64_t)first > h.n_rows) { fclose(f); return set_error(ORB_E_INVALID, "orbm_db_load: first row beyond the file"); }
+  const int64_t avail = (int64_t)h.n_rows - first;
+  if (count < 0 || count > avail) count = avail;
+  std::vector<uint8_t> rows((size_t)count * 32);
+  bool ok = fseek(f, (long)(sizeof(h) + (size_t)first * 32), SEEK_SET) == 0;
+  ok = ok && (rows.empty() || fread(rows.data(), 1, rows.size(), f) == rows.size());
+  fclose(f);
+  if (!ok) return set_error(ORB_E_INVALID, "orbm_db_load: %s is truncated", path);
+  return orbm_db_append(db, rows.data(), count, 0);
 }
 
 }  // extern "C"

@@ -204,6 +204,17 @@ def window_candidates(frame: FrameGrid, queries, query_desc, device: int = 0):
     return [(idx[o:o + c].copy(), dist[o:o + c].copy()) for o, c in zip(off, cnt)]
 
 
+def distinctive_descriptors(desc, offset, device: int = 0) -> np.ndarray:
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:305-370) for a batch of map points: point p
+    owns rows offset[p]..offset[p+1] of desc; returns the index (inside its range) of the descriptor
+    with the least median distance to the rest, -1 for an empty range."""
+    off = np.ascontiguousarray(offset, np.int32)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    best = np.zeros(len(off) - 1, np.int32)
+    check(_lib.load().orbm_distinctive_descriptors(device, ptr(d) if len(d) else None, ptr(off), len(off) - 1, ptr(best)))
+    return best
+
+
 class DescriptorDB:
     """One GPU-resident shard of the relocalization descriptor database:
     rows [row_base, row_base + n) of the global N x 32 matrix."""
@@ -219,6 +230,14 @@ class DescriptorDB:
 
     def append_device(self, dev_ptr: int, n: int):
         check(_lib.load().orbm_db_append(self._h, C.c_void_p(dev_ptr), n, 1))
+
+    def save(self, path: str):
+        """Flat interchange file (16-byte header + n x 32 bytes), orbm_db_save."""
+        check(_lib.load().orbm_db_save(self._h, str(path).encode()))
+
+    def load(self, path: str, first: int = 0, count: int = -1):
+        """Appends rows [first, first + count) of an interchange file (count < 0: to its end)."""
+        check(_lib.load().orbm_db_load(self._h, str(path).encode(), int(first), int(count)))
 
     def __len__(self):
         n = C.c_int64()

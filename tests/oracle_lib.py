@@ -73,6 +73,7 @@ def oracle(fast=False):
                                     C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double]
     L.orc_compute_stereo_matches.argtypes = [f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, C.c_int,
                                              C.c_void_p, C.c_void_p, i32p, i32p, i32p, C.c_float, C.c_float, f32p, f32p]
+    L.orc_distinctive_descriptors.argtypes = [u8p, i32p, C.c_int, i32p]
     _cache[key] = L
     return L
 

@@ -104,3 +104,43 @@ def test_stereo_search():
 def test_popc_peak_is_plausible():
     v = matcher.popc_peak(0)
     assert 1e12 < v < 2e13
+
+
+def test_distinctive_descriptors_batch():
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:305-370), a keyframe's worth of map points at once."""
+    rng = np.random.default_rng(6)
+    sizes = np.concatenate([[0, 1, 2, 3, 32, 33, 64, 200], rng.integers(1, 40, 500)])
+    off = np.zeros(len(sizes) + 1, np.int32)
+    np.cumsum(sizes, out=off[1:])
+    desc = synth.random_descriptors(int(off[-1]), 8)
+    for p in range(len(sizes)):  # observations of one point look alike; several are identical (median ties)
+        base = desc[off[p]] if sizes[p] else None
+        for j in range(off[p] + 1, off[p + 1]):
+            desc[j] = base if rng.random() < 0.15 else synth.flip_bits(base, int(rng.integers(0, 60)), rng)
+    want = np.zeros(len(sizes), np.int32)
+    oracle().orc_distinctive_descriptors(desc, off, len(sizes), want)
+    got = matcher.distinctive_descriptors(desc, off)
+    assert np.array_equal(got, want)
+    assert got[0] == -1 and (got[1:] >= 0).all() and len(np.unique(got[8:])) > 5
+
+
+def test_descriptor_db_file_round_trip(tmp_path):
+    db, q = synth.reloc_workload(5000, 50, 4, n_shards=2)
+    a = matcher.DescriptorDB(0, 0)
+    a.append(db)
+    path = tmp_path / "db.orbd"
+    a.save(path)
+    raw = path.read_bytes()
+    assert raw[:4] == b"ORBD" and int.from_bytes(raw[4:8], "little") == 1 and int.from_bytes(raw[8:16], "little") == 5000
+    assert raw[16:] == db.tobytes()
+    b = matcher.DescriptorDB(0, 0)
+    b.load(path)
+    assert len(b) == 5000 and b.top2(q).tobytes() == a.top2(q).tobytes()
+    # two shards straight from the file == the single scan
+    s0, s1 = matcher.DescriptorDB(0, 0), matcher.DescriptorDB(0, 2500)
+    s0.load(path, 0, 2500)
+    s1.load(path, 2500, -1)
+    merged, _ = matcher.merge_top2([s0.top2(q), s1.top2(q)])
+    whole = a.top2(q)
+    for f in ("best1", "best2", "idx"):
+        assert np.array_equal(merged[f], whole[f])
