@@ -65,6 +65,8 @@ struct ExtractParams {
   orbx_keypoint* out_kp;  uint8_t* out_desc;  int out_cap;
   int* out_count;                      // [frame]
   int total_cells;                     // sum over levels of nCols*nRows
+  int* pyr_bar;                        // grid-barrier counter of the fused pyramid kernel (null: per-level launches)
+  int pyr_max_grid;                    // CTAs of that kernel that can be resident at once
 };
 
 __device__ __forceinline__ const uint8_t* level_ptr(const ExtractParams& P, int l, int f) {
@@ -82,6 +84,7 @@ __device__ __forceinline__ int level_pitch(const ExtractParams& P, int l) {
 
 // kernel launchers (each returns an ORB_* code)
 int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches);
+int pyramid_fused_max_grid(int device);
 int launch_fast(const ExtractParams& P, cudaStream_t s, int* launches);
 int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches);
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches);

@@ -57,7 +57,8 @@ struct orbx_handle {
   Dev<uint8_t> l0, pyr, blur, qt_b, out_desc;
   Dev<unsigned long long> cand, qt_tmp;
   Dev<uint32_t> kept, qt_seq;
-  Dev<int> cand_count, kept_count, out_count;
+  Dev<int> cand_count, kept_count, out_count, pyr_bar;
+  int pyr_max_grid = -1;
   Dev<int4> rtab;
   Dev<uint32_t> qcode;
   Dev<int> blur_tiles;
@@ -241,7 +242,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       (rc = H->blur.reserve(nf * P.blur_frame + 256)) || (rc = H->cand.reserve(nf * P.cand_frame)) ||
       (rc = H->qt_b.reserve(nf * (P.cand_frame + kMaxLevels) + 16)) || (rc = H->qt_seq.reserve(nf * P.cand_frame)) || (rc = H->qt_tmp.reserve(nf * P.cand_frame)) ||
       (rc = H->kept.reserve(nf * P.kept_frame)) || (rc = H->cand_count.reserve(nf * nl)) ||
-      (rc = H->kept_count.reserve(nf * nl)) || (rc = H->out_count.reserve(nf)) ||
+      (rc = H->kept_count.reserve(nf * nl)) || (rc = H->out_count.reserve(nf)) || (rc = H->pyr_bar.reserve(1)) ||
       (rc = H->out_kp.reserve(nf * P.out_cap)) || (rc = H->out_desc.reserve(nf * P.out_cap * 32)))
     return rc;
   P.n_frames = n_frames;
@@ -249,6 +250,8 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
   P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p; P.qt_tmp = H->qt_tmp.p;
   P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p; P.qcode = H->qcode.p;
   P.out_kp = H->out_kp.p; P.out_desc = H->out_desc.p; P.out_count = H->out_count.p;
+  if (H->pyr_max_grid < 0) H->pyr_max_grid = pyramid_fused_max_grid(H->cfg.device);
+  P.pyr_bar = H->pyr_bar.p; P.pyr_max_grid = H->pyr_max_grid;
   return ORB_OK;
 }
 
@@ -275,6 +278,7 @@ static ExtractParams frame_range(const ExtractParams& P, int f0, int nf) {
   Q.out_kp += f * P.out_cap;
   Q.out_desc += f * (size_t)P.out_cap * 32;
   Q.out_count += f;
+  Q.pyr_bar = nullptr;  // chunks of one handle run concurrently on two streams: no shared barrier counter
   return Q;
 }
 

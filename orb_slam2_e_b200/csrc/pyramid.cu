@@ -7,6 +7,9 @@
 //                         axis, BORDER_REFLECT_101 -- src/ORBextractor.cc:1093-1094.
 //   border_copy_kernel  : builds the 19-px reflect-101 frame on demand for orbx_get_level.
 // All three are HBM-streaming byte kernels (bound: HBM bandwidth); no tensor-core work.
+#include <algorithm>
+#include <cstdlib>
+
 #include "extract.cuh"
 
 namespace orbfront {
@@ -14,15 +17,17 @@ namespace orbfront {
 // One warp marches down a strip of destination rows; each lane owns 4 adjacent destination
 // columns, keeps their horizontal taps in registers and reuses the horizontally interpolated
 // source row shared by consecutive destination rows.
-constexpr int kResizeStrip = 16;
+// The strip length trades redundant work (each strip interpolates its first source rows again) for
+// parallelism: 16 rows for batches that fill the machine anyway, 4 rows when one or a few frames
+// would otherwise leave a handful of warps walking long dependent chains.
+constexpr int kStripBatch = 16, kStripFew = 4;
 
-__global__ void __launch_bounds__(128)
-resize_level_kernel(const __grid_constant__ ExtractParams P, int l) {
+template <int kResizeStrip>
+__device__ __forceinline__ void resize_block(const ExtractParams& P, int l, int bx, int by, int f) {
   const LevelGeom& D = P.lv[l];
-  const int f = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int x0 = (blockIdx.x * 32 + lane) * 4;
-  const int y0 = (blockIdx.y * 4 + warp) * kResizeStrip;
+  const int x0 = (bx * 32 + lane) * 4;
+  const int y0 = (by * 4 + warp) * kResizeStrip;
   if (x0 >= D.w || y0 >= D.h) return;
   const uint8_t* src = level_ptr(P, l - 1, f);
   const int sp = level_pitch(P, l - 1);
@@ -77,13 +82,12 @@ resize_level_kernel(const __grid_constant__ ExtractParams P, int l) {
 // lane constants, and interpolates with DP2A on packed (c0, c1) 16-bit weights -- 11 instructions per
 // source row instead of 8 byte loads + 8 IMADs + their addressing.  Source rows are consumed in
 // order and requested one row ahead.  Arithmetic identical to resize_level_kernel.
-__global__ void __launch_bounds__(128)
-resize_level_words_kernel(const __grid_constant__ ExtractParams P, int l) {
+template <int kResizeStrip>
+__device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l, int bx, int by, int f) {
   const LevelGeom& D = P.lv[l];
-  const int f = blockIdx.z;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int x0 = (blockIdx.x * 32 + lane) * 4;
-  const int y0 = (blockIdx.y * 4 + warp) * kResizeStrip;
+  const int x0 = (bx * 32 + lane) * 4;
+  const int y0 = (by * 4 + warp) * kResizeStrip;
   if (x0 >= D.w || y0 >= D.h) return;
   const uint8_t* src = level_ptr(P, l - 1, f);
   const int sp = level_pitch(P, l - 1);
@@ -163,16 +167,80 @@ resize_level_words_kernel(const __grid_constant__ ExtractParams P, int l) {
   }
 }
 
-int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches) {
+template <int kStrip>
+__global__ void __launch_bounds__(128) resize_level_kernel(const __grid_constant__ ExtractParams P, int l) {
+  resize_block<kStrip>(P, l, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+template <int kStrip>
+__global__ void __launch_bounds__(128) resize_level_words_kernel(const __grid_constant__ ExtractParams P, int l) {
+  resize_words_block<kStrip>(P, l, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// Whole pyramid in ONE cooperative launch, for the tracking thread's case of one or two small frames
+// whose every level fits in a single wave: the seven per-level launches are each a few microseconds
+// of work behind a kernel boundary, and level l needs all of level l-1, so the levels meet at a grid
+// barrier instead.
+__global__ void __launch_bounds__(128) pyramid_fused_kernel(const __grid_constant__ ExtractParams P, int* bar) {
   for (int l = 1; l < P.nlevels; ++l) {
     const LevelGeom& D = P.lv[l];
-    dim3 grid(div_up(D.w, 128), div_up(D.h, 4 * kResizeStrip), P.n_frames);
-    if (D.resize_words) resize_level_words_kernel<<<grid, 128, 0, s>>>(P, l);
-    else resize_level_kernel<<<grid, 128, 0, s>>>(P, l);
+    const int nbx = div_up(D.w, 128), nby = div_up(D.h, 4 * kStripFew), total = nbx * nby * P.n_frames;
+    for (int b = blockIdx.x; b < total; b += gridDim.x) {
+      const int f = b / (nbx * nby), r = b - f * (nbx * nby);
+      if (D.resize_words) resize_words_block<kStripFew>(P, l, r % nbx, r / nbx, f);
+      else resize_block<kStripFew>(P, l, r % nbx, r / nbx, f);
+    }
+    if (l + 1 < P.nlevels) {  // level l complete and visible before anyone reads it
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1);
+        while (*(volatile int*)bar < l * (int)gridDim.x) __nanosleep(20);
+        __threadfence();
+      }
+      __syncthreads();
+    }
+  }
+}
+
+int pyramid_fused_max_grid(int device) {
+  int per_sm = 0, sms = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, pyramid_fused_kernel, 128, 0) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess)
+    return 0;
+  return per_sm * sms;
+}
+
+template <int kStrip>
+static int launch_levels(const ExtractParams& P, cudaStream_t s, int* launches) {
+  for (int l = 1; l < P.nlevels; ++l) {
+    const LevelGeom& D = P.lv[l];
+    dim3 grid(div_up(D.w, 128), div_up(D.h, 4 * kStrip), P.n_frames);
+    if (D.resize_words) resize_level_words_kernel<kStrip><<<grid, 128, 0, s>>>(P, l);
+    else resize_level_kernel<kStrip><<<grid, 128, 0, s>>>(P, l);
     ORB_LAUNCH_CHECK();
     ++*launches;
   }
   return ORB_OK;
+}
+
+int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches) {
+  if (P.nlevels < 2) return ORB_OK;
+  const LevelGeom& D = P.lv[1];
+  // warps the largest level offers with long strips; below about one warp per scheduler slot the
+  // short strips win (measured: 640x480 x1 76 -> 49 us, 3840x2160 x1 121 -> 88 us)
+  const long warps_batch = (long)div_up(D.w, 128) * div_up(D.h, kStripBatch) * P.n_frames;
+  if (warps_batch >= 148 * 32) return launch_levels<kStripBatch>(P, s, launches);
+  const int blocks_few = div_up(D.w, 128) * div_up(D.h, 4 * kStripFew) * P.n_frames;
+  if (P.nlevels > 2 && P.pyr_bar && blocks_few <= P.pyr_max_grid && !getenv("ORBX_NO_FUSED_PYRAMID")) {
+    int* bar = P.pyr_bar;
+    ORB_CUDA_TRY(cudaMemsetAsync(bar, 0, sizeof(int), s));
+    void* args[] = {(void*)&P, (void*)&bar};
+    ORB_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)pyramid_fused_kernel, dim3(blocks_few), dim3(128), args, 0, s));
+    count_launch();
+    ++*launches;
+    return ORB_OK;
+  }
+  return launch_levels<kStripFew>(P, s, launches);
 }
 
 // ------------------------------------------------------------------------------------
