@@ -18,6 +18,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 FLAGS = [f for f in FLAGS if f != "--use_fast_math=false"] + ["-fmad=false"]  # float paths must round per op
+FLAGS += os.environ.get("ORBFRONT_NVCC_FLAGS", "").split()  # developer builds (e.g. -DORBX_QT_PROFILE)
 
 
 def _sources():

@@ -22,6 +22,13 @@
 namespace orbfront {
 
 constexpr int kQtThreads = 256;
+
+#ifdef ORBX_QT_PROFILE  // developer build: cycle stamps of the level-0 CTA of frame 0 (tools/exp_qt_profile.py)
+__device__ long long g_qt_prof[32];
+#define QT_STAMP(k) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_qt_prof[k] = clock64(); } while (0)
+#else
+#define QT_STAMP(k) do { } while (0)
+#endif
 constexpr uint32_t kSeqMark = 0x8000u;  // "head of a child created by the final partial pass"
 
 struct QtCtl {  // control block in shared memory
@@ -141,6 +148,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   uint8_t* s_b = ngain + NP;
   QtCtl& C = *reinterpret_cast<QtCtl*>(smem + align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16));  // NP >= 512: radix counters alias the node tables
 
+  QT_STAMP(0);
   int n = P.cand_count[f * P.nlevels + l];
   n = min(n, G.cand_cap);
   uint32_t* kept = P.kept + (size_t)f * P.kept_frame + G.kept_off;
@@ -161,6 +169,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     gkeys[i] = ((unsigned long long)code << 32) | pay;
   }
   __syncthreads();
+  QT_STAMP(1);
   // sort by path code: global <-> shared ping-pong when the level fits, global <-> global scratch else
   int root_bits = 0;
   while ((1 << root_bits) < G.nIni) ++root_bits;
@@ -173,6 +182,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     __syncthreads();
   }
 
+  QT_STAMP(2);
   // boundary depths b[0..n], tables cnt[] / nexp[]
   for (int i = tid; i < kMaxDepth + 3; i += kQtThreads) { C.hist[i] = 0; C.dlt[i] = 0; }
   for (int i = tid; i <= n; i += kQtThreads) {
@@ -193,6 +203,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   }
   __syncthreads();
 
+  QT_STAMP(3);
   // replay of the reference's pass loop (ORBextractor.cc:593-739) on the tables
   if (tid == 0) {
     int acc = 0, acc2 = 0;
@@ -212,6 +223,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   }
   __syncthreads();
 
+  QT_STAMP(4);
   // ordered passes: biggest nodes first, stop as soon as the list holds N nodes (:676-737)
   bool first_ordered = true;
   while (C.mode == kModeOrdered) {
@@ -236,7 +248,9 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
       nval[m] = (uint32_t)m;
     }
     __syncthreads();
+    if (first_ordered) QT_STAMP(16);
     bitonic_sort(nkey, nval, mp);
+    if (first_ordered) QT_STAMP(17);
     // where does the running node count reach N?
     int carried = 0;
     for (int base = 0; base < M; base += kQtThreads) {
@@ -270,10 +284,15 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
         if (nsize >= N || nsize == size || d + 1 >= dmax) C.mode = kModeFull;  // :735
       }
     }
+    if (first_ordered) QT_STAMP(18);
+#ifdef ORBX_QT_PROFILE
+    if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) { g_qt_prof[19] += 1; if (first_ordered) g_qt_prof[20] = M; }
+#endif
     first_ordered = false;
     __syncthreads();
   }
 
+  QT_STAMP(5);
   // leaves: runs at depth dfin, plus the children of the nodes split by the final partial pass
   const int dfin = C.d, partial = C.partial, d_bfs = C.d_bfs;
   const uint32_t mag_h = (1u << 20) / (uint32_t)G.hCell + 1u, mag_w = (1u << 20) / (uint32_t)G.wCell + 1u;
@@ -282,6 +301,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   for (int i = tid; i < n; i += kQtThreads)
     if (b[i] <= dfin || (partial && (seq[i] & kSeqMark))) nhead[atomicAdd(&C.counter, 1)] = (uint32_t)i;
   __syncthreads();
+  QT_STAMP(6);
   const int L = min(C.counter, G.kept_cap);
   int lp = 1;
   while (lp < L) lp <<= 1;
@@ -315,9 +335,15 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     nval[m] = best_pay;
   }
   __syncthreads();
+  QT_STAMP(7);
   bitonic_sort(nkey, nval, lp);
+  QT_STAMP(8);
   for (int m = tid; m < L; m += kQtThreads) kept[m] = nval[m];
   if (tid == 0) P.kept_count[f * P.nlevels + l] = L;
+  QT_STAMP(9);
+#ifdef ORBX_QT_PROFILE
+  if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) { g_qt_prof[10] = n; g_qt_prof[11] = L; g_qt_prof[12] = C.d_bfs; g_qt_prof[13] = C.d; g_qt_prof[14] = dmax; g_qt_prof[15] = nbits; }
+#endif
 }
 
 int quadtree_smem_bytes(int S, int NP) {
@@ -343,3 +369,14 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
 }
 
 }  // namespace orbfront
+
+#ifdef ORBX_QT_PROFILE
+extern "C" int orbx_debug_qt_prof(long long* out) {
+  cudaDeviceSynchronize();
+  long long zero[32] = {0};
+  cudaMemcpyFromSymbol(out, orbfront::g_qt_prof, sizeof(zero));
+  cudaMemcpyToSymbol(orbfront::g_qt_prof, zero, sizeof(zero));
+  return 0;
+}
+#endif
+
