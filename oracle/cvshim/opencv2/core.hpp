@@ -8,7 +8,9 @@
 #pragma once
 #include <algorithm>
 #include <cassert>
+#include <climits>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <sstream>
@@ -140,6 +142,28 @@ class Mat {
     data = nullptr; rows = cols = 0; step = 0;
   }
   static MatZeros zeros(int r, int c, int type) { return MatZeros{r, c, type}; }
+  static Mat ones(int r, int c, int type) {
+    Mat m(r, c, type);
+    for (int y = 0; y < r; ++y)
+      for (int x = 0; x < c; ++x) {
+        if (type == CV_32F) m.at<float>(y, x) = 1.f;
+        else m.at<uchar>(y, x) = 1;
+      }
+    return m;
+  }
+  // u8 -> f32 (exact) or same-type copy; always a fresh buffer, so `view.convertTo(view, CV_32F)`
+  // detaches the view from the image it pointed into, as OpenCV does when the type changes
+  void convertTo(Mat& dst, int type) const {
+    Mat out(rows, cols, type);
+    for (int y = 0; y < rows; ++y)
+      for (int x = 0; x < cols; ++x) {
+        const float v = type_ == CV_32F ? at<float>(y, x) : (float)at<uchar>(y, x);
+        if (type == CV_32F) out.at<float>(y, x) = v;
+        else out.at<uchar>(y, x) = (uchar)v;
+      }
+    dst = out;
+  }
+  Mat reshape(int) const { return *this; }  // compile-only: reached only with lens distortion (see undistortPoints)
 
   Mat operator()(const Rect& r) const {
     Mat m(*this);
@@ -224,6 +248,38 @@ inline Mat operator*(double s, const Mat& a) { return mat_map(a, [s](float p) { 
 inline Mat operator*(const Mat& a, double s) { return s * a; }
 inline Mat operator/(const Mat& a, double s) { return mat_map(a, [s](float p) { return (float)(p / s); }); }
 inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
+enum { NORM_L1 = 2 };
+// cv::norm(a, b, NORM_L1) on f32: OpenCV accumulates |a - b| in double; the stereo refinement feeds it
+// integer-valued patches (sum < 2^24), for which every summation order gives the same value
+inline double norm(const Mat& a, const Mat& b, int type) {
+  assert(type == NORM_L1 && a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);
+  (void)type;
+  double s = 0;
+  for (int y = 0; y < a.rows; ++y)
+    for (int x = 0; x < a.cols; ++x) s += std::fabs((double)(a.at<float>(y, x) - b.at<float>(y, x)));
+  return s;
+}
+
+// cv::Mat_<T>(r, c) << a, b, c
+template <typename T>
+class Mat_ : public Mat {
+  int fill_;
+ public:
+  Mat_(int r, int c) : Mat(r, c, sizeof(T) == 4 ? CV_32F : CV_8U), fill_(0) {}
+  Mat_& operator<<(T v) { return (*this), v; }
+  Mat_& operator,(T v) {
+    this->template at<T>(fill_ / cols, fill_ % cols) = v;
+    ++fill_;
+    return *this;
+  }
+};
+
+// Lens undistortion is outside the pinned slice: every oracle scene uses distortion-free calibration
+// (Frame.cc:424-430 and :452 then skip this call).
+inline void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const Mat&) {
+  fprintf(stderr, "cvshim: cv::undistortPoints is not provided (use zero distortion coefficients)\n");
+  abort();
+}
 
 // cv::FileStorage / cv::FileNode: compile-only stand-ins (DBoW2's TemplatedVocabulary has virtual
 // save/load members over them; the oracle only uses its text loader).  Every read yields "absent".

@@ -12,13 +12,16 @@
 //   features_in_area    Frame.cc:342-395 (GetFeaturesInArea)
 //   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
 //   search_triangulation ORBmatcher.cc:858-1024 + :341-358
-//   distinctive_descriptor MapPoint.cc:333-363 (ComputeDistinctiveDescriptors; restatement only, unpinned)
+//   distinctive_descriptor MapPoint.cc:333-363 (ComputeDistinctiveDescriptors)
 // Parity status: hamming256, search_bow (both overloads) and window_search are pinned on the
 // reference's own src/ORBmatcher.cc (as is search_triangulation) compiled unmodified over mocks (oracle/_ref/libmatchref.so):
 // tests/test_projection_cpu.py runs the product header over this restatement against it on 31
-// scenes.  top2_bruteforce / merge_top2 (no such function in the reference) and stereo_search
-// (Frame.cc is not compilable here) stay "parity unpinned": known answers + an independent numpy
-// model in tests/test_oracle_match.py.
+// scenes.  stereo_search / compute_stereo_matches, features_in_area and distinctive_descriptor are
+// pinned on the reference's own src/Frame.cc and src/MapPoint.cc compiled unmodified
+// (oracle/_ref/libframeref.so, tests/test_frame_ref_cpu.py: bit-equal mvuRight / mvDepth, identical
+// index lists, identical chosen descriptors).  top2_bruteforce / merge_top2 have no counterpart in
+// the reference (its distance and update rule are the pinned ones above): known answers + an
+// independent numpy model in tests/test_oracle_match.py.
 #pragma once
 #include <algorithm>
 #include <climits>

@@ -175,6 +175,25 @@ void orc_compute_stereo_matches(const float* lx, const float* ly, const int* loc
   matchport::compute_stereo_matches(lx, ly, loct, ldesc, nl, rx, ry, roct, rdesc, nr, scale, inv_scale, L.data(), R.data(), mb, mbf,
                                     u_right, depth);
 }
+// lists back to back in out_idx, offsets in out_off[nq + 1]; returns the total (negative: cap too small)
+int orc_features_in_area(const float* x, const float* y, const int* octave, int n, float min_x, float min_y, float width_inv,
+                         float height_inv, int cols, int rows, const int* cell_off, const uint32_t* cell_idx, const float* qx,
+                         const float* qy, const float* qr, const int* qmin, const int* qmax, int nq, int* out_off, int* out_idx,
+                         int cap) {
+  matchport::GridFrame F{x, y, octave, nullptr, nullptr, n, min_x, min_y, width_inv, height_inv, cols, rows, cell_off, cell_idx};
+  std::vector<int> v;
+  int total = 0;
+  for (int q = 0; q < nq; ++q) {
+    out_off[q] = total;
+    matchport::features_in_area(F, qx[q], qy[q], qr[q], qmin[q], qmax[q], v);
+    for (size_t j = 0; j < v.size(); ++j) {
+      if (total < cap) out_idx[total] = v[j];
+      ++total;
+    }
+  }
+  out_off[nq] = total;
+  return total <= cap ? total : -total;
+}
 void orc_distinctive_descriptors(const uint8_t* desc, const int* offset, int n_points, int* best) {
   for (int p = 0; p < n_points; ++p) best[p] = matchport::distinctive_descriptor(desc + 32 * (size_t)offset[p], offset[p + 1] - offset[p]);
 }

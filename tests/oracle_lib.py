@@ -74,6 +74,8 @@ def oracle(fast=False):
     L.orc_compute_stereo_matches.argtypes = [f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, C.c_int,
                                              C.c_void_p, C.c_void_p, i32p, i32p, i32p, C.c_float, C.c_float, f32p, f32p]
     L.orc_distinctive_descriptors.argtypes = [u8p, i32p, C.c_int, i32p]
+    L.orc_features_in_area.argtypes = [f32p, f32p, i32p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
+                                       i32p, u32p, f32p, f32p, f32p, i32p, i32p, C.c_int, i32p, i32p, C.c_int]
     _cache[key] = L
     return L
 
@@ -105,6 +107,49 @@ def ref_lib(fast=False):
     L.orbref_scale.restype = C.c_float
     _cache[key] = L
     return L
+
+
+def frame_ref_lib():
+    """The reference's own Frame.cc + MapPoint.cc (+ ORBextractor.cc, DBoW2 vectors) over the shim
+    (oracle/_ref/libframeref.so, which imports ORBmatcher's constants and DescriptorDistance from
+    libmatchref.so); None when it is not built and cannot be (no /root/reference)."""
+    key = ("frameref",)
+    if key in _cache:
+        return _cache[key]
+    path = os.path.join(ORACLE_DIR, "_ref", "libframeref.so")
+    if not os.path.exists(path):
+        if os.path.isdir("/root/reference/src"):
+            subprocess.check_call(["make", "-C", ORACLE_DIR, "_ref/libframeref.so"], stdout=subprocess.DEVNULL)
+        else:
+            _cache[key] = None
+            return None
+    L = C.CDLL(path)
+    L.frameref_constants.argtypes = [i32p]
+    L.frameref_stereo.argtypes = [C.c_int, C.c_float, C.c_int, f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, i32p, u8p, C.c_int,
+                                  C.c_void_p, C.c_void_p, i32p, i32p, i32p, C.c_float, C.c_float, f32p, f32p]
+    L.frameref_features_in_area.argtypes = [f32p, f32p, i32p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p, f32p,
+                                            f32p, i32p, i32p, C.c_int, i32p, i32p, C.c_int]
+    L.frameref_distinctive.argtypes = [u8p, i32p, C.c_void_p, C.c_int, u8p]
+    _cache[key] = L
+    return L
+
+
+def ref_stereo_matches(L, cfg, kl, dl, kr, dr, levels_left, levels_right, mb, mbf):
+    """Frame::ComputeStereoMatches of the reference on given keypoints and pyramid levels."""
+    n_levels = len(levels_left)
+    PL = (C.c_void_p * n_levels)(*[a.ctypes.data for a in levels_left])
+    PR = (C.c_void_p * n_levels)(*[a.ctypes.data for a in levels_right])
+    for a, b in zip(levels_left, levels_right):
+        assert a.shape == b.shape and a.strides == b.strides and a.strides[1] == 1
+    step = np.array([a.strides[0] for a in levels_left], np.int32)
+    w = np.array([a.shape[1] for a in levels_left], np.int32)
+    h = np.array([a.shape[0] for a in levels_left], np.int32)
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    ur, z = np.zeros(len(kl), np.float32), np.zeros(len(kl), np.float32)
+    L.frameref_stereo(cfg[0], cfg[1], cfg[2], f(kl["x"]), f(kl["y"]), np.ascontiguousarray(kl["octave"], np.int32),
+                      np.ascontiguousarray(dl), len(kl), f(kr["x"]), f(kr["y"]), np.ascontiguousarray(kr["octave"], np.int32),
+                      np.ascontiguousarray(dr), len(kr), C.cast(PL, C.c_void_p), C.cast(PR, C.c_void_p), step, w, h, mb, mbf, ur, z)
+    return ur, z
 
 
 class _Ext:
