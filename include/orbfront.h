@@ -98,8 +98,8 @@ int orbx_batch_read_all(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int c
  * a level's quota by up to 3). */
 int orbx_frame_capacity(orbx_handle* h, int w, int ht, int* cap);
 /* Host-to-host batch in one call: frames are uploaded, extracted and their results downloaded in
- * chunks of chunk_frames (<= 0: an eighth of the batch, at least 32) on three streams, so PCIe traffic in both directions
- * overlaps the kernels.  Pinned host buffers give full overlap; pageable ones still work.  Output
+ * chunks of chunk_frames (<= 0: a sixteenth of the batch, at least 32) on copy streams either side of four rotating
+ * compute streams, so PCIe traffic in both directions overlaps the kernels and one chunk's tails overlap the next chunks.  Pinned host buffers give full overlap; pageable ones still work.  Output
  * layout as orbx_batch_read_all (frame f at row f*cap_per_frame; counts[f] keypoints).  Blocks
  * until every result is in host memory. */
 int orbx_extract_batch_host(orbx_handle* h, const uint8_t* imgs, int n, int w, int ht, size_t stride,

@@ -48,7 +48,8 @@ struct orbx_handle {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // copy streams + per-chunk events of orbx_extract_batch_host (upload | extract | download pipeline)
-  cudaStream_t s_up = nullptr, s_down = nullptr, s_alt = nullptr;  // s_alt: second compute stream (odd chunks)
+  cudaStream_t s_up = nullptr, s_down = nullptr, s_alt = nullptr;  // s_alt: second compute stream
+  std::vector<cudaStream_t> s_more;  // further compute streams (ORBX_COMPUTE_STREAMS > 2)
   std::vector<cudaEvent_t> ev_up, ev_done;
   int* pinned_counts = nullptr;  // page-locked staging for per-frame counts (a pageable destination would block the host per chunk)
   int pinned_counts_cap = 0;
@@ -317,6 +318,7 @@ int orbx_destroy(orbx_handle* H) {
   if (H->s_up) { cudaStreamSynchronize(H->s_up); cudaStreamDestroy(H->s_up); }
   if (H->s_down) { cudaStreamSynchronize(H->s_down); cudaStreamDestroy(H->s_down); }
   if (H->s_alt) { cudaStreamSynchronize(H->s_alt); cudaStreamDestroy(H->s_alt); }
+  for (cudaStream_t t : H->s_more) { cudaStreamSynchronize(t); cudaStreamDestroy(t); }
   if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
   for (cudaEvent_t e : H->ev_up) cudaEventDestroy(e);
   for (cudaEvent_t e : H->ev_done) cudaEventDestroy(e);
@@ -424,12 +426,12 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
     ORB_CUDA_TRY(cudaMallocHost(&H->pinned_counts, sizeof(int) * (size_t)n));
     H->pinned_counts_cap = n;
   }
-  // chunk schedule: the caller's size, else an eighth of the batch (at least 32 frames)
+  // chunk schedule: the caller's size, else a sixteenth of the batch (at least 32 frames)
   std::vector<int> chunk_begin;
   if (chunk_frames > 0) {
     for (int f0 = 0; f0 < n; f0 += chunk_frames) chunk_begin.push_back(f0);
   } else {
-    const int size = std::max(32, n / 8);  // measured best with two alternating compute streams (1024 frames: 128)
+    const int size = std::max(32, n / 16);  // measured best with four compute streams (1024 frames: 64; tools/exp_e2e_streams.py)
     for (int f0 = 0; f0 < n; f0 += size) chunk_begin.push_back(f0);
   }
   chunk_begin.push_back(n);
@@ -437,7 +439,13 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
   if (!H->s_up) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_up, cudaStreamNonBlocking));
   if (!H->s_down) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_down, cudaStreamNonBlocking));
   if (!H->s_alt) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_alt, cudaStreamNonBlocking));
-  static const bool two_streams = getenv("ORBX_ONE_COMPUTE_STREAM") == nullptr;
+  static const int n_comp_env = getenv("ORBX_COMPUTE_STREAMS") ? atoi(getenv("ORBX_COMPUTE_STREAMS")) : 4;
+  const int n_comp = std::min(std::max(n_comp_env, 1), 8);
+  while ((int)H->s_more.size() < n_comp - 2) {
+    cudaStream_t t = nullptr;
+    ORB_CUDA_TRY(cudaStreamCreateWithFlags(&t, cudaStreamNonBlocking));
+    H->s_more.push_back(t);
+  }
   while ((int)H->ev_up.size() < n_chunks) {
     cudaEvent_t a = nullptr, b = nullptr;
     ORB_CUDA_TRY(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -463,15 +471,15 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
                                        (size_t)ht, cudaMemcpyHostToDevice, H->s_up));
     }
     ORB_CUDA_TRY(cudaEventRecord(H->ev_up[c], H->s_up));
-    // consecutive chunks alternate between two compute streams: one chunk's tail (few CTAs left,
-    // latency-bound quadtree) overlaps the next chunk's streaming kernels
-    cudaStream_t cs = (two_streams && (c & 1)) ? H->s_alt : H->stream;
+    // consecutive chunks rotate over the compute streams: one chunk's tails (few CTAs left,
+    // latency-bound quadtree) overlap the streaming kernels of the chunks behind it
+    const int lane = c % n_comp;
+    cudaStream_t cs = lane == 0 ? H->stream : lane == 1 ? H->s_alt : H->s_more[lane - 2];
     ORB_CUDA_TRY(cudaStreamWaitEvent(cs, H->ev_up[c], 0));
     const ExtractParams Q = frame_range(P, f0, nf);
     for (int s = 0; s < ORBX_N_STAGES; ++s)
       if ((rc = stages[s](Q, cs, &launches))) return rc;
     ORB_CUDA_TRY(cudaEventRecord(H->ev_done[c], cs));
-    if (cs != H->stream) ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_done[c], 0));  // ev1 / later work on the handle's stream
     ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_down, H->ev_done[c], 0));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->pinned_counts + f0, H->out_count.p + f0, sizeof(int) * (size_t)nf, cudaMemcpyDeviceToHost, H->s_down));
     if (cap_per_frame == oc) {  // same row count on both sides: linear copies
@@ -487,6 +495,10 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
                                      32 * (size_t)oc, 32 * (size_t)oc, (size_t)nf, cudaMemcpyDeviceToHost, H->s_down));
     }
   }
+  // the other compute streams join the handle's stream once, at the end (a join per chunk would
+  // hold the next chunk of the handle's stream back until its predecessor has drained)
+  for (int c = std::max(0, n_chunks - n_comp); c < n_chunks; ++c)
+    if (c % n_comp != 0) ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_done[c], 0));
   ORB_CUDA_TRY(cudaEventRecord(H->ev1, H->stream));
   H->stage_valid = false;
   H->n_frames = n;
