@@ -322,6 +322,40 @@ int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, i
                         const orbx_keypoint* keys_right, const uint8_t* desc_right, int n_right,
                         float mb, float mbf, float* u_right, float* depth);
 
+/* ---- Rest of Frame construction ---------------------------------------------
+ * What the Frame constructors do with the extractor's output before tracking sees the frame
+ * (src/Frame.cc:85-120, :148-178, :207-240): UndistortKeyPoints, ComputeStereoFromRGBD (RGB-D only) and
+ * AssignFeaturesToGrid, plus -- once per camera -- ComputeImageBounds. */
+typedef struct orbx_camera {
+  float fx, fy, cx, cy;      /* mK (CV_32F 3x3): K(0,0), K(1,1), K(0,2), K(1,2) */
+  float k1, k2, p1, p2, k3;  /* mDistCoef (CV_32F): k3 = 0 when the settings file has none (src/Tracking.cc:66-77).
+                                k1 == 0 means "no distortion": keypoints are copied (src/Frame.cc:421-425) */
+  float bf;                  /* mbf (only read with a depth image) */
+} orbx_camera;
+typedef struct orbx_frame_bounds {
+  float min_x, min_y;           /* Frame::mnMinX, mnMinY */
+  float width_inv, height_inv;  /* mfGridElementWidthInv, mfGridElementHeightInv (src/Frame.cc:106-107) */
+  int32_t cols, rows;           /* FRAME_GRID_COLS x FRAME_GRID_ROWS (64 x 48, include/Frame.h:39-40) */
+} orbx_frame_bounds;
+/* cv::undistortPoints(src, dst, K, distCoef, Mat(), K) on n (x, y) float pairs, as
+ * Frame::UndistortKeyPoints (src/Frame.cc:419-449) and Frame::ComputeImageBounds (:451-485, the four
+ * corners) call it: five fixed-point iterations in double, result rounded to float.  With k1 == 0
+ * the points are copied.  Host memory; xy_out may alias xy. */
+int orbx_undistort_points(int device, const float* xy /* n x 2 */, int n, const orbx_camera* cam,
+                          float* xy_out /* n x 2 */);
+/* One launch for the rest of a Frame: xy_un[i] = mvKeysUn[i].pt (src/Frame.cc:419-449); the cell lists
+ * of AssignFeaturesToGrid (:245-260 with PosInGrid, :397-408) in the CSR layout orbm_grid_frame takes
+ * (cell (ix, iy) = entries [cell_off[ix*rows+iy], cell_off[ix*rows+iy+1]) of cell_idx, keypoint order
+ * inside a cell; *n_in_grid = keypoints that fall inside the grid); and, when depth != NULL,
+ * ComputeStereoFromRGBD (:703-727): depth_out[i] = mvDepth[i] = imDepth.at<float>(y, x) when positive,
+ * u_right[i] = mvuRight[i] = xy_un[i].x - bf / depth, else -1 for both.  depth is a CV_32F image
+ * (depth_stride in bytes) in host (depth_memory 0) or device (1) memory; everything else is host memory.
+ * cell_idx needs n entries, cell_off cols*rows + 1. */
+int orbx_frame_finish(int device, const orbx_keypoint* keys, int n, const orbx_camera* cam,
+                      const orbx_frame_bounds* grid, const float* depth, int depth_w, int depth_h,
+                      size_t depth_stride, int depth_memory, float* xy_un /* n x 2 */, float* u_right,
+                      float* depth_out, int32_t* cell_off, uint32_t* cell_idx, int* n_in_grid);
+
 /* ---- Vocabulary tree --------------------------------------------------------
  * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> as ORB-SLAM2 uses it (include/ORBVocabulary.h):
  * the k-ary tree stays resident on the device and descriptors are pushed down it in bulk

@@ -2,7 +2,8 @@
 //
 // CPU restatement of the five un-vendored OpenCV primitives that the reference
 // ORBextractor calls (reference: src/ORBextractor.cc:103 fastAtan2, :810/:822 FAST,
-// :1094 GaussianBlur, :1128 resize, :1130-1136 copyMakeBorder).  OpenCV itself is
+// :1094 GaussianBlur, :1128 resize, :1130-1136 copyMakeBorder), plus cv::undistortPoints
+// as Frame::UndistortKeyPoints / ComputeImageBounds call it (src/Frame.cc:438, :466).  OpenCV itself is
 // absent from /root/reference (CMakeLists.txt:20 `find_package(OpenCV 3.4 REQUIRED)`),
 // so the arithmetic below restates the published OpenCV 4.x algorithms for CV_8U and
 // is pinned against the `cv2` 4.13.0 wheel by tests/test_oracle_prims.py.
@@ -236,6 +237,62 @@ static inline void fast9_16(const uint8_t* img, int w, int h, size_t step, int t
           s > r[w - 1] && s > r[w] && s > r[w + 1])
         out.push_back({x, y, s});
     }
+}
+
+// ---------------------------------------------------------------------------
+// cv::undistortPoints(src, dst, K, distCoeffs, R = Mat(), P) for CV_32FC2 points, as OpenCV 4.x
+// computes it when no TermCriteria is passed (calib3d undistortPoints -> cvUndistortPointsInternal
+// with TermCriteria(MAX_ITER, 5, 0.01): exactly five iterations, no epsilon test).  Everything is
+// double; K and the coefficients arrive as CV_32F and are widened; the 14-entry coefficient array
+// (k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4 tauX tauY) is zero beyond the n_dist given, the tilt matrix is
+// the identity for tau = 0 and RR = P * I.  Reference call sites: src/Frame.cc:438 and :466
+// (R empty, P = mK).  Pinned against cv2 4.13.0 by tests/test_frame_finish_cpu.py.
+static inline void undistort_points(const float* src_xy, int n, const float* K9, const float* dist, int n_dist,
+                                    const float* P9, float* dst_xy) {
+  double A[3][3], RR[3][3], k[14] = {0};
+  for (int i = 0; i < 9; ++i) A[i / 3][i % 3] = (double)K9[i];
+  for (int i = 0; i < n_dist && i < 14; ++i) k[i] = (double)dist[i];
+  for (int i = 0; i < 3; ++i)       // RR = PP * I  (cvMatMul)
+    for (int j = 0; j < 3; ++j) {
+      double acc = 0;
+      for (int t = 0; t < 3; ++t) acc += (double)P9[i * 3 + t] * (t == j ? 1.0 : 0.0);
+      RR[i][j] = acc;
+    }
+  const double fx = A[0][0], fy = A[1][1], ifx = 1. / fx, ify = 1. / fy, cx = A[0][2], cy = A[1][2];
+  const double invMatTilt[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  for (int i = 0; i < n; ++i) {
+    double x = src_xy[2 * i], y = src_xy[2 * i + 1], x0, y0, u = x, v = y;
+    x = (x - cx) * ifx;
+    y = (y - cy) * ify;
+    if (dist && n_dist > 0) {
+      const double vec[3] = {x, y, 1};
+      double ut[3];
+      for (int r = 0; r < 3; ++r) ut[r] = invMatTilt[r][0] * vec[0] + invMatTilt[r][1] * vec[1] + invMatTilt[r][2] * vec[2];
+      const double invProj = ut[2] ? 1. / ut[2] : 1;
+      x0 = x = invProj * ut[0];
+      y0 = y = invProj * ut[1];
+      for (int j = 0; j < 5; ++j) {
+        const double r2 = x * x + y * y;
+        const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+        if (icdist < 0) {
+          x = (u - cx) * ifx;
+          y = (v - cy) * ify;
+          break;
+        }
+        const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+        const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+        x = (x0 - deltaX) * icdist;
+        y = (y0 - deltaY) * icdist;
+      }
+    }
+    const double xx = RR[0][0] * x + RR[0][1] * y + RR[0][2];
+    const double yy = RR[1][0] * x + RR[1][1] * y + RR[1][2];
+    const double ww = 1. / (RR[2][0] * x + RR[2][1] * y + RR[2][2]);
+    x = xx * ww;
+    y = yy * ww;
+    dst_xy[2 * i] = (float)x;
+    dst_xy[2 * i + 1] = (float)y;
+  }
 }
 
 }  // namespace cvprims

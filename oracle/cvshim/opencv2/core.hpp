@@ -163,7 +163,7 @@ class Mat {
       }
     dst = out;
   }
-  Mat reshape(int) const { return *this; }  // compile-only: reached only with lens distortion (see undistortPoints)
+  Mat reshape(int) const { return *this; }  // N x 2 x 1ch <-> N x 1 x 2ch share one layout (see undistortPoints)
 
   Mat operator()(const Rect& r) const {
     Mat m(*this);
@@ -274,11 +274,21 @@ class Mat_ : public Mat {
   }
 };
 
-// Lens undistortion is outside the pinned slice: every oracle scene uses distortion-free calibration
-// (Frame.cc:424-430 and :452 then skip this call).
-inline void undistortPoints(const Mat&, Mat&, const Mat&, const Mat&, const Mat&, const Mat&) {
-  fprintf(stderr, "cvshim: cv::undistortPoints is not provided (use zero distortion coefficients)\n");
-  abort();
+// cv::undistortPoints as Frame.cc:438 / :466 call it: src = dst = an N x 2 CV_32F matrix (the shim's
+// reshape() is the identity, the memory layout of N x 2 x 1 channel and N x 1 x 2 channels being the
+// same), cameraMatrix = P = mK (3 x 3 CV_32F), distCoeffs 4 x 1 or 5 x 1 CV_32F, R empty.  Forwards to
+// oracle/cvprims.hpp (pinned against cv2 4.13.0).
+inline void undistortPoints(const Mat& src, Mat& dst, const Mat& K, const Mat& D, const Mat& R, const Mat& P) {
+  assert(src.cols == 2 && R.data == nullptr && K.rows == 3 && K.cols == 3 && P.rows == 3 && P.cols == 3);
+  float k9[9], p9[9], d[14] = {0};
+  for (int i = 0; i < 9; ++i) { k9[i] = K.at<float>(i / 3, i % 3); p9[i] = P.at<float>(i / 3, i % 3); }
+  const int nd = D.rows * D.cols;
+  for (int i = 0; i < nd && i < 14; ++i) d[i] = D.rows == 1 ? D.at<float>(0, i) : D.at<float>(i, 0);
+  std::vector<float> in((size_t)src.rows * 2), out((size_t)src.rows * 2);
+  for (int i = 0; i < src.rows; ++i) { in[2 * i] = src.at<float>(i, 0); in[2 * i + 1] = src.at<float>(i, 1); }
+  cvprims::undistort_points(in.data(), src.rows, k9, d, nd, p9, out.data());
+  if (dst.data != src.data || dst.rows != src.rows) dst.create(src.rows, 2, CV_32F);
+  for (int i = 0; i < src.rows; ++i) { dst.at<float>(i, 0) = out[2 * i]; dst.at<float>(i, 1) = out[2 * i + 1]; }
 }
 
 // cv::FileStorage / cv::FileNode: compile-only stand-ins (DBoW2's TemplatedVocabulary has virtual

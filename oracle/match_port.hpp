@@ -13,6 +13,8 @@
 //   window_search       ORBmatcher.cc:46-132 (and the best-only loops of :491-604, :1529-1800)
 //   search_triangulation ORBmatcher.cc:858-1024 + :341-358
 //   distinctive_descriptor MapPoint.cc:333-363 (ComputeDistinctiveDescriptors)
+//   undistort_keypoints / image_bounds / assign_features_to_grid / stereo_from_rgbd  Frame.cc:419-485, :245-260, :703-727
+//     (pinned on the reference's own Frame.cc in libframeref.so and, for cv::undistortPoints, on cv2 4.13: tests/test_frame_finish_cpu.py)
 // Parity status: hamming256, search_bow (both overloads) and window_search are pinned on the
 // reference's own src/ORBmatcher.cc (as is search_triangulation) compiled unmodified over mocks (oracle/_ref/libmatchref.so):
 // tests/test_projection_cpu.py runs the product header over this restatement against it on 31
@@ -29,6 +31,8 @@
 #include <cstdint>
 #include <cstring>
 #include <vector>
+
+#include "cvprims.hpp"
 
 namespace matchport {
 
@@ -340,6 +344,61 @@ static inline void features_in_area(const GridFrame& F, float x, float y, float 
         const float disty = F.y[k] - y;
         if (fabs(distx) < r && fabs(disty) < r) vIndices.push_back(k);
       }
+    }
+  }
+}
+
+// The rest of the Frame constructors (Frame.cc:85-120) after extraction, restated:
+//   UndistortKeyPoints :419-449, ComputeImageBounds :451-485, ComputeStereoFromRGBD :703-727,
+//   AssignFeaturesToGrid :245-260 with PosInGrid :397-408.
+// cam = fx fy cx cy; dist = k1 k2 p1 p2 [k3].  cv::undistortPoints is cvprims::undistort_points.
+static inline void camera_k9(const float* cam, float* K9) {
+  const float k[9] = {cam[0], 0.f, cam[2], 0.f, cam[1], cam[3], 0.f, 0.f, 1.f};
+  memcpy(K9, k, sizeof(k));
+}
+static inline void undistort_keypoints(const float* xy, int n, const float* cam, const float* dist, int n_dist, float* xy_un) {
+  if (dist[0] == 0.0) {  // mDistCoef.at<float>(0)==0.0: mvKeysUn = mvKeys
+    memcpy(xy_un, xy, (size_t)n * 2 * sizeof(float));
+    return;
+  }
+  float K9[9];
+  camera_k9(cam, K9);
+  cvprims::undistort_points(xy, n, K9, dist, n_dist, K9, xy_un);
+}
+// bounds = mnMinX mnMaxX mnMinY mnMaxY
+static inline void image_bounds(int w, int h, const float* cam, const float* dist, int n_dist, float* bounds) {
+  if (dist[0] != 0.0) {
+    float m[8] = {0.f, 0.f, (float)w, 0.f, 0.f, (float)h, (float)w, (float)h};
+    undistort_keypoints(m, 4, cam, dist, n_dist, m);
+    bounds[0] = std::min(m[0], m[4]);
+    bounds[1] = std::max(m[2], m[6]);
+    bounds[2] = std::min(m[1], m[3]);
+    bounds[3] = std::max(m[5], m[7]);
+  } else {
+    bounds[0] = 0.0f; bounds[1] = (float)w; bounds[2] = 0.0f; bounds[3] = (float)h;
+  }
+}
+// cells[(ix, iy) -> ix*rows+iy] = keypoint indices in push_back order
+static inline void assign_features_to_grid(const float* xy_un, int n, float min_x, float min_y, float width_inv, float height_inv,
+                                           int cols, int rows, std::vector<std::vector<int>>& cells) {
+  cells.assign((size_t)cols * rows, std::vector<int>());
+  for (int i = 0; i < n; ++i) {
+    const int posX = (int)round((xy_un[2 * i] - min_x) * width_inv);
+    const int posY = (int)round((xy_un[2 * i + 1] - min_y) * height_inv);
+    if (posX < 0 || posX >= cols || posY < 0 || posY >= rows) continue;
+    cells[(size_t)posX * rows + posY].push_back(i);
+  }
+}
+static inline void stereo_from_rgbd(const float* xy, const float* xy_un, int n, const float* depth, int depth_w, float mbf,
+                                    float* u_right, float* depth_out) {
+  for (int i = 0; i < n; ++i) {
+    u_right[i] = -1.f;
+    depth_out[i] = -1.f;
+    const float v = xy[2 * i + 1], u = xy[2 * i];
+    const float d = depth[(size_t)(int)v * depth_w + (int)u];
+    if (d > 0) {
+      depth_out[i] = d;
+      u_right[i] = xy_un[2 * i] - mbf / d;
     }
   }
 }

@@ -194,6 +194,28 @@ int orc_features_in_area(const float* x, const float* y, const int* octave, int 
   out_off[nq] = total;
   return total <= cap ? total : -total;
 }
+// rest of Frame construction (matchport::undistort_keypoints ... stereo_from_rgbd); cell lists as CSR
+void orc_undistort_points(const float* xy, int n, const float* cam, const float* dist, int n_dist, float* out) {
+  matchport::undistort_keypoints(xy, n, cam, dist, n_dist, out);
+}
+void orc_image_bounds(int w, int h, const float* cam, const float* dist, int n_dist, float* bounds) {
+  matchport::image_bounds(w, h, cam, dist, n_dist, bounds);
+}
+int orc_frame_finish(const float* xy, int n, const float* cam, const float* dist, int n_dist, float bf, float min_x, float min_y,
+                     float width_inv, float height_inv, int cols, int rows, const float* depth, int depth_w, float* xy_un,
+                     float* u_right, float* depth_out, int* cell_off, int* cell_idx) {
+  matchport::undistort_keypoints(xy, n, cam, dist, n_dist, xy_un);
+  if (depth) matchport::stereo_from_rgbd(xy, xy_un, n, depth, depth_w, bf, u_right, depth_out);
+  std::vector<std::vector<int>> cells;
+  matchport::assign_features_to_grid(xy_un, n, min_x, min_y, width_inv, height_inv, cols, rows, cells);
+  int total = 0;
+  for (size_t c = 0; c < cells.size(); ++c) {
+    cell_off[c] = total;
+    for (int i : cells[c]) cell_idx[total++] = i;
+  }
+  cell_off[cells.size()] = total;
+  return total;
+}
 void orc_distinctive_descriptors(const uint8_t* desc, const int* offset, int n_points, int* best) {
   for (int p = 0; p < n_points; ++p) best[p] = matchport::distinctive_descriptor(desc + 32 * (size_t)offset[p], offset[p + 1] - offset[p]);
 }

@@ -12,6 +12,8 @@
 //   Frame::ComputeStereoMatches (Frame.cc:527-700)            -> matchport::compute_stereo_matches
 //   Frame::AssignFeaturesToGrid / GetFeaturesInArea (:245-260, :342-395) -> matchport::features_in_area
 //   MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:310-369) -> matchport::distinctive_descriptor
+//   Frame::UndistortKeyPoints / ComputeImageBounds / ComputeStereoFromRGBD / AssignFeaturesToGrid
+//   (:419-485, :703-727, :245-260; tests/test_frame_finish_cpu.py)     -> matchport::frame_finish
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
@@ -107,6 +109,51 @@ int frameref_features_in_area(const float* kx, const float* ky, const int* koct,
   }
   out_off[nq] = total;
   return total <= cap ? total : -total;
+}
+
+// The rest of the Frame constructors after extraction (Frame.cc:85-120): ComputeImageBounds on a
+// w x h image, the grid-element inverses exactly as :106-107 spell them, UndistortKeyPoints,
+// ComputeStereoFromRGBD (when depth != NULL) and AssignFeaturesToGrid -- all the reference's own code.
+// cam = fx fy cx cy, dist = k1 k2 p1 p2 [k3] (n_dist 4 or 5, as Tracking.cc:66-77 builds mDistCoef).
+// bounds_out = mnMinX mnMaxX mnMinY mnMaxY mfGridElementWidthInv mfGridElementHeightInv.
+// cell_off has FRAME_GRID_COLS*FRAME_GRID_ROWS + 1 entries in (ix, iy) -> ix*ROWS+iy order.
+int frameref_finish(const float* kx, const float* ky, int n, const float* cam, const float* dist, int n_dist, float bf, int w, int h,
+                    const float* depth, float* bounds_out, float* xy_un, float* u_right, float* depth_out, int* cell_off,
+                    int* cell_idx) {
+  cv::Mat K = cv::Mat::zeros(3, 3, CV_32F);
+  K.at<float>(0, 0) = cam[0]; K.at<float>(1, 1) = cam[1]; K.at<float>(0, 2) = cam[2]; K.at<float>(1, 2) = cam[3];
+  K.at<float>(2, 2) = 1.f;
+  cv::Mat D(n_dist, 1, CV_32F);
+  for (int i = 0; i < n_dist; ++i) D.at<float>(i) = dist[i];
+  Frame F;
+  F.mK = K.clone();
+  F.mDistCoef = D.clone();
+  F.mbf = bf;
+  F.N = n;
+  F.mvKeys.resize((size_t)n);
+  for (int i = 0; i < n; ++i) F.mvKeys[i] = cv::KeyPoint(kx[i], ky[i], 31.f, -1.f, 0.f, 0);
+  cv::Mat im(h, w, CV_8U);
+  F.UndistortKeyPoints();
+  F.ComputeImageBounds(im);
+  Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / (Frame::mnMaxX - Frame::mnMinX);    // Frame.cc:106-107
+  Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / (Frame::mnMaxY - Frame::mnMinY);
+  bounds_out[0] = Frame::mnMinX; bounds_out[1] = Frame::mnMaxX; bounds_out[2] = Frame::mnMinY; bounds_out[3] = Frame::mnMaxY;
+  bounds_out[4] = Frame::mfGridElementWidthInv; bounds_out[5] = Frame::mfGridElementHeightInv;
+  if (depth) {
+    cv::Mat imDepth(h, w, CV_32F, (void*)depth, (size_t)w * 4);
+    F.ComputeStereoFromRGBD(imDepth);
+    for (int i = 0; i < n; ++i) { u_right[i] = F.mvuRight[i]; depth_out[i] = F.mvDepth[i]; }
+  }
+  F.AssignFeaturesToGrid();
+  for (int i = 0; i < n; ++i) { xy_un[2 * i] = F.mvKeysUn[i].pt.x; xy_un[2 * i + 1] = F.mvKeysUn[i].pt.y; }
+  int total = 0;
+  for (int ix = 0; ix < FRAME_GRID_COLS; ++ix)
+    for (int iy = 0; iy < FRAME_GRID_ROWS; ++iy) {
+      cell_off[ix * FRAME_GRID_ROWS + iy] = total;
+      for (size_t j = 0; j < F.mGrid[ix][iy].size(); ++j) cell_idx[total++] = (int)F.mGrid[ix][iy][j];
+    }
+  cell_off[FRAME_GRID_COLS * FRAME_GRID_ROWS] = total;
+  return total;
 }
 
 // MapPoint::ComputeDistinctiveDescriptors for n_points map points; point p is observed by

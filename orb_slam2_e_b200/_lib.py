@@ -58,6 +58,15 @@ _lib = None
 _vp, _i, _f, _sz, _i64 = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int64
 _ip = C.POINTER(C.c_int)
 
+class Camera(C.Structure):
+    _fields_ = [("fx", _f), ("fy", _f), ("cx", _f), ("cy", _f), ("k1", _f), ("k2", _f), ("p1", _f), ("p2", _f), ("k3", _f),
+                ("bf", _f)]
+
+
+class FrameBounds(C.Structure):
+    _fields_ = [("min_x", _f), ("min_y", _f), ("width_inv", _f), ("height_inv", _f), ("cols", C.c_int32), ("rows", C.c_int32)]
+
+
 # name -> (restype, argtypes); every symbol include/orbfront.h declares
 SIGNATURES = {
     "orb_last_error": (C.c_char_p, []),
@@ -100,6 +109,9 @@ SIGNATURES = {
     "orbm_window_candidates": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _ip]),
     "orbm_search_triangulation": (_i, [_i, C.POINTER(TriKeyFrame), C.POINTER(TriKeyFrame), _vp, _f, _f, _vp, _vp, _i, _i, _vp, _ip]),
     "orbx_stereo_matches": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
+    "orbx_undistort_points": (_i, [_i, _vp, _i, C.POINTER(Camera), _vp]),
+    "orbx_frame_finish": (_i, [_i, _vp, _i, C.POINTER(Camera), C.POINTER(FrameBounds), _vp, _i, _i, _sz, _i, _vp, _vp, _vp,
+                               _vp, _vp, _ip]),
     "orbm_vocab_create": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, C.POINTER(C.c_void_p)]),
     "orbm_vocab_load_text": (_i, [_i, C.c_char_p, C.POINTER(C.c_void_p)]),
     "orbm_vocab_info": (_i, [_vp, _ip, _ip, _ip, _ip]),

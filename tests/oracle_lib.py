@@ -74,6 +74,10 @@ def oracle(fast=False):
     L.orc_compute_stereo_matches.argtypes = [f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, i32p, u8p, C.c_int, f32p, f32p, C.c_int,
                                              C.c_void_p, C.c_void_p, i32p, i32p, i32p, C.c_float, C.c_float, f32p, f32p]
     L.orc_distinctive_descriptors.argtypes = [u8p, i32p, C.c_int, i32p]
+    L.orc_undistort_points.argtypes = [f32p, C.c_int, f32p, f32p, C.c_int, f32p]
+    L.orc_image_bounds.argtypes = [C.c_int, C.c_int, f32p, f32p, C.c_int, f32p]
+    L.orc_frame_finish.argtypes = [f32p, C.c_int, f32p, f32p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
+                                   C.c_int, C.c_int, C.c_void_p, C.c_int, f32p, f32p, f32p, i32p, i32p]
     L.orc_features_in_area.argtypes = [f32p, f32p, i32p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
                                        i32p, u32p, f32p, f32p, f32p, i32p, i32p, C.c_int, i32p, i32p, C.c_int]
     _cache[key] = L
@@ -130,8 +134,54 @@ def frame_ref_lib():
     L.frameref_features_in_area.argtypes = [f32p, f32p, i32p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, f32p, f32p,
                                             f32p, i32p, i32p, C.c_int, i32p, i32p, C.c_int]
     L.frameref_distinctive.argtypes = [u8p, i32p, C.c_void_p, C.c_int, u8p]
+    L.frameref_finish.argtypes = [f32p, f32p, C.c_int, f32p, f32p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, f32p, f32p,
+                                  f32p, f32p, i32p, i32p]
     _cache[key] = L
     return L
+
+
+def ref_frame_finish(L, x, y, camera, depth=None):
+    """The reference's own Frame code (libframeref.so) after extraction: camera = (w, h, (fx, fy, cx, cy), dist, bf)."""
+    w, h, cam, dist, bf = camera
+    n = len(x)
+    cam = np.array(cam, np.float32)
+    dist = np.array(dist, np.float32)
+    bounds = np.zeros(6, np.float32)
+    xy = np.zeros((n, 2), np.float32)
+    ur, dz = np.full(n, -2, np.float32), np.full(n, -2, np.float32)
+    off = np.zeros(64 * 48 + 1, np.int32)
+    idx = np.zeros(max(n, 1), np.int32)
+    if depth is not None:
+        assert depth.shape == (h, w) and depth.dtype == np.float32 and depth.flags.c_contiguous
+    total = L.frameref_finish(np.ascontiguousarray(x, np.float32), np.ascontiguousarray(y, np.float32), n, cam, dist, len(dist), bf, w,
+                              h, None if depth is None else depth.ctypes.data, bounds, xy, ur, dz, off, idx)
+    out = dict(bounds=bounds, xy_un=xy, cell_off=off, cell_idx=idx[:total].copy())
+    if depth is not None:
+        out.update(u_right=ur, depth=dz)
+    return out
+
+
+def port_frame_finish(L, x, y, camera, depth=None):
+    """The restatement (oracle/match_port.hpp) of the same: bounds, undistortion, RGB-D stereo, grid."""
+    w, h, cam, dist, bf = camera
+    n = len(x)
+    cam = np.array(cam, np.float32)
+    dist = np.array(dist, np.float32)
+    b = np.zeros(4, np.float32)
+    L.orc_image_bounds(w, h, cam, dist, len(dist), b)
+    f32 = np.float32
+    winv, hinv = f32(64) / (b[1] - b[0]), f32(48) / (b[3] - b[2])
+    xy_in = np.ascontiguousarray(np.stack([x, y], 1), np.float32)
+    xy = np.zeros((n, 2), np.float32)
+    ur, dz = np.full(n, -2, np.float32), np.full(n, -2, np.float32)
+    off = np.zeros(64 * 48 + 1, np.int32)
+    idx = np.zeros(max(n, 1), np.int32)
+    total = L.orc_frame_finish(xy_in, n, cam, dist, len(dist), bf, b[0], b[2], winv, hinv, 64, 48,
+                               None if depth is None else depth.ctypes.data, w, xy, ur, dz, off, idx)
+    out = dict(bounds=np.array([b[0], b[1], b[2], b[3], winv, hinv], np.float32), xy_un=xy, cell_off=off, cell_idx=idx[:total].copy())
+    if depth is not None:
+        out.update(u_right=ur, depth=dz)
+    return out
 
 
 def ref_stereo_matches(L, cfg, kl, dl, kr, dr, levels_left, levels_right, mb, mbf):
