@@ -76,7 +76,65 @@ class ORBextractor {
           "ORBextractor::ComputeStereoMatches");
   }
 
+  /* Extension: the rest of the Frame constructors after extraction in one device call --
+   * Frame::UndistortKeyPoints (src/Frame.cc:419-449), ComputeStereoFromRGBD (:703-727, when imDepth is
+   * not empty; CV_32F as Tracking::GrabImageRGBD leaves it) and AssignFeaturesToGrid (:245-260).  K and
+   * distCoef are Frame::mK / mDistCoef (CV_32F), the four grid numbers Frame's statics.  mvuRight /
+   * mvDepth are only written with a depth image.  Grid is Frame::mGrid (any [cols][rows] array of
+   * index vectors). */
+  template <class Grid>
+  static void FinishFrame(const std::vector<cv::KeyPoint>& mvKeys, const cv::Mat& K, const cv::Mat& distCoef, float mbf,
+                          float mnMinX, float mnMinY, float gridElementWidthInv, float gridElementHeightInv,
+                          const cv::Mat& imDepth, std::vector<cv::KeyPoint>& mvKeysUn, std::vector<float>& mvuRight,
+                          std::vector<float>& mvDepth, Grid& mGrid, int gridCols = 64, int gridRows = 48, int device = 0) {
+    const orbx_camera cam = Camera(K, distCoef, mbf);
+    const orbx_frame_bounds fb = {mnMinX, mnMinY, gridElementWidthInv, gridElementHeightInv, gridCols, gridRows};
+    const int n = (int)mvKeys.size();
+    std::vector<float> xy(2 * (size_t)n);
+    std::vector<int32_t> off((size_t)gridCols * gridRows + 1);
+    std::vector<uint32_t> idx((size_t)n);
+    const bool rgbd = !imDepth.empty();
+    if (rgbd) { mvuRight.assign((size_t)n, -1.0f); mvDepth.assign((size_t)n, -1.0f); }
+    Check(orbx_frame_finish(device, reinterpret_cast<const orbx_keypoint*>(mvKeys.data()), n, &cam, &fb,
+                            rgbd ? reinterpret_cast<const float*>(imDepth.data) : nullptr, imDepth.cols, imDepth.rows,
+                            (size_t)imDepth.step, 0, xy.data(), rgbd ? mvuRight.data() : nullptr, rgbd ? mvDepth.data() : nullptr,
+                            off.data(), idx.data(), nullptr),
+          "ORBextractor::FinishFrame");
+    mvKeysUn = mvKeys;
+    for (int i = 0; i < n; ++i) { mvKeysUn[i].pt.x = xy[2 * (size_t)i]; mvKeysUn[i].pt.y = xy[2 * (size_t)i + 1]; }
+    for (int ix = 0; ix < gridCols; ++ix)
+      for (int iy = 0; iy < gridRows; ++iy) {
+        const int c = ix * gridRows + iy;
+        mGrid[ix][iy].assign(idx.begin() + off[c], idx.begin() + off[c + 1]);
+      }
+  }
+  /* Extension: Frame::ComputeImageBounds (src/Frame.cc:451-485) for a cols x rows image. */
+  static void ComputeImageBounds(const cv::Mat& K, const cv::Mat& distCoef, int cols, int rows, float& mnMinX, float& mnMaxX,
+                                 float& mnMinY, float& mnMaxY, int device = 0) {
+    const orbx_camera cam = Camera(K, distCoef, 0.f);
+    if (cam.k1 != 0.0f) {
+      float m[8] = {0.f, 0.f, (float)cols, 0.f, 0.f, (float)rows, (float)cols, (float)rows};
+      Check(orbx_undistort_points(device, m, 4, &cam, m), "ORBextractor::ComputeImageBounds");
+      mnMinX = std::min(m[0], m[4]);
+      mnMaxX = std::max(m[2], m[6]);
+      mnMinY = std::min(m[1], m[3]);
+      mnMaxY = std::max(m[5], m[7]);
+    } else {
+      mnMinX = 0.0f; mnMaxX = (float)cols; mnMinY = 0.0f; mnMaxY = (float)rows;
+    }
+  }
+
  protected:
+  static orbx_camera Camera(const cv::Mat& K, const cv::Mat& distCoef, float bf) {
+    orbx_camera c;
+    c.fx = K.at<float>(0, 0); c.fy = K.at<float>(1, 1); c.cx = K.at<float>(0, 2); c.cy = K.at<float>(1, 2);
+    const int nd = distCoef.rows * distCoef.cols;  // 4 x 1 or 5 x 1 (src/Tracking.cc:66-77)
+    const float* d = reinterpret_cast<const float*>(distCoef.data);
+    c.k1 = nd > 0 ? d[0] : 0.f; c.k2 = nd > 1 ? d[1] : 0.f; c.p1 = nd > 2 ? d[2] : 0.f; c.p2 = nd > 3 ? d[3] : 0.f;
+    c.k3 = nd > 4 ? d[4] : 0.f;
+    c.bf = bf;
+    return c;
+  }
   std::vector<cv::Point> pattern;  // kept for layout; the pattern lives in the library
 
   int nfeatures;

@@ -111,6 +111,41 @@ int dropin_stereo(const DropKp* kl, const uint8_t* dl, int nl, const DropKp* kr,
   } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
 }
 
+// the rest of a Frame constructor (Frame.cc:85-120) the drop-in way: bounds once, then one device call
+int dropin_finish_frame(const DropKp* keys, int n, const float* cam, const float* dist, int n_dist, float bf, int w, int h_,
+                        const float* depth, float* bounds, float* xy_un, float* u_right, float* depth_out, int* cell_off, int* cell_idx) {
+  try {
+    cv::Mat K = cv::Mat::zeros(3, 3, CV_32F);
+    K.at<float>(0, 0) = cam[0]; K.at<float>(1, 1) = cam[1]; K.at<float>(0, 2) = cam[2]; K.at<float>(1, 2) = cam[3]; K.at<float>(2, 2) = 1.f;
+    cv::Mat D(n_dist, 1, CV_32F);
+    for (int i = 0; i < n_dist; ++i) D.at<float>(i) = dist[i];
+    float minX, maxX, minY, maxY;
+    ORBextractor::ComputeImageBounds(K, D, w, h_, minX, maxX, minY, maxY);
+    const float wInv = static_cast<float>(64) / (maxX - minX), hInv = static_cast<float>(48) / (maxY - minY);
+    bounds[0] = minX; bounds[1] = maxX; bounds[2] = minY; bounds[3] = maxY; bounds[4] = wInv; bounds[5] = hInv;
+    std::vector<cv::KeyPoint> keysv((size_t)n), un;
+    memcpy((void*)keysv.data(), keys, sizeof(DropKp) * (size_t)n);
+    std::vector<float> ur, dz;
+    std::vector<std::size_t> grid[64][48];
+    cv::Mat imDepth;
+    if (depth) imDepth = cv::Mat(h_, w, CV_32F, (void*)depth, (size_t)w * 4);
+    ORBextractor::FinishFrame(keysv, K, D, bf, minX, minY, wInv, hInv, imDepth, un, ur, dz, grid);
+    int total = 0;
+    for (int ix = 0; ix < 64; ++ix)
+      for (int iy = 0; iy < 48; ++iy) {
+        cell_off[ix * 48 + iy] = total;
+        for (std::size_t v : grid[ix][iy]) cell_idx[total++] = (int)v;
+      }
+    cell_off[64 * 48] = total;
+    for (int i = 0; i < n; ++i) {
+      xy_un[2 * i] = un[i].pt.x; xy_un[2 * i + 1] = un[i].pt.y;
+      if (un[i].octave != keysv[i].octave || un[i].angle != keysv[i].angle) { g_err = "mvKeysUn lost keypoint fields"; return -1000000; }
+      if (depth) { u_right[i] = ur[i]; depth_out[i] = dz[i]; }
+    }
+    return total;
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
 }  // extern "C"
 
 // ---- matcher scenes shared with the reference build (oracle/ref_match_harness.cc)

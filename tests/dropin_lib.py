@@ -52,10 +52,12 @@ def load():
                                 C.c_float, i32p, i32p]
     L.dropin_stereo_frame.argtypes = [C.c_void_p, C.c_void_p, u8p, u8p, C.c_int, C.c_int, C.c_size_t, C.c_float, C.c_float,
                                       C.c_void_p, u8p, f32p, f32p, C.c_int]
+    L.dropin_finish_frame.argtypes = [C.c_void_p, C.c_int, f32p, f32p, C.c_int, C.c_float, C.c_int, C.c_int, C.c_void_p, f32p, f32p,
+                                      f32p, f32p, i32p, i32p]
     _lib = L
     return L
 
 
 SYMBOLS = ["dropin_error", "dropin_create", "dropin_destroy", "dropin_extract", "dropin_level_size", "dropin_get_level",
            "dropin_scale", "dropin_table", "dropin_levels", "dropin_scale_factor", "dropin_distance", "dropin_search_bow",
-           "dropin_stereo", "dropin_stereo_frame"]
+           "dropin_stereo", "dropin_stereo_frame", "dropin_finish_frame"]

@@ -118,3 +118,28 @@ def test_empty_and_bad_arguments():
                                     np.zeros(4, np.float32), 4, 0.0, fb.min_x, fb.min_y, fb.width_inv, fb.height_inv, 10, 7, None, 640,
                                     xy, np.zeros(500, np.float32), np.zeros(500, np.float32), off, idx)
     assert np.array_equal(got["cell_off"], off) and np.array_equal(got["cell_idx"].astype(np.int32), idx[:tot])
+
+
+@pytest.mark.parametrize("case", ["tum1_rgbd", "euroc_mono", "tum3_rgbd_nodist"])
+def test_cpp_finish_frame_reproduces_reference_fixture(case):
+    """include/ORBextractor.h FinishFrame / ComputeImageBounds (the calls a patched Frame.cc makes) over cv:: types."""
+    import dropin_lib
+    L = dropin_lib.load()
+    camname, n, seed, with_depth = FINISH_CASES[case]
+    w, h, cam, dist, bf = CAMERAS[camname]
+    x, y = keypoints(camname, n, seed)
+    k = _keys(x, y)
+    k["octave"] = np.arange(n) % 8
+    k["angle"] = np.linspace(0, 359, n, dtype=np.float32)
+    depth = depth_image(camname, seed) if with_depth else None
+    bounds = np.zeros(6, np.float32); xy = np.zeros((n, 2), np.float32)
+    ur, dz = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    off = np.zeros(64 * 48 + 1, np.int32); idx = np.zeros(n, np.int32)
+    tot = L.dropin_finish_frame(k.ctypes.data, n, np.array(cam, np.float32), np.array(dist, np.float32), len(dist), bf, w, h,
+                                None if depth is None else depth.ctypes.data, bounds, xy, ur, dz, off, idx)
+    assert tot >= 0, L.dropin_error()
+    got = dict(bounds=bounds, xy_un=xy, cell_off=off, cell_idx=idx[:tot], u_right=ur, depth=dz)
+    for name in ("bounds", "xy_un", "cell_off", "cell_idx", "u_right", "depth"):
+        key = "ref/%s/%s" % (case, name)
+        if key in REF.files:
+            assert got[name].tobytes() == REF[key].tobytes(), (case, name)
