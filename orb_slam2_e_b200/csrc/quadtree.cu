@@ -21,7 +21,8 @@
 
 namespace orbfront {
 
-constexpr int kQtThreads = 256;
+constexpr int kQtThreads = 256;       // batches: many small CTAs per SM hide each other's latency
+constexpr int kQtThreadsWide = 1024;  // one or a few frames: a level's CTA is the critical path, so it gets 4x the lanes
 
 #ifdef ORBX_QT_PROFILE  // developer build: cycle stamps of the level-0 CTA of frame 0 (tools/exp_qt_profile.py)
 __device__ long long g_qt_prof[32];
@@ -33,16 +34,17 @@ constexpr uint32_t kSeqMark = 0x8000u;  // "head of a child created by the final
 
 struct QtCtl {  // control block in shared memory
   int hist[kMaxDepth + 3], dlt[kMaxDepth + 3], cnt[kMaxDepth + 3], nexp[kMaxDepth + 3];
-  int d, size, mode, d_bfs, partial, counter, mstar, scan_tmp[kQtThreads / 32], scan_total, run_base;
+  int d, size, mode, d_bfs, partial, counter, mstar, scan_tmp[kQtThreadsWide / 32], scan_total, run_base;
 };
 enum { kModeFull = 0, kModeOrdered = 1 };
 
 // In-place ascending bitonic sort of np (power of two) 64-bit keys with optional 32-bit values
 // (node tables: at most a few hundred entries).  One compare-exchange per thread and step.
+template <int T>
 __device__ void bitonic_sort(unsigned long long* a, uint32_t* v, int np) {
   for (int k = 2; k <= np; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int t = threadIdx.x; t < (np >> 1); t += kQtThreads) {
+      for (int t = threadIdx.x; t < (np >> 1); t += T) {
         const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), x = i | j;
         const unsigned long long ai = a[i], ax = a[x];
         if ((ai > ax) == ((i & k) == 0)) {
@@ -56,6 +58,7 @@ __device__ void bitonic_sort(unsigned long long* a, uint32_t* v, int np) {
 }
 
 // Inclusive scan of one int per thread across the CTA; returns the thread's inclusive prefix.
+template <int T>
 __device__ int block_inclusive_scan(int v, QtCtl& C) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -67,7 +70,7 @@ __device__ int block_inclusive_scan(int v, QtCtl& C) {
   __syncthreads();
   int base = 0;
   for (int w = 0; w < warp; ++w) base += C.scan_tmp[w];
-  if (threadIdx.x == kQtThreads - 1) C.scan_total = base + v;
+  if (threadIdx.x == T - 1) C.scan_total = base + v;
   __syncthreads();
   return base + v;
 }
@@ -77,25 +80,37 @@ __device__ int block_inclusive_scan(int v, QtCtl& C) {
 // contiguous chunk; per-(warp, digit) counters scanned in (digit, warp) order give every key its
 // stable destination: base + rank among the warp's equal digits (__match_any_sync).  O(n) per pass
 // instead of the O(n log^2 n) compare-exchanges of a sorting network.  Returns the sorted buffer.
+template <int T>
 __device__ unsigned long long* radix_sort_codes(unsigned long long* a, unsigned long long* b, int n, int nbits,
-                                                uint32_t* whist /* [8][256] */, QtCtl& C) {
-  constexpr int kWarps = kQtThreads / 32;
+                                                uint32_t* whist /* [T / 32][256] */, QtCtl& C) {
+  constexpr int kWarps = T / 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  const int per_warp = ((n + kQtThreads - 1) / kQtThreads) * 32;
+  const int per_warp = ((n + T - 1) / T) * 32;
   const int lo = min(n, warp * per_warp), hi = min(n, lo + per_warp);
   for (int shift = 32; shift < 32 + nbits; shift += 8) {
-    for (int i = tid; i < kWarps * 256; i += kQtThreads) whist[i] = 0;
+    for (int i = tid; i < kWarps * 256; i += T) whist[i] = 0;
     __syncthreads();
     for (int i = lo + lane; i < hi; i += 32) atomicAdd(&whist[warp * 256 + (int)((a[i] >> shift) & 255u)], 1u);
     __syncthreads();
-    {
+    if constexpr (kWarps <= 8) {  // T == 256: one thread per digit value, the warps' counts stay in registers
       uint32_t c[kWarps], tot = 0;
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) { c[w] = whist[w * 256 + tid]; tot += c[w]; }
-      uint32_t base = (uint32_t)block_inclusive_scan((int)tot, C) - tot;
+      uint32_t base = (uint32_t)block_inclusive_scan<T>((int)tot, C) - tot;
 #pragma unroll
       for (int w = 0; w < kWarps; ++w) { whist[w * 256 + tid] = base; base += c[w]; }
+    } else {  // wider CTAs: threads beyond 255 only take part in the scan's barriers
+      uint32_t tot = 0;
+      if (tid < 256) {
+#pragma unroll 8
+        for (int w = 0; w < kWarps; ++w) tot += whist[w * 256 + tid];
+      }
+      uint32_t base = (uint32_t)block_inclusive_scan<T>((int)tot, C) - tot;
+      if (tid < 256) {
+#pragma unroll 8
+        for (int w = 0; w < kWarps; ++w) { const uint32_t c = whist[w * 256 + tid]; whist[w * 256 + tid] = base; base += c; }
+      }
     }
     __syncthreads();
     for (int i0 = lo; i0 < hi; i0 += 32) {
@@ -131,7 +146,8 @@ __device__ __forceinline__ uint32_t bfs_creation_key(uint32_t code, int k, int d
   return prefix ^ mask;
 }
 
-__global__ void __launch_bounds__(kQtThreads)
+template <int T>
+__global__ void __launch_bounds__(T)
 quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
@@ -163,7 +179,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   uint16_t* seq = in_smem ? s_seq : reinterpret_cast<uint16_t*>(P.qt_seq + (size_t)f * P.cand_frame + G.cand_off);
 
   // FAST stores the payload only; attach the path code (all lanes busy), in place
-  for (int i = tid; i < n; i += kQtThreads) {
+  for (int i = tid; i < n; i += T) {
     const uint32_t pay = (uint32_t)gkeys[i];
     const uint32_t code = __ldg(&P.qcode[G.qx + (int)(pay & 0xfff)]) | __ldg(&P.qcode[G.qy + (int)((pay >> 12) & 0xfff)]);
     gkeys[i] = ((unsigned long long)code << 32) | pay;
@@ -175,17 +191,17 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   while ((1 << root_bits) < G.nIni) ++root_bits;
   const int nbits = 2 * dmax + root_bits;
   unsigned long long* other = in_smem ? s_keys : P.qt_tmp + (size_t)f * P.cand_frame + G.cand_off;
-  unsigned long long* keys = radix_sort_codes(gkeys, other, n, nbits, reinterpret_cast<uint32_t*>(nkey), C);
+  unsigned long long* keys = radix_sort_codes<T>(gkeys, other, n, nbits, reinterpret_cast<uint32_t*>(nkey), C);
   if (in_smem && keys != s_keys) {  // even number of passes: bring the result into shared memory
-    for (int i = tid; i < n; i += kQtThreads) s_keys[i] = keys[i];
+    for (int i = tid; i < n; i += T) s_keys[i] = keys[i];
     keys = s_keys;
     __syncthreads();
   }
 
   QT_STAMP(2);
   // boundary depths b[0..n], tables cnt[] / nexp[]
-  for (int i = tid; i < kMaxDepth + 3; i += kQtThreads) { C.hist[i] = 0; C.dlt[i] = 0; }
-  for (int i = tid; i <= n; i += kQtThreads) {
+  for (int i = tid; i < kMaxDepth + 3; i += T) { C.hist[i] = 0; C.dlt[i] = 0; }
+  for (int i = tid; i <= n; i += T) {
     int v = 0;
     if (i > 0 && i < n) {
       const uint32_t x = (uint32_t)(keys[i - 1] >> 32) ^ (uint32_t)(keys[i] >> 32);
@@ -196,7 +212,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     if (i < n) seq[i] = 0;
   }
   __syncthreads();
-  for (int i = tid; i < n; i += kQtThreads) {
+  for (int i = tid; i < n; i += T) {
     const int a = b[i], e = b[i + 1];
     atomicAdd(&C.hist[a], 1);
     if (a < e) { atomicAdd(&C.dlt[a], 1); atomicAdd(&C.dlt[e], -1); }
@@ -230,13 +246,13 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     const int d = C.d, size = C.size;
     if (tid == 0) { C.counter = 0; C.mstar = 0x7fffffff; }
     __syncthreads();
-    for (int i = tid; i < n; i += kQtThreads)
+    for (int i = tid; i < n; i += T)
       if (b[i] <= d && b[i + 1] > d) nhead[atomicAdd(&C.counter, 1)] = (uint32_t)i;
     __syncthreads();
     const int M = C.counter;
     int mp = 1;
     while (mp < M) mp <<= 1;
-    for (int m = tid; m < mp; m += kQtThreads) {
+    for (int m = tid; m < mp; m += T) {
       if (m >= M) { nkey[m] = ~0ull; nval[m] = 0; continue; }
       const int h = (int)nhead[m];
       int e = h + 1, children = 1;
@@ -249,14 +265,14 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     }
     __syncthreads();
     if (first_ordered) QT_STAMP(16);
-    bitonic_sort(nkey, nval, mp);
+    bitonic_sort<T>(nkey, nval, mp);
     if (first_ordered) QT_STAMP(17);
     // where does the running node count reach N?
     int carried = 0;
-    for (int base = 0; base < M; base += kQtThreads) {
+    for (int base = 0; base < M; base += T) {
       const int j = base + tid;
       const int g = j < M ? ngain[nval[j]] : 0;
-      const int incl = block_inclusive_scan(g, C) + carried;
+      const int incl = block_inclusive_scan<T>(g, C) + carried;
       if (j < M && size + incl >= N) atomicMin(&C.mstar, j);
       carried += C.scan_total;
       __syncthreads();
@@ -264,7 +280,7 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
     const bool stops = C.mstar != 0x7fffffff;
     const int n_split = stops ? C.mstar + 1 : M;
     // the split nodes' children get their creation sequence (parent's place in the order, quadrant)
-    for (int j = tid; j < n_split; j += kQtThreads) {
+    for (int j = tid; j < n_split; j += T) {
       const int h = (int)nhead[nval[j]];
       int p = h;
       do {
@@ -298,14 +314,14 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   const uint32_t mag_h = (1u << 20) / (uint32_t)G.hCell + 1u, mag_w = (1u << 20) / (uint32_t)G.wCell + 1u;
   if (tid == 0) C.counter = 0;
   __syncthreads();
-  for (int i = tid; i < n; i += kQtThreads)
+  for (int i = tid; i < n; i += T)
     if (b[i] <= dfin || (partial && (seq[i] & kSeqMark))) nhead[atomicAdd(&C.counter, 1)] = (uint32_t)i;
   __syncthreads();
   QT_STAMP(6);
   const int L = min(C.counter, G.kept_cap);
   int lp = 1;
   while (lp < L) lp <<= 1;
-  for (int m = tid; m < lp; m += kQtThreads) {
+  for (int m = tid; m < lp; m += T) {
     if (m >= L) { nkey[m] = ~0ull; nval[m] = 0; continue; }
     const int p = (int)nhead[m];
     const bool child = partial && (seq[p] & kSeqMark);
@@ -336,9 +352,9 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   }
   __syncthreads();
   QT_STAMP(7);
-  bitonic_sort(nkey, nval, lp);
+  bitonic_sort<T>(nkey, nval, lp);
   QT_STAMP(8);
-  for (int m = tid; m < L; m += kQtThreads) kept[m] = nval[m];
+  for (int m = tid; m < L; m += T) kept[m] = nval[m];
   if (tid == 0) P.kept_count[f * P.nlevels + l] = L;
   QT_STAMP(9);
 #ifdef ORBX_QT_PROFILE
@@ -353,16 +369,27 @@ int quadtree_smem_bytes(int S, int NP) {
 int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
   int nmax = 1;
   for (int l = 0; l < P.nlevels; ++l) nmax = std::max(nmax, P.lv[l].kept_cap);
-  int NP = 512;  // >= 8 KB for the radix counters that alias the node tables (8 warps x 256 x 4 B <= NP x 16)
+  // One or a few frames (at most two CTAs per SM in all): every (frame, level) CTA runs at once and the
+  // level-0 CTA is the critical path, so CTAs are 1024 wide and keep up to 8192 keys in shared memory.
+  // Batches: 256-thread CTAs with 2048 keys, many per SM (occupancy beats residency there).
+  static const int wide_env = getenv("ORBX_QT_WIDE") ? atoi(getenv("ORBX_QT_WIDE")) : -1;
+  const bool wide = wide_env >= 0 ? wide_env != 0 : (long long)P.n_frames * P.nlevels <= 2 * 148;
+  const int threads = wide ? kQtThreadsWide : kQtThreads;
+  int NP = threads * 2;  // the radix counters ((threads / 32) x 256 x 4 B) alias the node tables (NP x 16 B)
   while (NP < nmax) NP <<= 1;
-  int S = 2048;  // levels with more candidates sort through global scratch (L2); occupancy beats residency here
+  int S = wide ? 8192 : 2048;  // levels with more candidates sort through global scratch (L2)
   if (const char* e = getenv("ORBX_QT_SMEM_KEYS")) S = std::max(256, atoi(e));
   while (S & (S - 1)) S &= S - 1;  // power of two
   S = std::max(S, NP);             // node arrays alias nothing, but n_nodes <= n keys
   const int smem = quadtree_smem_bytes(S, NP);
   if (smem > 227 * 1024) return set_error(ORB_E_INVALID, "quadtree: %d bytes of shared memory needed (nfeatures too large)", smem);
-  ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  quadtree_select_kernel<<<dim3(P.nlevels, P.n_frames), kQtThreads, smem, s>>>(P, S, NP);
+  if (wide) {
+    ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel<kQtThreadsWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    quadtree_select_kernel<kQtThreadsWide><<<dim3(P.nlevels, P.n_frames), kQtThreadsWide, smem, s>>>(P, S, NP);
+  } else {
+    ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel<kQtThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    quadtree_select_kernel<kQtThreads><<<dim3(P.nlevels, P.n_frames), kQtThreads, smem, s>>>(P, S, NP);
+  }
   ORB_LAUNCH_CHECK();
   ++*launches;
   return ORB_OK;
