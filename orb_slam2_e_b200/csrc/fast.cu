@@ -136,6 +136,26 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
       }
       head += count_;
     };
+    int whead = 0;  // listed words already unpacked into the pixel queue
+    auto expand = [&](int count_) {
+      int e = 0, n = 0;
+      if (lane < count_) { e = wlist[whead + lane]; n = __popc(e & 15); }
+      int incl = n;
+#pragma unroll
+      for (int s = 1; s < 32; s <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, s);
+        if (lane >= s) incl += o;
+      }
+      int pos = tail + incl - n;
+      const int pix = (e >> 8) << 6 | ((e >> 4) & 15) << 2;
+#pragma unroll
+      for (int b = 0; b < 4; ++b)
+        if (e >> b & 1) S.queue[(pos++) & (kQueue - 1)] = (uint16_t)(pix + b);
+      tail += __shfl_sync(0xffffffffu, incl, 31);
+      whead += count_;
+      __syncwarp();
+      while (tail - head >= 32) drain(32);
+    };
     __syncwarp();
     for (int base = 0; base < ngroups; base += 32) {
       const int gid = base + lane;
@@ -156,26 +176,20 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
         flags = fl & (0x80808080u >> (32 - 8 * nvalid));
         S.score[(py + 1) * (kScorePitch / 4) + g + 1] = 0;  // cleared before any of its pixels is scored
       }
-      {  // groups with a prefilter survivor are the only score words that can hold a corner
+      {  // groups with a prefilter survivor are the only score words that can hold a corner; their
+         // entry keeps the four survivor bits, so pixels are unpacked once per 32 listed words
+         // instead of once per 32 visited words
         const uint32_t m = __ballot_sync(0xffffffffu, flags != 0);
-        if (flags != 0) wlist[nw + __popc(m & lt_mask)] = (uint16_t)(py << 4 | g);
+        if (flags != 0) {
+          const uint32_t nib = (((flags >> 7) & 0x01010101u) * 0x01020408u) >> 24;  // bit b = pixel b survives
+          wlist[nw + __popc(m & lt_mask)] = (uint16_t)(py << 8 | g << 4 | nib);
+        }
         nw += __popc(m);
       }
-      const int n = __popc(flags);
-      int incl = n;
-#pragma unroll
-      for (int s = 1; s < 32; s <<= 1) {
-        const int o = __shfl_up_sync(0xffffffffu, incl, s);
-        if (lane >= s) incl += o;
-      }
-      int pos = tail + incl - n;
-#pragma unroll
-      for (int b = 0; b < 4; ++b)
-        if (flags >> (8 * b + 7) & 1u) S.queue[(pos++) & (kQueue - 1)] = (uint16_t)(py << 6 | (4 * g + b));
-      tail += __shfl_sync(0xffffffffu, incl, 31);
       __syncwarp();
-      while (tail - head >= 32) drain(32);
+      if (nw - whead >= 32) expand(32);
     }
+    if (nw > whead) expand(nw - whead);
     drain(tail - head);
     __syncwarp();
 
@@ -187,7 +201,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
         uint32_t e = 0, w = 0;
         if (base + lane < nw) {
           e = wlist[base + lane];
-          w = S.score[((e >> 4) + 1) * (kScorePitch / 4) + (e & 15) + 1];
+          w = S.score[((e >> 8) + 1) * (kScorePitch / 4) + ((e >> 4) & 15) + 1];
         }
         const uint32_t m = __ballot_sync(0xffffffffu, w != 0);
         if (w != 0) wlist[kept_w + __popc(m & lt_mask)] = (uint16_t)e;
@@ -204,7 +218,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
       int py = 0, g = 0;
       if (base + lane < nw) {
         const int e = wlist[base + lane];
-        py = e >> 4; g = e & 15;
+        py = e >> 8; g = (e >> 4) & 15;
         w = S.score[(py + 1) * (kScorePitch / 4) + g + 1];
       }
 #pragma unroll
