@@ -87,7 +87,8 @@ int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches);
 int pyramid_fused_max_grid(int device);
 int launch_fast(const ExtractParams& P, cudaStream_t s, int* launches);
 int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches);
-int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches);
+// after_quadtree: kept_count is valid, levels without keypoints are skipped like the reference does
+int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree = true);
 int launch_describe(const ExtractParams& P, cudaStream_t s, int* launches);
 int launch_border_copy(const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, cudaStream_t s);
 

@@ -262,7 +262,7 @@ constexpr int kBlurRows = kBlurTH + 6, kBlurBody = 21;
 static_assert(kBlurRows % kBlurBody == 0, "row loop must be whole bodies");
 
 __global__ void __launch_bounds__(kBlurWarps * 32, 8)
-blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */) {
+blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */, int skip_empty_levels) {
   const int lane = threadIdx.x & 31;
   const int tile = blockIdx.x * kBlurWarps + (threadIdx.x >> 5);
   if (tile >= tile_base[P.nlevels]) return;
@@ -270,7 +270,8 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   while (l + 1 < P.nlevels && tile >= tile_base[l + 1]) ++l;
   const LevelGeom& G = P.lv[l];
   const int f = blockIdx.z;
-  if (P.kept_count[f * P.nlevels + l] == 0) return;  // reference skips levels without keypoints (:1089)
+  // the reference skips levels without keypoints (:1089); only possible when the quadtree has already run
+  if (skip_empty_levels && P.kept_count[f * P.nlevels + l] == 0) return;
   const int t = tile - tile_base[l];
   const int tiles_x = div_up(G.w, kBlurTW);
   const int tx0 = (t % tiles_x) * kBlurTW;
@@ -358,10 +359,10 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   }
 }
 
-int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches) {
+int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree) {
   int total = 0;
   for (int l = 0; l < P.nlevels; ++l) total += div_up(P.lv[l].w, kBlurTW) * div_up(P.lv[l].h, kBlurTH);
-  blur_kernel<<<dim3(div_up(total, kBlurWarps), 1, P.n_frames), kBlurWarps * 32, 0, s>>>(P, P.blur_tiles);
+  blur_kernel<<<dim3(div_up(total, kBlurWarps), 1, P.n_frames), kBlurWarps * 32, 0, s>>>(P, P.blur_tiles, after_quadtree ? 1 : 0);
   ORB_LAUNCH_CHECK();
   ++*launches;
   return ORB_OK;
