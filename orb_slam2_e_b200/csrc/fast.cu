@@ -29,7 +29,7 @@ constexpr int kCellMax = 60;                 // wCell,hCell <= 59 (ceil(width/fl
 constexpr int kQueue = 256;                  // ring queue entries (py << 6 | px)
 // Per-warp shared memory: tile[(maxH+6) x PITCH] | score[(maxH+2) x PITCH] | queue[kQueue] u16, later reused
 // for the cell's NMS survivors | wlist (score words with a prefilter survivor).
-// PITCH (bytes, multiple of 4, >= widest cell + 8) is a template parameter so the 16 ring offsets
+// PITCH (bytes, multiple of 8, >= widest cell + 8) is a template parameter so the 16 ring offsets
 // stay immediates; tile/score column = px + 4 (word aligned groups of 4 pixels).
 
 // exact strength of the pixel whose centre byte is at p (tile pitch kTilePitch)
@@ -88,22 +88,38 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   const uint8_t* src = level_ptr(P, l, f) + (size_t)(vy0 - 3) * sp + (vx0 - 4);
   const int tw = min(vw + 8, G.w - (vx0 - 4)), th = vh + 6;
   {
-    // word-wise: every pitch is a multiple of 4, so all rows share the byte misalignment `sh`;
-    // a tile word is the funnel shift of two aligned global words (independent loads, unrolled)
-    const int sh = (int)(reinterpret_cast<uintptr_t>(src) & 3);
-    const uint32_t* asrc = reinterpret_cast<const uint32_t*>(src - sh);
-    const int spw = sp >> 2, nwt = (tw + 3) >> 2;
-    // lane <-> (row within a group of rpi rows, word): the addresses then advance by constants
-    const int rpi = 32 / nwt;  // nwt <= 17
-    const int lr = lane / nwt, lc = lane - lr * nwt;
+    // quad-wise: every base and pitch is a multiple of 16, so all rows share the byte shift `sh` and the
+    // word shift `wsh` of the tile origin inside its 16-byte quad.  A lane loads the two aligned quads
+    // around four tile words, funnel-shifts the five words they span (the word shift is uniform per
+    // cell: a four-way switch, static register indices) and stores them as two 8-byte halves.
+    // A quad is loaded only if it starts inside the level row, so no load leaves the row whatever
+    // its pitch; rows per pass = 32 / quads per row.
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(src);
+    const int sh8 = (int)(a0 & 3) * 8, wsh = (int)(a0 >> 2) & 3;
+    const uint4* qsrc = reinterpret_cast<const uint4*>(a0 & ~(uintptr_t)15);
+    const int xq0 = (vx0 - 4) - (int)(a0 & 15);  // level column of the first quad (>= 0: rows start 16-byte aligned)
+    const int spq = sp >> 4, nq = (tw + 15) >> 4;  // nq <= 5
+    const int rpi = 32 / nq;
+    const int lr = lane / nq, lq = lane - lr * nq;
     if (lr < rpi) {
-      const uint32_t* a = asrc + (size_t)lr * spw + lc;
-      uint32_t* d = S.tile + lr * kTileWords + lc;
-      const int astep = rpi * spw, dstep = rpi * kTileWords;
-#pragma unroll 4
+      const bool in0 = xq0 + 16 * lq < G.w, in1 = xq0 + 16 * lq + 16 < G.w && (sh8 | wsh) != 0;
+      const bool st0 = 4 * lq < kTileWords, st1 = 4 * lq + 2 < kTileWords;  // PITCH is a multiple of 8
+      const uint4* a = qsrc + (size_t)lr * spq + lq;
+      uint2* d = reinterpret_cast<uint2*>(S.tile + lr * kTileWords + 4 * lq);
+      const int astep = rpi * spq, dstep = rpi * (kTileWords / 2);
+#pragma unroll 2
       for (int r = lr; r < th; r += rpi) {
-        const uint32_t lo = __ldg(a), hi = sh ? __ldg(a + 1) : 0u;
-        *d = __funnelshift_r(lo, hi, 8 * sh);
+        const uint4 q0 = in0 ? __ldg(a) : make_uint4(0, 0, 0, 0);
+        const uint4 q1 = in1 ? __ldg(a + 1) : make_uint4(0, 0, 0, 0);
+        uint32_t w0, w1, w2, w3, w4;
+        switch (wsh) {
+          case 0: w0 = q0.x; w1 = q0.y; w2 = q0.z; w3 = q0.w; w4 = q1.x; break;
+          case 1: w0 = q0.y; w1 = q0.z; w2 = q0.w; w3 = q1.x; w4 = q1.y; break;
+          case 2: w0 = q0.z; w1 = q0.w; w2 = q1.x; w3 = q1.y; w4 = q1.z; break;
+          default: w0 = q0.w; w1 = q1.x; w2 = q1.y; w3 = q1.z; w4 = q1.w; break;
+        }
+        if (st0) d[0] = make_uint2(__funnelshift_r(w0, w1, sh8), __funnelshift_r(w1, w2, sh8));
+        if (st1) d[1] = make_uint2(__funnelshift_r(w2, w3, sh8), __funnelshift_r(w3, w4, sh8));
         a += astep;
         d += dstep;
       }
@@ -260,8 +276,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
 template <int PITCH>
 static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) {
   const int qk_entries = std::max(kQueue, (((PITCH - 8) / 2 + 1) * (max_h / 2 + 1) + 1) & ~1);  // as in the kernel
-  const int warp_bytes = (max_h + 6) * PITCH + (max_h + 2) * PITCH + 2 * qk_entries + 2 * ((max_h * ((PITCH - 8) / 4) + 1) & ~1);
-  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((66+62)*68 + 1860 + 1770) < 48 KB
+  const int warp_bytes = (int)align_up<size_t>((max_h + 6) * PITCH + (max_h + 2) * PITCH + 2 * qk_entries + 2 * ((max_h * ((PITCH - 8) / 4) + 1) & ~1), 16);  // tiles stay 16-byte aligned
+  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((65+61)*72 + 2 * 1024 + 2 * 944) < 48 KB
   dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
   fast_cells_kernel<PITCH><<<grid, kFastWarps * 32, smem, s>>>(P, max_h, warp_bytes);
   ORB_LAUNCH_CHECK();
@@ -278,7 +294,7 @@ int launch_fast(const ExtractParams& P, cudaStream_t s, int* launches) {
   if (need <= 40) rc = launch_fast_pitch<40>(P, s, max_h);
   else if (need <= 48) rc = launch_fast_pitch<48>(P, s, max_h);
   else if (need <= 56) rc = launch_fast_pitch<56>(P, s, max_h);
-  else rc = launch_fast_pitch<68>(P, s, max_h);
+  else rc = launch_fast_pitch<72>(P, s, max_h);
   if (rc) return rc;
   ++*launches;
   return ORB_OK;
