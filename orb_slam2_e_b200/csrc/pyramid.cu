@@ -113,57 +113,67 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   const int src_w = P.lv[l - 1].w;
   const bool need1 = (first & ~3) + 4 < src_w, need2 = (first & ~3) + 8 < src_w;
 
-  int hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};  // horizontally interpolated source rows rowB-1 and rowB, already >> 4
-  int rowB = -1;
-  // source rows are consumed in order from two register sets that alternate (no moves, which would
-  // wait for the load): the set just consumed is refilled with the row after next, so two rows stay
-  // in flight and a destination row that advances by two source rows does not wait for a fresh load
+  // Horizontally interpolated source rows (already >> 4) live in two register sets that alternate
+  // with the parity of the consumed row, like the word sets they are made from: no moves (a move
+  // would wait for the load), and the vertical step is compiled once per parity.
+  uint32_t h0[4] = {0, 0, 0, 0}, h1[4] = {0, 0, 0, 0};
+  // source rows are consumed in order: the word set just consumed is refilled with the row after
+  // next, so two rows stay in flight and a destination row that advances by two source rows does
+  // not wait for a fresh load.  The request pointer walks down the source and stops at its last row.
   uint32_t wa0 = 0, wa1 = 0, wa2 = 0, wb0 = 0, wb1 = 0, wb2 = 0;
-  auto request = [&](int sy, uint32_t& a, uint32_t& b, uint32_t& c) {
-    const uint32_t* p = wsrc + (size_t)min(sy, src_h - 1) * spw;
-    a = __ldg(p);
-    b = need1 ? __ldg(p + 1) : 0u;
-    c = need2 ? __ldg(p + 2) : 0u;
+  const int first_row = __ldg(&P.rtab[D.ytab + y0]).x;
+  int rowB = first_row - 1;  // last consumed source row
+  int req = first_row;       // next source row to request
+  const uint32_t* preq = wsrc + (size_t)min(req, src_h - 1) * spw;
+  auto request = [&](uint32_t& a, uint32_t& b, uint32_t& c) {
+    a = __ldg(preq);
+    b = need1 ? __ldg(preq + 1) : 0u;
+    c = need2 ? __ldg(preq + 2) : 0u;
+    if (++req < src_h) preq += spw;
   };
-  auto consume = [&](uint32_t w0, uint32_t w1, uint32_t w2) {
+  auto consume = [&](uint32_t w0, uint32_t w1, uint32_t w2, uint32_t (&h)[4]) {
     const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh);
     const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) hA[k] = hB[k];
-    hB[0] = (int)(__dp2a_lo(coef[0], p01, 0u) >> 4);
-    hB[1] = (int)(__dp2a_hi(coef[1], p01, 0u) >> 4);
-    hB[2] = (int)(__dp2a_lo(coef[2], p23, 0u) >> 4);
-    hB[3] = (int)(__dp2a_hi(coef[3], p23, 0u) >> 4);
+    h[0] = __dp2a_lo(coef[0], p01, 0u) >> 4;
+    h[1] = __dp2a_hi(coef[1], p01, 0u) >> 4;
+    h[2] = __dp2a_lo(coef[2], p23, 0u) >> 4;
+    h[3] = __dp2a_hi(coef[3], p23, 0u) >> 4;
   };
-  const int y1 = min(y0 + kResizeStrip, D.h);
-  int next_src = __ldg(&P.rtab[D.ytab + y0]).x;  // source row held by the set that is consumed next
-  bool use_a = true;
-  request(next_src, wa0, wa1, wa2);
-  request(next_src + 1, wb0, wb1, wb2);
-  for (int y = y0; y < y1; ++y) {
-    const int4 t = __ldg(&P.rtab[D.ytab + y]);
-    const int sy0 = t.x, sy1 = t.w, b0 = t.y, b1 = t.z;
-    while (rowB < sy1) {  // sy1 is non-decreasing and advances by at most 2 per destination row
-      if (use_a) {
-        consume(wa0, wa1, wa2);
-        request(next_src + 2, wa0, wa1, wa2);
-      } else {
-        consume(wb0, wb1, wb2);
-        request(next_src + 2, wb0, wb1, wb2);
-      }
-      use_a = !use_a;
-      rowB = next_src;
-      ++next_src;
-    }
-    const bool same = sy0 == sy1;  // clamped rows at the top / bottom border
+  const int rows = min(kResizeStrip, D.h - y0), dpitch = D.pitch;
+  const int4* ytab = P.rtab + D.ytab + y0;
+  bool odd = false;  // parity of the number of consumed rows: the next row goes to (wb, h1) when set
+  request(wa0, wa1, wa2);
+  request(wb0, wb1, wb2);
+  // (b0 * a) >> 16 is the high word of (b0 << 16) * a: one IMAD.HI with the running sum as addend
+  auto vertical = [&](const uint32_t (&older)[4], const uint32_t (&newer)[4], uint32_t B0, uint32_t B1, bool same) {
     uint32_t u[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const int a = same ? hB[k] : hA[k];
-      u[k] = (uint32_t)(((b0 * a) >> 16) + ((b1 * hB[k]) >> 16) + 2) << 6;  // result byte = bits 8..15
+      const uint32_t a = same ? newer[k] : older[k];
+      u[k] = (__umulhi(B1, newer[k]) + (__umulhi(B0, a) + 2u)) << 6;  // result byte = bits 8..15
     }
     *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(u[0], u[1], 0x0051), __byte_perm(u[2], u[3], 0x0051), 0x5410);
-    dst += D.pitch;  // pitch padding absorbs the tail
+    dst += dpitch;  // pitch padding absorbs the tail
+  };
+  for (int i = 0; i < rows; ++i) {
+    const int4 t = __ldg(ytab + i);
+    const int sy1 = t.w;
+#pragma unroll 1
+    while (rowB < sy1) {  // one or two trips: sy1 is non-decreasing and advances by at most 2 per destination row
+      if (!odd) {
+        consume(wa0, wa1, wa2, h0);
+        request(wa0, wa1, wa2);
+      } else {
+        consume(wb0, wb1, wb2, h1);
+        request(wb0, wb1, wb2);
+      }
+      odd = !odd;
+      ++rowB;
+    }
+    const bool same = t.x == sy1;  // clamped rows at the top / bottom border
+    const uint32_t B0 = (uint32_t)t.y << 16, B1 = (uint32_t)t.z << 16;
+    if (odd) vertical(h1, h0, B0, B1, same);  // the row consumed last went to h0
+    else vertical(h0, h1, B0, B1, same);
   }
 }
 
