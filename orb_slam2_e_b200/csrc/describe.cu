@@ -73,10 +73,8 @@ constexpr int kPatchRows = 2 * kPatchR + 1; // 37
 constexpr int kPatchWords = 10;             // 37 bytes at any 4-byte misalignment fit 10 aligned words
 constexpr int kPatchPitch = 4 * kPatchWords;
 
-// cvRound for |v| < 2^22 without the XU pipe: adding 1.5 * 2^23 leaves round-half-even(v) in the mantissa
-__device__ __forceinline__ int round_rn_small(float v) {
-  return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000;
-}
+// cvRound for |v| < 2^22 without the XU pipe: adding 1.5 * 2^23 (12582912.0f, bits 0x4B400000) leaves
+// round-half-even(v) in the mantissa; the kernel folds the constant into the patch offset.
 
 constexpr int kKpPerWarp = 4;  // keypoint slots per warp: amortises the per-CTA pattern table fill
 
@@ -149,13 +147,15 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
     const int sp = level_pitch(P, l);
     int colsum = 0, m01 = 0;
     {
+      // rows +v and -v together: one bound test, colsum += a + b, m01 += v * (a - b)
       const uint8_t* cp = level_ptr(P, l, f) + (size_t)y * sp + (x + u);
+      if (vlim >= 0) colsum = cp[0];
 #pragma unroll
-      for (int v = -kHalfPatch; v <= kHalfPatch; ++v) {
-        if ((v < 0 ? -v : v) <= vlim) {
-          const int val = cp[v * sp];
-          colsum += val;
-          m01 += v * val;
+      for (int v = 1; v <= kHalfPatch; ++v) {
+        if (v <= vlim) {
+          const int a = cp[v * sp], b = cp[-v * sp];
+          colsum += a + b;
+          m01 += v * (a - b);
         }
       }
     }
@@ -180,7 +180,12 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
     ca = __shfl_sync(0xffffffffu, ca, 0);
     sa = __shfl_sync(0xffffffffu, sa, 0);
     __syncwarp();  // patch visible to every lane
-    const uint8_t* pc = reinterpret_cast<const uint8_t*>(patch_s[warp]) + kPatchR * kPatchPitch + kPatchR + shift;
+    // cvRound of the rotated coordinates is the add-1.5*2^23 trick; the constant left in the float's
+    // bit pattern (0x4B400000 per coordinate) is taken out of the patch offset once per keypoint
+    // instead of once per coordinate: offset = ybits * pitch + xbits + kbase (mod 2^32)
+    const uint8_t* patch_bytes = reinterpret_cast<const uint8_t*>(&patch_s[0][0]);
+    const uint32_t kbase = (uint32_t)(warp * (int)sizeof(patch_s[0]) + kPatchR * kPatchPitch + kPatchR + shift) -
+                           0x4B400000u * (uint32_t)(kPatchPitch + 1);
     uint32_t byte = 0;
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
@@ -188,9 +193,9 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const float2 p = patf[(t * 2 + e) * 32 + lane];
-        const int yy = round_rn_small(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)));
-        const int xx = round_rn_small(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)));
-        val[e] = pc[yy * kPatchPitch + xx];
+        const uint32_t yb = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.x, sa), __fmul_rn(p.y, ca)), 12582912.0f));
+        const uint32_t xb = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.x, ca), __fmul_rn(p.y, sa)), 12582912.0f));
+        val[e] = patch_bytes[yb * (uint32_t)kPatchPitch + kbase + xb];
       }
       byte |= (uint32_t)(val[0] < val[1]) << t;
     }
