@@ -314,7 +314,7 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   if (left) selA = 0x1234u;  // x = -4..-1 <- x = 4, 3, 2, 1 out of (b, c)
 
   if (active) {
-    uint32_t ring[7][4];
+    uint32_t ring[7][4] = {}, hn[4];
     constexpr int kAhead = 3;  // the three words of row yy+3 are requested while row yy is filtered
     uint32_t pa[kAhead], pb[kAhead], pc[kAhead];
     const uint8_t* rowp = src + (size_t)(y_inside ? y0 - 3 : 0) * sp + x0;  // next row to fetch (y_inside)
@@ -346,18 +346,20 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
           const uint32_t a = left ? __byte_perm(b0, c0, selA) : a0;
           const uint32_t b = __byte_perm(a0, b0, selB);
           const uint32_t c = __byte_perm(c_from_ab ? a0 : b0, c_from_ab ? b0 : c0, selC);
-          uint32_t* h = ring[r % 7];
-          h[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
-          h[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
-          h[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
-          h[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
+          // the ring keeps (row yy-1, row yy) as u16 pairs, so the vertical taps are three DP2A and one IMAD
+          hn[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
+          hn[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
+          hn[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
+          hn[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) ring[r % 7][k] = __byte_perm(ring[(r + 6) % 7][k], hn[k], 0x5432);  // horizontal sums are <= 255 * 256
         }
         if ((r >= 6 || blk > 0) && rows_left > 0) {  // the ring holds the 7 horizontal rows of the next output row
           uint32_t acc[4];
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            acc[k] = 18u * (ring[(r + 1) % 7][k] + ring[r % 7][k]) + 34u * (ring[(r + 2) % 7][k] + ring[(r + 6) % 7][k]) +
-                     48u * (ring[(r + 3) % 7][k] + ring[(r + 5) % 7][k]) + (56u * ring[(r + 4) % 7][k] + 32768u);
+          for (int k = 0; k < 4; ++k)  // rows yy-6..yy: pairs written at yy-5, yy-3, yy-1 and the row just filtered
+            acc[k] = __dp2a_lo(ring[(r + 2) % 7][k], K1, __dp2a_hi(ring[(r + 4) % 7][k], K1,
+                     __dp2a_lo(ring[(r + 6) % 7][k], K2, 18u * hn[k] + 32768u)));
           // result bytes are bits 16..23 of each sum; pitch padding absorbs the bytes past the row's end
           *reinterpret_cast<uint32_t*>(outp) =
               __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
