@@ -173,7 +173,7 @@ def run_reference_arm(args):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------ GPU arm ----------------
@@ -217,9 +217,20 @@ def run_gpu_arm(args):
             "clocks": ex["clocks"], "roofline": ex["roofline"], "roofline_pipeline": ex["roofline_pipeline"],
             "cpu_baseline": cpu, "matching": match,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if dist is not None:
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def _emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -239,6 +250,13 @@ def main():
     ap.add_argument("--no-match", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
+    # stdout carries exactly ONE JSON line: native libraries (NCCL prints its version banner on fd 1
+    # whenever the box sets NCCL_DEBUG) write to stderr for the whole run, and _emit() writes the line
+    # to the saved descriptor
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
     else:
