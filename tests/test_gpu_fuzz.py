@@ -97,3 +97,32 @@ def test_wide_and_tall_aspect_ratios():
     # the GPU path refuses such frames instead of inventing a result
     with pytest.raises(OrbFrontError):
         ORBextractor(800, 1.2, 2, 20, 7)(rng.integers(0, 256, (900, 100), dtype=np.uint8))
+
+
+def _max_cell_width(w, nlevels, scale):
+    """Widest FAST cell over the levels, with the constructor's arithmetic (ORBextractor.cc:771-787)."""
+    widest, s = 0, 1.0
+    for _ in range(nlevels):
+        lw = int(round(np.float32(w) * np.float32(1.0 / np.float32(s))))
+        box = lw - 2 * 16
+        ncols = box // 30
+        widest = max(widest, -(-box // ncols))
+        s = np.float32(s * scale)
+    return widest
+
+
+@pytest.mark.parametrize("w,h,nlevels,scale,lo,hi", [
+    (640, 200, 3, 1.2, 30, 40),    # pitch 40: cells up to 32 px
+    (152, 150, 2, 1.1, 33, 40),    # pitch 48: cells up to 36 px
+    (118, 140, 1, 1.2, 41, 48),    # pitch 56
+    (326, 250, 8, 1.2, 49, 59),    # pitch 72: the 91-px top level is a single 59-px cell
+    (90, 120, 1, 1.2, 49, 59),     # pitch 72, single level, single 58-px column
+])
+def test_every_fast_tile_pitch_and_staging_shift(w, h, nlevels, scale, lo, hi):
+    """One case per tile-pitch template of fast_cells_kernel (40 / 48 / 56 / 72 bytes); cell origins at
+    19 + j * wCell give every byte and word misalignment of the 16-byte quad staging."""
+    widest = _max_cell_width(w, nlevels, scale)
+    assert lo <= widest <= hi, widest
+    rng = np.random.default_rng(w * 1000 + h)
+    for kind in ("noise", "blobs"):
+        check(make_image(kind, h, w, rng), (400, scale, nlevels, 20, 7))
