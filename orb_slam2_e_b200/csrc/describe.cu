@@ -150,10 +150,15 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
       // rows +v and -v together: one bound test, colsum += a + b, m01 += v * (a - b)
       const uint8_t* cp = level_ptr(P, l, f) + (size_t)y * sp + (x + u);
       if (vlim >= 0) colsum = cp[0];
+      const uint8_t* pp = cp;  // rows y + v and y - v by running pointers: one 64-bit add per load
+      const uint8_t* pm = cp;
 #pragma unroll
       for (int v = 1; v <= kHalfPatch; ++v) {
+        pp += sp;
+        pm -= sp;
+        asm("" : "+l"(pp), "+l"(pm));  // keep them as pointers: the compiler otherwise re-derives base + offset (two more adds per load)
         if (v <= vlim) {
-          const int a = cp[v * sp], b = cp[-v * sp];
+          const int a = *pp, b = *pm;
           colsum += a + b;
           m01 += v * (a - b);
         }
