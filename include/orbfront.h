@@ -8,7 +8,9 @@
  * Conventions: plain C types only; every function returns ORB_OK (0) or a negative ORB_E_*
  * code and records a thread-local message readable through orb_last_error().  No function
  * falls back to a CPU implementation: without a CUDA device they fail with ORB_E_NO_DEVICE.
- * Handles are not thread-safe but independent (one CUDA stream each), matching the reference,
+ * Handles are not thread-safe but independent (one CUDA stream each -- a handle also owns a few
+ * internal streams that fork from and join back into it, so ordering against the handle's stream
+ * orders against all of a call's work), matching the reference,
  * which never shares an ORBextractor between threads (Frame.cc:78-81) and constructs a stack
  * ORBmatcher per call site (Tracking.cc:1750).
  */
