@@ -66,6 +66,9 @@ struct orbx_handle {
   Dev<int4> rtab;
   Dev<uint32_t> qcode;
   Dev<int> blur_tiles;
+  Dev<FastBand> fast_bands;
+  Dev<uint8_t> fast_zeros;
+  int fast_grid = 0;
   Dev<orbx_keypoint> out_kp;
   Dev<uint8_t> border_tmp;
   int n_frames = 0;       // frames of the last batch (0: nothing extracted yet)
@@ -129,8 +132,8 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
     P.ini_th = c.ini_th_fast;
     P.min_th = c.min_th_fast;
     size_t off = 0;
-    int cell_base = 0, cand_off = 0, kept_off = 0, tab = 0, tiles = 0;
-    std::vector<int> blur_tiles(nl + 1, 0);
+    int cell_base = 0, cand_off = 0, kept_off = 0, tab = 0, tiles = 0, tiles_few = 0;
+    std::vector<int> blur_tiles(2 * (nl + 1), 0);  // first tile of each level: 56-row tiles, then 14-row tiles (pyramid.cu kBlurTH / kBlurTHFew)
     for (int l = 0; l < nl; ++l) {
       LevelGeom& G = P.lv[l];
       G.w = cv_round((float)w * H->inv_scale[l]);
@@ -172,9 +175,12 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       G.xtab = tab; tab += G.w;
       G.ytab = tab; tab += G.h;
       blur_tiles[l] = tiles;
-      tiles += div_up(G.w, 128) * div_up(G.h, 36);  // blur_kernel warp tiles (pyramid.cu kBlurTW x kBlurTH)
+      tiles += div_up(G.w, 128) * div_up(G.h, 56);
+      blur_tiles[nl + 1 + l] = tiles_few;
+      tiles_few += div_up(G.w, 128) * div_up(G.h, 14);
     }
     blur_tiles[nl] = tiles;
+    blur_tiles[2 * nl + 1] = tiles_few;
     P.total_cells = cell_base;
     P.pyr_frame = P.blur_frame = off;
     P.cand_frame = (size_t)cand_off;
@@ -230,10 +236,21 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
         qcode.push_back(code);
       }
     }
-    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(nl + 1)) || (rc = H->qcode.reserve(qcode.size()))) return rc;
+    std::vector<FastBand> bands;
+    if ((rc = fast_build_bands(P, bands))) return rc;
+    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(2 * (nl + 1))) || (rc = H->qcode.reserve(qcode.size())) ||
+        (rc = H->fast_bands.reserve(bands.size())))
+      return rc;
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->fast_bands.p, bands.data(), bands.size() * sizeof(FastBand), cudaMemcpyHostToDevice, H->stream));
+    if ((size_t)P.fast_score_bytes > H->fast_zeros.cap) {
+      if ((rc = H->fast_zeros.reserve((size_t)P.fast_score_bytes))) return rc;
+      ORB_CUDA_TRY(cudaMemsetAsync(H->fast_zeros.p, 0, H->fast_zeros.cap, H->stream));
+    }
+    P.fast_zeros = H->fast_zeros.p;
+    H->fast_grid = fast_band_grid(P, H->cfg.device);
     ORB_CUDA_TRY(cudaMemcpyAsync(H->qcode.p, qcode.data(), qcode.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->rtab.p, taps.data(), taps.size() * sizeof(int4), cudaMemcpyHostToDevice, H->stream));
-    ORB_CUDA_TRY(cudaMemcpyAsync(H->blur_tiles.p, blur_tiles.data(), (nl + 1) * sizeof(int), cudaMemcpyHostToDevice, H->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(H->blur_tiles.p, blur_tiles.data(), blur_tiles.size() * sizeof(int), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));  // host vectors go out of scope
     H->w = w; H->h = h;
     H->l0_pitch = align_up<size_t>((size_t)w + 4, 64);
@@ -252,7 +269,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
   P.n_frames = n_frames;
   P.pyr = H->pyr.p; P.blur = H->blur.p; P.cand = H->cand.p; P.cand_count = H->cand_count.p;
   P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p; P.qt_tmp = H->qt_tmp.p;
-  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p; P.qcode = H->qcode.p;
+  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p; P.qcode = H->qcode.p; P.fast_bands = H->fast_bands.p; P.fast_zeros = H->fast_zeros.p; P.fast_grid = H->fast_grid;
   P.out_kp = H->out_kp.p; P.out_desc = H->out_desc.p; P.out_count = H->out_count.p;
   if (H->pyr_max_grid < 0) H->pyr_max_grid = pyramid_fused_max_grid(H->cfg.device);
   P.pyr_bar = H->pyr_bar.p; P.pyr_max_grid = H->pyr_max_grid;

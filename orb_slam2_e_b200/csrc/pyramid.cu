@@ -79,9 +79,12 @@ __device__ __forceinline__ void resize_block(const ExtractParams& P, int l, int 
 // Word-wise variant for scale factors up to ~2 (every 4-pixel destination group reads source
 // columns spanning at most 8 bytes): per source row a lane loads three aligned words, shifts its
 // 8-byte window into place, picks the (left, right) byte pairs with two PRMTs whose selectors are
-// lane constants, and interpolates with DP2A on packed (c0, c1) 16-bit weights -- 11 instructions per
-// source row instead of 8 byte loads + 8 IMADs + their addressing.  Source rows are consumed in
-// order and requested one row ahead.  Arithmetic identical to resize_level_kernel.
+// lane constants, and interpolates with DP2A on packed (c0, c1) 16-bit weights.  Every destination row
+// interpolates its two source rows itself: the round-1 kernel kept the row shared by consecutive
+// destination rows in registers, and the bookkeeping for that (row parity, request/consume pointers,
+// clamped-row cases) was 40 % of its executed instructions -- more than the 15 instructions per row it
+// saved.  The row loop below has no branch and no state carried between rows; rows clamped at the
+// top / bottom border simply read the same source row twice.  Arithmetic identical to resize_block.
 template <int kResizeStrip>
 __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l, int bx, int by, int f) {
   const LevelGeom& D = P.lv[l];
@@ -91,7 +94,6 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   if (x0 >= D.w || y0 >= D.h) return;
   const uint8_t* src = level_ptr(P, l - 1, f);
   const int sp = level_pitch(P, l - 1);
-  const int src_h = P.lv[l - 1].h;
   uint8_t* dst = P.pyr + (size_t)f * P.pyr_frame + D.off + (size_t)y0 * D.pitch + x0;
 
   // lane constants
@@ -106,32 +108,24 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
     if (k < 2) sel01 |= pair << (8 * k); else sel23 |= pair << (8 * (k - 2));
   }
   const int sh = (first & 3) * 8;
-  const uint32_t* wsrc = reinterpret_cast<const uint32_t*>(src) + (first >> 2);
-  const int spw = sp >> 2;
+  const uint8_t* wsrc = src + (first & ~3);
+  asm("" : "+l"(wsrc));  // one 64-bit lane pointer: otherwise the uniform base is re-added to every row address (2 more adds per source row)
   // a window word is loaded only if it starts inside the source row (the taps never select bytes
   // past the row's last pixel), so no load leaves the row whatever its pitch
   const int src_w = P.lv[l - 1].w;
   const bool need1 = (first & ~3) + 4 < src_w, need2 = (first & ~3) + 8 < src_w;
-
-  // Horizontally interpolated source rows (already >> 4) live in two register sets that alternate
-  // with the parity of the consumed row, like the word sets they are made from: no moves (a move
-  // would wait for the load), and the vertical step is compiled once per parity.
-  uint32_t h0[4] = {0, 0, 0, 0}, h1[4] = {0, 0, 0, 0};
-  // source rows are consumed in order: the word set just consumed is refilled with the row after
-  // next, so two rows stay in flight and a destination row that advances by two source rows does
-  // not wait for a fresh load.  The request pointer walks down the source and stops at its last row.
-  uint32_t wa0 = 0, wa1 = 0, wa2 = 0, wb0 = 0, wb1 = 0, wb2 = 0;
-  const int first_row = __ldg(&P.rtab[D.ytab + y0]).x;
-  int rowB = first_row - 1;  // last consumed source row
-  int req = first_row;       // next source row to request
-  const uint32_t* preq = wsrc + (size_t)min(req, src_h - 1) * spw;
-  auto request = [&](uint32_t& a, uint32_t& b, uint32_t& c) {
-    a = __ldg(preq);
-    b = need1 ? __ldg(preq + 1) : 0u;
-    c = need2 ? __ldg(preq + 2) : 0u;
-    if (++req < src_h) preq += spw;
+  // The six window words of destination row i+1 are requested before row i is interpolated, and the
+  // row table is read two rows ahead, so a warp always has one destination row of loads in flight
+  // (ncu, first version of this loop: 13 of 16 resident warps stalled on the row loads).
+  struct Win { uint32_t a0, a1, a2, b0, b1, b2; };
+  auto request = [&](const int4& t, Win& w) {
+    const uint32_t* pa = reinterpret_cast<const uint32_t*>(wsrc + (size_t)((uint32_t)t.x * (unsigned long long)(uint32_t)sp));
+    const uint32_t* pb = reinterpret_cast<const uint32_t*>(wsrc + (size_t)((uint32_t)t.w * (unsigned long long)(uint32_t)sp));
+    w.a0 = __ldg(pa); w.a1 = need1 ? __ldg(pa + 1) : 0u; w.a2 = need2 ? __ldg(pa + 2) : 0u;
+    w.b0 = __ldg(pb); w.b1 = need1 ? __ldg(pb + 1) : 0u; w.b2 = need2 ? __ldg(pb + 2) : 0u;
   };
-  auto consume = [&](uint32_t w0, uint32_t w1, uint32_t w2, uint32_t (&h)[4]) {
+  // horizontally interpolated source row, already >> 4
+  auto hrow = [&](uint32_t w0, uint32_t w1, uint32_t w2, uint32_t (&h)[4]) {
     const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh);
     const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
     h[0] = __dp2a_lo(coef[0], p01, 0u) >> 4;
@@ -141,39 +135,26 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   };
   const int rows = min(kResizeStrip, D.h - y0), dpitch = D.pitch;
   const int4* ytab = P.rtab + D.ytab + y0;
-  bool odd = false;  // parity of the number of consumed rows: the next row goes to (wb, h1) when set
-  request(wa0, wa1, wa2);
-  request(wb0, wb1, wb2);
-  // (b0 * a) >> 16 is the high word of (b0 << 16) * a: one IMAD.HI with the running sum as addend
-  auto vertical = [&](const uint32_t (&older)[4], const uint32_t (&newer)[4], uint32_t B0, uint32_t B1, bool same) {
-    uint32_t u[4];
+  int4 t_cur = __ldg(ytab), t_nxt = __ldg(ytab + min(1, rows - 1));
+  Win w_cur;
+  request(t_cur, w_cur);
+#pragma unroll 2
+  for (int i = 0; i < rows; ++i) {
+    Win w_nxt;
+    request(t_nxt, w_nxt);  // the last iteration re-requests the last row (cached)
+    const int4 t_nn = __ldg(ytab + min(i + 2, rows - 1));
+    uint32_t hA[4], hB[4], u[4];
+    hrow(w_cur.a0, w_cur.a1, w_cur.a2, hA);
+    hrow(w_cur.b0, w_cur.b1, w_cur.b2, hB);
+    // (b * a) >> 16 is the high word of (b << 16) * a: one IMAD.HI with the running sum as addend
+    const uint32_t B0 = (uint32_t)t_cur.y << 16, B1 = (uint32_t)t_cur.z << 16;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const uint32_t a = same ? newer[k] : older[k];
-      u[k] = (__umulhi(B1, newer[k]) + (__umulhi(B0, a) + 2u)) << 6;  // result byte = bits 8..15
-    }
+    for (int k = 0; k < 4; ++k) u[k] = (__umulhi(B1, hB[k]) + (__umulhi(B0, hA[k]) + 2u)) << 6;  // result byte = bits 8..15
     *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(u[0], u[1], 0x0051), __byte_perm(u[2], u[3], 0x0051), 0x5410);
     dst += dpitch;  // pitch padding absorbs the tail
-  };
-  for (int i = 0; i < rows; ++i) {
-    const int4 t = __ldg(ytab + i);
-    const int sy1 = t.w;
-#pragma unroll 1
-    while (rowB < sy1) {  // one or two trips: sy1 is non-decreasing and advances by at most 2 per destination row
-      if (!odd) {
-        consume(wa0, wa1, wa2, h0);
-        request(wa0, wa1, wa2);
-      } else {
-        consume(wb0, wb1, wb2, h1);
-        request(wb0, wb1, wb2);
-      }
-      odd = !odd;
-      ++rowB;
-    }
-    const bool same = t.x == sy1;  // clamped rows at the top / bottom border
-    const uint32_t B0 = (uint32_t)t.y << 16, B1 = (uint32_t)t.z << 16;
-    if (odd) vertical(h1, h0, B0, B1, same);  // the row consumed last went to h0
-    else vertical(h0, h1, B0, B1, same);
+    w_cur = w_nxt;
+    t_cur = t_nxt;
+    t_nxt = t_nn;
   }
 }
 
@@ -260,19 +241,20 @@ __device__ __forceinline__ int reflect101(int p, int n) {
   return p;  // valid for |overshoot| < n, which holds for 3-px taps on levels >= 7 px
 }
 
-// Blur: one warp per 128-column x 36-row tile, each lane owns 4 adjacent columns (one 32-bit
+// Blur: one warp per 128-column x kBlurTH-row tile, each lane owns 4 adjacent columns (one 32-bit
 // word) and marches down the rows.  Horizontal 7 taps = two DP4A per output on byte windows
-// funnel-shifted out of three aligned words; the last 7 horizontal rows live in registers (ring),
-// vertical 7 taps use the kernel's symmetry and PRMT packs byte 2 of the four sums.  The 42 input
-// rows run as 2 x 21: 21 is the common period of the 7-row ring and the 3-deep load pipeline, so
-// register indices stay static while the loop body (about 20 KB of SASS) stays inside the 32 KB
-// instruction cache -- the fully unrolled form stalled on instruction fetch.  No shared memory.
-constexpr int kBlurTW = 128, kBlurTH = 36, kBlurWarps = 4;
-constexpr int kBlurRows = kBlurTH + 6, kBlurBody = 21;
-static_assert(kBlurRows % kBlurBody == 0, "row loop must be whole bodies");
+// funnel-shifted out of three aligned words; the last 7 horizontal rows live in registers as u16 pairs
+// (row-1, row), so the vertical taps are three DP2A and one IMAD; PRMT packs byte 2 of the four sums.
+// Round 2: the row loop has no branch.  The source row pointer walks the BORDER_REFLECT_101 sequence by
+// itself (its step flips sign above row 0 and from row h-1 on), stores past the tile's last row are
+// predicated off, and the body is 14 rows = the common period of the 7-row ring and the 2-deep load
+// pipeline (about 10 KB of SASS).  The round-1 loop spent 43 % of its instructions on the three
+// warp-uniform branches per row and their address arithmetic.  No shared memory.
+constexpr int kBlurTW = 128, kBlurWarps = 4, kBlurBody = 14;
+constexpr int kBlurTH = 56, kBlurTHFew = 14;  // rows per tile: batches / one or a few frames (more, shorter warps)
 
 __global__ void __launch_bounds__(kBlurWarps * 32, 8)
-blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */, int skip_empty_levels) {
+blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */, int th, int skip_empty_levels) {
   const int lane = threadIdx.x & 31;
   const int tile = blockIdx.x * kBlurWarps + (threadIdx.x >> 5);
   if (tile >= tile_base[P.nlevels]) return;
@@ -284,18 +266,14 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   if (skip_empty_levels && P.kept_count[f * P.nlevels + l] == 0) return;
   const int t = tile - tile_base[l];
   const int tiles_x = div_up(G.w, kBlurTW);
-  const int tx0 = (t % tiles_x) * kBlurTW;
-  const int x0 = tx0 + 4 * lane, y0 = (t / tiles_x) * kBlurTH;
-  const uint8_t* src = level_ptr(P, l, f);
-  const int sp = level_pitch(P, l);
-  uint8_t* dst = P.blur + (size_t)f * P.blur_frame + G.off;
-  // Row edges without a divergent path: every lane with a pixel in the row runs the word-wise loop on
-  // its 12-byte window [x0-4, x0+8); where the window leaves the row, BORDER_REFLECT_101 is applied
-  // by three PRMTs whose selectors are lane constants (identity for interior lanes).
+  const int ty = t / tiles_x, tx = t - ty * tiles_x;
+  const int x0 = tx * kBlurTW + 4 * lane, y0 = ty * th;
   const int e = G.w - x0;  // pixels of this lane's window that exist from x0 on (>= 8: no right edge)
-  const bool active = e > 0;
-  // tiles away from the top/bottom border walk a running row pointer; the others reflect per row
-  const bool y_inside = y0 >= 3 && y0 + kBlurTH + 3 <= G.h;
+  if (e <= 0) return;
+  const int sp = level_pitch(P, l);
+  // Row edges without a divergent path: every lane runs the word-wise loop on its 12-byte window
+  // [x0-4, x0+8); where the window leaves the row, BORDER_REFLECT_101 is applied by three PRMTs whose
+  // selectors are lane constants (identity for interior lanes).
   constexpr uint32_t K1 = 18u | 34u << 8 | 48u << 16 | 56u << 24, K2 = 48u | 34u << 8 | 18u << 16;
   // window byte i (0..11) <-> x0-4+i; byte i >= e+4 mirrors to 2(e+3)-i, byte i < 4 of lane x0 = 0 to 8-i.
   // a' = PRMT(b, c, selA); b' = PRMT(a, b, selB); c' = PRMT(lo, hi, selC) with (lo, hi) = (a, b) if e <= 4 else (b, c)
@@ -312,69 +290,72 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
     }
   }
   if (left) selA = 0x1234u;  // x = -4..-1 <- x = 4, 3, 2, 1 out of (b, c)
+  const bool ld_a = !left, ld_c = e > 4;  // never read a word that starts outside the row
 
-  if (active) {
-    uint32_t ring[7][4] = {}, hn[4];
-    constexpr int kAhead = 3;  // the three words of row yy+3 are requested while row yy is filtered
-    uint32_t pa[kAhead], pb[kAhead], pc[kAhead];
-    const uint8_t* rowp = src + (size_t)(y_inside ? y0 - 3 : 0) * sp + x0;  // next row to fetch (y_inside)
-    auto fetch = [&](int yy, uint32_t& a, uint32_t& b, uint32_t& c) {
-      const uint8_t* p = rowp;
-      if (y_inside) {
-        rowp += sp;
-      } else {
-        const int y = y0 + yy - 3;
-        p = src + (size_t)reflect101(min(y, G.h + 2), G.h) * sp + x0;  // rows past h+2 are never used
-      }
-      const uint32_t* w = reinterpret_cast<const uint32_t*>(p);
-      a = left ? 0u : __ldg(w - 1);
-      b = __ldg(w);
-      c = e > 4 ? __ldg(w + 1) : 0u;  // never read a word that starts past the row
-    };
+  const int rows_out = min(th, G.h - y0);
+  // source row of input step yy is reflect101(y0 - 3 + yy): the pointer starts there and steps by
+  // +-sp, downwards (in memory: backwards) while the un-reflected row is above row 0 or at / below row h-1
+  int yin = y0 - 3;
+  const uint8_t* rowp = level_ptr(P, l, f) + (size_t)reflect101(min(yin, G.h + 2), G.h) * sp + x0;
+  const unsigned turn = (unsigned)(G.h - 1);
+  uint32_t pa[2], pb[2], pc[2];
+  auto fetch = [&](uint32_t& a, uint32_t& b, uint32_t& c) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(rowp);
+    a = ld_a ? __ldg(w - 1) : 0u;
+    b = __ldg(w);
+    c = ld_c ? __ldg(w + 1) : 0u;
+    rowp += (unsigned)yin >= turn ? -(ptrdiff_t)sp : (ptrdiff_t)sp;
+    ++yin;
+  };
+  fetch(pa[0], pb[0], pc[0]);
+  fetch(pa[1], pb[1], pc[1]);
+  uint32_t ring[7][4] = {}, hn[4];
+  uint8_t* outp = P.blur + (size_t)f * P.blur_frame + G.off + (size_t)y0 * G.pitch + x0;  // next output row
+  int out_left = rows_out;
+  // one input row: horizontal taps into the ring; kOut: the ring then holds the 7 rows of the next output row
+  auto step = [&](const int r, const bool kOut) {  // r: input step modulo 14
+    const uint32_t a0 = pa[r & 1], b0 = pb[r & 1], c0 = pc[r & 1];
+    fetch(pa[r & 1], pb[r & 1], pc[r & 1]);  // row yy + 2 (a few rows past the tile are fetched and never used)
+    const uint32_t a = left ? __byte_perm(b0, c0, selA) : a0;
+    const uint32_t b = __byte_perm(a0, b0, selB);
+    const uint32_t c = __byte_perm(c_from_ab ? a0 : b0, c_from_ab ? b0 : c0, selC);
+    hn[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
+    hn[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
+    hn[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
+    hn[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
 #pragma unroll
-    for (int k = 0; k < kAhead; ++k) fetch(k, pa[k], pb[k], pc[k]);
-    uint8_t* outp = dst + (size_t)y0 * G.pitch + x0;  // next output row
-    int rows_left = min(kBlurTH, G.h - y0);
-#pragma unroll 1
-    for (int blk = 0; blk < kBlurRows / kBlurBody; ++blk) {
+    for (int k = 0; k < 4; ++k) ring[r % 7][k] = __byte_perm(ring[(r + 6) % 7][k], hn[k], 0x5432);  // (row yy-1, row yy); horizontal sums are <= 255 * 256
+    if (kOut) {
+      uint32_t acc[4];
 #pragma unroll
-      for (int r = 0; r < kBlurBody; ++r) {
-        const int yy = blk * kBlurBody + r;
-        {
-          const uint32_t a0 = pa[r % kAhead], b0 = pb[r % kAhead], c0 = pc[r % kAhead];
-          if (yy + kAhead < kBlurRows) fetch(yy + kAhead, pa[r % kAhead], pb[r % kAhead], pc[r % kAhead]);
-          const uint32_t a = left ? __byte_perm(b0, c0, selA) : a0;
-          const uint32_t b = __byte_perm(a0, b0, selB);
-          const uint32_t c = __byte_perm(c_from_ab ? a0 : b0, c_from_ab ? b0 : c0, selC);
-          // the ring keeps (row yy-1, row yy) as u16 pairs, so the vertical taps are three DP2A and one IMAD
-          hn[0] = __dp4a(__funnelshift_r(a, b, 8), K1, __dp4a(__funnelshift_r(b, c, 8), K2, 0u));
-          hn[1] = __dp4a(__funnelshift_r(a, b, 16), K1, __dp4a(__funnelshift_r(b, c, 16), K2, 0u));
-          hn[2] = __dp4a(__funnelshift_r(a, b, 24), K1, __dp4a(__funnelshift_r(b, c, 24), K2, 0u));
-          hn[3] = __dp4a(b, K1, __dp4a(c, K2, 0u));
-#pragma unroll
-          for (int k = 0; k < 4; ++k) ring[r % 7][k] = __byte_perm(ring[(r + 6) % 7][k], hn[k], 0x5432);  // horizontal sums are <= 255 * 256
-        }
-        if ((r >= 6 || blk > 0) && rows_left > 0) {  // the ring holds the 7 horizontal rows of the next output row
-          uint32_t acc[4];
-#pragma unroll
-          for (int k = 0; k < 4; ++k)  // rows yy-6..yy: pairs written at yy-5, yy-3, yy-1 and the row just filtered
-            acc[k] = __dp2a_lo(ring[(r + 2) % 7][k], K1, __dp2a_hi(ring[(r + 4) % 7][k], K1,
-                     __dp2a_lo(ring[(r + 6) % 7][k], K2, 18u * hn[k] + 32768u)));
-          // result bytes are bits 16..23 of each sum; pitch padding absorbs the bytes past the row's end
-          *reinterpret_cast<uint32_t*>(outp) =
-              __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
-          outp += G.pitch;
-          --rows_left;
-        }
-      }
+      for (int k = 0; k < 4; ++k)  // rows yy-6..yy: pairs written at yy-5, yy-3, yy-1 and the row just filtered
+        acc[k] = __dp2a_lo(ring[(r + 2) % 7][k], K1, __dp2a_hi(ring[(r + 4) % 7][k], K1,
+                 __dp2a_lo(ring[(r + 6) % 7][k], K2, 18u * hn[k] + 32768u)));
+      // result bytes are bits 16..23 of each sum; pitch padding absorbs the bytes past the row's end
+      const uint32_t v = __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
+      if (out_left > 0) *reinterpret_cast<uint32_t*>(outp) = v;
+      outp += G.pitch;
+      --out_left;
     }
+  };
+#pragma unroll
+  for (int r = 0; r < 6; ++r) step(r, false);
+#pragma unroll 1
+  while (out_left > 0) {
+#pragma unroll
+    for (int j = 0; j < kBlurBody; ++j) step(6 + j, true);  // (6 + j) % 14 keeps ring slot and pipeline slot static
   }
 }
 
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree) {
+  // blur_tiles (extractor.cu) is built for kBlurTH-row tiles; a few frames use kBlurTHFew-row tiles, whose
+  // table is the second half of the same array
+  const bool few = (long)P.n_frames * div_up(P.lv[0].w, kBlurTW) * div_up(P.lv[0].h, kBlurTH) < 2 * 148;
+  const int th = few ? kBlurTHFew : kBlurTH;
   int total = 0;
-  for (int l = 0; l < P.nlevels; ++l) total += div_up(P.lv[l].w, kBlurTW) * div_up(P.lv[l].h, kBlurTH);
-  blur_kernel<<<dim3(div_up(total, kBlurWarps), 1, P.n_frames), kBlurWarps * 32, 0, s>>>(P, P.blur_tiles, after_quadtree ? 1 : 0);
+  for (int l = 0; l < P.nlevels; ++l) total += div_up(P.lv[l].w, kBlurTW) * div_up(P.lv[l].h, th);
+  blur_kernel<<<dim3(div_up(total, kBlurWarps), 1, P.n_frames), kBlurWarps * 32, 0, s>>>(P, P.blur_tiles + (few ? P.nlevels + 1 : 0), th,
+                                                                                       after_quadtree ? 1 : 0);
   ORB_LAUNCH_CHECK();
   ++*launches;
   return ORB_OK;
