@@ -15,8 +15,6 @@
 // pattern never leave the image; only the blur's +-3 taps do, and they reflect in-kernel.
 // orbx_get_level(with_border) builds the BORDER_REFLECT_101 frame on demand.
 #pragma once
-#include <vector>
-
 #include "common.cuh"
 
 namespace orbfront {
@@ -45,23 +43,6 @@ struct LevelGeom {
   int resize_words;         // every 4-px destination group reads a source window of <= 8 bytes: word-wise resize kernel
 };
 
-// One CTA of the FAST kernel (fast.cu): a run of cells of one cell row of one level.  Built on the
-// host (fast_build_bands); coordinates with suffix _t are byte offsets inside a tile row, whose byte
-// 16 is level column x_lo (a multiple of 16; the 16 bytes before it are padding so that the word left
-// of the first scored word exists).
-struct FastBand {
-  uint16_t level, row0, vh;   // first scored level row (19 + ci * hCell) and the number of scored rows
-  uint16_t x_lo, copy16;      // level column of tile byte 16; 16-byte units staged per row
-  uint16_t xa_t, xb_t;        // scored pixels of a tile row: [xa_t, xb_t)
-  uint16_t nc;                // cells of this band; cell k covers tile bytes [xa_t + k * wCell, +wCell)
-  uint16_t wlo, ncw;          // first tile word holding a scored pixel, number of such words
-  uint16_t R, rps, nrounds;   // row splits, rows per split, 8-row rounds per split
-  uint16_t tp;                // tile / score pitch in bytes (tp % 64 == 32)
-  uint16_t mag_w;             // (v * mag_w) >> 20 == v / wCell for v < 4096
-  uint16_t mag_ncw;           // (t * mag_ncw) >> 16 == t / ncw for t < 256
-};
-static_assert(sizeof(FastBand) == 32, "FastBand is read as two 16-byte quads");
-
 struct ExtractParams {
   LevelGeom lv[kMaxLevels];
   int nlevels, n_frames;
@@ -84,11 +65,6 @@ struct ExtractParams {
   orbx_keypoint* out_kp;  uint8_t* out_desc;  int out_cap;
   int* out_count;                      // [frame]
   int total_cells;                     // sum over levels of nCols*nRows
-  const FastBand* fast_bands;          // [n_bands] CTAs of the FAST kernel, all levels
-  int n_bands;
-  int fast_tile_bytes, fast_score_bytes, fast_mask_words;  // shared-memory carve-up of the FAST kernel (maxima over bands)
-  const uint8_t* fast_zeros;           // >= fast_score_bytes zero bytes (source of the score tile's TMA clear)
-  int fast_grid;                       // persistent CTAs of the FAST kernel (0: chosen at launch)
   int* pyr_bar;                        // grid-barrier counter of the fused pyramid kernel (null: per-level launches)
   int pyr_max_grid;                    // CTAs of that kernel that can be resident at once
 };
@@ -110,10 +86,6 @@ __device__ __forceinline__ int level_pitch(const ExtractParams& P, int l) {
 int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches);
 int pyramid_fused_max_grid(int device);
 int launch_fast(const ExtractParams& P, cudaStream_t s, int* launches);
-int launch_fast_cells(const ExtractParams& P, cudaStream_t s, int* launches);  // round-1 kernel (one warp per cell), ORBX_FAST_CELLS=1
-// fills `bands` and P.n_bands / P.fast_*_bytes for the level geometry in P (host; fast.cu)
-int fast_build_bands(ExtractParams& P, std::vector<FastBand>& bands);
-int fast_band_grid(const ExtractParams& P, int device);  // resident CTAs of the persistent FAST kernel (0 on error)
 int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches);
 // after_quadtree: kept_count is valid, levels without keypoints are skipped like the reference does
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree = true);

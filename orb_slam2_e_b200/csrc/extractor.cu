@@ -66,9 +66,6 @@ struct orbx_handle {
   Dev<int4> rtab;
   Dev<uint32_t> qcode;
   Dev<int> blur_tiles;
-  Dev<FastBand> fast_bands;
-  Dev<uint8_t> fast_zeros;
-  int fast_grid = 0;
   Dev<orbx_keypoint> out_kp;
   Dev<uint8_t> border_tmp;
   int n_frames = 0;       // frames of the last batch (0: nothing extracted yet)
@@ -236,18 +233,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
         qcode.push_back(code);
       }
     }
-    std::vector<FastBand> bands;
-    if ((rc = fast_build_bands(P, bands))) return rc;
-    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(2 * (nl + 1))) || (rc = H->qcode.reserve(qcode.size())) ||
-        (rc = H->fast_bands.reserve(bands.size())))
-      return rc;
-    ORB_CUDA_TRY(cudaMemcpyAsync(H->fast_bands.p, bands.data(), bands.size() * sizeof(FastBand), cudaMemcpyHostToDevice, H->stream));
-    if ((size_t)P.fast_score_bytes > H->fast_zeros.cap) {
-      if ((rc = H->fast_zeros.reserve((size_t)P.fast_score_bytes))) return rc;
-      ORB_CUDA_TRY(cudaMemsetAsync(H->fast_zeros.p, 0, H->fast_zeros.cap, H->stream));
-    }
-    P.fast_zeros = H->fast_zeros.p;
-    H->fast_grid = fast_band_grid(P, H->cfg.device);
+    if ((rc = H->rtab.reserve(taps.size())) || (rc = H->blur_tiles.reserve(2 * (nl + 1))) || (rc = H->qcode.reserve(qcode.size()))) return rc;
     ORB_CUDA_TRY(cudaMemcpyAsync(H->qcode.p, qcode.data(), qcode.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->rtab.p, taps.data(), taps.size() * sizeof(int4), cudaMemcpyHostToDevice, H->stream));
     ORB_CUDA_TRY(cudaMemcpyAsync(H->blur_tiles.p, blur_tiles.data(), blur_tiles.size() * sizeof(int), cudaMemcpyHostToDevice, H->stream));
@@ -269,7 +255,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
   P.n_frames = n_frames;
   P.pyr = H->pyr.p; P.blur = H->blur.p; P.cand = H->cand.p; P.cand_count = H->cand_count.p;
   P.kept = H->kept.p; P.kept_count = H->kept_count.p; P.qt_b = H->qt_b.p; P.qt_seq = H->qt_seq.p; P.qt_tmp = H->qt_tmp.p;
-  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p; P.qcode = H->qcode.p; P.fast_bands = H->fast_bands.p; P.fast_zeros = H->fast_zeros.p; P.fast_grid = H->fast_grid;
+  P.rtab = H->rtab.p; P.blur_tiles = H->blur_tiles.p; P.qcode = H->qcode.p;
   P.out_kp = H->out_kp.p; P.out_desc = H->out_desc.p; P.out_count = H->out_count.p;
   if (H->pyr_max_grid < 0) H->pyr_max_grid = pyramid_fused_max_grid(H->cfg.device);
   P.pyr_bar = H->pyr_bar.p; P.pyr_max_grid = H->pyr_max_grid;
