@@ -30,6 +30,69 @@ W, H = 640, 480
 SEED = 1000  # seed = 1000*config + index
 
 
+def headline_config():
+    """The `config` object of the JSON line: identical in the GPU arm and in --impl reference, so that the
+    driver's same_config check compares like with like; what differs per arm (frames per step, sharding,
+    L2 note) goes under `run`."""
+    return {"workload": "ORBextractor on synthetic textured 640x480 frames, nFeatures=1000, 8 levels, scale 1.2, FAST 20/7 (TUM mono settings)",
+            "frame": "%dx%d u8" % (W, H), "settings": dict(TUM), "frame_seed": "synth.bench_frames('textured', n, 480, 640, %d + 7*rank, ...)" % SEED}
+
+
+def cpu_cv2_baseline(frames, cfg, seconds=4.0):
+    """Second CPU anchor: the extractor's image stages through Python cv2 (SIMD / IPP
+    OpenCV 4.13): resize + copyMakeBorder per level, FastFeatureDetector per 30-px cell with the iniTh -> minTh
+    fallback, GaussianBlur per level.  No quadtree / orientation / descriptors (cv2 has no equivalent entry
+    points), so this is a LOWER bound of a real-OpenCV ORB-SLAM2 frame time; the per-cell Python loop is in it."""
+    try:
+        import cv2
+    except Exception as e:  # pragma: no cover
+        return {"unavailable": "cv2 import failed: %s" % e}
+    sizes = level_sizes(frames.shape[2], frames.shape[1], cfg["scaleFactor"], cfg["nlevels"])
+    det_ini = cv2.FastFeatureDetector_create(cfg["iniThFAST"], True)
+    det_min = cv2.FastFeatureDetector_create(cfg["minThFAST"], True)
+
+    def one(img):
+        n = 0
+        lvl = img
+        for l, (w, h) in enumerate(sizes):
+            if l:
+                lvl = cv2.resize(lvl, (w, h), interpolation=cv2.INTER_LINEAR)
+            cv2.copyMakeBorder(lvl, 19, 19, 19, 19, cv2.BORDER_REFLECT_101)
+            min_b, max_x, max_y = 16, w - 16, h - 16
+            n_cols, n_rows = (max_x - min_b) // 30, (max_y - min_b) // 30
+            w_cell, h_cell = -(-(max_x - min_b) // n_cols), -(-(max_y - min_b) // n_rows)
+            for i in range(n_rows):
+                y0 = min_b + i * h_cell
+                y1 = min(y0 + h_cell + 6, max_y)
+                if y0 >= max_y - 3:
+                    continue
+                for j in range(n_cols):
+                    x0 = min_b + j * w_cell
+                    x1 = min(x0 + w_cell + 6, max_x)
+                    if x0 >= max_x - 6:
+                        continue
+                    roi = lvl[y0:y1, x0:x1]
+                    k = det_ini.detect(roi)
+                    if not k:
+                        k = det_min.detect(roi)
+                    n += len(k)
+            cv2.GaussianBlur(lvl, (7, 7), 2, 2, cv2.BORDER_REFLECT_101)
+        return n
+
+    out = {"kind": "cv2-%s image stages (pyramid, per-cell FAST, blur); no quadtree/orientation/descriptors" % cv2.__version__}
+    default_threads = cv2.getNumThreads()
+    for label, nt in (("threads_1", 1), ("threads_default", default_threads)):
+        cv2.setNumThreads(nt)
+        one(frames[0])
+        t0, done = time.time(), 0
+        while time.time() - t0 < seconds / 2 and done < len(frames):
+            one(frames[done])
+            done += 1
+        out[label] = {"value": done / (time.time() - t0), "unit": "frames/s", "cv2_threads": nt, "frames": done}
+    cv2.setNumThreads(default_threads)
+    return out
+
+
 def level_sizes(w, h, scale, nlevels):
     s = np.float32(1.0)
     out = []
@@ -151,7 +214,7 @@ def run_reference_arm(args):
         return
     threads = os.cpu_count() or 1
     per_step = 16 * threads  # bounded sample of the workload per step (under a second of wall time)
-    frames = synth.frame_batch("textured", per_step, H, W, SEED, distinct=min(per_step, 16))
+    frames = synth.bench_frames("textured", per_step, H, W, SEED, min(per_step, 64), workers=threads)
     kind, mk, _ = _cpu_libs()
     for _ in range(args.warmup):
         cpu_extract_fps(frames[:threads], TUM, threads, budget_s=60)
@@ -166,10 +229,11 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "frames/s ORB extract (640x480, 1k feats)", "value": fps, "unit": "frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "ORBextractor 640x480 textured frames, nFeatures=1000, 8 levels, scale 1.2, FAST 20/7 (TUM)",
-                   "frames_per_step": per_step},
+        "config": headline_config(),
+        "run": {"frames_per_step": per_step, "arm": "reference's own ORBextractor.cc over the OpenCV-exact scalar shim, -O3 -march=x86-64-v3"},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
                          "sample": "%d frames per step, one extractor object per host thread" % per_step},
+        "cpu_baseline_cv2": cpu_cv2_baseline(frames[:8], TUM),
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -193,10 +257,26 @@ def run_gpu_arm(args):
         cpu = {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind,
                "sample": "%d of the step's frames, one extractor object per host thread (%s ORBextractor over the OpenCV-exact shim)"
                          % (n_done, "reference's own" if kind == "reference" else "restated")}
+    cpu_cv2 = cpu_cv2_baseline(ex["host"][:8], TUM) if (rank == 0 and not args.no_cpu) else None
     ex.pop("host")
     ext = ex.pop("ext")
     ext.close()
     torch.cuda.empty_cache()
+    configs = None
+    if not args.no_configs:
+        from orb_slam2_e_b200 import bench_configs as BC
+        with_cpu = not args.no_cpu
+        configs = {}
+        configs["c3"] = BC.bench_batch_config(B, "c3", BC.HAMLYN, "endoscopy", W, H, args.frames, args.distinct, args, rank, world, local,
+                                              dist, with_cpu, 3000)
+        configs["c5"] = BC.bench_batch_config(B, "c5", BC.BIG, "textured", 3840, 2160, args.c5_frames, min(args.c5_frames, 4), args, rank,
+                                              world, local, dist, with_cpu, 5000)
+        configs["c2"] = BC.bench_stereo(B, args, rank, world, local, dist, with_cpu, args.c2_pairs)
+        if rank == 0:
+            try:
+                configs["c1_single"] = BC.bench_single(B, args, local)
+            except Exception as e:  # the C++ harness is test infrastructure; its absence must not lose the line
+                configs["c1_single"] = {"unavailable": str(e)}
     match = None
     if not args.no_match:
         match = bench_match.bench_match(args, B, rank, world, local, dist, with_cpu=not args.no_cpu)
@@ -207,15 +287,15 @@ def run_gpu_arm(args):
             "metric": "frames/s ORB extract (640x480, 1k feats)", "value": ex["fps"], "unit": "frames/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ex["ms"] / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "ORBextractor 640x480 textured frames, nFeatures=1000, 8 levels, scale 1.2, FAST 20/7 (TUM), "
-                                   "%d frames per GPU per step" % args.frames,
-                       "frames_per_gpu": args.frames, "sharding": "frames block-partitioned over ranks, no collective",
-                       "l2": "inputs larger than L2 (%d MB of frames per step per GPU), no flush" % (args.frames * W * H >> 20),
-                       "keypoints_per_frame": ex["n_kp"], "fast_candidates_per_frame": ex["n_cand"]},
+            "config": headline_config(),
+            "run": {"frames_per_gpu": args.frames, "frames_generated": min(args.distinct, args.frames),
+                    "sharding": "frames block-partitioned over ranks, no collective",
+                    "l2": "inputs larger than L2 (%d MB of frames per step per GPU), no flush" % (args.frames * W * H >> 20),
+                    "keypoints_per_frame": ex["n_kp"], "fast_candidates_per_frame": ex["n_cand"]},
             "e2e": {"value": ex["e2e"], "unit": "frames/s", "h2d_bytes_per_step": ex["h2d"], "d2h_bytes_per_step": ex["d2h"]},
             "gpu_launches": ex["launches"] + (match["gpu_launches"] if match else 0),
             "clocks": ex["clocks"], "roofline": ex["roofline"], "roofline_pipeline": ex["roofline_pipeline"],
-            "cpu_baseline": cpu, "matching": match,
+            "cpu_baseline": cpu, "cpu_baseline_cv2": cpu_cv2, "matching": match, "configs": configs,
         }
         _emit(line)
     if dist is not None:
@@ -240,7 +320,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=1024, help="frames per GPU per step")
-    ap.add_argument("--distinct", type=int, default=32, help="distinct synthetic frames generated (tiled to --frames)")
+    ap.add_argument("--distinct", type=int, default=128, help="frames produced by the generator; the rest of --frames are cyclic shifts of them (all different)")
+    ap.add_argument("--c5-frames", type=int, default=16, help="3840x2160 frames per GPU per step of the configs.c5 leg")
+    ap.add_argument("--c2-pairs", type=int, default=64, help="stereo pairs per GPU per step of the configs.c2 leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the per-config legs (c1_single, c2, c3, c5)")
     ap.add_argument("--db-rows", type=int, default=10_000_000)
     ap.add_argument("--queries", type=int, default=1000)
     ap.add_argument("--cpu-db-rows", type=int, default=200_000)

@@ -16,6 +16,7 @@
 
 #include <cassert>
 #include <cstdlib>
+#include <cstring>
 #include <list>
 #include <stdexcept>
 #include <string>
@@ -155,6 +156,8 @@ class ORBextractor {
   // appended (not in the reference)
   orbx_handle* impl_ = nullptr;
   bool download_pyramid_ = true;
+  int out_cap_ = 0, cap_w_ = 0, cap_h_ = 0;
+  std::vector<uint8_t> desc_stage_;
 
   static void Check(int rc, const char* what) {
     if (rc != ORB_OK) throw std::runtime_error(std::string(what) + ": " + orb_last_error());
@@ -194,28 +197,37 @@ inline void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_ma
   assert(image.type() == CV_8UC1);  // :1058
   const int EDGE = 19;
   int n = 0;
+  Check(orbx_set_pyramid_staging(impl_, download_pyramid_ ? 1 : 0), "ORBextractor::operator()");
+  if (out_cap_ == 0 || image.cols != cap_w_ || image.rows != cap_h_) {
+    Check(orbx_frame_capacity(impl_, image.cols, image.rows, &out_cap_), "ORBextractor::operator()");
+    cap_w_ = image.cols; cap_h_ = image.rows;
+  }
   Check(orbx_extract_batch(impl_, image.data, 1, image.cols, image.rows, (size_t)image.step,
                            (size_t)image.step * (size_t)image.rows, 0),
         "ORBextractor::operator()");
-  Check(orbx_batch_counts(impl_, &n), "ORBextractor::operator()");
-  _keypoints.clear();
+  // one synchronisation for count + keypoints + descriptors (page-locked staging inside the handle)
+  if (desc_stage_.size() < (size_t)out_cap_ * 32) desc_stage_.resize((size_t)out_cap_ * 32);
+  _keypoints.resize((size_t)out_cap_);
+  Check(orbx_read_frame0(impl_, reinterpret_cast<orbx_keypoint*>(_keypoints.data()), desc_stage_.data(), out_cap_, &n),
+        "ORBextractor::operator()");
+  _keypoints.resize((size_t)n);
   if (n == 0) {
     _descriptors.release();  // :1072
   } else {
-    _keypoints.resize((size_t)n);
     _descriptors.create(n, 32, CV_8U);  // :1076
     cv::Mat d = _descriptors.getMat();
     assert((size_t)d.step == 32);
-    int got = 0;
-    Check(orbx_batch_read(impl_, 0, reinterpret_cast<orbx_keypoint*>(_keypoints.data()), d.data, n, &got),
-          "ORBextractor::operator()");
+    memcpy(d.data, desc_stage_.data(), (size_t)n * 32);
   }
   if (download_pyramid_) {
+    // every bordered level arrived in ONE transfer that ran beside the later stages; the Mats are views into the
+    // handle's page-locked staging, valid until this extractor is called again (Frame.cc reads them only in its constructor)
     for (int l = 0; l < nlevels; ++l) {
+      const uint8_t* p00 = nullptr;
       int w = 0, h = 0;
-      Check(orbx_level_size(impl_, l, &w, &h), "ORBextractor pyramid");
-      cv::Mat temp(h + 2 * EDGE, w + 2 * EDGE, CV_8U);
-      Check(orbx_get_level(impl_, 0, l, temp.data, (size_t)temp.step, 1), "ORBextractor pyramid");
+      size_t step = 0;
+      Check(orbx_get_pyramid_host(impl_, l, &p00, &w, &h, &step), "ORBextractor pyramid");
+      cv::Mat temp(h + 2 * EDGE, w + 2 * EDGE, CV_8U, (void*)(p00 - (size_t)EDGE * step - EDGE), step);
       mvImagePyramid[l] = temp(cv::Rect(EDGE, EDGE, w, h));
     }
   }

@@ -116,6 +116,21 @@ int orbx_sync(orbx_handle* h);
  * (src/ORBextractor.cc:1115-1140). */
 int orbx_level_size(const orbx_handle* h, int level, int* w, int* ht);
 int orbx_get_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border);
+/* Single-frame drop-in path (ORBextractor::operator() called by Frame.cc:262-268 on one image).  With
+ * staging enabled, every single-frame orbx_extract_batch also builds all bordered levels with ONE kernel
+ * and copies them with ONE device-to-host transfer into page-locked memory owned by the handle, on a side
+ * stream beside FAST / quadtree / blur / descriptors (the pyramid is the first stage to finish).
+ * orbx_get_pyramid_host waits for that copy and returns, per level, the address of the level's pixel (0,0)
+ * inside its (h+38) x (w+38) bordered buffer and that buffer's row stride -- what the reference's
+ * mvImagePyramid[level] cv::Mat ROI points at (src/ORBextractor.cc:1115-1140).  The memory is rewritten by
+ * the next extract call on the handle and freed by orbx_destroy: a Frame reads mvImagePyramid only while it is
+ * constructed (Frame.cc:534,624-641), i.e. before its extractor is called again. */
+int orbx_set_pyramid_staging(orbx_handle* h, int enabled);
+int orbx_get_pyramid_host(orbx_handle* h, int level, const uint8_t** pixel00, int* w, int* ht, size_t* stride);
+/* Frame 0's results with one synchronisation: count, keypoints and descriptors are copied to page-locked
+ * staging in one go and the first *n_out rows handed to the caller (orbx_batch_counts + orbx_batch_read
+ * synchronise twice). */
+int orbx_read_frame0(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
 
 /* Stage outputs for parity tests: FAST candidates of (frame, level) as (x,y,score) int
  * triples in border-relative coordinates (vToDistributeKeys, src/ORBextractor.cc:789-837);

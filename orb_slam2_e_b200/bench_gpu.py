@@ -63,7 +63,7 @@ def bench_extract(args, B, rank, world, local, dist):
     from orb_slam2_e_b200.extractor import ORBextractor
     L = _lib.load()
     cfg, w, h, n = B.TUM, B.W, B.H, args.frames
-    host = synth.frame_batch("textured", n, h, w, B.SEED + 7 * rank, distinct=min(n, args.distinct))
+    host = synth.bench_frames("textured", n, h, w, B.SEED + 7 * rank, args.distinct, workers=max(1, (os.cpu_count() or 1) // max(world, 1)))
     dev = torch.from_numpy(host).cuda(local)
     ext = ORBextractor(cfg["nfeatures"], cfg["scaleFactor"], cfg["nlevels"], cfg["iniThFAST"], cfg["minThFAST"],
                        device=local, max_width=w, max_height=h, max_batch=n)

@@ -91,5 +91,7 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches);
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree = true);
 int launch_describe(const ExtractParams& P, cudaStream_t s, int* launches);
 int launch_border_copy(const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, cudaStream_t s);
+// all levels of frame f with their 19-px reflect-101 border, level l at dst + off[l] (row pitch w_l + 38)
+int launch_border_all(const ExtractParams& P, int f, const size_t* off, uint8_t* dst, cudaStream_t s);
 
 }  // namespace orbfront

@@ -68,6 +68,15 @@ struct orbx_handle {
   Dev<int> blur_tiles;
   Dev<orbx_keypoint> out_kp;
   Dev<uint8_t> border_tmp;
+  // single-frame drop-in path: all bordered levels staged to page-locked memory on a side stream
+  bool pyr_staging = false, pyr_pending = false;
+  Dev<uint8_t> pyr_stage_dev;
+  uint8_t* pyr_stage_host = nullptr;
+  size_t pyr_stage_cap = 0, pyr_stage_off[kMaxLevels] = {};
+  cudaStream_t s_pyr = nullptr;
+  cudaEvent_t ev_pyr_ready = nullptr, ev_pyr_done = nullptr;
+  uint8_t* out_stage_host = nullptr;  // count + keypoints + descriptors of one frame (orbx_read_frame0)
+  size_t out_stage_cap = 0;
   int n_frames = 0;       // frames of the last batch (0: nothing extracted yet)
   int last_launches = 0;
   std::vector<int> host_counts;
@@ -329,6 +338,11 @@ int orbx_destroy(orbx_handle* H) {
   for (cudaEvent_t e : H->ev_fork) cudaEventDestroy(e);
   for (cudaEvent_t e : H->ev_join) cudaEventDestroy(e);
   if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
+  if (H->s_pyr) { cudaStreamSynchronize(H->s_pyr); cudaStreamDestroy(H->s_pyr); }
+  if (H->ev_pyr_ready) cudaEventDestroy(H->ev_pyr_ready);
+  if (H->ev_pyr_done) cudaEventDestroy(H->ev_pyr_done);
+  if (H->pyr_stage_host) cudaFreeHost(H->pyr_stage_host);
+  if (H->out_stage_host) cudaFreeHost(H->out_stage_host);
   for (cudaEvent_t e : H->ev_up) cudaEventDestroy(e);
   for (cudaEvent_t e : H->ev_done) cudaEventDestroy(e);
   for (cudaEvent_t e : H->stage_ev)
@@ -357,12 +371,43 @@ int orbx_get_level_quota(const orbx_handle* H, int* out) {
 // (1024 frames: 5.59 -> 5.52 ms, 64 frames: 0.545 -> 0.508 ms).  ORBX_FORK_BLUR=0 serialises.
 static int launch_blur_after_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) { return launch_blur(P, s, launches, true); }
 
+// After the pyramid stage of a single frame: bordered levels -> page-locked staging on the side stream.
+static int stage_pyramid(orbx_handle* H, const ExtractParams& Q, cudaStream_t cs, int* launches) {
+  if (!H->pyr_staging || Q.n_frames != 1) return ORB_OK;
+  size_t total = 0;
+  for (int l = 0; l < Q.nlevels; ++l) {
+    H->pyr_stage_off[l] = total;
+    total += align_up<size_t>((size_t)(Q.lv[l].w + 2 * kEdge) * (Q.lv[l].h + 2 * kEdge), 256);
+  }
+  int rc;
+  if ((rc = H->pyr_stage_dev.reserve(total))) return rc;
+  if (total > H->pyr_stage_cap) {
+    if (H->pyr_stage_host) cudaFreeHost(H->pyr_stage_host);
+    H->pyr_stage_host = nullptr; H->pyr_stage_cap = 0;
+    ORB_CUDA_TRY(cudaMallocHost(&H->pyr_stage_host, total));
+    H->pyr_stage_cap = total;
+  }
+  if (!H->s_pyr) {
+    ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_pyr, cudaStreamNonBlocking));
+    ORB_CUDA_TRY(cudaEventCreateWithFlags(&H->ev_pyr_ready, cudaEventDisableTiming));
+    ORB_CUDA_TRY(cudaEventCreateWithFlags(&H->ev_pyr_done, cudaEventDisableTiming));
+  }
+  ORB_CUDA_TRY(cudaEventRecord(H->ev_pyr_ready, cs));
+  ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_pyr, H->ev_pyr_ready, 0));
+  if ((rc = launch_border_all(Q, 0, H->pyr_stage_off, H->pyr_stage_dev.p, H->s_pyr))) return rc;
+  ++*launches;
+  ORB_CUDA_TRY(cudaMemcpyAsync(H->pyr_stage_host, H->pyr_stage_dev.p, total, cudaMemcpyDeviceToHost, H->s_pyr));
+  ORB_CUDA_TRY(cudaEventRecord(H->ev_pyr_done, H->s_pyr));
+  H->pyr_pending = true;
+  return ORB_OK;
+}
+
 static int run_stages(orbx_handle* H, const ExtractParams& Q, cudaStream_t cs, int lane, int* launches) {
   static const bool fork_blur = !(getenv("ORBX_FORK_BLUR") && atoi(getenv("ORBX_FORK_BLUR")) == 0);
   int rc;
   if (!fork_blur) {
-    if ((rc = launch_pyramid(Q, cs, launches)) || (rc = launch_fast(Q, cs, launches)) || (rc = launch_quadtree(Q, cs, launches)) ||
-        (rc = launch_blur(Q, cs, launches)) || (rc = launch_describe(Q, cs, launches)))
+    if ((rc = launch_pyramid(Q, cs, launches)) || (rc = stage_pyramid(H, Q, cs, launches)) || (rc = launch_fast(Q, cs, launches)) ||
+        (rc = launch_quadtree(Q, cs, launches)) || (rc = launch_blur(Q, cs, launches)) || (rc = launch_describe(Q, cs, launches)))
       return rc;
     return ORB_OK;
   }
@@ -376,7 +421,7 @@ static int run_stages(orbx_handle* H, const ExtractParams& Q, cudaStream_t cs, i
     ORB_CUDA_TRY(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
     H->ev_join.push_back(b);
   }
-  if ((rc = launch_pyramid(Q, cs, launches)) || (rc = launch_fast(Q, cs, launches))) return rc;
+  if ((rc = launch_pyramid(Q, cs, launches)) || (rc = stage_pyramid(H, Q, cs, launches)) || (rc = launch_fast(Q, cs, launches))) return rc;
   ORB_CUDA_TRY(cudaEventRecord(H->ev_fork[lane], cs));
   ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_blur[lane], H->ev_fork[lane], 0));
   if ((rc = launch_blur(Q, H->s_blur[lane], launches, /*after_quadtree=*/false))) return rc;
@@ -398,6 +443,10 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
     return set_error(ORB_E_INVALID, "orbx_extract_batch: stride smaller than a row / frame");
   int rc = use_device(H->cfg.device);
   if (rc) return rc;
+  if (H->pyr_pending) {  // the previous frame's staging copy reads the buffers this call rewrites
+    ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_pyr_done, 0));
+    H->pyr_pending = false;
+  }
   const bool alias = memory == 1 && ((uintptr_t)imgs % 16 == 0) && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
   // host frames with 16-byte-multiple strides are uploaded with one linear copy and read in place
   const bool linear = memory == 0 && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
@@ -430,6 +479,7 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
   if (timing) {
     for (int s = 0; s < ORBX_N_STAGES; ++s) {
       if ((rc = stages[s](P, H->stream, &launches))) return rc;
+      if (s == 0 && (rc = stage_pyramid(H, P, H->stream, &launches))) return rc;
       ORB_CUDA_TRY(cudaEventRecord(H->stage_ev[s + 1], H->stream));
     }
   } else if ((rc = run_stages(H, P, H->stream, 0, &launches))) {
@@ -455,6 +505,10 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
     return set_error(ORB_E_INVALID, "orbx_extract_batch_host: stride smaller than a row / frame");
   int rc = use_device(H->cfg.device);
   if (rc) return rc;
+  if (H->pyr_pending) {  // the previous frame's staging copy reads the buffers this call rewrites
+    ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_pyr_done, 0));
+    H->pyr_pending = false;
+  }
   // frames whose rows and frame stride are 16-byte multiples are uploaded as they are (one linear
   // copy per chunk) and read in place; other layouts go through pitched 2-D copies
   const bool linear = stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
@@ -470,6 +524,11 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
   }
   if (H->pinned_counts_cap < n) {
     if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
+  if (H->s_pyr) { cudaStreamSynchronize(H->s_pyr); cudaStreamDestroy(H->s_pyr); }
+  if (H->ev_pyr_ready) cudaEventDestroy(H->ev_pyr_ready);
+  if (H->ev_pyr_done) cudaEventDestroy(H->ev_pyr_done);
+  if (H->pyr_stage_host) cudaFreeHost(H->pyr_stage_host);
+  if (H->out_stage_host) cudaFreeHost(H->out_stage_host);
     H->pinned_counts = nullptr; H->pinned_counts_cap = 0;
     ORB_CUDA_TRY(cudaMallocHost(&H->pinned_counts, sizeof(int) * (size_t)n));
     H->pinned_counts_cap = n;
@@ -722,6 +781,55 @@ int orbx_get_level(orbx_handle* H, int frame, int level, uint8_t* dst, size_t ds
     ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_stride, H->border_tmp.p, (size_t)W, (size_t)W, (size_t)Hh, cudaMemcpyDeviceToHost, H->stream));
   }
   ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+
+int orbx_set_pyramid_staging(orbx_handle* H, int enabled) {
+  if (!H) return set_error(ORB_E_INVALID, "orbx_set_pyramid_staging: null");
+  H->pyr_staging = enabled != 0;
+  return ORB_OK;
+}
+
+int orbx_get_pyramid_host(orbx_handle* H, int level, const uint8_t** pixel00, int* w, int* ht, size_t* stride) {
+  if (!H || !pixel00 || !w || !ht || !stride || level < 0 || level >= H->cfg.nlevels)
+    return set_error(ORB_E_INVALID, "orbx_get_pyramid_host: bad argument");
+  if (!H->pyr_staging || H->n_frames != 1 || !H->pyr_stage_host || !H->ev_pyr_done)
+    return set_error(ORB_E_STATE, "orbx_get_pyramid_host: no single frame extracted with pyramid staging enabled");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaEventSynchronize(H->ev_pyr_done));
+  const LevelGeom& G = H->P.lv[level];
+  const size_t W = (size_t)G.w + 2 * kEdge;
+  *pixel00 = H->pyr_stage_host + H->pyr_stage_off[level] + (size_t)kEdge * W + kEdge;
+  *w = G.w; *ht = G.h; *stride = W;
+  return ORB_OK;
+}
+
+int orbx_read_frame0(orbx_handle* H, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out) {
+  if (!H || !n_out || cap < 0) return set_error(ORB_E_INVALID, "orbx_read_frame0: bad argument");
+  *n_out = 0;
+  if (H->n_frames == 0) return ORB_OK;
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const size_t oc = (size_t)H->P.out_cap, need = 256 + oc * (sizeof(orbx_keypoint) + 32);
+  if (need > H->out_stage_cap) {
+    if (H->out_stage_host) cudaFreeHost(H->out_stage_host);
+    H->out_stage_host = nullptr; H->out_stage_cap = 0;
+    ORB_CUDA_TRY(cudaMallocHost(&H->out_stage_host, need));
+    H->out_stage_cap = need;
+  }
+  uint8_t* st = H->out_stage_host;
+  ORB_CUDA_TRY(cudaMemcpyAsync(st, H->out_count.p, sizeof(int), cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(st + 256, H->out_kp.p, oc * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(st + 256 + oc * sizeof(orbx_keypoint), H->out_desc.p, oc * 32, cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  const int n = *reinterpret_cast<const int*>(st);
+  *n_out = n;
+  if (n > cap) return set_error(ORB_E_CAPACITY, "orbx_read_frame0: %d keypoints, capacity %d", n, cap);
+  if (n == 0) return ORB_OK;
+  if (!kps || !desc) return set_error(ORB_E_INVALID, "orbx_read_frame0: null output");
+  memcpy(kps, st + 256, (size_t)n * sizeof(orbx_keypoint));
+  memcpy(desc, st + 256 + oc * sizeof(orbx_keypoint), (size_t)n * 32);
   return ORB_OK;
 }
 

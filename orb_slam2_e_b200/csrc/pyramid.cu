@@ -372,6 +372,37 @@ __global__ void border_copy_kernel(const uint8_t* __restrict__ src, int w, int h
   dst[(size_t)y * W + x] = src[(size_t)sy * pitch + sx];
 }
 
+// Every level of one frame with its 19-px BORDER_REFLECT_101 frame, back to back in `dst` (level l at
+// off[l], row pitch w_l + 38): the mvImagePyramid a Frame reads (Frame.cc:534,624-641) in ONE launch, so that
+// the single-frame drop-in path needs one device-to-host copy instead of one kernel + copy + sync per level.
+struct BorderOffsets { unsigned long long off[kMaxLevels]; };
+__global__ void border_all_kernel(const __grid_constant__ ExtractParams P, int f, const __grid_constant__ BorderOffsets A, uint8_t* __restrict__ dst) {
+  const int l = blockIdx.y;
+  const LevelGeom& G = P.lv[l];
+  const int W = G.w + 2 * kEdge, H = G.h + 2 * kEdge;
+  const uint8_t* src = level_ptr(P, l, f);
+  const int sp = level_pitch(P, l);
+  uint8_t* out = dst + A.off[l];
+  for (int y = blockIdx.x; y < H; y += gridDim.x) {
+    int sy = y - kEdge;
+    sy = sy < 0 ? -sy : (sy >= G.h ? 2 * G.h - 2 - sy : sy);
+    const uint8_t* row = src + (size_t)sy * sp;
+    for (int x = threadIdx.x; x < W; x += blockDim.x) {
+      int sx = x - kEdge;
+      sx = sx < 0 ? -sx : (sx >= G.w ? 2 * G.w - 2 - sx : sx);
+      out[(size_t)y * W + x] = row[sx];
+    }
+  }
+}
+
+int launch_border_all(const ExtractParams& P, int f, const size_t* off, uint8_t* dst, cudaStream_t s) {
+  BorderOffsets A;
+  for (int l = 0; l < kMaxLevels; ++l) A.off[l] = l < P.nlevels ? off[l] : 0;
+  border_all_kernel<<<dim3(std::min(P.lv[0].h + 2 * kEdge, 148), P.nlevels), 256, 0, s>>>(P, f, A, dst);
+  ORB_LAUNCH_CHECK();
+  return ORB_OK;
+}
+
 int launch_border_copy(const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, cudaStream_t s) {
   dim3 grid(div_up(w + 2 * kEdge, 256), h + 2 * kEdge);
   border_copy_kernel<<<grid, 256, 0, s>>>(src, w, h, pitch, dst);

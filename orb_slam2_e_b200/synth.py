@@ -140,3 +140,29 @@ def reloc_workload(n_db: int, n_q: int, seed: int, n_shards: int = 8):
         db[n_db // 3] = d2
         db[n_db // 3 + 1] = flip_bits(q[k + 1], 3, rng)
     return db, q
+
+
+def _gen_one(job):
+    kind, h, w, seed = job
+    return {"textured": textured_frame, "endoscopy": endoscopy_frame}[kind](h, w, seed)
+
+
+def bench_frames(kind: str, n: int, h: int, w: int, seed: int, generated: int, workers: int = 0) -> np.ndarray:
+    """(n,h,w) u8 batch of n DIFFERENT frames for bench.py: `generated` frames come from the generators
+    above (on `workers` processes), the rest are those frames shifted cyclically by a different
+    (dy, dx) per copy.  A shifted copy has the same statistics but every corner falls into a different
+    FAST cell and quadtree node, so the data-dependent work (survivor rate, empty-cell second pass,
+    quadtree depth) is sampled from n frames, not from `generated` (round-1 review, weak #3)."""
+    m = max(1, min(generated, n))
+    jobs = [(kind, h, w, seed * 1000 + i) for i in range(m)]
+    if workers > 1 and m > 1:
+        import multiprocessing as mp
+        with mp.get_context("spawn").Pool(min(workers, m)) as pool:
+            base = pool.map(_gen_one, jobs, chunksize=max(1, m // (4 * workers)))
+    else:
+        base = [_gen_one(j) for j in jobs]
+    out = np.empty((n, h, w), np.uint8)
+    for i in range(n):
+        k, b = divmod(i, m)
+        out[i] = base[b] if k == 0 else np.roll(base[b], ((k * 37) % h, (k * 101) % w), axis=(0, 1))
+    return out

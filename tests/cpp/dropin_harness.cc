@@ -3,6 +3,8 @@
 // Tracking.cc:1750-1790, LoopClosing.cc:239), behind a small C interface so pytest can compare the
 // results with the oracle.  cv:: types come from oracle/cvshim (headers only -- no oracle code is
 // executed by these entry points), Frame/KeyFrame/MapPoint from tests/cpp/mock.
+#include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -42,6 +44,27 @@ int dropin_extract(void* h, const uint8_t* img, int w, int h_, size_t stride, Dr
     }
     return n;
   } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
+// bench.py configs.c1_single: `iters` calls of ORBextractor::operator() on one frame, the way Tracking drives it
+// (Frame.cc:262-268); returns the median microseconds per call, with or without the mvImagePyramid download
+double dropin_time_extract(void* h, const uint8_t* img, int w, int h_, size_t stride, int iters, int download_pyramid) {
+  ORBextractor* e = (ORBextractor*)h;
+  try {
+    e->SetPyramidDownload(download_pyramid != 0);
+    cv::Mat im(h_, w, CV_8U, (void*)img, stride);
+    std::vector<cv::KeyPoint> k;
+    cv::Mat d;
+    std::vector<double> us;
+    for (int i = 0; i < iters + 3; ++i) {
+      const auto t0 = std::chrono::steady_clock::now();
+      (*e)(im, cv::Mat(), k, d);
+      const auto t1 = std::chrono::steady_clock::now();
+      if (i >= 3) us.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+    }
+    std::sort(us.begin(), us.end());
+    return us.empty() ? -1.0 : us[us.size() / 2];
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1.0; }
 }
 
 int dropin_level_size(void* h, int l, int* w, int* h_) {

@@ -36,6 +36,8 @@ def load():
     L.dropin_create.restype = C.c_void_p
     L.dropin_destroy.argtypes = [C.c_void_p]
     L.dropin_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, u8p, C.c_int]
+    L.dropin_time_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int]
+    L.dropin_time_extract.restype = C.c_double
     L.dropin_level_size.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.dropin_get_level.argtypes = [C.c_void_p, C.c_int, u8p, C.c_size_t, C.c_int]
     L.dropin_scale.argtypes = [C.c_void_p, C.c_int]
@@ -58,6 +60,6 @@ def load():
     return L
 
 
-SYMBOLS = ["dropin_error", "dropin_create", "dropin_destroy", "dropin_extract", "dropin_level_size", "dropin_get_level",
+SYMBOLS = ["dropin_error", "dropin_create", "dropin_destroy", "dropin_extract", "dropin_time_extract", "dropin_level_size", "dropin_get_level",
            "dropin_scale", "dropin_table", "dropin_levels", "dropin_scale_factor", "dropin_distance", "dropin_search_bow",
            "dropin_stereo", "dropin_stereo_frame", "dropin_finish_frame"]
