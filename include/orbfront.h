@@ -338,6 +338,13 @@ int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, i
                         const orbx_keypoint* keys_left, const uint8_t* desc_left, int n_left,
                         const orbx_keypoint* keys_right, const uint8_t* desc_right, int n_right,
                         float mb, float mbf, float* u_right, float* depth);
+/* The same for a batch of pairs held by ONE handle: pair p = frames (2p, 2p+1) of its last batch (left, right).
+ * Keypoints, descriptors and counts are read where the extraction left them on the device, three launches cover
+ * every pair (row search, refinement, median rejection on the device), one transfer brings mvuRight / mvDepth
+ * back: u_right / depth hold cap_per_frame floats per pair (>= orbx_frame_capacity), row i = left keypoint i in
+ * output order, -1 where unmatched and past the left image's keypoint count. */
+int orbx_stereo_matches_batch(orbx_handle* h, int n_pairs, float mb, float mbf, float* u_right, float* depth,
+                              int cap_per_frame);
 
 /* ---- Rest of Frame construction ---------------------------------------------
  * What the Frame constructors do with the extractor's output before tracking sees the frame

@@ -112,6 +112,7 @@ SIGNATURES = {
     "orbm_window_candidates": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _ip]),
     "orbm_search_triangulation": (_i, [_i, C.POINTER(TriKeyFrame), C.POINTER(TriKeyFrame), _vp, _f, _f, _vp, _vp, _i, _i, _vp, _ip]),
     "orbx_stereo_matches": (_i, [_vp, _i, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
+    "orbx_stereo_matches_batch": (_i, [_vp, _i, _f, _f, _vp, _vp, _i]),
     "orbx_undistort_points": (_i, [_i, _vp, _i, C.POINTER(Camera), _vp]),
     "orbx_frame_finish": (_i, [_i, _vp, _i, C.POINTER(Camera), C.POINTER(FrameBounds), _vp, _i, _i, _sz, _i, _vp, _vp, _vp,
                                _vp, _vp, _ip]),

@@ -68,6 +68,15 @@ struct PyramidView {
   int n_levels, device;
 };
 int pyramid_view(orbx_handle* h, int frame, PyramidView* out);  // waits for the handle's stream
+// Device-resident results of an extractor handle's last batch, for kernels that consume them in place
+// (batched stereo matching).  frame f: keypoints kp + f * out_cap, descriptors desc + 32 * f * out_cap, count[f].
+struct BatchView {
+  const orbx_keypoint* kp; const uint8_t* desc; const int* count;
+  int out_cap, n_frames, device;
+  size_t level0_frame_stride, level_frame_stride;  // bytes between consecutive frames of level 0 / of levels >= 1
+  cudaStream_t stream;                             // the handle's stream (work queued there is ordered after the extraction)
+};
+int batch_view(orbx_handle* h, BatchView* out);  // does not wait
 
 #ifdef __CUDACC__
 #define ORB_HD __host__ __device__

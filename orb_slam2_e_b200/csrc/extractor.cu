@@ -547,7 +547,11 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
       chunk_begin.push_back(f0);
     }
   } else {
-    const int size = std::max(32, n / 16);  // measured best with four compute streams (1024 frames: 64; tools/exp_e2e_streams.py)
+    // a sixteenth of the batch, at least 32 frames (measured best for 640x480 with four compute streams: 64 of 1024,
+    // tools/exp_e2e_streams.py), but no more than about 20 MB of frames per chunk, so that a batch of a few large
+    // frames (16 x 3840x2160) is still pipelined: upload of chunk c+1 beside the kernels of chunk c
+    const size_t frame_bytes = std::max<size_t>(1, frame_stride);
+    const int size = std::max(1, std::min(std::max(32, n / 16), (int)std::max<size_t>(1, (20u << 20) / frame_bytes)));
     for (int f0 = 0; f0 < n; f0 += size) chunk_begin.push_back(f0);
   }
   chunk_begin.push_back(n);
@@ -747,6 +751,16 @@ int pyramid_view(orbx_handle* H, int frame, PyramidView* out) {
   out->n_levels = H->cfg.nlevels;
   out->device = H->cfg.device;
   ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+int batch_view(orbx_handle* H, BatchView* out) {
+  if (!H || !out) return set_error(ORB_E_INVALID, "batch_view: bad argument");
+  if (H->n_frames == 0) return set_error(ORB_E_STATE, "nothing extracted yet");
+  const ExtractParams& P = H->P;
+  out->kp = P.out_kp; out->desc = P.out_desc; out->count = P.out_count;
+  out->out_cap = P.out_cap; out->n_frames = H->n_frames; out->device = H->cfg.device;
+  out->level0_frame_stride = P.l0_frame; out->level_frame_stride = P.pyr_frame;
+  out->stream = H->stream;
   return ORB_OK;
 }
 }  // namespace orbfront

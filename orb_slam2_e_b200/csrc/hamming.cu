@@ -318,14 +318,10 @@ __global__ void __launch_bounds__(128) triangulation_kernel(const TriArgs A) {
 // Stereo row-band search (Frame.cc:537-610): one warp per left keypoint; the reference's
 // per-row candidate lists are replaced by evaluating the band predicate directly, which
 // visits the same candidates in the same (increasing iR) order.
-__global__ void __launch_bounds__(128)
-stereo_search_kernel(const orbx_keypoint* __restrict__ L, const uint4* __restrict__ ldesc, int nl,
-                     const orbx_keypoint* __restrict__ R, const uint4* __restrict__ rdesc, int nr,
-                     const float* __restrict__ scale, int n_rows, float min_d, float max_d,
-                     int* __restrict__ best_idx, int* __restrict__ best_dist) {
-  const int lane = threadIdx.x & 31;
-  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (i >= nl) return;
+__device__ __forceinline__ void stereo_search_one(int i, int lane, const orbx_keypoint* __restrict__ L, const uint4* __restrict__ ldesc,
+                                                  const orbx_keypoint* __restrict__ R, const uint4* __restrict__ rdesc, int nr,
+                                                  const float* __restrict__ scale, int n_rows, float min_d, float max_d,
+                                                  int* __restrict__ best_idx, int* __restrict__ best_dist) {
   const orbx_keypoint kl = L[i];
   const int row = (int)kl.y;
   const float minU = kl.x - max_d, maxU = kl.x - min_d;
@@ -359,6 +355,18 @@ stereo_search_kernel(const orbx_keypoint* __restrict__ L, const uint4* __restric
   }
 }
 
+
+__global__ void __launch_bounds__(128)
+stereo_search_kernel(const orbx_keypoint* __restrict__ L, const uint4* __restrict__ ldesc, int nl,
+                     const orbx_keypoint* __restrict__ R, const uint4* __restrict__ rdesc, int nr,
+                     const float* __restrict__ scale, int n_rows, float min_d, float max_d,
+                     int* __restrict__ best_idx, int* __restrict__ best_dist) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= nl) return;
+  stereo_search_one(i, lane, L, ldesc, R, rdesc, nr, scale, n_rows, min_d, max_d, best_idx, best_dist);
+}
+
 // ------------------------------------------------------------------------------------
 // Sub-pixel stereo refinement (Frame.cc:613-684): for a left keypoint whose best right keypoint is
 // closer than thOrbDist, slide an 11x11 patch of the left pyramid level over 11 columns of the
@@ -374,18 +382,19 @@ struct StereoRefineArgs {
   float* u_right; float* depth; int* sad;  // [nl]; sad = -1 where nothing was assigned
 };
 
-__global__ void __launch_bounds__(128) stereo_refine_kernel(const StereoRefineArgs A) {
-  const int lane = threadIdx.x & 31;
-  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (i >= A.nl) return;
+// A = the pair's arrays; off_*: byte offsets of the pair's frames inside the pyramids of A.pl / A.pr (0 for the single-pair call)
+__device__ __forceinline__ void stereo_refine_one(const StereoRefineArgs& A, int i, int lane, const orbx_keypoint* __restrict__ L,
+                                                  const orbx_keypoint* __restrict__ R, const int* __restrict__ best_idx,
+                                                  const int* __restrict__ best_dist, float* __restrict__ u_right, float* __restrict__ depth,
+                                                  int* __restrict__ sad, size_t off_l0, size_t off_l, size_t off_r0, size_t off_r) {
   float out_u = -1.0f, out_z = -1.0f;
   int out_sad = -1;
-  const int bd = A.best_dist[i];
+  const int bd = best_dist[i];
   if (bd >= 0 && bd < A.th_orb) {  // warp-uniform
-    const orbx_keypoint kl = A.L[i];
+    const orbx_keypoint kl = L[i];
     const int oct = kl.octave;
     const float uL = kl.x;
-    const float uR0 = A.R[A.best_idx[i]].x;
+    const float uR0 = R[best_idx[i]].x;
     const float sf = A.pl.inv_scale[oct];
     const float scaleduL = roundf(kl.x * sf), scaledvL = roundf(kl.y * sf), scaleduR0 = roundf(uR0 * sf);
     constexpr int w = 5, Ls = 5;
@@ -397,8 +406,8 @@ __global__ void __launch_bounds__(128) stereo_refine_kernel(const StereoRefineAr
     const bool ok = !(iniu < 0 || endu >= A.pr.w[oct]) && x0 >= 0 && y0 >= 0 && x0 + 2 * w < W && y0 + 2 * w < H && r0 >= 0 &&
                     r0 + 2 * (w + Ls) < A.pr.w[oct] && y0 + 2 * w < A.pr.h[oct];
     if (ok) {
-      const uint8_t* pl = A.pl.px[oct] + (size_t)y0 * A.pl.pitch[oct] + x0;
-      const uint8_t* pr = A.pr.px[oct] + (size_t)y0 * A.pr.pitch[oct] + r0;
+      const uint8_t* pl = A.pl.px[oct] + (oct == 0 ? off_l0 : off_l) + (size_t)y0 * A.pl.pitch[oct] + x0;
+      const uint8_t* pr = A.pr.px[oct] + (oct == 0 ? off_r0 : off_r) + (size_t)y0 * A.pr.pitch[oct] + r0;
       const int cL = pl[(size_t)w * A.pl.pitch[oct] + w];
       int sums[2 * Ls + 1];
 #pragma unroll
@@ -440,7 +449,86 @@ __global__ void __launch_bounds__(128) stereo_refine_kernel(const StereoRefineAr
       }
     }
   }
-  if (lane == 0) { A.u_right[i] = out_u; A.depth[i] = out_z; A.sad[i] = out_sad; }
+  if (lane == 0) { u_right[i] = out_u; depth[i] = out_z; sad[i] = out_sad; }
+}
+
+
+__global__ void __launch_bounds__(128) stereo_refine_kernel(const __grid_constant__ StereoRefineArgs A) {
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= A.nl) return;
+  stereo_refine_one(A, i, lane, A.L, A.R, A.best_idx, A.best_dist, A.u_right, A.depth, A.sad, 0, 0, 0, 0);
+}
+
+// ------------------------------------------------------------------------------------
+// Batched form: pair p = frames (2p, 2p+1) of ONE extractor handle's last batch; keypoints, descriptors and counts are read
+// where the extraction left them on the device (BatchView), grid.y = pair.  Same per-keypoint code as the single-pair kernels.
+struct StereoBatchArgs {
+  BatchView B;
+  StereoRefineArgs A;  // A.pl = A.pr = frame 0's pyramid; per-pair arrays are indexed [pair][out_cap]
+  int* best_idx; int* best_dist;
+  int n_rows;
+};
+
+__global__ void __launch_bounds__(128) stereo_search_batch_kernel(const __grid_constant__ StereoBatchArgs S) {
+  const int lane = threadIdx.x & 31, p = blockIdx.y;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int nl = min(S.B.count[2 * p], S.B.out_cap), nr = min(S.B.count[2 * p + 1], S.B.out_cap);
+  if (i >= nl) return;
+  const size_t fl = (size_t)(2 * p) * S.B.out_cap, fr = fl + S.B.out_cap, o = (size_t)p * S.B.out_cap;
+  stereo_search_one(i, lane, S.B.kp + fl, reinterpret_cast<const uint4*>(S.B.desc) + 2 * fl, S.B.kp + fr,
+                    reinterpret_cast<const uint4*>(S.B.desc) + 2 * fr, nr, S.A.pl.scale, S.n_rows, S.A.min_d, S.A.max_d, S.best_idx + o,
+                    S.best_dist + o);
+}
+
+__global__ void __launch_bounds__(128) stereo_refine_batch_kernel(const __grid_constant__ StereoBatchArgs S) {
+  const int lane = threadIdx.x & 31, p = blockIdx.y;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (i >= S.B.out_cap) return;
+  const size_t fl = (size_t)(2 * p) * S.B.out_cap, fr = fl + S.B.out_cap, o = (size_t)p * S.B.out_cap;
+  if (i >= min(S.B.count[2 * p], S.B.out_cap)) {  // rows past the left image's keypoints: unmatched (Frame.cc:529-530)
+    if (lane == 0) { S.A.u_right[o + i] = -1.0f; S.A.depth[o + i] = -1.0f; S.A.sad[o + i] = -1; }
+    return;
+  }
+  stereo_refine_one(S.A, i, lane, S.B.kp + fl, S.B.kp + fr, S.best_idx + o, S.best_dist + o, S.A.u_right + o, S.A.depth + o, S.A.sad + o,
+                    (size_t)(2 * p) * S.B.level0_frame_stride, (size_t)(2 * p) * S.B.level_frame_stride,
+                    (size_t)(2 * p + 1) * S.B.level0_frame_stride, (size_t)(2 * p + 1) * S.B.level_frame_stride);
+}
+
+// Median rejection (Frame.cc:687-700), one CTA per pair: median = the (n/2)-th smallest patch distance among the n matched
+// keypoints (bisection on the value, 0 <= sad <= 121 * 510 < 2^16), matches at or above 1.5 * 1.4 * median are dropped.
+__global__ void __launch_bounds__(256) stereo_median_batch_kernel(const __grid_constant__ StereoBatchArgs S) {
+  __shared__ int s_cnt;
+  const int p = blockIdx.x, tid = threadIdx.x;
+  const size_t o = (size_t)p * S.B.out_cap;
+  const int nl = min(S.B.count[2 * p], S.B.out_cap);
+  const int* sad = S.A.sad + o;
+  auto count_le = [&](int v) {  // matched keypoints with sad <= v (v = -1 counts nobody)
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    int c = 0;
+    for (int i = tid; i < nl; i += 256) { const int d = sad[i]; c += d >= 0 && d <= v; }
+    for (int s = 16; s > 0; s >>= 1) c += __shfl_xor_sync(0xffffffffu, c, s);
+    if ((tid & 31) == 0 && c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    const int r = s_cnt;
+    __syncthreads();
+    return r;
+  };
+  const int n = count_le(0x7fffffff);
+  if (n == 0) return;  // the reference indexes an empty vector here
+  const int k = n / 2;
+  int lo = 0, hi = 65535;  // smallest v with #(sad <= v) >= k + 1
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (count_le(mid) >= k + 1) hi = mid; else lo = mid + 1;
+  }
+  const float median = (float)lo;
+  const float thDist = 1.5f * 1.4f * median;
+  for (int i = tid; i < nl; i += 256) {
+    const int d = sad[i];
+    if (d >= 0 && !((float)d < thDist)) { S.A.u_right[o + i] = -1.0f; S.A.depth[o + i] = -1.0f; }
+  }
 }
 
 // ------------------------------------------------------------------------------------
@@ -1060,6 +1148,51 @@ int orbx_stereo_matches(orbx_handle* left, int frame_left, orbx_handle* right, i
     if (vDistIdx[i].first < thDist) break;
     u_right[vDistIdx[i].second] = -1;
     depth[vDistIdx[i].second] = -1;
+  }
+  return ORB_OK;
+}
+
+int orbx_stereo_matches_batch(orbx_handle* h, int n_pairs, float mb, float mbf, float* u_right, float* depth, int cap_per_frame) {
+  if (!h || n_pairs < 0 || (n_pairs > 0 && (!u_right || !depth))) return set_error(ORB_E_INVALID, "orbx_stereo_matches_batch: bad argument");
+  if (n_pairs == 0) return ORB_OK;
+  StereoBatchArgs S;
+  int rc;
+  if ((rc = batch_view(h, &S.B))) return rc;
+  if (2 * n_pairs > S.B.n_frames) return set_error(ORB_E_INVALID, "orbx_stereo_matches_batch: %d pairs need %d frames, the last batch had %d", n_pairs, 2 * n_pairs, S.B.n_frames);
+  if (cap_per_frame < S.B.out_cap) return set_error(ORB_E_CAPACITY, "orbx_stereo_matches_batch: cap_per_frame %d < %d", cap_per_frame, S.B.out_cap);
+  if (S.B.out_cap >= (1 << kRowBits)) return set_error(ORB_E_INVALID, "orbx_stereo_matches_batch: too many keypoints per frame");
+  if ((rc = pyramid_view(h, 0, &S.A.pl))) return rc;  // also selects the device
+  S.A.pr = S.A.pl;
+  const size_t slots = (size_t)n_pairs * S.B.out_cap;
+  Layout L;
+  const size_t o_best = L.place(slots * 8), o_sad = L.place(slots * 4), o_res = L.place(slots * 8), o_end = L.bytes;
+  CallScratch* C = nullptr;
+  if ((rc = call_scratch(S.B.device, L.bytes, &C))) return rc;
+  uint8_t* d = C->dev;
+  S.best_idx = (int*)(d + o_best); S.best_dist = S.best_idx + slots;
+  S.n_rows = S.A.pl.h[0];                       // :535
+  S.A.L = S.A.R = nullptr; S.A.nl = 0; S.A.best_idx = S.A.best_dist = nullptr;
+  S.A.min_d = 0; S.A.max_d = mbf / mb; S.A.mbf = mbf;  // :557-559
+  S.A.th_orb = (ORBM_TH_HIGH + ORBM_TH_LOW) / 2;       // :532
+  S.A.u_right = (float*)(d + o_res); S.A.depth = S.A.u_right + slots; S.A.sad = (int*)(d + o_sad);
+  // the handle's stream orders this after the extraction; the per-thread scratch is free because every call that uses it
+  // ends with a synchronisation
+  cudaStream_t st = S.B.stream;
+  const dim3 grid(div_up(S.B.out_cap, 4), n_pairs);
+  stereo_search_batch_kernel<<<grid, 128, 0, st>>>(S);
+  ORB_LAUNCH_CHECK();
+  stereo_refine_batch_kernel<<<grid, 128, 0, st>>>(S);
+  ORB_LAUNCH_CHECK();
+  stereo_median_batch_kernel<<<n_pairs, 256, 0, st>>>(S);
+  ORB_LAUNCH_CHECK();
+  ORB_CUDA_TRY(cudaMemcpyAsync(C->host + o_res, d + o_res, o_end - o_res, cudaMemcpyDeviceToHost, st));
+  ORB_CUDA_TRY(cudaStreamSynchronize(st));
+  const float* ur = reinterpret_cast<const float*>(C->host + o_res);
+  const float* z = ur + slots;
+  for (int p = 0; p < n_pairs; ++p) {
+    memcpy(u_right + (size_t)p * cap_per_frame, ur + (size_t)p * S.B.out_cap, sizeof(float) * (size_t)S.B.out_cap);
+    memcpy(depth + (size_t)p * cap_per_frame, z + (size_t)p * S.B.out_cap, sizeof(float) * (size_t)S.B.out_cap);
+    for (int i = S.B.out_cap; i < cap_per_frame; ++i) u_right[(size_t)p * cap_per_frame + i] = depth[(size_t)p * cap_per_frame + i] = -1.0f;
   }
   return ORB_OK;
 }

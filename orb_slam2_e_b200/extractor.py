@@ -221,3 +221,13 @@ def stereo_matches(left: "ORBextractor", right: "ORBextractor", keys_left, desc_
     check(_lib.load().orbx_stereo_matches(left._h, frame_left, right._h, frame_right, ptr(kl), ptr(dl), len(kl), ptr(kr), ptr(dr),
                                           len(kr), float(mb), float(mbf), ptr(ur), ptr(z)))
     return ur, z
+
+
+def stereo_matches_batch(ext: "ORBextractor", n_pairs: int, mb: float, mbf: float):
+    """Frame::ComputeStereoMatches for pairs (2p, 2p+1) of `ext`'s last batch, read in place on the device
+    (orbx_stereo_matches_batch): returns (mvuRight, mvDepth) as (n_pairs, cap) float arrays, row i = left keypoint i."""
+    cap = ext.out_cap
+    ur = np.zeros((n_pairs, cap), np.float32)
+    z = np.zeros((n_pairs, cap), np.float32)
+    check(_lib.load().orbx_stereo_matches_batch(ext._h, n_pairs, float(mb), float(mbf), ptr(ur), ptr(z), cap))
+    return ur, z
