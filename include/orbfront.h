@@ -196,6 +196,25 @@ int orbm_db_get_stream(orbm_db* db, void** cuda_stream);
 int orbm_merge_top2(const orbm_top2* shards, int n_shards, int nq, float ratio, int th,
                     orbm_top2* out, uint8_t* accept /* may be NULL */);
 
+/* The sharded search as ONE call (BASELINE.json config 4): every member scans its shard, one ncclAllGather of
+ * nq x 16 B per rank exchanges the per-shard results, a device kernel merges them (orbm_merge_top2's rule: the lowest
+ * shard wins ties, i.e. the lowest global row, as ORBmatcher.cc:417-426 scanning rows in order would) and applies
+ * ORBmatcher.cc:429-431, one transfer returns nq x 17 B -- all on the shard's stream, no host synchronisation in between.
+ * Ranks must be ordered by row_base.  NCCL is bound at run time (dlopen libnccl.so.2); ORB_E_STATE if it is absent.
+ *   multi-process (one rank per GPU, e.g. under torchrun or MPI): rank 0 calls orbm_group_unique_id and hands the 128
+ *     bytes to the others by whatever means the application has; every rank calls orbm_group_create on its own shard and
+ *     later orbm_group_search with the same queries; every rank receives the merged answer;
+ *   single process, several GPUs: orbm_group_create_local over one shard per device (ncclCommInitAll). */
+typedef struct orbm_group orbm_group;
+int orbm_group_unique_id(uint8_t* id128 /* 128 bytes out */);
+int orbm_group_create(orbm_db* shard, int rank, int n_ranks, const uint8_t* id128, orbm_group** out);
+int orbm_group_create_local(orbm_db* const* shards, int n_shards, orbm_group** out);
+int orbm_group_search(orbm_group* g, const uint8_t* q /* host, nq x 32 */, int nq, float ratio, int th,
+                      orbm_top2* out /* host, nq */, uint8_t* accept /* host, nq; may be NULL */);
+/* device milliseconds of the last search on the first local shard's stream: its scan, and everything up to the answer's copy */
+int orbm_group_last_ms(orbm_group* g, float* scan_ms, float* total_ms);
+int orbm_group_destroy(orbm_group* g);
+
 /* A DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) flattened to CSR: node ids
  * ascending, off[n_nodes+1], feature indices in insertion order. */
 typedef struct {

@@ -105,6 +105,12 @@ SIGNATURES = {
     "orbm_db_sync": (_i, [_vp]),
     "orbm_db_last_ms": (_i, [_vp, C.POINTER(_f), _ip]),
     "orbm_merge_top2": (_i, [_vp, _i, _i, _f, _i, _vp, _vp]),
+    "orbm_group_unique_id": (_i, [_vp]),
+    "orbm_group_create": (_i, [_vp, _i, _i, _vp, C.POINTER(_vp)]),
+    "orbm_group_create_local": (_i, [_vp, _i, C.POINTER(_vp)]),
+    "orbm_group_search": (_i, [_vp, _vp, _i, _f, _i, _vp, _vp]),
+    "orbm_group_last_ms": (_i, [_vp, C.POINTER(_f), C.POINTER(_f)]),
+    "orbm_group_destroy": (_i, [_vp]),
     "orbm_search_bow": (_i, [_i, _vp, _i, _vp, _i, C.POINTER(FeatVec), C.POINTER(FeatVec), _vp, _vp, _vp, _vp, _f,
                              _i, _i, _vp, _ip]),
     "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),

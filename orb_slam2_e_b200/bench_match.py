@@ -28,20 +28,11 @@ def bench_match(args, B, rank, world, local, dist, with_cpu):
     shard_t[torch.from_numpy(plant_rows).to(shard_t.device)] = torch.from_numpy(plant).to(shard_t.device)
     db = matcher.DescriptorDB(local, row_base=lo)
     db.append_device(shard_t.data_ptr(), rows)
-    q_dev = torch.from_numpy(q_host).cuda(local)
-    out_dev = torch.zeros((Q, 2), dtype=torch.int64, device=f"cuda:{local}")  # orbm_top2 = 16 bytes
-    gathered = torch.zeros((world, Q, 2), dtype=torch.int64, device=f"cuda:{local}")
+    # the whole step behind the C ABI: scan -> ncclAllGather -> device merge + acceptance -> nq x 17 B to the host
+    group = matcher.ShardGroup.from_torch(db) if dist is not None else matcher.ShardGroup.local([db])
 
     def step():
-        db.top2_device(q_dev.data_ptr(), Q, out_dev.data_ptr())
-        db.sync()
-        if dist is not None:
-            dist.all_gather_into_tensor(gathered.view(-1), out_dev.view(-1))
-            res = gathered
-        else:
-            res = out_dev.unsqueeze(0)
-        shards = res.cpu().numpy().view(_lib.TOP2_DTYPE).reshape(world, Q)
-        return reloc.merge_shards(shards, 0.75, 45)
+        return group.search(q_host, 0.75, 45)
 
     for _ in range(max(args.warmup, 1)):
         merged, acc = step()
@@ -51,7 +42,7 @@ def bench_match(args, B, rank, world, local, dist, with_cpu):
     kern_ms = 0.0
     for _ in range(args.steps):
         merged, acc = step()
-        kern_ms += db.last_ms()[0]
+        kern_ms += group.last_ms()[0]
     torch.cuda.synchronize()
     dt = _max_over_ranks(time.perf_counter() - t0, dist, local)
     kern_ms = _max_over_ranks(kern_ms, dist, local) / args.steps
@@ -64,11 +55,36 @@ def bench_match(args, B, rank, world, local, dist, with_cpu):
         "metric": "Hamming Gmatch/s (top-2, ratio 0.75)", "value": gmatch, "unit": "Gmatch/s", "scaling": "strong",
         "kernel_only_gmatch_s_per_gpu": Q * rows / (kern_ms * 1e-3) / 1e9, "ms_per_step": dt / args.steps * 1e3,
         "kernel_ms": kern_ms, "gpu_launches": launches, "accepted": int(acc.sum()),
-        "config": {"workload": "%d queries x %d-row database, %d shard(s), NCCL all-gather merge" % (Q, D, world)},
+        "config": {"workload": "%d queries x %d-row database, %d shard(s), orbm_group_search: scan + ncclAllGather + device merge inside liborbfront.so, "
+                               "host queries in, host answer out" % (Q, D, world)},
         "roofline": {"bound": "popc", "achieved": achieved / 1e12, "peak": popc_peak / 1e12, "unit": "Tpopc/s",
                      "frac": achieved / popc_peak, "peak_source": "measured in this run (orbm_popc_peak)",
                      "ops_per_match": 8},
     }
+    if world > 1:
+        # rank 0 rebuilds every shard (same seeds), scans all D rows on its own GPU and compares with the merged answer
+        ok_n = True
+        if rank == 0:
+            whole = matcher.DescriptorDB(local, row_base=0)
+            for r in range(world):
+                lo_r, hi_r = reloc.shard_range(D, r, world)
+                g_r = torch.Generator(device=f"cuda:{local}")
+                g_r.manual_seed(4000 + r)
+                t_r = torch.randint(0, 256, (hi_r - lo_r, 32), dtype=torch.uint8, device=f"cuda:{local}", generator=g_r)
+                rng_r = np.random.default_rng(99 + r)
+                rows_r = rng_r.integers(0, hi_r - lo_r, size=Q // 2)
+                plant_r = np.stack([synth.flip_bits(q_host[i], int(rng_r.integers(5, 61)), rng_r) for i in range(Q // 2)])
+                t_r[torch.from_numpy(rows_r).to(t_r.device)] = torch.from_numpy(plant_r).to(t_r.device)
+                whole.append_device(t_r.data_ptr(), hi_r - lo_r)
+                del t_r
+            single = whole.top2(q_host)
+            one, acc_one = matcher.merge_top2([single], 0.75, 45)
+            ok_n = bool(np.array_equal(one, merged) and np.array_equal(acc_one, acc))
+            whole.close()
+            torch.cuda.empty_cache()
+        res["parity_n_shards"] = ok_n
+        if not ok_n:
+            raise SystemExit("bench: merged %d-shard answer differs from one scan of the whole database" % world)
     if with_cpu and rank == 0:
         # oracle check + CPU baseline on a bounded slice of this rank's shard
         n_slice = min(rows, args.cpu_db_rows)

@@ -11,7 +11,9 @@
 // traffic is ~nq times below the popc time).  Tensor cores are not used: XOR+POPC is not a
 // multiply-accumulate contraction.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -707,7 +709,9 @@ int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int 
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
   const int qblocks = nq_pad / kQPerCta;
   long long want = std::max(1, (2 * sms) / qblocks);
-  long long rows_per_cta = align_up<long long>(std::max<long long>(div_up<long long>(std::max<int64_t>(db->n, 1), want), 1), kTileRows);
+  // equal shares: the kernel's last tile may be partial, so rows per CTA need not be whole tiles (rounding a 1.25 M-row
+  // shard of the 8-GPU case up to 256-row tiles left 8 of the 296 CTA slots empty and 3 % more rows on the others)
+  long long rows_per_cta = std::max<long long>(div_up<long long>(std::max<int64_t>(db->n, 1), want), 1);
   rows_per_cta = std::min<long long>(rows_per_cta, 1ll << kRowBits);
   const int n_chunks = (int)std::max<long long>(div_up<long long>(db->n, rows_per_cta), 0);
   const uint32_t* dq = nullptr;
@@ -1268,6 +1272,280 @@ int orbm_db_load(orbm_db* db, const char* path, int64_t first, int64_t count) {
   fclose(f);
   if (!ok) return set_error(ORB_E_INVALID, "orbm_db_load: %s is truncated", path);
   return orbm_db_append(db, rows.data(), count, 0);
+}
+
+}  // extern "C"
+
+// ====================================================================================
+// Sharded relocalization search behind the C ABI: every rank (or device) scans its shard, ONE
+// ncclAllGather of nq x 16 B per rank exchanges the per-shard (best1, best2, idx), a device kernel merges them with
+// the rule of orbm_merge_top2 and applies the acceptance test of ORBmatcher.cc:429-431, and one transfer of
+// nq x 17 B brings the answer to the host -- all on the shard's stream with no host synchronisation in between.
+// NCCL is bound at run time (dlopen of the libnccl.so.2 already in the process, e.g. PyTorch's, else the system's),
+// so liborbfront.so neither links it nor needs it for anything else.
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace {
+
+struct NcclApi {
+  void* lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  ncclResult_t (*GetVersion)(int*) = nullptr;
+};
+
+int nccl_api(const NcclApi** out) {
+  static NcclApi api;
+  static int state = 0;  // 0 untried, 1 ok, -1 failed
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  if (state == 0) {
+    // ORBFRONT_NCCL_LIB names a specific library; otherwise the libnccl.so.2 already in the process (PyTorch's, if PyTorch
+    // was loaded first) or the system's
+    const char* names[] = {getenv("ORBFRONT_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char* n : names)
+      if (!api.lib && n && *n) api.lib = dlopen(n, RTLD_NOW | RTLD_LOCAL);
+    state = -1;
+    if (api.lib) {
+      bool ok = true;
+      auto sym = [&](const char* name) { void* p = dlsym(api.lib, name); ok = ok && p; return p; };
+      api.GetUniqueId = (decltype(api.GetUniqueId))sym("ncclGetUniqueId");
+      api.CommInitRank = (decltype(api.CommInitRank))sym("ncclCommInitRank");
+      api.CommInitAll = (decltype(api.CommInitAll))sym("ncclCommInitAll");
+      api.CommDestroy = (decltype(api.CommDestroy))sym("ncclCommDestroy");
+      api.AllGather = (decltype(api.AllGather))sym("ncclAllGather");
+      api.GroupStart = (decltype(api.GroupStart))sym("ncclGroupStart");
+      api.GroupEnd = (decltype(api.GroupEnd))sym("ncclGroupEnd");
+      api.GetErrorString = (decltype(api.GetErrorString))sym("ncclGetErrorString");
+      api.GetVersion = (decltype(api.GetVersion))sym("ncclGetVersion");
+      if (ok) state = 1;
+    }
+  }
+  if (state != 1) return set_error(ORB_E_STATE, "NCCL is not available (dlopen libnccl.so.2: %s)", api.lib ? "symbols missing" : dlerror());
+  *out = &api;
+  return ORB_OK;
+}
+
+#define ORB_NCCL_TRY(api, expr)                                                                               \
+  do {                                                                                                        \
+    ncclResult_t _r = (expr);                                                                                 \
+    if (_r != ncclSuccess)                                                                                    \
+      return set_error(ORB_E_CUDA, "%s failed: %s (%s:%d)", #expr, (api)->GetErrorString(_r), __FILE__, __LINE__); \
+  } while (0)
+
+// shards[s * nq + q], shards in increasing row order -> one result per query + acceptance (orbm_merge_top2 on the device)
+__global__ void merge_top2_kernel(const orbm_top2* __restrict__ shards, int n_shards, int nq, float ratio, int th,
+                                  orbm_top2* __restrict__ out, uint8_t* __restrict__ accept) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  int b1 = 256, b2 = 256;
+  long long idx = -1;
+  for (int s = 0; s < n_shards; ++s) {  // strict <: the lowest shard (= lowest global row) wins ties
+    const orbm_top2 p = shards[(size_t)s * nq + q];
+    if (p.idx >= 0 && p.best1 < b1) { b2 = b1; b1 = p.best1; idx = p.idx; }
+    else if (p.idx >= 0 && p.best1 < b2) b2 = p.best1;
+    if (p.best2 < b2) b2 = p.best2;
+  }
+  orbm_top2 r;
+  r.best1 = b1; r.best2 = b2; r.idx = idx;
+  out[q] = r;
+  accept[q] = (uint8_t)((b1 <= th) && ((float)b1 < __fmul_rn(ratio, (float)b2)));
+}
+
+}  // namespace
+
+struct orbm_group {
+  int n_local = 0, n_ranks = 0, rank0 = 0;  // shards held by this process, ranks of the communicator, rank of shards[0]
+  std::vector<orbm_db*> shards;
+  std::vector<ncclComm_t> comms;
+  std::vector<orbm_top2*> gathered;   // per local shard: [n_ranks][cap_q] on its device
+  std::vector<orbm_top2*> local_out;  // per local shard: [cap_q]
+  std::vector<uint32_t*> dq;          // per local shard: queries
+  orbm_top2* merged = nullptr;        // device of shards[0]
+  uint8_t* accept = nullptr;
+  uint8_t* host = nullptr;            // page-locked: queries in, merged + accept out
+  int cap_q = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;  // shards[0]'s stream: start, scan done, answer on the host
+  bool timed = false;
+};
+
+static int group_reserve(orbm_group* g, int nq) {
+  if (nq <= g->cap_q) return ORB_OK;
+  const int cap = (int)align_up<size_t>((size_t)nq, 256);
+  for (int i = 0; i < g->n_local; ++i) {
+    int rc = use_device(g->shards[i]->device);
+    if (rc) return rc;
+    if (g->gathered[i]) cudaFree(g->gathered[i]);
+    if (g->local_out[i]) cudaFree(g->local_out[i]);
+    if (g->dq[i]) cudaFree(g->dq[i]);
+    g->gathered[i] = nullptr; g->local_out[i] = nullptr; g->dq[i] = nullptr;
+    ORB_CUDA_TRY(cudaMalloc(&g->gathered[i], sizeof(orbm_top2) * (size_t)cap * g->n_ranks));
+    ORB_CUDA_TRY(cudaMalloc(&g->local_out[i], sizeof(orbm_top2) * (size_t)cap));
+    ORB_CUDA_TRY(cudaMalloc(&g->dq[i], 32 * (size_t)cap));
+  }
+  int rc = use_device(g->shards[0]->device);
+  if (rc) return rc;
+  if (g->merged) cudaFree(g->merged);
+  if (g->accept) cudaFree(g->accept);
+  if (g->host) cudaFreeHost(g->host);
+  g->merged = nullptr; g->accept = nullptr; g->host = nullptr;
+  ORB_CUDA_TRY(cudaMalloc(&g->merged, sizeof(orbm_top2) * (size_t)cap));
+  ORB_CUDA_TRY(cudaMalloc(&g->accept, (size_t)cap));
+  ORB_CUDA_TRY(cudaMallocHost(&g->host, (size_t)cap * (32 + sizeof(orbm_top2) + 1)));
+  g->cap_q = cap;
+  return ORB_OK;
+}
+
+static int group_init_common(orbm_group* g) {
+  g->gathered.assign(g->n_local, nullptr);
+  g->local_out.assign(g->n_local, nullptr);
+  g->dq.assign(g->n_local, nullptr);
+  int rc = use_device(g->shards[0]->device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaEventCreate(&g->ev0));
+  ORB_CUDA_TRY(cudaEventCreate(&g->ev1));
+  ORB_CUDA_TRY(cudaEventCreate(&g->ev2));
+  return ORB_OK;
+}
+
+extern "C" {
+
+int orbm_group_unique_id(uint8_t* id128) {
+  if (!id128) return set_error(ORB_E_INVALID, "orbm_group_unique_id: null");
+  const NcclApi* N;
+  int rc = nccl_api(&N);
+  if (rc) return rc;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  ORB_NCCL_TRY(N, N->GetUniqueId(&id));
+  memcpy(id128, &id, 128);
+  return ORB_OK;
+}
+
+int orbm_group_create(orbm_db* shard, int rank, int n_ranks, const uint8_t* id128, orbm_group** out) {
+  if (!shard || !out || !id128 || n_ranks < 1 || rank < 0 || rank >= n_ranks) return set_error(ORB_E_INVALID, "orbm_group_create: bad argument");
+  const NcclApi* N;
+  int rc = nccl_api(&N);
+  if (rc || (rc = use_device(shard->device))) return rc;
+  orbm_group* g = new orbm_group();
+  g->n_local = 1; g->n_ranks = n_ranks; g->rank0 = rank;
+  g->shards.push_back(shard);
+  g->comms.assign(1, nullptr);
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  ncclResult_t r = N->CommInitRank(&g->comms[0], n_ranks, id, rank);
+  if (r != ncclSuccess) { delete g; return set_error(ORB_E_CUDA, "ncclCommInitRank failed: %s", N->GetErrorString(r)); }
+  if ((rc = group_init_common(g))) { orbm_group_destroy(g); return rc; }
+  *out = g;
+  return ORB_OK;
+}
+
+int orbm_group_create_local(orbm_db* const* shards, int n_shards, orbm_group** out) {
+  if (!shards || !out || n_shards < 1) return set_error(ORB_E_INVALID, "orbm_group_create_local: bad argument");
+  const NcclApi* N;
+  int rc = nccl_api(&N);
+  if (rc) return rc;
+  std::vector<int> devs;
+  for (int i = 0; i < n_shards; ++i) {
+    if (!shards[i]) return set_error(ORB_E_INVALID, "orbm_group_create_local: null shard");
+    if (i && shards[i]->row_base < shards[i - 1]->row_base) return set_error(ORB_E_INVALID, "orbm_group_create_local: shards must be ordered by row_base");
+    for (int d : devs)
+      if (d == shards[i]->device) return set_error(ORB_E_INVALID, "orbm_group_create_local: one shard per device (NCCL ranks of one communicator need distinct devices)");
+    devs.push_back(shards[i]->device);
+  }
+  orbm_group* g = new orbm_group();
+  g->n_local = n_shards; g->n_ranks = n_shards; g->rank0 = 0;
+  g->shards.assign(shards, shards + n_shards);
+  g->comms.assign(n_shards, nullptr);
+  ncclResult_t r = N->CommInitAll(g->comms.data(), n_shards, devs.data());
+  if (r != ncclSuccess) { delete g; return set_error(ORB_E_CUDA, "ncclCommInitAll failed: %s", N->GetErrorString(r)); }
+  if ((rc = group_init_common(g))) { orbm_group_destroy(g); return rc; }
+  *out = g;
+  return ORB_OK;
+}
+
+int orbm_group_search(orbm_group* g, const uint8_t* q, int nq, float ratio, int th, orbm_top2* out, uint8_t* accept) {
+  if (!g || nq < 0 || (nq > 0 && (!q || !out))) return set_error(ORB_E_INVALID, "orbm_group_search: bad argument");
+  if (nq == 0) return ORB_OK;
+  const NcclApi* N;
+  int rc = nccl_api(&N);
+  if (rc || (rc = group_reserve(g, nq))) return rc;
+  orbm_db* d0 = g->shards[0];
+  memcpy(g->host, q, (size_t)nq * 32);
+  // queries to every local device, scan of every local shard (device-resident form of orbm_top2_search)
+  for (int i = 0; i < g->n_local; ++i) {
+    orbm_db* db = g->shards[i];
+    if ((rc = use_device(db->device))) return rc;
+    if (i == 0) ORB_CUDA_TRY(cudaEventRecord(g->ev0, db->stream));
+    ORB_CUDA_TRY(cudaMemcpyAsync(g->dq[i], g->host, (size_t)nq * 32, cudaMemcpyHostToDevice, db->stream));
+    if ((rc = orbm_top2_search(db, reinterpret_cast<const uint8_t*>(g->dq[i]), nq, g->local_out[i], 1))) return rc;
+    if (i == 0) ORB_CUDA_TRY(cudaEventRecord(g->ev1, db->stream));
+  }
+  // one all-gather of nq x 16 B per rank, on the shards' streams
+  if (g->n_ranks > 1) {
+    if (g->n_local > 1) ORB_NCCL_TRY(N, N->GroupStart());
+    for (int i = 0; i < g->n_local; ++i) {
+      if ((rc = use_device(g->shards[i]->device))) return rc;
+      ORB_NCCL_TRY(N, N->AllGather(g->local_out[i], g->gathered[i], (size_t)nq * sizeof(orbm_top2), ncclUint8, g->comms[i], g->shards[i]->stream));
+    }
+    if (g->n_local > 1) ORB_NCCL_TRY(N, N->GroupEnd());
+  }
+  if ((rc = use_device(d0->device))) return rc;
+  const orbm_top2* src = g->n_ranks > 1 ? g->gathered[0] : g->local_out[0];
+  merge_top2_kernel<<<div_up(nq, 128), 128, 0, d0->stream>>>(src, g->n_ranks, nq, ratio, th, g->merged, g->accept);
+  ORB_LAUNCH_CHECK();
+  uint8_t* h_out = g->host + (size_t)g->cap_q * 32;
+  uint8_t* h_acc = h_out + (size_t)g->cap_q * sizeof(orbm_top2);
+  ORB_CUDA_TRY(cudaMemcpyAsync(h_out, g->merged, (size_t)nq * sizeof(orbm_top2), cudaMemcpyDeviceToHost, d0->stream));
+  ORB_CUDA_TRY(cudaMemcpyAsync(h_acc, g->accept, (size_t)nq, cudaMemcpyDeviceToHost, d0->stream));
+  ORB_CUDA_TRY(cudaEventRecord(g->ev2, d0->stream));
+  for (int i = g->n_local - 1; i >= 0; --i) {  // the other local devices only have to finish their all-gather
+    if ((rc = use_device(g->shards[i]->device))) return rc;
+    ORB_CUDA_TRY(cudaStreamSynchronize(g->shards[i]->stream));
+  }
+  g->timed = true;
+  memcpy(out, h_out, (size_t)nq * sizeof(orbm_top2));
+  if (accept) memcpy(accept, h_acc, (size_t)nq);
+  return ORB_OK;
+}
+
+int orbm_group_last_ms(orbm_group* g, float* scan_ms, float* total_ms) {
+  if (!g || !g->timed) return set_error(ORB_E_STATE, "orbm_group_last_ms: no search has run");
+  int rc = use_device(g->shards[0]->device);
+  if (rc) return rc;
+  if (scan_ms) ORB_CUDA_TRY(cudaEventElapsedTime(scan_ms, g->ev0, g->ev1));
+  if (total_ms) ORB_CUDA_TRY(cudaEventElapsedTime(total_ms, g->ev0, g->ev2));
+  return ORB_OK;
+}
+
+int orbm_group_destroy(orbm_group* g) {
+  if (!g) return ORB_OK;
+  const NcclApi* N = nullptr;
+  nccl_api(&N);
+  for (int i = 0; i < g->n_local; ++i) {
+    cudaSetDevice(g->shards[i]->device);
+    cudaStreamSynchronize(g->shards[i]->stream);
+    if (i < (int)g->gathered.size() && g->gathered[i]) cudaFree(g->gathered[i]);
+    if (i < (int)g->local_out.size() && g->local_out[i]) cudaFree(g->local_out[i]);
+    if (i < (int)g->dq.size() && g->dq[i]) cudaFree(g->dq[i]);
+    if (N && g->comms[i]) N->CommDestroy(g->comms[i]);
+  }
+  cudaSetDevice(g->shards[0]->device);
+  if (g->merged) cudaFree(g->merged);
+  if (g->accept) cudaFree(g->accept);
+  if (g->host) cudaFreeHost(g->host);
+  if (g->ev0) cudaEventDestroy(g->ev0);
+  if (g->ev1) cudaEventDestroy(g->ev1);
+  if (g->ev2) cudaEventDestroy(g->ev2);
+  delete g;
+  return ORB_OK;
 }
 
 }  // extern "C"

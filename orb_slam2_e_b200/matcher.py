@@ -295,3 +295,78 @@ def popc_peak(device: int = 0) -> float:
     v = C.c_double()
     check(_lib.load().orbm_popc_peak(device, C.byref(v)))
     return v.value
+
+
+class ShardGroup:
+    """The sharded search behind the C ABI (orbm_group_*): scan -> ncclAllGather -> device merge + acceptance ->
+    one small transfer, all inside liborbfront.so.  Build with `from_torch` (one rank per process; the NCCL unique id
+    travels over the existing torch.distributed group) or `local` (one process, one shard per device)."""
+
+    def __init__(self, handle, dbs):
+        self._h, self._dbs = handle, dbs  # keeps the shards alive
+
+    @staticmethod
+    def _nccl_first():
+        """liborbfront.so binds NCCL with dlopen("libnccl.so.2"); PyTorch links its own bundled libnccl.so.2.  Whichever is
+        loaded first serves both (same SONAME), and PyTorch cannot run on an older system NCCL: load PyTorch's first."""
+        try:
+            import torch  # noqa: F401
+        except Exception:
+            pass
+
+    @staticmethod
+    def unique_id() -> np.ndarray:
+        ShardGroup._nccl_first()
+        uid = np.zeros(128, np.uint8)
+        check(_lib.load().orbm_group_unique_id(ptr(uid)))
+        return uid
+
+    @classmethod
+    def create(cls, db: "DescriptorDB", rank: int, world: int, uid: np.ndarray) -> "ShardGroup":
+        cls._nccl_first()
+        h = C.c_void_p()
+        uid = np.ascontiguousarray(uid, np.uint8)
+        check(_lib.load().orbm_group_create(db._h, rank, world, ptr(uid), C.byref(h)))
+        return cls(h, [db])
+
+    @classmethod
+    def from_torch(cls, db: "DescriptorDB", group=None) -> "ShardGroup":
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        dev = f"cuda:{db.device}" if dist.get_backend(group) == "nccl" else "cpu"
+        t = torch.from_numpy(cls.unique_id() if rank == 0 else np.zeros(128, np.uint8)).to(dev)
+        dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        return cls.create(db, rank, world, t.cpu().numpy())
+
+    @classmethod
+    def local(cls, dbs) -> "ShardGroup":
+        cls._nccl_first()
+        h = C.c_void_p()
+        arr = (C.c_void_p * len(dbs))(*[d._h for d in dbs])
+        check(_lib.load().orbm_group_create_local(arr, len(dbs), C.byref(h)))
+        return cls(h, list(dbs))
+
+    def search(self, queries, ratio: float = 0.75, th: int = TH_LOW):
+        q = _desc(queries)
+        out = np.zeros(len(q), TOP2_DTYPE)
+        acc = np.zeros(len(q), np.uint8)
+        check(_lib.load().orbm_group_search(self._h, ptr(q), len(q), float(ratio), int(th), ptr(out), ptr(acc)))
+        return out, acc.astype(bool)
+
+    def last_ms(self):
+        a, b = C.c_float(), C.c_float()
+        check(_lib.load().orbm_group_last_ms(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def close(self):
+        if self._h:
+            _lib.load().orbm_group_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+

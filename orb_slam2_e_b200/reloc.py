@@ -58,6 +58,14 @@ class ShardedDescriptorDB:
         self.shard.append_device(dev_ptr, n)
 
     def search(self, queries, ratio: float = 0.75, th: int = matcher.TH_LOW):
+        """(merged, accept) of the whole database on every rank.  On GPUs the whole step runs inside liborbfront.so
+        (matcher.ShardGroup: scan -> ncclAllGather -> device merge); the torch.distributed + host merge below is the
+        form the CPU (gloo) tests of the exchange use."""
+        import torch.distributed as dist
+        if self.world > 1 and dist.is_initialized() and dist.get_backend(self.group) == "nccl":
+            if getattr(self, "_group", None) is None:
+                self._group = matcher.ShardGroup.from_torch(self.shard, self.group)
+            return self._group.search(queries, ratio, th)
         local = self.shard.top2(queries)
         gathered = exchange_top2(local, self.group, None if self.world == 1 else f"cuda:{self.device}")
         return merge_shards(gathered, ratio, th)
