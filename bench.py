@@ -292,7 +292,11 @@ def run_gpu_arm(args):
                     "sharding": "frames block-partitioned over ranks, no collective",
                     "l2": "inputs larger than L2 (%d MB of frames per step per GPU), no flush" % (args.frames * W * H >> 20),
                     "keypoints_per_frame": ex["n_kp"], "fast_candidates_per_frame": ex["n_cand"]},
-            "e2e": {"value": ex["e2e"], "unit": "frames/s", "h2d_bytes_per_step": ex["h2d"], "d2h_bytes_per_step": ex["d2h"]},
+            "e2e": {"value": ex["e2e"], "unit": "frames/s", "h2d_bytes_per_step": ex["h2d"], "d2h_bytes_per_step": ex["d2h"],
+                    "h2d_ceiling_gbs": ex["h2d_gbs"], "h2d_ceiling_frames_s": ex["h2d_ceiling_fps"],
+                    "frac_of_h2d_ceiling": ex["e2e"] / ex["h2d_ceiling_fps"],
+                    "h2d_ceiling_note": "copy-only probe in this run: the step's frames from the same pinned buffer, no kernels, "
+                                        "all ranks at once, max over ranks (aggregate GB/s)"},
             "gpu_launches": ex["launches"] + (match["gpu_launches"] if match else 0),
             "clocks": ex["clocks"], "roofline": ex["roofline"], "roofline_pipeline": ex["roofline_pipeline"],
             "cpu_baseline": cpu, "cpu_baseline_cv2": cpu_cv2, "matching": match, "configs": configs,

@@ -132,6 +132,10 @@ int orbx_get_pyramid_host(orbx_handle* h, int level, const uint8_t** pixel00, in
  * synchronise twice). */
 int orbx_read_frame0(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
 
+/* The 7x7 sigma-2 Gaussian of `level` (src/ORBextractor.cc:1093-1094), w x h pixels without border: the image
+ * computeOrbDescriptor samples.  For parity tests of the blur stage itself. */
+int orbx_get_blur_level(orbx_handle* h, int frame, int level, uint8_t* dst, size_t dst_stride);
+
 /* Stage outputs for parity tests: FAST candidates of (frame, level) as (x,y,score) int
  * triples in border-relative coordinates (vToDistributeKeys, src/ORBextractor.cc:789-837);
  * order is unspecified (the reference's order is a function of (x,y)). */

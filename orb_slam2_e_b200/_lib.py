@@ -89,6 +89,7 @@ SIGNATURES = {
     "orbx_set_pyramid_staging": (_i, [_vp, _i]),
     "orbx_get_pyramid_host": (_i, [_vp, _i, C.POINTER(_vp), _ip, _ip, C.POINTER(_sz)]),
     "orbx_read_frame0": (_i, [_vp, _vp, _vp, _i, _ip]),
+    "orbx_get_blur_level": (_i, [_vp, _i, _i, _vp, _sz]),
     "orbx_get_candidates": (_i, [_vp, _i, _i, _vp, _i, _ip]),
     "orbx_last_batch_ms": (_i, [_vp, C.POINTER(_f), _ip]),
     "orbx_get_stream": (_i, [_vp, C.POINTER(_vp)]),

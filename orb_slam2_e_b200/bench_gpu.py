@@ -130,6 +130,27 @@ def bench_extract(args, B, rank, world, local, dist):
     _barrier(dist)
     e2e_fps = world * n * args.steps / dt
     assert int(cnt.sum()) == int(counts.sum()), "e2e path returned a different keypoint count"
+
+    # ---- host-feed ceiling: the same frames copied from the same pinned buffer, no kernels, all ranks at once
+    probe = torch.empty_like(dev)
+    cs = torch.cuda.Stream(device=local)
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(cs):
+        probe.copy_(pin_in, non_blocking=True)
+    cs.synchronize()
+    _barrier(dist)
+    reps = 3
+    with torch.cuda.stream(cs):
+        p0.record(cs)
+        for _ in range(reps):
+            probe.copy_(pin_in, non_blocking=True)
+        p1.record(cs)
+    p1.synchronize()
+    h2d_ms = _max_over_ranks(p0.elapsed_time(p1), dist, local) / reps
+    _barrier(dist)
+    h2d_gbs = world * host.nbytes / (h2d_ms * 1e-3) / 1e9
+    h2d_ceiling_fps = world * n / (h2d_ms * 1e-3)
+    del probe
     sampler.stop()
 
     # ---- roofline of the dominant kernel + of the whole pipeline
@@ -153,5 +174,5 @@ def bench_extract(args, B, rank, world, local, dist):
     pipe = b_alg * world * n * args.steps / (ms * 1e-3) / 1e9 / world
     roof_pipe = {"bound": "hbm", "achieved": pipe, "peak": peak, "unit": "GB/s", "frac": pipe / peak,
                  "algorithmic_bytes_per_frame": b_alg, "note": "SURVEY 8d B_alg x frames/s per GPU"}
-    return dict(fps=fps, ms=ms, e2e=e2e_fps, h2d=int(host.nbytes), d2h=int(n * cap * 60 + 4 * n), launches=launches,
+    return dict(h2d_gbs=h2d_gbs, h2d_ceiling_fps=h2d_ceiling_fps, fps=fps, ms=ms, e2e=e2e_fps, h2d=int(host.nbytes), d2h=int(n * cap * 60 + 4 * n), launches=launches,
                 clocks=clocks, roofline=roof, roofline_pipeline=roof_pipe, n_kp=n_kp, n_cand=n_cand, host=host, ext=ext)

@@ -133,6 +133,10 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
   ExtractParams& P = H->P;
   const bool geom_changed = (w != H->w || h != H->h);
   if (geom_changed) {
+    // every early return below leaves P half-built: forget the old size first, so that the next call -- whatever its
+    // size -- rebuilds the geometry instead of running the kernels on it
+    H->w = H->h = 0;
+    H->n_frames = 0;
     memset(&P, 0, sizeof(P));
     P.nlevels = nl;
     P.ini_th = c.ini_th_fast;
@@ -275,6 +279,17 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
 
 // ====================================================================================
 extern "C" {
+
+// max_width / max_height / max_batch of orbx_create, when given, are limits: everything was sized for them up front,
+// and a larger frame or batch would reallocate on the hot path.
+static int check_limits(const orbx_handle* H, int n, int w, int ht) {
+  const orbx_config& c = H->cfg;
+  if (c.max_width > 0 && c.max_height > 0 && (w > c.max_width || ht > c.max_height))
+    return set_error(ORB_E_INVALID, "frame %dx%d exceeds the %dx%d the handle was created for", w, ht, c.max_width, c.max_height);
+  if (c.max_width > 0 && c.max_height > 0 && c.max_batch > 0 && n > c.max_batch)
+    return set_error(ORB_E_INVALID, "batch of %d frames exceeds max_batch %d of orbx_create", n, c.max_batch);
+  return ORB_OK;
+}
 
 // The parameter block of frames [f0, f0 + nf) of the configured batch.
 static ExtractParams frame_range(const ExtractParams& P, int f0, int nf) {
@@ -447,6 +462,7 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
     ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_pyr_done, 0));
     H->pyr_pending = false;
   }
+  if ((rc = check_limits(H, n, w, ht))) return rc;
   const bool alias = memory == 1 && ((uintptr_t)imgs % 16 == 0) && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
   // host frames with 16-byte-multiple strides are uploaded with one linear copy and read in place
   const bool linear = memory == 0 && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
@@ -509,6 +525,7 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
     ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_pyr_done, 0));
     H->pyr_pending = false;
   }
+  if ((rc = check_limits(H, n, w, ht))) return rc;
   // frames whose rows and frame stride are 16-byte multiples are uploaded as they are (one linear
   // copy per chunk) and read in place; other layouts go through pitched 2-D copies
   const bool linear = stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
@@ -844,6 +861,21 @@ int orbx_read_frame0(orbx_handle* H, orbx_keypoint* kps, uint8_t* desc, int cap,
   if (!kps || !desc) return set_error(ORB_E_INVALID, "orbx_read_frame0: null output");
   memcpy(kps, st + 256, (size_t)n * sizeof(orbx_keypoint));
   memcpy(desc, st + 256 + oc * sizeof(orbx_keypoint), (size_t)n * 32);
+  return ORB_OK;
+}
+
+int orbx_get_blur_level(orbx_handle* H, int frame, int level, uint8_t* dst, size_t dst_stride) {
+  if (!H || !dst || level < 0 || level >= H->cfg.nlevels) return set_error(ORB_E_INVALID, "orbx_get_blur_level: bad argument");
+  if (H->n_frames == 0) return set_error(ORB_E_STATE, "orbx_get_blur_level: nothing extracted yet");
+  if (frame < 0 || frame >= H->n_frames) return set_error(ORB_E_INVALID, "orbx_get_blur_level: frame out of range");
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const ExtractParams& P = H->P;
+  const LevelGeom& G = P.lv[level];
+  if (dst_stride < (size_t)G.w) return set_error(ORB_E_INVALID, "orbx_get_blur_level: dst_stride too small");
+  ORB_CUDA_TRY(cudaMemcpy2DAsync(dst, dst_stride, P.blur + (size_t)frame * P.blur_frame + G.off, (size_t)G.pitch, (size_t)G.w, (size_t)G.h,
+                                 cudaMemcpyDeviceToHost, H->stream));
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
   return ORB_OK;
 }
 

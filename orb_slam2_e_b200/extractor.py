@@ -181,6 +181,14 @@ class ORBextractor:
         check(self._L.orbx_get_level(self._h, frame, l, ptr(out), out.strides[0], int(with_border)))
         return out
 
+    def blur_level(self, l: int, frame: int = 0) -> np.ndarray:
+        """7x7 sigma-2 Gaussian of level l as the descriptor stage sees it (ORBextractor.cc:1093-1094)."""
+        w, h = C.c_int(), C.c_int()
+        check(self._L.orbx_level_size(self._h, l, C.byref(w), C.byref(h)))
+        out = np.zeros((h.value, w.value), np.uint8)
+        check(self._L.orbx_get_blur_level(self._h, frame, l, ptr(out), out.strides[0]))
+        return out
+
     @property
     def mvImagePyramid(self):
         """Level images of the last frame as views into their 19-px-bordered buffers, like the

@@ -1,0 +1,70 @@
+"""The blur stage itself (ORBextractor.cc:1093-1094): every blurred level of the CUDA path, pixel for pixel, against the
+oracle's cv::GaussianBlur restatement (orc_blur7, pinned to cv2 4.13 in test_golden.py / test_oracle_prims.py) applied
+to the CUDA path's own pyramid level -- including levels whose width is not a multiple of 4 or 128 (edge lanes of the
+BORDER_REFLECT_101 PRMT selectors), tiles cut by the level's bottom, and both tile heights (batch / few frames).
+Also: a rejected frame size must not leave the handle in a state where the next good frame is processed with a
+half-built geometry (round-1 advisor finding)."""
+import numpy as np
+import pytest
+
+import oracle_lib
+from orb_slam2_e_b200 import synth
+from orb_slam2_e_b200._lib import OrbFrontError
+from orb_slam2_e_b200.extractor import ORBextractor
+
+pytestmark = pytest.mark.gpu
+
+
+def _blur_ref(img):
+    L = oracle_lib.oracle()
+    img = np.ascontiguousarray(img)
+    dst = np.zeros_like(img)
+    L.orc_blur7(img, img.shape[1], img.shape[0], img.strides[0], dst, dst.strides[0])
+    return dst
+
+
+@pytest.mark.parametrize("shape,cfg,batch", [
+    ((480, 640), (1000, 1.2, 8, 20, 7), 1),
+    ((480, 640), (1000, 1.2, 8, 20, 7), 40),     # 56-row tiles (batch path)
+    ((376, 1241), (2000, 1.2, 8, 20, 7), 2),     # odd width: partial last word, right-edge reflection inside a lane
+    ((131, 197), (300, 1.3, 3, 20, 7), 1),       # small levels, widths 197 / 152 / 117
+    ((101, 129), (200, 1.1, 2, 20, 7), 3),       # one pixel past a 128-column tile: a tile that is 1 px wide
+])
+def test_blurred_levels_equal_oracle(shape, cfg, batch):
+    h, w = shape
+    frames = np.stack([synth.textured_frame(h, w, 4200 + i) for i in range(min(batch, 3))])
+    frames = np.ascontiguousarray(np.tile(frames, ((batch + len(frames) - 1) // len(frames), 1, 1))[:batch])
+    ext = ORBextractor(*cfg)
+    ext.extract_batch(frames, read=False)
+    for f in sorted({0, batch - 1}):
+        for l in range(cfg[2]):
+            level = ext.level(l, f)
+            got = ext.blur_level(l, f)
+            want = _blur_ref(level)
+            assert got.shape == want.shape
+            bad = np.argwhere(got != want)
+            assert len(bad) == 0, (f, l, level.shape, bad[:5])
+
+
+def test_rejected_size_does_not_poison_the_handle():
+    cfg = (1000, 1.2, 8, 20, 7)
+    img = synth.textured_frame(480, 640, 77)
+    ext = ORBextractor(*cfg)
+    k0, d0 = ext(img)
+    with pytest.raises(OrbFrontError):
+        ext(synth.textured_frame(40, 40, 1))  # level 0 is too small for the 30-px cell grid
+    k1, d1 = ext(img)
+    assert np.array_equal(k0, k1) and np.array_equal(d0, d1)
+    pk, pd = oracle_lib.PortExtractor(*cfg).extract(img)
+    for name in ("x", "y", "octave", "response", "size"):
+        assert np.array_equal(k1[name], pk[name]), name
+    assert np.array_equal(d1, pd)
+
+
+def test_limits_given_at_creation_are_enforced():
+    ext = ORBextractor(500, 1.2, 4, 20, 7, max_width=320, max_height=240, max_batch=2)
+    ext(synth.textured_frame(240, 320, 3))
+    with pytest.raises(OrbFrontError):
+        ext(synth.textured_frame(480, 640, 3))
+    with pytest.raises(OrbFrontError):
+        ext.extract_batch(np.stack([synth.textured_frame(240, 320, 3)] * 3))
