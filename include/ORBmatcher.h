@@ -79,6 +79,10 @@ class ORBmatcher {
   // Brute force constrained to ORB that belong to the same vocabulary node -- on the GPU.
   int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);
   int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);
+  // Extension (not in the reference): every candidate keyframe of one relocalization against the current frame in ONE
+  // device call -- the loop of src/Tracking.cc:1768-1795.  vvpMapPointMatches[i] and the returned counts equal what
+  // SearchByBoW(vpKFs[i], F, ...) gives; NULL or bad keyframes get an empty result and 0.
+  std::vector<int> SearchByBoW(const std::vector<KeyFrame*>& vpKFs, Frame& F, std::vector<std::vector<MapPoint*> >& vvpMapPointMatches);
 
   int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
                               int windowSize = 10);
@@ -282,6 +286,55 @@ inline int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint
         "ORBmatcher::SearchByBoW");
   for (int f = 0; f < n2 && f < F.N; ++f)
     if (out[f] >= 0) vpMapPointMatches[f] = vpMapPointsKF[out[f]];
+  return nmatches;
+}
+
+inline std::vector<int> ORBmatcher::SearchByBoW(const std::vector<KeyFrame*>& vpKFs, Frame& F,
+                                                std::vector<std::vector<MapPoint*> >& vvpMapPointMatches) {
+  const size_t K = vpKFs.size();
+  vvpMapPointMatches.assign(K, std::vector<MapPoint*>());
+  std::vector<int> nmatches(K, 0);
+  const int n2 = F.mDescriptors.rows;
+  FlatFeatVec fv2(F.mFeatVec);
+  std::vector<uint8_t> t2;
+  std::vector<float> a2 = Angles(F.mvKeys);
+  orbm_bow_side side2 = {Rows(F.mDescriptors, t2), n2, &fv2.c, NULL, a2.data()};
+  // host-side packing per candidate; everything stays alive until the call returns
+  struct Cand { std::vector<MapPoint*> mps; std::vector<uint8_t> valid, tmp; std::vector<float> ang; std::vector<int32_t> out; };
+  std::vector<Cand> c(K);
+  std::vector<FlatFeatVec*> fvs(K, (FlatFeatVec*)NULL);
+  std::vector<orbm_bow_side> side1;
+  std::vector<int32_t*> outs;
+  std::vector<size_t> which;
+  for (size_t i = 0; i < K; ++i) {
+    KeyFrame* pKF = vpKFs[i];
+    if (!pKF || pKF->isBad()) continue;  // Tracking.cc:1771-1772 discards them
+    Cand& ci = c[i];
+    ci.mps = pKF->GetMapPointMatches();
+    const int n1 = pKF->mDescriptors.rows;
+    ci.valid = GoodFlags(ci.mps);
+    ci.valid.resize((size_t)n1, 0);
+    ci.ang = Angles(pKF->mvKeysUn);
+    ci.out.assign((size_t)n2, -1);
+    fvs[i] = new FlatFeatVec(pKF->mFeatVec);
+    orbm_bow_side s1 = {Rows(pKF->mDescriptors, ci.tmp), n1, &fvs[i]->c, ci.valid.data(), ci.ang.data()};
+    side1.push_back(s1);
+    outs.push_back(ci.out.data());
+    which.push_back(i);
+  }
+  std::vector<int> nm(side1.size(), 0);
+  const int rc = side1.empty() ? ORB_OK
+                               : orbm_search_bow_batch(Device(), side1.data(), (int)side1.size(), &side2, mfNNratio,
+                                                       mbCheckOrientation ? 1 : 0, 0, outs.data(), nm.data());
+  for (size_t i = 0; i < K; ++i) delete fvs[i];
+  Check(rc, "ORBmatcher::SearchByBoW (batch)");
+  for (size_t j = 0; j < which.size(); ++j) {
+    const size_t i = which[j];
+    vvpMapPointMatches[i] = std::vector<MapPoint*>(F.N, static_cast<MapPoint*>(NULL));
+    for (int f = 0; f < n2 && f < F.N; ++f)
+      if (c[i].out[f] >= 0) vvpMapPointMatches[i][f] = c[i].mps[c[i].out[f]];
+    nmatches[i] = nm[j];
+  }
   return nmatches;
 }
 

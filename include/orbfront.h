@@ -239,6 +239,23 @@ int orbm_search_bow(int device, const uint8_t* desc1, int n1, const uint8_t* des
                     const uint8_t* valid2, const float* angle1, const float* angle2, float nnratio,
                     int check_orientation, int kf_kf, int32_t* out, int* n_matches);
 
+/* Relocalization and loop detection call SearchByBoW once per candidate keyframe against the same Frame / KeyFrame
+ * (src/Tracking.cc:1768-1795, src/LoopClosing.cc:265).  The batched form takes the K candidates at once: the shared
+ * side 2 is uploaded once, the K searches run as one launch (grid.y = K) with their own claim masks, and the K result
+ * vectors come back in one transfer.  Results equal K orbm_search_bow calls.  side1[p] = candidate p (descriptors,
+ * FeatureVector, MapPoint validity, keypoint angles); side2 = the Frame (valid may be NULL for kf_kf = 0);
+ * out[p] has side2->n entries for kf_kf = 0 and side1[p].n entries for kf_kf = 1; n_matches[p] = the reference's
+ * return value for candidate p.  All pointers are host memory. */
+typedef struct orbm_bow_side {
+  const uint8_t* desc;      /* n x 32 */
+  int32_t n;
+  const orbm_featvec* fv;
+  const uint8_t* valid;     /* n flags: feature has a non-bad MapPoint */
+  const float* angle;       /* n keypoint angles (degrees); may be NULL when check_orientation = 0 */
+} orbm_bow_side;
+int orbm_search_bow_batch(int device, const orbm_bow_side* side1, int k, const orbm_bow_side* side2, float nnratio,
+                          int check_orientation, int kf_kf, int32_t* const* out, int* n_matches);
+
 /* Descriptor part of Frame::ComputeStereoMatches -- src/Frame.cc:527-610: per left keypoint the
  * best right keypoint on its row band (octave within +-1, uR in [uL-max_d, uL-min_d]) with
  * initial bound TH_HIGH.  best_dist = -1 for keypoints the reference skips before the scan.

@@ -36,6 +36,10 @@ class FeatVec(C.Structure):
     _fields_ = [("node", C.c_void_p), ("off", C.c_void_p), ("idx", C.c_void_p), ("n_nodes", C.c_int32)]
 
 
+class BowSide(C.Structure):  # orbm_bow_side
+    _fields_ = [("desc", C.c_void_p), ("n", C.c_int32), ("fv", C.POINTER(FeatVec)), ("valid", C.c_void_p), ("angle", C.c_void_p)]
+
+
 class GridFrame(C.Structure):  # orbm_grid_frame
     _fields_ = [("x", C.c_void_p), ("y", C.c_void_p), ("octave", C.c_void_p), ("u_right", C.c_void_p),
                 ("desc", C.c_void_p), ("n", C.c_int32), ("min_x", C.c_float), ("min_y", C.c_float),
@@ -114,6 +118,7 @@ SIGNATURES = {
     "orbm_group_destroy": (_i, [_vp]),
     "orbm_search_bow": (_i, [_i, _vp, _i, _vp, _i, C.POINTER(FeatVec), C.POINTER(FeatVec), _vp, _vp, _vp, _vp, _f,
                              _i, _i, _vp, _ip]),
+    "orbm_search_bow_batch": (_i, [_i, C.POINTER(BowSide), _i, C.POINTER(BowSide), _f, _i, _i, C.POINTER(_vp), _vp]),
     "orbm_stereo_search": (_i, [_i, _vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i, _f, _f, _vp, _vp]),
     "orbm_window_search": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, C.POINTER(WindowParams), _vp, _ip, _ip]),
     "orbm_window_candidates": (_i, [_i, C.POINTER(GridFrame), _vp, _vp, _i, _vp, _vp, _vp, _vp, _i, _ip]),

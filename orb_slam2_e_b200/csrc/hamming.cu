@@ -192,7 +192,7 @@ struct BowArgs {
   int* n_matches;  // accepted matches (before the orientation filter)
 };
 
-__global__ void __launch_bounds__(128) bow_node_kernel(const BowArgs A) {
+__device__ __forceinline__ void bow_nodes(const BowArgs& A) {
   const int lane = threadIdx.x & 31;
   const int warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), n_warps = gridDim.x * (blockDim.x >> 5);
   int nm = 0;
@@ -238,11 +238,17 @@ __global__ void __launch_bounds__(128) bow_node_kernel(const BowArgs A) {
   }
   if (lane == 0 && nm) atomicAdd(A.n_matches, nm);
 }
+__global__ void __launch_bounds__(128) bow_node_kernel(const __grid_constant__ BowArgs A) { bow_nodes(A); }
+// batched form: problem blockIdx.y of K independent searches (one candidate keyframe each)
+__global__ void __launch_bounds__(128) bow_node_batch_kernel(const BowArgs* __restrict__ args) {
+  const BowArgs A = args[blockIdx.y];
+  if (A.n_pairs > 0) bow_nodes(A);
+}
 
 // ComputeThreeMaxima (ORBmatcher.cc:1802-1843) and the removal of matches outside the three
 // dominant rotation bins (:468-486).  One warp.
-__global__ void __launch_bounds__(32) bow_finish_kernel(const int* __restrict__ hist, int* __restrict__ out,
-                                                        const uint8_t* __restrict__ bin_of, int n_out, int* __restrict__ n_matches) {
+__device__ __forceinline__ void bow_finish(const int* __restrict__ hist, int* __restrict__ out, const uint8_t* __restrict__ bin_of,
+                                           int n_out, int* __restrict__ n_matches) {
   const int lane = threadIdx.x;
   int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
   for (int i = 0; i < ORBM_HISTO_LENGTH; ++i) {
@@ -261,6 +267,14 @@ __global__ void __launch_bounds__(32) bow_finish_kernel(const int* __restrict__ 
   }
   for (int s = 16; s > 0; s >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, s);
   if (lane == 0) *n_matches -= dropped;
+}
+__global__ void __launch_bounds__(32) bow_finish_kernel(const int* __restrict__ hist, int* __restrict__ out,
+                                                        const uint8_t* __restrict__ bin_of, int n_out, int* __restrict__ n_matches) {
+  bow_finish(hist, out, bin_of, n_out, n_matches);
+}
+__global__ void __launch_bounds__(32) bow_finish_batch_kernel(const BowArgs* __restrict__ args) {
+  const BowArgs A = args[blockIdx.x];
+  if (A.n_pairs > 0 && A.check_ori) bow_finish(A.hist, A.out, A.bin_of, A.n_out, A.n_matches);
 }
 
 // ------------------------------------------------------------------------------------
@@ -924,6 +938,143 @@ int orbm_search_bow(int device, const uint8_t* desc1, int n1, const uint8_t* des
   ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
   memcpy(out, h + o_out, (size_t)n_out * 4);
   memcpy(n_matches, h + o_nm, 4);
+  return ORB_OK;
+}
+
+// K independent searches against one shared side 2 (the current Frame; a KeyFrame for kf_kf = 1) in one upload, two launches
+// (grid.y = K) and one download.  Each search has its own claim mask, histogram and output, exactly like K calls of
+// orbm_search_bow -- which a problem falls back to if one of its features sits in two common nodes.
+int orbm_search_bow_batch(int device, const orbm_bow_side* side1, int k, const orbm_bow_side* side2, float nnratio,
+                          int check_orientation, int kf_kf, int32_t* const* out, int* n_matches) {
+  if (k < 0 || !side2 || (k > 0 && (!side1 || !out || !n_matches))) return set_error(ORB_E_INVALID, "orbm_search_bow_batch: bad argument");
+  if (k == 0) return ORB_OK;
+  const int n2 = side2->n;
+  if (n2 < 0 || !side2->fv || (n2 > 0 && !side2->desc) || (check_orientation && n2 > 0 && !side2->angle) || (kf_kf && n2 > 0 && !side2->valid))
+    return set_error(ORB_E_INVALID, "orbm_search_bow_batch: bad side 2");
+  const orbm_featvec* fv2 = side2->fv;
+  const int ni2 = fv2->n_nodes ? fv2->off[fv2->n_nodes] : 0;
+  for (int i = 0; i < ni2; ++i)
+    if (fv2->idx[i] >= (uint32_t)n2) return set_error(ORB_E_INVALID, "orbm_search_bow_batch: feature index out of range");
+  int rc = use_device(device);
+  if (rc) return rc;
+  // ---- pass 1: per problem, the common-node ranges (ordered-map merge, ORBmatcher.cc:381-465) and the layout
+  struct Prob { int n1, ni1, n_out, n_pairs; size_t o_d1, o_pairs, o_i1, o_v1, o_a1, o_claim, o_hist, o_bin, o_out, o_nm; bool serial; };
+  std::vector<Prob> pr((size_t)k);
+  std::vector<std::vector<BowPair> > pairs((size_t)k);
+  Layout L;
+  const size_t o_args = L.place((size_t)k * sizeof(BowArgs));
+  const size_t o_d2 = L.place((size_t)n2 * 32), o_i2 = L.place((size_t)ni2 * 4), o_v2 = L.place(n2), o_a2 = L.place((size_t)n2 * 4);
+  std::vector<uint8_t> seen;
+  for (int p = 0; p < k; ++p) {
+    const orbm_bow_side& s1 = side1[p];
+    Prob& q = pr[p];
+    if (s1.n < 0 || !s1.fv || (!out[p] && (kf_kf ? s1.n : n2) > 0) || (s1.n > 0 && (!s1.desc || !s1.valid)) ||
+        (check_orientation && s1.n > 0 && !s1.angle))
+      return set_error(ORB_E_INVALID, "orbm_search_bow_batch: bad side 1 of problem %d", p);
+    q.n1 = s1.n; q.n_out = kf_kf ? s1.n : n2; q.n_pairs = 0; q.serial = false;
+    q.ni1 = s1.fv->n_nodes ? s1.fv->off[s1.fv->n_nodes] : 0;
+    n_matches[p] = 0;
+    for (int i = 0; i < q.n_out; ++i) out[p][i] = -1;
+    if (q.n1 == 0 || n2 == 0) continue;
+    const orbm_featvec* fv1 = s1.fv;
+    for (int i = 0; i < q.ni1; ++i)
+      if (fv1->idx[i] >= (uint32_t)q.n1) return set_error(ORB_E_INVALID, "orbm_search_bow_batch: feature index out of range");
+    for (int a = 0, b = 0; a < fv1->n_nodes && b < fv2->n_nodes;) {
+      if (fv1->node[a] == fv2->node[b]) {
+        const BowPair bp{fv1->off[a], fv1->off[a + 1] - fv1->off[a], fv2->off[b], fv2->off[b + 1] - fv2->off[b]};
+        if (bp.l2 > 65535) return set_error(ORB_E_INVALID, "orbm_search_bow_batch: node with more than 65535 features");
+        pairs[p].push_back(bp);
+        ++a; ++b;
+      } else if (fv1->node[a] < fv2->node[b]) {
+        a = (int)(std::lower_bound(fv1->node + a, fv1->node + fv1->n_nodes, fv2->node[b]) - fv1->node);
+      } else {
+        b = (int)(std::lower_bound(fv2->node + b, fv2->node + fv2->n_nodes, fv1->node[a]) - fv2->node);
+      }
+    }
+    // nodes run in parallel only if no feature sits in two common nodes (always true for a DBoW2 FeatureVector)
+    for (int side = 0; side < 2 && !q.serial; ++side) {
+      const int n = side ? n2 : q.n1;
+      const uint32_t* idx = side ? fv2->idx : fv1->idx;
+      seen.assign((size_t)n, 0);
+      for (const BowPair& bp : pairs[p]) {
+        const int o = side ? bp.o2 : bp.o1, l = side ? bp.l2 : bp.l1;
+        for (int i = 0; i < l && !q.serial; ++i) {
+          uint8_t& f = seen[idx[o + i]];
+          if (f) q.serial = true;
+          f = 1;
+        }
+      }
+    }
+    if (q.serial || pairs[p].empty()) continue;
+    q.n_pairs = (int)pairs[p].size();
+    q.o_d1 = L.place((size_t)q.n1 * 32); q.o_pairs = L.place((size_t)q.n_pairs * sizeof(BowPair)); q.o_i1 = L.place((size_t)q.ni1 * 4);
+    q.o_v1 = L.place(q.n1); q.o_a1 = L.place((size_t)q.n1 * 4); q.o_claim = L.place(n2); q.o_hist = L.place(ORBM_HISTO_LENGTH * 4);
+    q.o_bin = L.place(q.n_out);
+  }
+  const size_t o_up_end = L.bytes;
+  for (int p = 0; p < k; ++p)
+    if (pr[p].n_pairs) { pr[p].o_out = L.place((size_t)pr[p].n_out * 4); pr[p].o_nm = L.place(4); }
+  const size_t o_end = L.bytes;
+  bool any = false;
+  for (int p = 0; p < k; ++p) any = any || pr[p].n_pairs > 0;
+  if (any) {
+    CallScratch* S = nullptr;
+    if ((rc = call_scratch(device, L.bytes, &S))) return rc;
+    uint8_t *h = S->host, *d = S->dev;
+    memcpy(h + o_d2, side2->desc, (size_t)n2 * 32);
+    memcpy(h + o_i2, fv2->idx, (size_t)ni2 * 4);
+    if (side2->valid) memcpy(h + o_v2, side2->valid, n2);
+    if (check_orientation) memcpy(h + o_a2, side2->angle, (size_t)n2 * 4);
+    BowArgs* args = reinterpret_cast<BowArgs*>(h + o_args);
+    int max_pairs = 0;
+    for (int p = 0; p < k; ++p) {
+      const Prob& q = pr[p];
+      BowArgs& A = args[p];
+      memset(&A, 0, sizeof(A));
+      if (!q.n_pairs) continue;
+      const orbm_bow_side& s1 = side1[p];
+      memcpy(h + q.o_d1, s1.desc, (size_t)q.n1 * 32);
+      memcpy(h + q.o_pairs, pairs[p].data(), (size_t)q.n_pairs * sizeof(BowPair));
+      memcpy(h + q.o_i1, s1.fv->idx, (size_t)q.ni1 * 4);
+      memcpy(h + q.o_v1, s1.valid, q.n1);
+      if (check_orientation) memcpy(h + q.o_a1, s1.angle, (size_t)q.n1 * 4);
+      memset(h + q.o_claim, 0, (size_t)n2);
+      memset(h + q.o_hist, 0, ORBM_HISTO_LENGTH * 4);
+      memset(h + q.o_out, 0xff, (size_t)q.n_out * 4);  // -1
+      memset(h + q.o_nm, 0, 4);
+      A.desc1 = (const uint4*)(d + q.o_d1); A.desc2 = (const uint4*)(d + o_d2);
+      A.pairs = (const BowPair*)(d + q.o_pairs); A.n_pairs = q.n_pairs;
+      A.idx1 = (const uint32_t*)(d + q.o_i1); A.idx2 = (const uint32_t*)(d + o_i2);
+      A.valid1 = d + q.o_v1; A.valid2 = side2->valid ? d + o_v2 : nullptr;
+      A.ang1 = (const float*)(d + q.o_a1); A.ang2 = (const float*)(d + o_a2);
+      A.ratio = nnratio; A.check_ori = check_orientation; A.kf_kf = kf_kf; A.n_out = q.n_out;
+      A.claimed2 = d + q.o_claim; A.out = (int*)(d + q.o_out); A.bin_of = d + q.o_bin;
+      A.hist = (int*)(d + q.o_hist); A.n_matches = (int*)(d + q.o_nm);
+      max_pairs = std::max(max_pairs, q.n_pairs);
+    }
+    // the download block is initialised on the host (-1 / 0), so it is uploaded as well
+    ORB_CUDA_TRY(cudaMemcpyAsync(d, h, o_end, cudaMemcpyHostToDevice, S->stream));
+    bow_node_batch_kernel<<<dim3(div_up(max_pairs, 4), k), 128, 0, S->stream>>>((const BowArgs*)(d + o_args));
+    ORB_LAUNCH_CHECK();
+    if (check_orientation) {
+      bow_finish_batch_kernel<<<k, 32, 0, S->stream>>>((const BowArgs*)(d + o_args));
+      ORB_LAUNCH_CHECK();
+    }
+    ORB_CUDA_TRY(cudaMemcpyAsync(h + o_up_end, d + o_up_end, o_end - o_up_end, cudaMemcpyDeviceToHost, S->stream));
+    ORB_CUDA_TRY(cudaStreamSynchronize(S->stream));
+    for (int p = 0; p < k; ++p)
+      if (pr[p].n_pairs) {
+        memcpy(out[p], h + pr[p].o_out, (size_t)pr[p].n_out * 4);
+        memcpy(&n_matches[p], h + pr[p].o_nm, 4);
+      }
+  }
+  for (int p = 0; p < k; ++p)
+    if (pr[p].serial) {
+      const orbm_bow_side& s1 = side1[p];
+      if ((rc = orbm_search_bow(device, s1.desc, s1.n, side2->desc, n2, s1.fv, fv2, s1.valid, side2->valid, s1.angle, side2->angle, nnratio,
+                                check_orientation, kf_kf, out[p], &n_matches[p])))
+        return rc;
+    }
   return ORB_OK;
 }
 

@@ -108,6 +108,40 @@ class ORBmatcher:
             self.mfNNratio, int(self.mbCheckOrientation), int(kf_kf), ptr(out), C.byref(nm)))
         return nm.value, out
 
+    def SearchByBoWBatch(self, candidates, desc2, featvec2, valid2=None, angles2=None, kf_kf: bool = False):
+        """SearchByBoW of K candidate keyframes against one Frame / KeyFrame in ONE call (Tracking.cc:1768-1795 loops
+        over the candidates; orbm_search_bow_batch).  candidates: list of (desc1, featvec1, valid1, angles1).
+        Returns a list of (nmatches, matches), equal to K SearchByBoW calls."""
+        keep = []
+        d2 = _desc(desc2) if len(desc2) else np.zeros((0, 32), np.uint8)
+        f2 = _FlatFeatVec(featvec2)
+        v2 = None if valid2 is None else np.ascontiguousarray(valid2, np.uint8)
+        a2 = None if angles2 is None else np.ascontiguousarray(angles2, np.float32)
+        if kf_kf and v2 is None:
+            raise ValueError("KF-KF search needs valid2")
+        side2 = _lib.BowSide(ptr(d2).value if len(d2) else None, len(d2), C.pointer(f2.c), None if v2 is None else ptr(v2).value,
+                             None if a2 is None else ptr(a2).value)
+        k = len(candidates)
+        sides = (_lib.BowSide * max(k, 1))()
+        outs, out_ptrs = [], (C.c_void_p * max(k, 1))()
+        for p, (desc1, featvec1, valid1, angles1) in enumerate(candidates):
+            d1 = _desc(desc1) if len(desc1) else np.zeros((0, 32), np.uint8)
+            f1 = _FlatFeatVec(featvec1)
+            v1 = np.ascontiguousarray(valid1, np.uint8)
+            a1 = None if angles1 is None else np.ascontiguousarray(angles1, np.float32)
+            if self.mbCheckOrientation and (a1 is None or a2 is None):
+                raise ValueError("orientation check needs keypoint angles")
+            keep.append((d1, f1, v1, a1))
+            sides[p] = _lib.BowSide(ptr(d1).value if len(d1) else None, len(d1), C.pointer(f1.c), ptr(v1).value if len(v1) else None,
+                                    None if a1 is None else ptr(a1).value)
+            o = np.zeros(len(d1) if kf_kf else len(d2), np.int32)
+            outs.append(o)
+            out_ptrs[p] = ptr(o).value if len(o) else None
+        nm = np.zeros(max(k, 1), np.int32)
+        check(_lib.load().orbm_search_bow_batch(self.device, sides, k, C.byref(side2), self.mfNNratio, int(self.mbCheckOrientation),
+                                                int(kf_kf), out_ptrs, ptr(nm)))
+        return [(int(nm[p]), outs[p]) for p in range(k)]
+
     def StereoSearch(self, kps_left, desc_left, kps_right, desc_right, scale_factors, n_rows, min_d, max_d):
         """Descriptor part of Frame::ComputeStereoMatches (Frame.cc:527-610): (bestIdxR, bestDist)."""
         kl = np.ascontiguousarray(kps_left, _lib.KEYPOINT_DTYPE)

@@ -120,6 +120,54 @@ int dropin_stereo_frame(void* hl, void* hr, const uint8_t* left, const uint8_t* 
   } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
 }
 
+// ORBmatcher::SearchByBoW(vector<KeyFrame*>, Frame&, ...) -- the product's batched extension: K candidate keyframes (arrays
+// of K pointers) against one frame.  out[k] as in orbm_search_bow (kf_kf = 0); a NULL d1[k] stands for a bad keyframe.
+int dropin_search_bow_batch(int K, const uint8_t* const* d1, const int* n1, const uint32_t* const* node1, const int32_t* const* off1,
+                            const uint32_t* const* idx1, const int* nn1, const uint8_t* const* state1, const float* const* a1,
+                            const uint8_t* d2, int n2, const uint32_t* node2, const int32_t* off2, const uint32_t* idx2, int nn2,
+                            const float* a2, float ratio, int check_ori, int32_t* const* out, int32_t* nm) {
+  try {
+    std::vector<std::unique_ptr<MapPoint> > pool;
+    std::vector<std::unique_ptr<KeyFrame> > kfs;
+    std::vector<KeyFrame*> ptrs;
+    auto fill = [](DBoW2::FeatureVector& fv, const uint32_t* node, const int32_t* off, const uint32_t* idx, int n_nodes) {
+      for (int i = 0; i < n_nodes; ++i) fv[node[i]] = std::vector<unsigned int>(idx + off[i], idx + off[i + 1]);
+    };
+    for (int k = 0; k < K; ++k) {
+      kfs.emplace_back(new KeyFrame());
+      KeyFrame& kf = *kfs.back();
+      if (!d1[k]) { kf.mbBad = true; ptrs.push_back(&kf); continue; }
+      kf.mDescriptors = cv::Mat(n1[k], 32, CV_8U, (void*)d1[k], 32);
+      kf.mvKeysUn.resize((size_t)n1[k]);
+      for (int i = 0; i < n1[k]; ++i) kf.mvKeysUn[i].angle = a1[k] ? a1[k][i] : 0.f;
+      kf.mvpMapPoints.assign((size_t)n1[k], static_cast<MapPoint*>(NULL));
+      for (int i = 0; i < n1[k]; ++i)
+        if (state1[k][i]) { pool.emplace_back(new MapPoint(state1[k][i] == 2)); kf.mvpMapPoints[i] = pool.back().get(); }
+      fill(kf.mFeatVec, node1[k], off1[k], idx1[k], nn1[k]);
+      ptrs.push_back(&kf);
+    }
+    Frame F;
+    F.N = n2;
+    F.mDescriptors = cv::Mat(n2, 32, CV_8U, (void*)d2, 32);
+    F.mvKeys.resize((size_t)n2);
+    for (int i = 0; i < n2; ++i) F.mvKeys[i].angle = a2 ? a2[i] : 0.f;
+    fill(F.mFeatVec, node2, off2, idx2, nn2);
+    ORBmatcher matcher(ratio, check_ori != 0);
+    std::vector<std::vector<MapPoint*> > res;
+    const std::vector<int> n = matcher.SearchByBoW(ptrs, F, res);
+    for (int k = 0; k < K; ++k) {
+      nm[k] = n[k];
+      for (int f = 0; f < n2; ++f) {
+        out[k][f] = -1;
+        if (!res[k].empty() && res[k][f])
+          for (int i = 0; i < n1[k]; ++i)
+            if (kfs[k]->mvpMapPoints[i] == res[k][f]) out[k][f] = i;
+      }
+    }
+    return 0;
+  } catch (const std::exception& ex) { g_err = ex.what(); return -1000001; }
+}
+
 int dropin_stereo(const DropKp* kl, const uint8_t* dl, int nl, const DropKp* kr, const uint8_t* dr, int nr, const float* scale,
                   int n_levels, int n_rows, float min_d, float max_d, int32_t* best_idx, int32_t* best_dist) {
   try {

@@ -182,6 +182,8 @@ class KeyFrame : public FrameCommon {
   std::vector<std::vector<std::vector<size_t> > > mGrid;
   std::vector<MapPoint*> mvpMapPoints;
   cv::Mat Tcw;  // 4x4 f32
+  bool mbBad = false;
+  bool isBad() { return mbBad; }  // include/KeyFrame.h:102 (under mMutexConnections in the reference)
 
   KeyFrame() {}
   // KeyFrame.cc:30-65: takes the frame's keypoints, descriptors, grid and bounds

@@ -50,6 +50,9 @@ def load():
     L.dropin_distance.argtypes = [u8p, u8p]
     L.dropin_search_bow.argtypes = [u8p, C.c_int, u8p, C.c_int, u32p, i32p, u32p, C.c_int, u32p, i32p, u32p, C.c_int,
                                     u8p, u8p, f32p, f32p, C.c_float, C.c_int, C.c_int, i32p]
+    pp = C.POINTER(C.c_void_p)
+    L.dropin_search_bow_batch.argtypes = [C.c_int, pp, i32p, pp, pp, pp, i32p, pp, pp, u8p, C.c_int, u32p, i32p, u32p, C.c_int, f32p,
+                                          C.c_float, C.c_int, pp, i32p]
     L.dropin_stereo.argtypes = [C.c_void_p, u8p, C.c_int, C.c_void_p, u8p, C.c_int, f32p, C.c_int, C.c_int, C.c_float,
                                 C.c_float, i32p, i32p]
     L.dropin_stereo_frame.argtypes = [C.c_void_p, C.c_void_p, u8p, u8p, C.c_int, C.c_int, C.c_size_t, C.c_float, C.c_float,
@@ -61,5 +64,5 @@ def load():
 
 
 SYMBOLS = ["dropin_error", "dropin_create", "dropin_destroy", "dropin_extract", "dropin_time_extract", "dropin_level_size", "dropin_get_level",
-           "dropin_scale", "dropin_table", "dropin_levels", "dropin_scale_factor", "dropin_distance", "dropin_search_bow",
+           "dropin_scale", "dropin_table", "dropin_levels", "dropin_scale_factor", "dropin_distance", "dropin_search_bow", "dropin_search_bow_batch",
            "dropin_stereo", "dropin_stereo_frame", "dropin_finish_frame"]

@@ -40,6 +40,37 @@ def bow_case(seed, n1=300, n2=320, n_nodes=40, shared=0.7, dup_frac=0.5, valid_f
     return dict(d1=d1, d2=d2, fv1=fv1, fv2=fv2, v1=v1, v2=v2, a1=ang1, a2=ang2)
 
 
+def bow_candidates(base, k, n1=400, seed=0):
+    """k candidate keyframes for the FRAME of `base` (its side 2): each has planted noisy copies of frame descriptors in
+    the frame feature's vocabulary node with a coherent rotation, plus unrelated features.  Returns bow_case-like dicts
+    sharing d2 / fv2 / v2 / a2 with `base` (the K searches of one relocalization, Tracking.cc:1768-1795)."""
+    node_of = {}
+    for node, lst in base["fv2"].items():
+        for j in lst:
+            node_of[j] = node
+    nodes = sorted(base["fv2"])
+    n2 = len(base["d2"])
+    out = []
+    for c in range(k):
+        rng = np.random.default_rng(seed * 1000 + c)
+        n = n1 + 37 * c
+        d1 = synth.random_descriptors(n, seed * 77 + c)
+        node1 = [nodes[int(x)] for x in rng.integers(0, len(nodes), n)]
+        ang1 = rng.uniform(0, 360, n).astype(np.float32)
+        m = min(n, n2) // 2
+        for i, j in zip(rng.choice(n, m, replace=False), rng.choice(n2, m, replace=False)):
+            d1[i] = synth.flip_bits(base["d2"][j], int(rng.integers(0, 50)), rng)
+            if rng.random() < 0.7:
+                node1[i] = node_of[int(j)]
+            ang1[i] = np.float32((base["a2"][j] + (25.0 if rng.random() < 0.8 else rng.uniform(0, 360)) + rng.normal(0, 3)) % 360)
+        fv1 = {}
+        for i in rng.permutation(n):
+            fv1.setdefault(int(node1[i]), []).append(int(i))
+        v1 = (rng.random(n) < 0.8).astype(np.uint8)
+        out.append(dict(d1=d1, d2=base["d2"], fv1=fv1, fv2=base["fv2"], v1=v1, v2=base["v2"], a1=ang1, a2=base["a2"]))
+    return out
+
+
 def flat_fv(fv):
     nodes = sorted(fv)
     off = np.zeros(len(nodes) + 1, np.int32)

@@ -88,6 +88,42 @@ def test_search_by_bow_through_cpp_class(kf_kf, check_ori):
         assert np.array_equal(got, out)
 
 
+@pytest.mark.parametrize("check_ori", [False, True])
+def test_batched_search_by_bow_through_cpp_class(check_ori):
+    """ORBmatcher::SearchByBoW(vector<KeyFrame*>, Frame&, ...) (the loop of Tracking.cc:1768-1795 as one device call) equals
+    the reference's own SearchByBoW(KeyFrame*, Frame&, ...) run once per candidate (oracle/_ref/libmatchref.so when it
+    travelled with the snapshot, else the restatement), with a bad keyframe among the candidates."""
+    import ctypes as C
+    L = dropin_lib.load()
+    base = mc.bow_case(21, n1=500, n2=700, n_nodes=30)
+    n2, off2, i2 = mc.flat_fv(base["fv2"])
+    cases = mc.bow_candidates(base, 6, n1=350, seed=9)
+    K = len(cases) + 1  # the last candidate is a bad keyframe
+    def states(v):
+        s = v.astype(np.uint8).copy()
+        bad = np.flatnonzero(v == 0)
+        s[bad[::2]] = 2
+        return s
+    arr = lambda xs: (C.c_void_p * K)(*[None if x is None else x.ctypes.data for x in xs])
+    flat = [mc.flat_fv(c["fv1"]) for c in cases]
+    st = [states(c["v1"]) for c in cases]
+    outs = [np.zeros(700, np.int32) for _ in range(K)]
+    nm = np.zeros(K, np.int32)
+    d1 = [np.ascontiguousarray(c["d1"]) for c in cases]
+    a1 = [np.ascontiguousarray(c["a1"], np.float32) for c in cases]
+    rc = L.dropin_search_bow_batch(K, arr(d1 + [None]), np.array([len(x) for x in d1] + [0], np.int32), arr([f[0] for f in flat] + [None]),
+                                   arr([f[1] for f in flat] + [None]), arr([f[2] for f in flat] + [None]),
+                                   np.array([len(f[0]) for f in flat] + [0], np.int32), arr(st + [None]), arr(a1 + [None]),
+                                   base["d2"], 700, n2, off2, i2, len(n2), np.ascontiguousarray(base["a2"], np.float32), 0.75,
+                                   int(check_ori), arr(outs), nm)
+    assert rc == 0, L.dropin_error()
+    for k, c in enumerate(cases):
+        want_nm, want = mc.oracle_bow(oracle(), c, 0.75, check_ori, False)
+        assert nm[k] == want_nm and np.array_equal(outs[k], want), k
+    assert nm[K - 1] == 0 and np.all(outs[K - 1] == -1)
+    assert nm[:-1].sum() > 100
+
+
 def test_stereo_search_through_cpp_class():
     L = dropin_lib.load()
     kl, dl, kr, dr, scale, n_rows = mc.stereo_case(4, nl=1500, nr=1600)

@@ -84,6 +84,31 @@ def test_search_by_bow(kf_kf, check_ori):
         assert nm > 20
 
 
+@pytest.mark.parametrize("kf_kf", [False, True])
+@pytest.mark.parametrize("check_ori", [False, True])
+def test_search_by_bow_batch_equals_sequential_calls(kf_kf, check_ori):
+    """K candidate keyframes against one frame in one call == the oracle's (and orbm_search_bow's) K sequential searches;
+    includes a candidate without features, one without a common node, and one whose list repeats a feature (serial fallback)."""
+    base = mc.bow_case(7, n1=600, n2=640, n_nodes=30)
+    cands, want = [], []
+    for seed, c in enumerate(mc.bow_candidates(base, 8, n1=300, seed=5)):
+        if seed == 5:  # a feature listed under two nodes: nodes are no longer independent
+            k0, k1 = sorted(c["fv1"])[:2]
+            c["fv1"][k1] = list(c["fv1"][k1]) + [c["fv1"][k0][0]]
+        cands.append((c["d1"], c["fv1"], c["v1"], c["a1"]))
+        want.append(mc.oracle_bow(oracle(), c, 0.75, check_ori, kf_kf))
+    cands.append((np.zeros((0, 32), np.uint8), {}, np.zeros(0, np.uint8), np.zeros(0, np.float32)))
+    want.append((0, np.full(0 if kf_kf else 640, -1, np.int32)))
+    cands.append((base["d1"][:5], {10 ** 6: [0, 1, 2]}, np.ones(5, np.uint8), np.zeros(5, np.float32)))
+    want.append((0, np.full(5 if kf_kf else 640, -1, np.int32)))
+    m = matcher.ORBmatcher(0.75, check_ori)
+    got = m.SearchByBoWBatch(cands, base["d2"], base["fv2"], base["v2"] if kf_kf else None, base["a2"], kf_kf=kf_kf)
+    assert len(got) == len(want)
+    for p, ((gnm, gout), (nm, out)) in enumerate(zip(got, want)):
+        assert gnm == nm and np.array_equal(gout, out), p
+    assert sum(nm for nm, _ in want) > 100
+
+
 def test_search_by_bow_empty():
     m = matcher.ORBmatcher(0.75, False)
     d = synth.random_descriptors(10, 1)
