@@ -196,14 +196,32 @@ def cpu_extract_fps(frames, cfg, threads, budget_s=20.0):
 
 
 def cpu_match_rate(db, q, threads):
-    """Gmatch/s of the reference's SWAR DescriptorDistance + top-2 rule on host threads."""
+    """Gmatch/s of the brute-force scan on host threads.  kind "reference": the reference's own
+    ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1848-1864, compiled unmodified into oracle/_ref/libmatchref_fast.so)
+    called on one-row cv::Mat views with the update rule of :417-426; kind "port": the restatement, when that library did
+    not travel with the snapshot."""
+    import ctypes as C
     _, _, ol = _cpu_libs()
-    L = ol.oracle(fast=True)
     d1 = np.zeros(len(q), np.int32); i1 = np.zeros(len(q), np.int64); d2 = np.zeros(len(q), np.int32)
+    path = os.path.join(ROOT, "oracle", "_ref", "libmatchref_fast.so")
+    kind = "port"
+    fn = None
+    if os.path.exists(path):
+        try:
+            R = C.CDLL(path)
+            R.refm_top2_scan_mt.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+            R.refm_top2_scan_mt.restype = None
+            fn = lambda: R.refm_top2_scan_mt(q.ctypes.data, len(q), db.ctypes.data, len(db), d1.ctypes.data, i1.ctypes.data, d2.ctypes.data, threads)
+            kind = "reference"
+        except (OSError, AttributeError):
+            fn = None
+    if fn is None:
+        L = ol.oracle(fast=True)
+        fn = lambda: L.orc_top2_mt(q, len(q), db, len(db), d1, i1, d2, threads)
     t0 = time.time()
-    L.orc_top2_mt(q, len(q), db, len(db), d1, i1, d2, threads)
+    fn()
     dt = time.time() - t0
-    return len(q) * len(db) / dt / 1e9, (d1, d2, i1)
+    return len(q) * len(db) / dt / 1e9, (d1, d2, i1), kind
 
 
 def run_reference_arm(args):
