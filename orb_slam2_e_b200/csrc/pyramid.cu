@@ -114,8 +114,8 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   // past the row's last pixel), so no load leaves the row whatever its pitch
   const int src_w = P.lv[l - 1].w;
   const bool need1 = (first & ~3) + 4 < src_w, need2 = (first & ~3) + 8 < src_w;
-  // The six window words of destination row i+1 are requested before row i is interpolated, and the
-  // row table is read two rows ahead, so a warp always has one destination row of loads in flight
+  // The six window words of destination rows i+1 and i+2 are requested before row i is interpolated, and
+  // the row table is read three rows ahead, so a warp always has two destination rows of loads in flight
   // (ncu, first version of this loop: 13 of 16 resident warps stalled on the row loads).
   struct Win { uint32_t a0, a1, a2, b0, b1, b2; };
   auto request = [&](const int4& t, Win& w) {
@@ -135,14 +135,16 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   };
   const int rows = min(kResizeStrip, D.h - y0), dpitch = D.pitch;
   const int4* ytab = P.rtab + D.ytab + y0;
-  int4 t_cur = __ldg(ytab), t_nxt = __ldg(ytab + min(1, rows - 1));
-  Win w_cur;
+  // two destination rows of loads in flight, row table read three rows ahead
+  int4 t_cur = __ldg(ytab), t_n1 = __ldg(ytab + min(1, rows - 1)), t_n2 = __ldg(ytab + min(2, rows - 1));
+  Win w_cur, w_n1;
   request(t_cur, w_cur);
-#pragma unroll 2
+  request(t_n1, w_n1);
+#pragma unroll 3
   for (int i = 0; i < rows; ++i) {
-    Win w_nxt;
-    request(t_nxt, w_nxt);  // the last iteration re-requests the last row (cached)
-    const int4 t_nn = __ldg(ytab + min(i + 2, rows - 1));
+    Win w_n2;
+    request(t_n2, w_n2);  // the last iterations re-request the last row (cached)
+    const int4 t_n3 = __ldg(ytab + min(i + 3, rows - 1));
     uint32_t hA[4], hB[4], u[4];
     hrow(w_cur.a0, w_cur.a1, w_cur.a2, hA);
     hrow(w_cur.b0, w_cur.b1, w_cur.b2, hB);
@@ -152,9 +154,11 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
     for (int k = 0; k < 4; ++k) u[k] = (__umulhi(B1, hB[k]) + (__umulhi(B0, hA[k]) + 2u)) << 6;  // result byte = bits 8..15
     *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(u[0], u[1], 0x0051), __byte_perm(u[2], u[3], 0x0051), 0x5410);
     dst += dpitch;  // pitch padding absorbs the tail
-    w_cur = w_nxt;
-    t_cur = t_nxt;
-    t_nxt = t_nn;
+    w_cur = w_n1;
+    w_n1 = w_n2;
+    t_cur = t_n1;
+    t_n1 = t_n2;
+    t_n2 = t_n3;
   }
 }
 
