@@ -190,6 +190,22 @@ int orbm_db_destroy(orbm_db* db);
  * (copies inside the call); memory = 1: both are device buffers on db's device and the call is
  * asynchronous on the db's stream (orbm_db_sync to wait). */
 int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int memory);
+
+/* The same search with no allocation anywhere in the call, for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  It has no counterpart in the reference.
+ * rows (n_rows x 32 bytes, 16-byte aligned), q (nq x 32
+ * bytes) and out (nq results) are DEVICE buffers on `device` that the caller owns; row_base is added to the
+ * returned indices; the two kernels are launched on cuda_stream (NULL = the default stream) and the call
+ * returns without waiting.  The per-chunk partial results go to a static device array of 304 x 1024 8-byte
+ * entries (2 432 KiB, held by every GPU that loads the library until exit): a call needs
+ * ceil(nq / 1024) * 1024 x (row chunks) entries, which on a 148-SM GPU admits any nq <= 311 296 against up to
+ * 2^20 x floor(296 / ceil(nq / 1024)) rows; larger calls are rejected with ORB_E_INVALID and a message that
+ * states both numbers.  Every call on a device shares that array (it keeps the last call's contents; nothing
+ * in it has to start at zero, each entry that is read is written earlier in the same call), so two calls that
+ * overlap on the GPU -- different streams, or different threads -- race: serialise them.  Results are those
+ * of orbm_top2_search on the same rows and queries. */
+int orbm_top2_search_noalloc(int device, const uint8_t* rows, int64_t n_rows, int64_t row_base, const uint8_t* q,
+                             int nq, orbm_top2* out, void* cuda_stream);
 int orbm_db_sync(orbm_db* db);
 int orbm_db_last_ms(orbm_db* db, float* ms, int* launches);
 int orbm_db_get_stream(orbm_db* db, void** cuda_stream);

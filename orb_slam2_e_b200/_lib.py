@@ -107,6 +107,7 @@ SIGNATURES = {
     "orbm_db_size": (_i, [_vp, C.POINTER(_i64)]),
     "orbm_db_destroy": (_i, [_vp]),
     "orbm_top2_search": (_i, [_vp, _vp, _i, _vp, _i]),
+    "orbm_top2_search_noalloc": (_i, [_i, _vp, _i64, _i64, _vp, _i, _vp, _vp]),
     "orbm_db_sync": (_i, [_vp]),
     "orbm_db_last_ms": (_i, [_vp, C.POINTER(_f), _ip]),
     "orbm_merge_top2": (_i, [_vp, _i, _i, _f, _i, _vp, _vp]),

@@ -786,6 +786,84 @@ int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int 
   return ORB_OK;
 }
 
+}  // extern "C"
+
+// ---- allocation-free top-2 search ---------------------------------------------------------------------------
+// The per-CTA partial results of the scan live in a file-scope device array instead of a cudaMalloc'd buffer.
+// 304 x 1024 entries of 8 bytes = 2 432 KiB on every GPU that loads the library, until exit: two CTAs per SM
+// (296 on a B200) x the 1024 queries of a CTA, rounded up -- the most top2_scan_kernel's grid produces here.
+namespace {
+constexpr size_t kNoAllocEntries = 304u * 1024u;
+static __device__ __align__(256) uint2 g_noalloc_partial[kNoAllocEntries];
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+uint2* g_noalloc_ptr[kNoAllocMaxDevices];  // device address of g_noalloc_partial per device (the host-side name is not one)
+int g_noalloc_sms[kNoAllocMaxDevices];
+
+// once per device, with that device current
+int noalloc_setup(int device, uint2** ptr, int* sms) {
+  if (device < 0 || device >= kNoAllocMaxDevices) return set_error(ORB_E_INVALID, "orbm_top2_search_noalloc: device %d out of range", device);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_partial);
+    if (e != cudaSuccess || !p) {
+      return set_error(ORB_E_CUDA, "orbm_top2_search_noalloc: cudaGetSymbolAddress failed on device %d: %s", device,
+                       cudaGetErrorString(e));
+    }
+    int n = 0;
+    e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess || n < 1) return set_error(ORB_E_CUDA, "orbm_top2_search_noalloc: SM count: %s", cudaGetErrorString(e));
+    g_noalloc_sms[device] = n;
+    g_noalloc_ptr[device] = static_cast<uint2*>(p);
+  }
+  *ptr = g_noalloc_ptr[device];
+  *sms = g_noalloc_sms[device];
+  return ORB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int orbm_top2_search_noalloc(int device, const uint8_t* rows, int64_t n_rows, int64_t row_base, const uint8_t* q, int nq,
+                             orbm_top2* out, void* cuda_stream) {
+  if (n_rows < 0 || row_base < 0 || nq < 0 || (n_rows > 0 && !rows) || (nq > 0 && (!q || !out)))
+    return set_error(ORB_E_INVALID, "orbm_top2_search_noalloc: bad argument");
+  if ((reinterpret_cast<uintptr_t>(rows) & 15) || (reinterpret_cast<uintptr_t>(q) & 3) || (reinterpret_cast<uintptr_t>(out) & 7))
+    return set_error(ORB_E_INVALID, "orbm_top2_search_noalloc: rows must be 16-byte, q 4-byte and out 8-byte aligned");
+  if (nq == 0) return ORB_OK;
+  int rc = use_device(device);
+  if (rc) return rc;
+  uint2* partial = nullptr;
+  int sms = 0;
+  if ((rc = noalloc_setup(device, &partial, &sms))) return rc;
+  // the same chunking as orbm_top2_search
+  const int nq_pad = align_up(nq, kQPerCta);
+  const int qblocks = nq_pad / kQPerCta;
+  const long long want = std::max(1, (2 * sms) / qblocks);
+  long long rows_per_cta = std::max<long long>(div_up<long long>(std::max<int64_t>(n_rows, 1), want), 1);
+  rows_per_cta = std::min<long long>(rows_per_cta, 1ll << kRowBits);
+  const long long n_chunks = div_up<long long>(n_rows, rows_per_cta);
+  if ((unsigned long long)std::max<long long>(n_chunks, 1) * (unsigned long long)nq_pad > kNoAllocEntries || n_chunks > 0x7fffffffll) {
+    return set_error(ORB_E_INVALID,
+                     "orbm_top2_search_noalloc: %d queries x %lld row chunks need %lld scratch entries, the static scratch holds %zu "
+                     "(up to %zu queries against up to %lld rows per call on this GPU)",
+                     nq, n_chunks, std::max<long long>(n_chunks, 1) * nq_pad, kNoAllocEntries, kNoAllocEntries,
+                     (long long)want << kRowBits);
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+  if (n_chunks > 0) {
+    top2_scan_kernel<<<dim3((unsigned)n_chunks, qblocks), kTopThreads, 0, s>>>(reinterpret_cast<const uint4*>(rows), n_rows,
+                                                                              (int)rows_per_cta, reinterpret_cast<const uint32_t*>(q),
+                                                                              nq, nq_pad, partial);
+    ORB_LAUNCH_CHECK();
+  }
+  // every entry the fold reads was written by the scan of this call: nothing in the scratch has to start at zero
+  top2_reduce_kernel<<<div_up(nq, 128), 128, 0, s>>>(partial, (int)n_chunks, (int)rows_per_cta, nq, nq_pad, row_base, out);
+  ORB_LAUNCH_CHECK();
+  return ORB_OK;
+}
+
 int orbm_db_sync(orbm_db* db) {
   if (!db) return set_error(ORB_E_INVALID, "orbm_db_sync: null");
   int rc = use_device(db->device);
