@@ -127,8 +127,7 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   }
   __syncwarp();
 
-  const int ng = (vw + 3) >> 2, ngroups = ng * vh;
-  const uint32_t magic = (1u << 20) / (uint32_t)ng + 1u;  // gid / ng == (gid * magic) >> 20 (gid < 1024, ng < 16)
+  const int ng = (vw + 3) >> 2;  // 4-pixel groups per row
   int* const count = &P.cand_count[f * P.nlevels + l];
   unsigned long long* const out = P.cand + (size_t)f * P.cand_frame + G.cand_off;
 
@@ -137,6 +136,18 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   for (int i = lane; i < kScorePitch / 4; i += 32) { S.score[i] = 0; S.score[(vh + 1) * (kScorePitch / 4) + i] = 0; }
   for (int r = 1 + lane; r <= vh; r += 32) { S.score[r * (kScorePitch / 4)] = 0; S.score[r * (kScorePitch / 4) + ng + 1] = 0; }
 
+  // prefilter lane constants: pair gp = groups 2gp, 2gp+1 of row lr (+ rpi per pass)
+  const int ngp = (ng + 1) >> 1, rpi = 32 / ngp;  // ng <= 15: at least 4 rows per pass
+  const int lr = lane / ngp, gp = lane - lr * ngp;
+  const bool lane_on = lr < rpi;
+  const uint32_t* const prow = &S.tile[(lr + 3) * kTileWords + 2 * gp];
+  uint32_t* const srow = &S.score[(lr + 1) * (kScorePitch / 4) + 2 * gp + 1];
+  auto valid_mask = [&](int g) {  // bit 7 of the bytes of group g that lie inside the cell
+    const int nvalid = min(4, vw - 4 * g);
+    return nvalid <= 0 ? 0u : 0x80808080u >> (32 - 8 * nvalid);
+  };
+  const uint32_t mask0 = valid_mask(2 * gp), mask1 = valid_mask(2 * gp + 1);
+  const uint32_t ent0 = (uint32_t)(2 * gp) << 4;
   // One detection pass at threshold T; returns the number of keypoints it appended.
   auto detect = [&](const int T) -> int {
     const uint32_t K = 0x01010101u * (uint32_t)(127 - min(T, 126));
@@ -173,37 +184,53 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
       while (tail - head >= 32) drain(32);
     };
     __syncwarp();
-    for (int base = 0; base < ngroups; base += 32) {
-      const int gid = base + lane;
-      uint32_t flags = 0;
-      int py = 0, g = 0;
-      if (gid < ngroups) {
-        py = (int)(((uint32_t)gid * magic) >> 20);
-        g = gid - py * ng;
-        const uint32_t* r0 = &S.tile[(py + 3) * kTileWords + g + 1];  // word holding the 4 centres
-        const uint32_t c = r0[0], lw = r0[-1], rw = r0[1];
-        const uint32_t* um = r0 - 2 * kTileWords;
-        const uint32_t* dm = r0 + 2 * kTileWords;
-        uint32_t fl = gt(__vabsdiffu4(c, r0[-3 * kTileWords]) | __vabsdiffu4(c, r0[3 * kTileWords]));
-        fl &= gt(__vabsdiffu4(c, __funnelshift_r(c, rw, 24)) | __vabsdiffu4(c, __funnelshift_r(lw, c, 8)));
-        fl &= gt(__vabsdiffu4(c, __funnelshift_r(dm[0], dm[1], 16)) | __vabsdiffu4(c, __funnelshift_r(um[-1], um[0], 16)));
-        fl &= gt(__vabsdiffu4(c, __funnelshift_r(um[0], um[1], 16)) | __vabsdiffu4(c, __funnelshift_r(dm[-1], dm[0], 16)));
-        const int nvalid = min(4, vw - 4 * g);  // pixels of this group inside the cell
-        flags = fl & (0x80808080u >> (32 - 8 * nvalid));
-        S.score[(py + 1) * (kScorePitch / 4) + g + 1] = 0;  // cleared before any of its pixels is scored
+    // Prefilter, two horizontally adjacent 4-pixel groups per lane: lane <-> (row lr of the pass, pair gp), rows
+    // advance by rpi per pass, so the loop carries two pointers instead of deriving (row, group) from a flat index.
+    // The pair shares its loads (six 8-byte and four 4-byte reads instead of 22 words) and two of its twelve
+    // funnel shifts ((x+2) of the left group is (x-2) of the right one).
+    for (int base = 0; base < vh; base += rpi) {
+      const int py = base + lr;
+      uint32_t flags0 = 0, flags1 = 0;
+      if (lane_on && py < vh) {
+        const uint32_t* r0 = prow + base * kTileWords;  // word 2gp of the centre row: (lw, c0) (c1, rw)
+        const uint2 m0 = *reinterpret_cast<const uint2*>(r0), m1 = *reinterpret_cast<const uint2*>(r0 + 2);
+        const uint2 u0 = *reinterpret_cast<const uint2*>(r0 - 2 * kTileWords), u1 = *reinterpret_cast<const uint2*>(r0 - 2 * kTileWords + 2);
+        const uint2 d0 = *reinterpret_cast<const uint2*>(r0 + 2 * kTileWords), d1 = *reinterpret_cast<const uint2*>(r0 + 2 * kTileWords + 2);
+        const uint32_t t0 = r0[-3 * kTileWords + 1], t1 = r0[-3 * kTileWords + 2];
+        const uint32_t b0 = r0[3 * kTileWords + 1], b1 = r0[3 * kTileWords + 2];
+        const uint32_t c0 = m0.y, c1 = m1.x;
+        const uint32_t umid = __funnelshift_r(u0.y, u1.x, 16), dmid = __funnelshift_r(d0.y, d1.x, 16);
+        uint32_t fl = gt(__vabsdiffu4(c0, t0) | __vabsdiffu4(c0, b0));
+        fl &= gt(__vabsdiffu4(c0, __funnelshift_r(c0, c1, 24)) | __vabsdiffu4(c0, __funnelshift_r(m0.x, c0, 8)));
+        fl &= gt(__vabsdiffu4(c0, dmid) | __vabsdiffu4(c0, __funnelshift_r(u0.x, u0.y, 16)));
+        fl &= gt(__vabsdiffu4(c0, umid) | __vabsdiffu4(c0, __funnelshift_r(d0.x, d0.y, 16)));
+        flags0 = fl & mask0;
+        fl = gt(__vabsdiffu4(c1, t1) | __vabsdiffu4(c1, b1));
+        fl &= gt(__vabsdiffu4(c1, __funnelshift_r(c1, m1.y, 24)) | __vabsdiffu4(c1, __funnelshift_r(c0, c1, 8)));
+        fl &= gt(__vabsdiffu4(c1, __funnelshift_r(d1.x, d1.y, 16)) | __vabsdiffu4(c1, umid));
+        fl &= gt(__vabsdiffu4(c1, __funnelshift_r(u1.x, u1.y, 16)) | __vabsdiffu4(c1, dmid));
+        flags1 = fl & mask1;
+        uint32_t* sc = srow + base * (kScorePitch / 4);  // cleared before any of its pixels is scored
+        sc[0] = 0;
+        sc[1] = 0;
       }
       {  // groups with a prefilter survivor are the only score words that can hold a corner; their
          // entry keeps the four survivor bits, so pixels are unpacked once per 32 listed words
          // instead of once per 32 visited words
-        const uint32_t m = __ballot_sync(0xffffffffu, flags != 0);
-        if (flags != 0) {
-          const uint32_t nib = (((flags >> 7) & 0x01010101u) * 0x01020408u) >> 24;  // bit b = pixel b survives
-          wlist[nw + __popc(m & lt_mask)] = (uint16_t)(py << 8 | g << 4 | nib);
+        const uint32_t ma = __ballot_sync(0xffffffffu, flags0 != 0), mb = __ballot_sync(0xffffffffu, flags1 != 0);
+        int at = nw + __popc(ma & lt_mask) + __popc(mb & lt_mask);
+        if (flags0 != 0) {
+          const uint32_t nib = (((flags0 >> 7) & 0x01010101u) * 0x01020408u) >> 24;  // bit b = pixel b survives
+          wlist[at++] = (uint16_t)(py << 8 | ent0 | nib);
         }
-        nw += __popc(m);
+        if (flags1 != 0) {
+          const uint32_t nib = (((flags1 >> 7) & 0x01010101u) * 0x01020408u) >> 24;
+          wlist[at] = (uint16_t)((py << 8 | ent0 | nib) + 16);
+        }
+        nw += __popc(ma) + __popc(mb);
       }
       __syncwarp();
-      if (nw - whead >= 32) expand(32);
+      while (nw - whead >= 32) expand(32);
     }
     if (nw > whead) expand(nw - whead);
     drain(tail - head);

@@ -8,7 +8,8 @@ import sys
 
 path = sys.argv[1]
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+kf = ["-k", "regex:" + os.environ["NCU_KERNEL"]] if os.environ.get("NCU_KERNEL") else []  # NCU_KERNEL=fast_cells: only that kernel
+out = subprocess.run(["ncu", "-i", path] + kf + ["--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
 fname = "?"
 data = []
 hdr = None
