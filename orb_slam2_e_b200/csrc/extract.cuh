@@ -31,6 +31,7 @@ struct LevelGeom {
   size_t off;               // byte offset of this level inside one frame's pyr/blur block
   // FAST cell grid (ORBextractor.cc:771-787)
   int nCols, nRows, wCell, hCell, cell_base;
+  uint32_t rcp_nCols;       // 2^32 / nCols + 1: x / nCols == __umulhi(x, rcp_nCols) while x * nCols < 2^32
   // quadtree (ORBextractor.cc:539-563)
   int boxW, boxH, nIni, quota, dmax;
   float hX;

@@ -143,7 +143,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
     P.min_th = c.min_th_fast;
     size_t off = 0;
     int cell_base = 0, cand_off = 0, kept_off = 0, tab = 0, tiles = 0, tiles_few = 0;
-    std::vector<int> blur_tiles(2 * (nl + 1), 0);  // first tile of each level: 56-row tiles, then 14-row tiles (pyramid.cu kBlurTH / kBlurTHFew)
+    std::vector<int> blur_tiles(2 * (nl + 1), 0);  // first warp tile of each level: 112-row tiles, then 14-row tiles (pyramid.cu kBlurTH / kBlurTHFew)
     for (int l = 0; l < nl; ++l) {
       LevelGeom& G = P.lv[l];
       G.w = cv_round((float)w * H->inv_scale[l]);
@@ -160,6 +160,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       G.wCell = (int)ceilf(width / G.nCols);
       G.hCell = (int)ceilf(height / G.nRows);
       G.cell_base = cell_base;
+      G.rcp_nCols = (uint32_t)((1ull << 32) / (unsigned)G.nCols + 1ull);
       cell_base += G.nCols * G.nRows;
       G.boxW = maxBX - minB;
       G.boxH = maxBY - minB;
@@ -185,9 +186,9 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       G.xtab = tab; tab += G.w;
       G.ytab = tab; tab += G.h;
       blur_tiles[l] = tiles;
-      tiles += div_up(G.w, 128) * div_up(G.h, 56);
+      tiles += div_up(div_up(G.w, 32) * div_up(G.h, 112), 4);  // pyramid.cu blur_warp_tiles(w, h, kBlurTH)
       blur_tiles[nl + 1 + l] = tiles_few;
-      tiles_few += div_up(G.w, 128) * div_up(G.h, 14);
+      tiles_few += div_up(div_up(G.w, 32) * div_up(G.h, 14), 4);
     }
     blur_tiles[nl] = tiles;
     blur_tiles[2 * nl + 1] = tiles_few;

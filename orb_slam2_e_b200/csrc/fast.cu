@@ -27,6 +27,9 @@ namespace orbfront {
 constexpr int kFastWarps = 4;
 constexpr int kCellMax = 60;                 // wCell,hCell <= 59 (ceil(width/floor(width/30)))
 constexpr int kQueue = 256;                  // ring queue entries (py << 6 | px)
+// x / d for small operands without the ~20-instruction integer division: (x * (65536 / d + 1)) >> 16 is exact while x * d < 65536
+__device__ __constant__ uint32_t c_rcp16[32] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115};
+__device__ __forceinline__ int small_div(int x, int d) { return (int)(((uint32_t)x * c_rcp16[d]) >> 16); }
 // Per-warp shared memory: tile[(maxH+6) x PITCH] | score[(maxH+2) x PITCH] | queue[kQueue] u16, later reused
 // for the cell's NMS survivors | wlist (score words with a prefilter survivor).
 // PITCH (bytes, multiple of 8, >= widest cell + 8) is a template parameter so the 16 ring offsets
@@ -77,7 +80,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   int l = 0;
   while (l + 1 < P.nlevels && cell >= P.lv[l + 1].cell_base) ++l;
   const LevelGeom& G = P.lv[l];
-  const int ci = (cell - G.cell_base) / G.nCols, cj = (cell - G.cell_base) % G.nCols;
+  const int ci = G.nCols == 1 ? cell - G.cell_base : (int)__umulhi((uint32_t)(cell - G.cell_base), G.rcp_nCols);  // / nCols
+  const int cj = (cell - G.cell_base) - ci * G.nCols;
   // valid (scored) region of the cell in level coordinates
   const int vx0 = kEdge + cj * G.wCell, vy0 = kEdge + ci * G.hCell;
   const int vw = min(G.wCell, G.w - kEdge - vx0), vh = min(G.hCell, G.h - kEdge - vy0);
@@ -99,8 +103,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
     const uint4* qsrc = reinterpret_cast<const uint4*>(a0 & ~(uintptr_t)15);
     const int xq0 = (vx0 - 4) - (int)(a0 & 15);  // level column of the first quad (>= 0: rows start 16-byte aligned)
     const int spq = sp >> 4, nq = (tw + 15) >> 4;  // nq <= 5
-    const int rpi = 32 / nq;
-    const int lr = lane / nq, lq = lane - lr * nq;
+    const int rpi = small_div(32, nq);
+    const int lr = small_div(lane, nq), lq = lane - lr * nq;
     if (lr < rpi) {
       const bool in0 = xq0 + 16 * lq < G.w, in1 = xq0 + 16 * lq + 16 < G.w && (sh8 | wsh) != 0;
       const bool st0 = 4 * lq < kTileWords, st1 = 4 * lq + 2 < kTileWords;  // PITCH is a multiple of 8
@@ -137,8 +141,8 @@ fast_cells_kernel(const __grid_constant__ ExtractParams P, int max_h, int warp_b
   for (int r = 1 + lane; r <= vh; r += 32) { S.score[r * (kScorePitch / 4)] = 0; S.score[r * (kScorePitch / 4) + ng + 1] = 0; }
 
   // prefilter lane constants: pair gp = groups 2gp, 2gp+1 of row lr (+ rpi per pass)
-  const int ngp = (ng + 1) >> 1, rpi = 32 / ngp;  // ng <= 15: at least 4 rows per pass
-  const int lr = lane / ngp, gp = lane - lr * ngp;
+  const int ngp = (ng + 1) >> 1, rpi = small_div(32, ngp);  // ng <= 15: at least 4 rows per pass
+  const int lr = small_div(lane, ngp), gp = lane - lr * ngp;
   const bool lane_on = lr < rpi;
   const uint32_t* const prow = &S.tile[(lr + 3) * kTileWords + 2 * gp];
   uint32_t* const srow = &S.score[(lr + 1) * (kScorePitch / 4) + 2 * gp + 1];

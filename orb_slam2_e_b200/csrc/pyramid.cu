@@ -22,13 +22,26 @@ namespace orbfront {
 // would otherwise leave a handful of warps walking long dependent chains.
 constexpr int kStripBatch = 16, kStripFew = 4;
 
+// Lane mapping (round 2): a warp owns four sub-tiles of 32 destination columns x kResizeStrip rows (8 lanes each),
+// consecutive in the level's row-major sub-tile order -- not one 128-column strip: level widths are rarely
+// multiples of 128, and the idle lanes of a row's last strip were 16 % of the executed thread slots.
+__host__ __device__ inline int resize_warp_tiles(int w, int h, int strip) { return div_up(div_up(w, 32) * div_up(h, strip), 4); }
+
 template <int kResizeStrip>
-__device__ __forceinline__ void resize_block(const ExtractParams& P, int l, int bx, int by, int f) {
+__device__ __forceinline__ bool resize_origin(const LevelGeom& D, int warp_tile, int* x0, int* y0) {
+  const int lane = threadIdx.x & 31;
+  const int t = warp_tile * 4 + (lane >> 3), tiles_x = div_up(D.w, 32);
+  const int ty = t / tiles_x, tx = t - ty * tiles_x;
+  *x0 = tx * 32 + 4 * (lane & 7);
+  *y0 = ty * kResizeStrip;
+  return *x0 < D.w && *y0 < D.h;
+}
+
+template <int kResizeStrip>
+__device__ __forceinline__ void resize_block(const ExtractParams& P, int l, int warp_tile, int f) {
   const LevelGeom& D = P.lv[l];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int x0 = (bx * 32 + lane) * 4;
-  const int y0 = (by * 4 + warp) * kResizeStrip;
-  if (x0 >= D.w || y0 >= D.h) return;
+  int x0, y0;
+  if (!resize_origin<kResizeStrip>(D, warp_tile, &x0, &y0)) return;
   const uint8_t* src = level_ptr(P, l - 1, f);
   const int sp = level_pitch(P, l - 1);
   uint8_t* dst = P.pyr + (size_t)f * P.pyr_frame + D.off;
@@ -86,12 +99,10 @@ __device__ __forceinline__ void resize_block(const ExtractParams& P, int l, int 
 // saved.  The row loop below has no branch and no state carried between rows; rows clamped at the
 // top / bottom border simply read the same source row twice.  Arithmetic identical to resize_block.
 template <int kResizeStrip>
-__device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l, int bx, int by, int f) {
+__device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l, int warp_tile, int f) {
   const LevelGeom& D = P.lv[l];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int x0 = (bx * 32 + lane) * 4;
-  const int y0 = (by * 4 + warp) * kResizeStrip;
-  if (x0 >= D.w || y0 >= D.h) return;
+  int x0, y0;
+  if (!resize_origin<kResizeStrip>(D, warp_tile, &x0, &y0)) return;
   const uint8_t* src = level_ptr(P, l - 1, f);
   const int sp = level_pitch(P, l - 1);
   uint8_t* dst = P.pyr + (size_t)f * P.pyr_frame + D.off + (size_t)y0 * D.pitch + x0;
@@ -164,11 +175,11 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
 
 template <int kStrip>
 __global__ void __launch_bounds__(128) resize_level_kernel(const __grid_constant__ ExtractParams P, int l) {
-  resize_block<kStrip>(P, l, blockIdx.x, blockIdx.y, blockIdx.z);
+  resize_block<kStrip>(P, l, blockIdx.x * 4 + (threadIdx.x >> 5), blockIdx.z);
 }
 template <int kStrip>
 __global__ void __launch_bounds__(128) resize_level_words_kernel(const __grid_constant__ ExtractParams P, int l) {
-  resize_words_block<kStrip>(P, l, blockIdx.x, blockIdx.y, blockIdx.z);
+  resize_words_block<kStrip>(P, l, blockIdx.x * 4 + (threadIdx.x >> 5), blockIdx.z);
 }
 
 // Whole pyramid in ONE cooperative launch, for the tracking thread's case of one or two small frames
@@ -178,11 +189,11 @@ __global__ void __launch_bounds__(128) resize_level_words_kernel(const __grid_co
 __global__ void __launch_bounds__(128) pyramid_fused_kernel(const __grid_constant__ ExtractParams P, int* bar) {
   for (int l = 1; l < P.nlevels; ++l) {
     const LevelGeom& D = P.lv[l];
-    const int nbx = div_up(D.w, 128), nby = div_up(D.h, 4 * kStripFew), total = nbx * nby * P.n_frames;
+    const int nb = div_up(resize_warp_tiles(D.w, D.h, kStripFew), 4), total = nb * P.n_frames;
     for (int b = blockIdx.x; b < total; b += gridDim.x) {
-      const int f = b / (nbx * nby), r = b - f * (nbx * nby);
-      if (D.resize_words) resize_words_block<kStripFew>(P, l, r % nbx, r / nbx, f);
-      else resize_block<kStripFew>(P, l, r % nbx, r / nbx, f);
+      const int f = b / nb, r = b - f * nb;
+      if (D.resize_words) resize_words_block<kStripFew>(P, l, r * 4 + (threadIdx.x >> 5), f);
+      else resize_block<kStripFew>(P, l, r * 4 + (threadIdx.x >> 5), f);
     }
     if (l + 1 < P.nlevels) {  // level l complete and visible before anyone reads it
       __syncthreads();
@@ -209,7 +220,7 @@ template <int kStrip>
 static int launch_levels(const ExtractParams& P, cudaStream_t s, int* launches) {
   for (int l = 1; l < P.nlevels; ++l) {
     const LevelGeom& D = P.lv[l];
-    dim3 grid(div_up(D.w, 128), div_up(D.h, 4 * kStrip), P.n_frames);
+    dim3 grid(div_up(resize_warp_tiles(D.w, D.h, kStrip), 4), 1, P.n_frames);
     if (D.resize_words) resize_level_words_kernel<kStrip><<<grid, 128, 0, s>>>(P, l);
     else resize_level_kernel<kStrip><<<grid, 128, 0, s>>>(P, l);
     ORB_LAUNCH_CHECK();
@@ -223,9 +234,9 @@ int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches) {
   const LevelGeom& D = P.lv[1];
   // warps the largest level offers with long strips; below about one warp per scheduler slot the
   // short strips win (measured: 640x480 x1 76 -> 49 us, 3840x2160 x1 121 -> 88 us)
-  const long warps_batch = (long)div_up(D.w, 128) * div_up(D.h, kStripBatch) * P.n_frames;
+  const long warps_batch = (long)resize_warp_tiles(D.w, D.h, kStripBatch) * P.n_frames;
   if (warps_batch >= 148 * 32) return launch_levels<kStripBatch>(P, s, launches);
-  const int blocks_few = div_up(D.w, 128) * div_up(D.h, 4 * kStripFew) * P.n_frames;
+  const int blocks_few = div_up(resize_warp_tiles(D.w, D.h, kStripFew), 4) * P.n_frames;
   if (P.nlevels > 2 && P.pyr_bar && blocks_few <= P.pyr_max_grid && !getenv("ORBX_NO_FUSED_PYRAMID")) {
     int* bar = P.pyr_bar;
     ORB_CUDA_TRY(cudaMemsetAsync(bar, 0, sizeof(int), s));
@@ -245,8 +256,7 @@ __device__ __forceinline__ int reflect101(int p, int n) {
   return p;  // valid for |overshoot| < n, which holds for 3-px taps on levels >= 7 px
 }
 
-// Blur: one warp per 128-column x kBlurTH-row tile, each lane owns 4 adjacent columns (one 32-bit
-// word) and marches down the rows.  Horizontal 7 taps = two DP4A per output on byte windows
+// Blur: each lane owns 4 adjacent columns (one 32-bit word) of a kBlurTH-row tile and marches down the rows.  Horizontal 7 taps = two DP4A per output on byte windows
 // funnel-shifted out of three aligned words; the last 7 horizontal rows live in registers as u16 pairs
 // (row-1, row), so the vertical taps are three DP2A and one IMAD; PRMT packs byte 2 of the four sums.
 // Round 2: the row loop has no branch.  The source row pointer walks the BORDER_REFLECT_101 sequence by
@@ -254,8 +264,14 @@ __device__ __forceinline__ int reflect101(int p, int n) {
 // predicated off, and the body is 14 rows = the common period of the 7-row ring and the 2-deep load
 // pipeline (about 10 KB of SASS).  The round-1 loop spent 43 % of its instructions on the three
 // warp-uniform branches per row and their address arithmetic.  No shared memory.
-constexpr int kBlurTW = 128, kBlurWarps = 4, kBlurBody = 14;
-constexpr int kBlurTH = 56, kBlurTHFew = 14;  // rows per tile: batches / one or a few frames (more, shorter warps)
+// Round 2, lane mapping: a warp owns FOUR sub-tiles of 32 columns (8 lanes each), consecutive in the level's
+// row-major sub-tile order, instead of one 128-column tile: level widths are rarely multiples of 128 (533, 444,
+// 370, 308, 257 ... for a 640-wide frame), and whole idle lanes in the last tile of a row were 12 % of the
+// executed thread slots; with 32-column granularity 3 % are.  Nothing in the row loop crosses lanes.
+constexpr int kBlurSubW = 32, kBlurWarps = 4, kBlurBody = 14;
+constexpr int kBlurTH = 112, kBlurTHFew = 14;  // rows per tile: batches / one or a few frames (more, shorter warps)
+
+__host__ __device__ inline int blur_warp_tiles(int w, int h, int th) { return div_up(div_up(w, kBlurSubW) * div_up(h, th), 4); }
 
 __global__ void __launch_bounds__(kBlurWarps * 32, 8)
 blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ tile_base /* nlevels+1 */, int th, int skip_empty_levels) {
@@ -268,12 +284,12 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
   const int f = blockIdx.z;
   // the reference skips levels without keypoints (:1089); only possible when the quadtree has already run
   if (skip_empty_levels && P.kept_count[f * P.nlevels + l] == 0) return;
-  const int t = tile - tile_base[l];
-  const int tiles_x = div_up(G.w, kBlurTW);
+  const int t = (tile - tile_base[l]) * 4 + (lane >> 3);  // this lane's sub-tile
+  const int tiles_x = div_up(G.w, kBlurSubW);
   const int ty = t / tiles_x, tx = t - ty * tiles_x;
-  const int x0 = tx * kBlurTW + 4 * lane, y0 = ty * th;
+  const int x0 = tx * kBlurSubW + 4 * (lane & 7), y0 = ty * th;
   const int e = G.w - x0;  // pixels of this lane's window that exist from x0 on (>= 8: no right edge)
-  if (e <= 0) return;
+  if (e <= 0 || y0 >= G.h) return;
   const int sp = level_pitch(P, l);
   // Row edges without a divergent path: every lane runs the word-wise loop on its 12-byte window
   // [x0-4, x0+8); where the window leaves the row, BORDER_REFLECT_101 is applied by three PRMTs whose
@@ -354,10 +370,10 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree) {
   // blur_tiles (extractor.cu) is built for kBlurTH-row tiles; a few frames use kBlurTHFew-row tiles, whose
   // table is the second half of the same array
-  const bool few = (long)P.n_frames * div_up(P.lv[0].w, kBlurTW) * div_up(P.lv[0].h, kBlurTH) < 2 * 148;
+  const bool few = (long)P.n_frames * blur_warp_tiles(P.lv[0].w, P.lv[0].h, kBlurTH) < 2 * 148;
   const int th = few ? kBlurTHFew : kBlurTH;
   int total = 0;
-  for (int l = 0; l < P.nlevels; ++l) total += div_up(P.lv[l].w, kBlurTW) * div_up(P.lv[l].h, th);
+  for (int l = 0; l < P.nlevels; ++l) total += blur_warp_tiles(P.lv[l].w, P.lv[l].h, th);
   blur_kernel<<<dim3(div_up(total, kBlurWarps), 1, P.n_frames), kBlurWarps * 32, 0, s>>>(P, P.blur_tiles + (few ? P.nlevels + 1 : 0), th,
                                                                                        after_quadtree ? 1 : 0);
   ORB_LAUNCH_CHECK();
