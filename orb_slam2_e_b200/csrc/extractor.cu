@@ -199,7 +199,7 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
     P.out_cap = kept_off;
     H->slots = kept_off;
     // resize taps (levels >= 1 read level l-1)
-    std::vector<int4> taps((size_t)tab, make_int4(0, 0, 0, 0));
+    std::vector<int4> taps((size_t)tab + 2, make_int4(0, 0, 0, 0));  // + 2: the resize row loop reads its table one row ahead
     for (int l = 1; l < nl; ++l) {
       axis_taps(P.lv[l - 1].w, P.lv[l].w, true, &taps[P.lv[l].xtab]);
       axis_taps(P.lv[l - 1].h, P.lv[l].h, false, &taps[P.lv[l].ytab]);
@@ -212,7 +212,8 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
         for (int x = x0; x <= xe; ++x) ok = ok && xt[x].x >= xt[x0].x && xt[x].w >= xt[x0].x && xt[x].w - xt[x0].x < 8 && xt[x].x - xt[x0].x < 8;
       }
       const int4* yt = &taps[P.lv[l].ytab];
-      for (int y = 0; y < P.lv[l].h && ok; ++y) ok = ok && (yt[y].w == yt[y].x || yt[y].w == yt[y].x + 1) && (y == 0 || yt[y].w >= yt[y - 1].w);
+      // rows: lower row = upper row + 1 (clamped at the last row), upper rows strictly increasing (the kernel walks the source rows once)
+      for (int y = 0; y < P.lv[l].h && ok; ++y) ok = ok && yt[y].x >= 0 && yt[y].w == std::min(yt[y].x + 1, P.lv[l - 1].h - 1) && (y == 0 || yt[y].x > yt[y - 1].x);
       P.lv[l].resize_words = ok ? 1 : 0;
     }
     int rc;

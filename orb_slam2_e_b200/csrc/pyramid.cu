@@ -92,12 +92,8 @@ __device__ __forceinline__ void resize_block(const ExtractParams& P, int l, int 
 // Word-wise variant for scale factors up to ~2 (every 4-pixel destination group reads source
 // columns spanning at most 8 bytes): per source row a lane loads three aligned words, shifts its
 // 8-byte window into place, picks the (left, right) byte pairs with two PRMTs whose selectors are
-// lane constants, and interpolates with DP2A on packed (c0, c1) 16-bit weights.  Every destination row
-// interpolates its two source rows itself: the round-1 kernel kept the row shared by consecutive
-// destination rows in registers, and the bookkeeping for that (row parity, request/consume pointers,
-// clamped-row cases) was 40 % of its executed instructions -- more than the 15 instructions per row it
-// saved.  The row loop below has no branch and no state carried between rows; rows clamped at the
-// top / bottom border simply read the same source row twice.  Arithmetic identical to resize_block.
+// lane constants, and interpolates with DP2A on packed (c0, c1) 16-bit weights.  Arithmetic identical to
+// resize_block.
 template <int kResizeStrip>
 __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l, int warp_tile, int f) {
   const LevelGeom& D = P.lv[l];
@@ -125,51 +121,63 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   // past the row's last pixel), so no load leaves the row whatever its pitch
   const int src_w = P.lv[l - 1].w;
   const bool need1 = (first & ~3) + 4 < src_w, need2 = (first & ~3) + 8 < src_w;
-  // The six window words of destination rows i+1 and i+2 are requested before row i is interpolated, and
-  // the row table is read three rows ahead, so a warp always has two destination rows of loads in flight
-  // (ncu, first version of this loop: 13 of 16 resident warps stalled on the row loads).
-  struct Win { uint32_t a0, a1, a2, b0, b1, b2; };
-  auto request = [&](const int4& t, Win& w) {
-    const uint32_t* pa = reinterpret_cast<const uint32_t*>(wsrc + (size_t)((uint32_t)t.x * (unsigned long long)(uint32_t)sp));
-    const uint32_t* pb = reinterpret_cast<const uint32_t*>(wsrc + (size_t)((uint32_t)t.w * (unsigned long long)(uint32_t)sp));
-    w.a0 = __ldg(pa); w.a1 = need1 ? __ldg(pa + 1) : 0u; w.a2 = need2 ? __ldg(pa + 2) : 0u;
-    w.b0 = __ldg(pb); w.b1 = need1 ? __ldg(pb + 1) : 0u; w.b2 = need2 ? __ldg(pb + 2) : 0u;
+  // The loop runs over SOURCE rows: consecutive destination rows share a source row five times out of six at
+  // scale 1.2 (row i's lower row is row i+1's upper row), so every source row is loaded and interpolated
+  // horizontally once, kept for one iteration, and a destination row is emitted whenever its upper row is the
+  // previous source row (the table guarantees strictly increasing upper rows and lower = upper + 1, clamped at
+  // the last row -- checked on the host, extractor.cu).  Three source rows of loads are in flight.
+  struct Win { uint32_t w0, w1, w2; };
+  const int rows = min(kResizeStrip, D.h - y0);
+  const ptrdiff_t dpitch = D.pitch;
+  const int4* yt = P.rtab + D.ytab + y0;
+  const int s_end = __ldg(yt + rows - 1).x + 1;  // last source row consumed (clamped when loaded)
+  const int row_max = min(s_end, P.lv[l - 1].h - 1);
+  int4 t_cur = __ldg(yt), t_nxt = __ldg(yt + 1);  // the table keeps one entry past the last level's rows (extractor.cu)
+  yt += 2;
+  asm("" : "+l"(yt));  // a lane pointer that walks the table: otherwise its address is re-derived from the parameters at every row
+  int nw = 1 + (int)need1 + (int)need2;  // window words that start inside the source row
+  asm("" : "+r"(nw));                    // compared with immediates in the loop (the two predicates were spilled and rebuilt per row)
+  auto request = [&](int row, Win& w) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(wsrc + (size_t)((uint32_t)min(row, row_max) * (unsigned long long)(uint32_t)sp));
+    w.w0 = __ldg(p); w.w1 = nw > 1 ? __ldg(p + 1) : 0u; w.w2 = nw > 2 ? __ldg(p + 2) : 0u;
   };
-  // horizontally interpolated source row, already >> 4
-  auto hrow = [&](uint32_t w0, uint32_t w1, uint32_t w2, uint32_t (&h)[4]) {
-    const uint32_t v0 = __funnelshift_r(w0, w1, sh), v1 = __funnelshift_r(w1, w2, sh);
+  int srow = t_cur.x;  // source row consumed next
+  Win wa, wb, wc;
+  request(srow, wa);
+  request(srow + 1, wb);
+  request(srow + 2, wc);
+  uint32_t h0[4] = {0, 0, 0, 0}, h1[4] = {0, 0, 0, 0};
+  // one source row: interpolate it horizontally (already >> 4) into hc, re-fill its window slot with row + 3, and emit
+  // the destination row whose upper row is the previous source row (hp)
+  auto step = [&](Win& w, const uint32_t (&hp)[4], uint32_t (&hc)[4]) {
+    const uint32_t v0 = __funnelshift_r(w.w0, w.w1, sh), v1 = __funnelshift_r(w.w1, w.w2, sh);
     const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
-    h[0] = __dp2a_lo(coef[0], p01, 0u) >> 4;
-    h[1] = __dp2a_hi(coef[1], p01, 0u) >> 4;
-    h[2] = __dp2a_lo(coef[2], p23, 0u) >> 4;
-    h[3] = __dp2a_hi(coef[3], p23, 0u) >> 4;
-  };
-  const int rows = min(kResizeStrip, D.h - y0), dpitch = D.pitch;
-  const int4* ytab = P.rtab + D.ytab + y0;
-  // two destination rows of loads in flight, row table read three rows ahead
-  int4 t_cur = __ldg(ytab), t_n1 = __ldg(ytab + min(1, rows - 1)), t_n2 = __ldg(ytab + min(2, rows - 1));
-  Win w_cur, w_n1;
-  request(t_cur, w_cur);
-  request(t_n1, w_n1);
-#pragma unroll 3
-  for (int i = 0; i < rows; ++i) {
-    Win w_n2;
-    request(t_n2, w_n2);  // the last iterations re-request the last row (cached)
-    const int4 t_n3 = __ldg(ytab + min(i + 3, rows - 1));
-    uint32_t hA[4], hB[4], u[4];
-    hrow(w_cur.a0, w_cur.a1, w_cur.a2, hA);
-    hrow(w_cur.b0, w_cur.b1, w_cur.b2, hB);
-    // (b * a) >> 16 is the high word of (b << 16) * a: one IMAD.HI with the running sum as addend
-    const uint32_t B0 = (uint32_t)t_cur.y << 16, B1 = (uint32_t)t_cur.z << 16;
+    request(srow + 3, w);
+    hc[0] = __dp2a_lo(coef[0], p01, 0u) >> 4;
+    hc[1] = __dp2a_hi(coef[1], p01, 0u) >> 4;
+    hc[2] = __dp2a_lo(coef[2], p23, 0u) >> 4;
+    hc[3] = __dp2a_hi(coef[3], p23, 0u) >> 4;
+    if (t_cur.x == srow - 1) {  // never true for the strip's first source row
+      // (b * a) >> 16 is the high word of (b << 16) * a: one IMAD.HI with the running sum as addend
+      const uint32_t B0 = (uint32_t)t_cur.y << 16, B1 = (uint32_t)t_cur.z << 16;
+      uint32_t u[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) u[k] = (__umulhi(B1, hB[k]) + (__umulhi(B0, hA[k]) + 2u)) << 6;  // result byte = bits 8..15
-    *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(u[0], u[1], 0x0051), __byte_perm(u[2], u[3], 0x0051), 0x5410);
-    dst += dpitch;  // pitch padding absorbs the tail
-    w_cur = w_n1;
-    w_n1 = w_n2;
-    t_cur = t_n1;
-    t_n1 = t_n2;
-    t_n2 = t_n3;
+      for (int k = 0; k < 4; ++k) u[k] = (__umulhi(B1, hc[k]) + (__umulhi(B0, hp[k]) + 2u)) << 6;  // result byte = bits 8..15
+      *reinterpret_cast<uint32_t*>(dst) = __byte_perm(__byte_perm(u[0], u[1], 0x0051), __byte_perm(u[2], u[3], 0x0051), 0x5410);
+      dst += dpitch;  // pitch padding absorbs the tail
+      t_cur = t_nxt;
+      t_nxt = __ldg(yt);
+      ++yt;
+    }
+    return ++srow > s_end;
+  };
+  for (;;) {  // 6 = window ring (3) x interpolated-row ping-pong (2): no register moves between iterations
+    if (step(wa, h0, h1)) break;
+    if (step(wb, h1, h0)) break;
+    if (step(wc, h0, h1)) break;
+    if (step(wa, h1, h0)) break;
+    if (step(wb, h0, h1)) break;
+    if (step(wc, h1, h0)) break;
   }
 }
 

@@ -68,3 +68,26 @@ def test_limits_given_at_creation_are_enforced():
         ext(synth.textured_frame(480, 640, 3))
     with pytest.raises(OrbFrontError):
         ext.extract_batch(np.stack([synth.textured_frame(240, 320, 3)] * 3))
+
+
+@pytest.mark.parametrize("shape,cfg,batch", [
+    ((480, 640), (1000, 1.2, 8, 20, 7), 64),
+    ((480, 640), (1200, 1.1, 6, 24, 7), 64),
+    ((376, 1241), (2000, 1.2, 8, 20, 7), 48),   # odd width and pitch
+    ((240, 322), (500, 1.2, 8, 20, 7), 200),     # small levels, many frames
+])
+def test_batch_pyramid_equals_single_frame_pyramid(shape, cfg, batch):
+    """Batches large enough to fill the GPU take the shared-memory-fed resize kernel (pyramid.cu
+    resize_rows_tma_kernel); one frame takes the register-fed one, which test_gpu_extract.py compares with the
+    oracle level by level.  Both must give the same pixels."""
+    h, w = shape
+    distinct = [synth.textured_frame(h, w, 4300 + i) for i in range(3)]
+    frames = np.ascontiguousarray(np.stack([distinct[i % 3] for i in range(batch)]))
+    big = ORBextractor(*cfg, max_width=w, max_height=h, max_batch=batch)
+    big.extract_batch(frames, read=False)
+    one = ORBextractor(*cfg)
+    for f in (0, batch // 2 + 1, batch - 1):
+        one(frames[f])
+        for l in range(cfg[2]):
+            assert np.array_equal(big.level(l, f), one.level(l, 0)), (f, l)
+            assert np.array_equal(big.blur_level(l, f), one.blur_level(l, 0)), (f, l)
