@@ -543,11 +543,6 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
   }
   if (H->pinned_counts_cap < n) {
     if (H->pinned_counts) cudaFreeHost(H->pinned_counts);
-  if (H->s_pyr) { cudaStreamSynchronize(H->s_pyr); cudaStreamDestroy(H->s_pyr); }
-  if (H->ev_pyr_ready) cudaEventDestroy(H->ev_pyr_ready);
-  if (H->ev_pyr_done) cudaEventDestroy(H->ev_pyr_done);
-  if (H->pyr_stage_host) cudaFreeHost(H->pyr_stage_host);
-  if (H->out_stage_host) cudaFreeHost(H->out_stage_host);
     H->pinned_counts = nullptr; H->pinned_counts_cap = 0;
     ORB_CUDA_TRY(cudaMallocHost(&H->pinned_counts, sizeof(int) * (size_t)n));
     H->pinned_counts_cap = n;

@@ -91,3 +91,34 @@ def test_batch_pyramid_equals_single_frame_pyramid(shape, cfg, batch):
         for l in range(cfg[2]):
             assert np.array_equal(big.level(l, f), one.level(l, 0)), (f, l)
             assert np.array_equal(big.blur_level(l, f), one.blur_level(l, 0)), (f, l)
+
+
+def test_pyramid_staging_survives_a_host_batch_on_the_same_handle():
+    """The page-locked pyramid staging of the single-frame drop-in path (orbx_set_pyramid_staging /
+    orbx_get_pyramid_host) and its side stream belong to the handle until orbx_destroy: a host-buffer batch in
+    between (which grows other page-locked buffers) must leave them usable."""
+    import ctypes as C
+    from orb_slam2_e_b200 import _lib
+    L = _lib.load()
+    cfg = (500, 1.2, 4, 20, 7)
+    h, w = 240, 320
+    ext = ORBextractor(*cfg, max_width=w, max_height=h, max_batch=40)
+    _lib.check(L.orbx_set_pyramid_staging(ext._h, 1))
+
+    def staged_level(level):
+        p, lw, lh, st = C.c_void_p(), C.c_int(), C.c_int(), C.c_size_t()
+        _lib.check(L.orbx_get_pyramid_host(ext._h, level, C.byref(p), C.byref(lw), C.byref(lh), C.byref(st)))
+        rows = (C.c_uint8 * (st.value * lh.value)).from_address(p.value)
+        return np.frombuffer(rows, np.uint8).reshape(lh.value, st.value)[:, :lw.value].copy()
+
+    a, b = synth.textured_frame(h, w, 4400), synth.textured_frame(h, w, 4401)
+    ext(a)
+    for l in range(cfg[2]):
+        assert np.array_equal(staged_level(l), ext.level(l, 0))
+    batch = np.ascontiguousarray(np.stack([synth.textured_frame(h, w, 4410 + i % 3) for i in range(40)]))
+    ext.extract_batch_host(batch)     # upload | extract | download pipeline: grows its own page-locked buffers
+    ext(b)
+    for l in range(cfg[2]):
+        assert np.array_equal(staged_level(l), ext.level(l, 0))
+    ext(a)
+    assert np.array_equal(staged_level(0), a)
