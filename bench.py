@@ -316,7 +316,7 @@ def run_gpu_arm(args):
                     "h2d_ceiling_note": "copy-only probe in this run: the step's frames from the same pinned buffer, no kernels, "
                                         "all ranks at once, max over ranks (aggregate GB/s)"},
             "gpu_launches": ex["launches"] + (match["gpu_launches"] if match else 0),
-            "clocks": ex["clocks"], "roofline": ex["roofline"], "roofline_pipeline": ex["roofline_pipeline"],
+            "clocks": ex["clocks"], "roofline": ex["roofline"], "roofline_issue": ex["roofline_issue"], "roofline_pipeline": ex["roofline_pipeline"],
             "cpu_baseline": cpu, "cpu_baseline_cv2": cpu_cv2, "matching": match, "configs": configs,
         }
         _emit(line)

@@ -167,7 +167,30 @@ def bench_extract(args, B, rank, world, local, dist):
             traffic = json.load(open(tpath)).get(dom)
         except Exception:
             traffic = None
-    roof = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+    # what ncu shows for every extractor kernel is an ISSUE bound (warp-instruction slots), not HBM: `roofline` keeps the
+    # contract's HBM figures for the dominant kernel and says so in `bound`; `roofline_issue` is the figure that explains
+    # the time: executed warp instructions (ncu, profiles/instr.json, scaled to this batch) / (SMs x 4 schedulers x SM clock)
+    roof_issue = None
+    ipath = os.path.join(B.ROOT, "profiles", "instr.json")
+    if os.path.exists(ipath):
+        try:
+            ij = json.load(open(ipath))
+            sms = torch.cuda.get_device_properties(local).multi_processor_count
+            mhz = float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 0)
+            slots = sms * 4 * mhz * 1e6  # warp instructions per second the GPU can issue at the clock it ran at
+            k_inst = ij["per_step"][dom] * n / 1024.0
+            s_inst = ij["per_step"]["total"] * n / 1024.0
+            step_ms = ms / args.steps
+            roof_issue = {"kernel": dom, "unit": "G warp-instructions/s", "peak": slots / 1e9, "sm_mhz": mhz, "sms": sms,
+                          "kernel_warp_instructions_per_step": k_inst, "achieved": k_inst / (stages[dom] * 1e-3) / 1e9,
+                          "frac": k_inst / (stages[dom] * 1e-3) / slots if slots else None,
+                          "step_warp_instructions": s_inst, "step_achieved": s_inst / (step_ms * 1e-3) / 1e9,
+                          "step_frac": s_inst / (step_ms * 1e-3) / slots if slots else None,
+                          "source": "profiles/instr.json (smsp__inst_executed.sum per 1024-frame launch, ncu --set full), scaled by frames/1024"}
+        except Exception as e:  # a missing or stale summary must not fail the bench
+            roof_issue = {"error": repr(e)}
+    roof = {"bound": "issue", "bound_note": "ncu: issue slots 71-83 % busy, DRAM < 45 % in every extractor kernel; achieved/peak/frac below are the HBM figures the contract asks for, roofline_issue the binding one",
+            "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom] * n / n_launch,
             "launches_per_step": n_launch, "kernel_ms_per_step": stages[dom], "stage_ms": stages,
             "stage_algorithmic_bytes_per_frame": alg}
@@ -175,4 +198,4 @@ def bench_extract(args, B, rank, world, local, dist):
     roof_pipe = {"bound": "hbm", "achieved": pipe, "peak": peak, "unit": "GB/s", "frac": pipe / peak,
                  "algorithmic_bytes_per_frame": b_alg, "note": "SURVEY 8d B_alg x frames/s per GPU"}
     return dict(h2d_gbs=h2d_gbs, h2d_ceiling_fps=h2d_ceiling_fps, fps=fps, ms=ms, e2e=e2e_fps, h2d=int(host.nbytes), d2h=int(n * cap * 60 + 4 * n), launches=launches,
-                clocks=clocks, roofline=roof, roofline_pipeline=roof_pipe, n_kp=n_kp, n_cand=n_cand, host=host, ext=ext)
+                clocks=clocks, roofline=roof, roofline_issue=roof_issue, roofline_pipeline=roof_pipe, n_kp=n_kp, n_cand=n_cand, host=host, ext=ext)

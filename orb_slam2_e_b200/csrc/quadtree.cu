@@ -24,7 +24,10 @@ namespace orbfront {
 constexpr int kQtThreads = 256;       // batches: many small CTAs per SM hide each other's latency
 constexpr int kQtThreadsWide = 1024;  // one or a few frames: a level's CTA is the critical path, so it gets 4x the lanes
 
-#ifdef ORBX_QT_PROFILE  // developer build: cycle stamps of the level-0 CTA of frame 0 (tools/exp_qt_profile.py)
+#ifdef ORBX_QT_PROFILE2  // developer build: cycles per phase summed over all CTAs, by level (tools/exp_qt_profile2.py)
+__device__ unsigned long long g_qt_acc[16][12];
+#define QT_STAMP(k) do { if (threadIdx.x == 0) qt_st[k] = clock64(); } while (0)
+#elif defined(ORBX_QT_PROFILE)  // developer build: cycle stamps of the level-0 CTA of frame 0 (tools/exp_qt_profile.py)
 __device__ long long g_qt_prof[32];
 #define QT_STAMP(k) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_qt_prof[k] = clock64(); } while (0)
 #else
@@ -89,10 +92,18 @@ __device__ unsigned long long* radix_sort_codes(unsigned long long* a, unsigned 
   const int per_warp = ((n + T - 1) / T) * 32;
   const int lo = min(n, warp * per_warp), hi = min(n, lo + per_warp);
   for (int shift = 32; shift < 32 + nbits; shift += 8) {
+#ifdef ORBX_QT_PROFILE2
+    long long r0 = clock64();
+#define RSTAMP(k) do { if (tid == 0) { const long long t = clock64(); atomicAdd(&g_qt_acc[15][k], (unsigned long long)(t - r0)); r0 = t; } } while (0)
+#else
+#define RSTAMP(k) do { } while (0)
+#endif
     for (int i = tid; i < kWarps * 256; i += T) whist[i] = 0;
     __syncthreads();
+    RSTAMP(0);
     for (int i = lo + lane; i < hi; i += 32) atomicAdd(&whist[warp * 256 + (int)((a[i] >> shift) & 255u)], 1u);
     __syncthreads();
+    RSTAMP(1);
     if constexpr (kWarps <= 8) {  // T == 256: one thread per digit value, the warps' counts stay in registers
       uint32_t c[kWarps], tot = 0;
 #pragma unroll
@@ -113,6 +124,7 @@ __device__ unsigned long long* radix_sort_codes(unsigned long long* a, unsigned 
       }
     }
     __syncthreads();
+    RSTAMP(2);
     for (int i0 = lo; i0 < hi; i0 += 32) {
       const int i = i0 + lane;
       const bool act = i < hi;
@@ -130,6 +142,7 @@ __device__ unsigned long long* radix_sort_codes(unsigned long long* a, unsigned 
       __syncwarp();
     }
     __syncthreads();
+    RSTAMP(3);
     unsigned long long* t = a; a = b; b = t;
   }
   return a;
@@ -164,6 +177,9 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   uint8_t* s_b = ngain + NP;
   QtCtl& C = *reinterpret_cast<QtCtl*>(smem + align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16));  // NP >= 512: radix counters alias the node tables
 
+#ifdef ORBX_QT_PROFILE2
+  long long qt_st[10];
+#endif
   QT_STAMP(0);
   int n = P.cand_count[f * P.nlevels + l];
   n = min(n, G.cand_cap);
@@ -221,21 +237,25 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
 
   QT_STAMP(3);
   // replay of the reference's pass loop (ORBextractor.cc:593-739) on the tables
-  if (tid == 0) {
-    int acc = 0, acc2 = 0;
-    for (int d = 0; d <= dmax + 1; ++d) {
-      acc += C.hist[d]; acc2 += C.dlt[d];
-      C.cnt[d] = d <= dmax ? acc : C.cnt[dmax];
-      C.nexp[d] = d <= dmax ? acc2 : 0;
+  if (tid < 32) {  // lane <-> depth (kMaxDepth + 3 <= 32): prefix sums by shuffles, the stop rules of every pass at once
+    const int dd = tid;
+    int c = dd <= dmax ? C.hist[dd] : 0, e = dd <= dmax ? C.dlt[dd] : 0;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) {
+      const int oc = __shfl_up_sync(0xffffffffu, c, s), oe = __shfl_up_sync(0xffffffffu, e, s);
+      if (dd >= s) { c += oc; e += oe; }
     }
-    int d = 0, size = C.cnt[0], mode = kModeFull;
-    while (true) {
-      const int prev = size;
-      if (d < dmax) { ++d; size = C.cnt[d]; }     // one breadth-first pass: split every divisible node
-      if (size >= N || size == prev) break;        // :669
-      if (size + 3 * C.nexp[d] > N) { mode = kModeOrdered; break; }  // :673
-    }
-    C.d = d; C.size = size; C.mode = mode; C.d_bfs = d; C.partial = 0;
+    if (dd > dmax) e = 0;  // cnt[d > dmax] = cnt[dmax] (the scan of zeros), nexp[d > dmax] = 0
+    if (dd < kMaxDepth + 3) { C.cnt[dd] = c; C.nexp[dd] = e; }
+    // pass d (1..dmax) ends the loop if the list reached N nodes or did not grow (:669), or if the next pass could
+    // overshoot (:673); if no pass does, the loop ends at dmax because the list no longer grows
+    const int prev = __shfl_up_sync(0xffffffffu, c, 1);
+    const bool stop = c >= N || c == prev, ordered = !stop && c + 3 * e > N;
+    const uint32_t m = __ballot_sync(0xffffffffu, dd >= 1 && dd <= dmax && (stop || ordered));
+    const int d = m ? __ffs(m) - 1 : dmax;
+    const int size = __shfl_sync(0xffffffffu, c, d);
+    const int mode = m && __shfl_sync(0xffffffffu, (int)ordered, d) ? kModeOrdered : kModeFull;
+    if (tid == 0) { C.d = d; C.size = size; C.mode = mode; C.d_bfs = d; C.partial = 0; }
   }
   __syncthreads();
 
@@ -357,6 +377,13 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   for (int m = tid; m < L; m += T) kept[m] = nval[m];
   if (tid == 0) P.kept_count[f * P.nlevels + l] = L;
   QT_STAMP(9);
+#ifdef ORBX_QT_PROFILE2
+  if (tid == 0) {
+    for (int k = 0; k < 9; ++k) atomicAdd(&g_qt_acc[l][k], (unsigned long long)(qt_st[k + 1] - qt_st[k]));
+    atomicAdd(&g_qt_acc[l][9], 1ull);
+    atomicAdd(&g_qt_acc[l][10], (unsigned long long)n);
+  }
+#endif
 #ifdef ORBX_QT_PROFILE
   if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) { g_qt_prof[10] = n; g_qt_prof[11] = L; g_qt_prof[12] = C.d_bfs; g_qt_prof[13] = C.d; g_qt_prof[14] = dmax; g_qt_prof[15] = nbits; }
 #endif
@@ -383,6 +410,9 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
   S = std::max(S, NP);             // node arrays alias nothing, but n_nodes <= n keys
   const int smem = quadtree_smem_bytes(S, NP);
   if (smem > 227 * 1024) return set_error(ORB_E_INVALID, "quadtree: %d bytes of shared memory needed (nfeatures too large)", smem);
+  // (measured, round 2: a second launch with twice the shared-memory keys for the levels that overflow S -- the two
+  // largest of a textured 640x480 frame -- makes those CTAs 30 % shorter but runs them at 4 per SM: 0.605 vs 0.613 ms
+  // for the kernel and a worse overlap with the blur; not kept.  tools/exp_qt_profile2.py has the per-phase cycles.)
   if (wide) {
     ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel<kQtThreadsWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     quadtree_select_kernel<kQtThreadsWide><<<dim3(P.nlevels, P.n_frames), kQtThreadsWide, smem, s>>>(P, S, NP);
@@ -397,6 +427,15 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
 
 }  // namespace orbfront
 
+#ifdef ORBX_QT_PROFILE2
+extern "C" int orbx_debug_qt_acc(unsigned long long* out) {
+  cudaDeviceSynchronize();
+  static unsigned long long zero[16 * 12];
+  cudaMemcpyFromSymbol(out, orbfront::g_qt_acc, sizeof(zero));
+  cudaMemcpyToSymbol(orbfront::g_qt_acc, zero, sizeof(zero));
+  return 0;
+}
+#endif
 #ifdef ORBX_QT_PROFILE
 extern "C" int orbx_debug_qt_prof(long long* out) {
   cudaDeviceSynchronize();
