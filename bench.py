@@ -313,6 +313,9 @@ def run_gpu_arm(args):
             "e2e": {"value": ex["e2e"], "unit": "frames/s", "h2d_bytes_per_step": ex["h2d"], "d2h_bytes_per_step": ex["d2h"],
                     "h2d_ceiling_gbs": ex["h2d_gbs"], "h2d_ceiling_frames_s": ex["h2d_ceiling_fps"],
                     "frac_of_h2d_ceiling": ex["e2e"] / ex["h2d_ceiling_fps"],
+                    "duplex_ceiling_frames_s": ex["duplex_ceiling_fps"], "frac_of_duplex_ceiling": ex["e2e"] / ex["duplex_ceiling_fps"],
+                    "duplex_ceiling_note": "the same probe with the step's result bytes copied device-to-host at the same time: what the host link "
+                                           "carries when both directions of the e2e call run with no kernels",
                     "h2d_ceiling_note": "copy-only probe in this run: the step's frames from the same pinned buffer, no kernels, "
                                         "all ranks at once, max over ranks (aggregate GB/s)"},
             "gpu_launches": ex["launches"] + (match["gpu_launches"] if match else 0),

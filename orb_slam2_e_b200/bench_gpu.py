@@ -150,7 +150,30 @@ def bench_extract(args, B, rank, world, local, dist):
     _barrier(dist)
     h2d_gbs = world * host.nbytes / (h2d_ms * 1e-3) / 1e9
     h2d_ceiling_fps = world * n / (h2d_ms * 1e-3)
-    del probe
+    # the same with the step's results going the other way at the same time (the e2e call moves both): on a host whose
+    # root complex / memory is the limit (8 GPUs) the two directions share it
+    out_dev = torch.empty(n * cap * 60 + 4 * n, dtype=torch.uint8, device=dev.device)
+    out_pin = torch.empty(n * cap * 60 + 4 * n, dtype=torch.uint8).pin_memory()
+    cs2 = torch.cuda.Stream(device=local)
+    q0, q1, q2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    _barrier(dist)
+    q0.record(cs)
+    cs2.wait_event(q0)
+    with torch.cuda.stream(cs):
+        for _ in range(reps):
+            probe.copy_(pin_in, non_blocking=True)
+        q1.record(cs)
+    with torch.cuda.stream(cs2):
+        for _ in range(reps):
+            out_pin.copy_(out_dev, non_blocking=True)
+        q2.record(cs2)
+    q1.synchronize()
+    q2.synchronize()
+    duplex_ms = _max_over_ranks(max(q0.elapsed_time(q1), q0.elapsed_time(q2)), dist, local) / reps
+    _barrier(dist)
+    duplex_fps = world * n / (duplex_ms * 1e-3)
+    del probe, out_dev, out_pin
     sampler.stop()
 
     # ---- roofline of the dominant kernel + of the whole pipeline
@@ -197,5 +220,5 @@ def bench_extract(args, B, rank, world, local, dist):
     pipe = b_alg * world * n * args.steps / (ms * 1e-3) / 1e9 / world
     roof_pipe = {"bound": "hbm", "achieved": pipe, "peak": peak, "unit": "GB/s", "frac": pipe / peak,
                  "algorithmic_bytes_per_frame": b_alg, "note": "SURVEY 8d B_alg x frames/s per GPU"}
-    return dict(h2d_gbs=h2d_gbs, h2d_ceiling_fps=h2d_ceiling_fps, fps=fps, ms=ms, e2e=e2e_fps, h2d=int(host.nbytes), d2h=int(n * cap * 60 + 4 * n), launches=launches,
+    return dict(h2d_gbs=h2d_gbs, h2d_ceiling_fps=h2d_ceiling_fps, duplex_ceiling_fps=duplex_fps, fps=fps, ms=ms, e2e=e2e_fps, h2d=int(host.nbytes), d2h=int(n * cap * 60 + 4 * n), launches=launches,
                 clocks=clocks, roofline=roof, roofline_issue=roof_issue, roofline_pipeline=roof_pipe, n_kp=n_kp, n_cand=n_cand, host=host, ext=ext)
