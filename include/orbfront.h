@@ -45,7 +45,8 @@ typedef struct orbx_handle orbx_handle;
 
 /* ORBextractor::ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST,
  * int minThFAST) -- reference: include/ORBextractor.h:53-54, src/ORBextractor.cc:410-470.
- * device/max_* size the device buffers once; frames larger than max_* are rejected. */
+ * device/max_* size the device buffers once; with max_* > 0 a larger frame or batch is rejected with
+ * ORB_E_INVALID by every extract call (no reallocation on the hot path); max_* = 0 lets the buffers grow on demand. */
 typedef struct {
   int nfeatures;
   float scale_factor;
@@ -86,7 +87,10 @@ int orbx_extract(orbx_handle* h, const uint8_t* img, int w, int ht, size_t strid
 /* Batched form (frames are independent): n frames of identical size, frame f at
  * imgs + f*frame_stride.  memory = 0: imgs is host memory (pinned or pageable), copied inside
  * the call.  memory = 1: imgs is device memory on the handle's device.  Results stay on the
- * device until read. */
+ * device until read.  Lifetime with memory = 1: frames whose stride and frame_stride are multiples of 16 are
+ * read IN PLACE as pyramid level 0, also after the call returns (orbx_get_level(level 0), orbx_get_pyramid_host,
+ * orbx_stereo_matches[_batch]); the buffer must stay valid and unmodified until the next extract call on the
+ * handle or its destruction.  Other layouts are copied into the handle. */
 int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs, int n, int w, int ht, size_t stride,
                        size_t frame_stride, int memory);
 /* Blocks until the batch is done; counts[f] = keypoints of frame f. */

@@ -704,11 +704,17 @@ int orbm_db_append(orbm_db* db, const uint8_t* rows, int64_t n, int memory) {
   int rc = use_device(db->device);
   if (rc) return rc;
   if (db->n + n > db->cap) {
-    int64_t ncap = std::max<int64_t>(db->n + n, db->cap + db->cap / 2);
+    // grow by half (at least to what is needed, at least 64 K rows = 2 MB): a shard built by many small appends is
+    // not reallocated and recopied at every call
+    int64_t ncap = std::max<int64_t>(std::max<int64_t>(db->n + n, db->cap + db->cap / 2), 1 << 16);
     uint4* np = nullptr;
     ORB_CUDA_TRY(cudaMalloc(&np, (size_t)ncap * 32));
-    if (db->n) ORB_CUDA_TRY(cudaMemcpyAsync(np, db->rows, (size_t)db->n * 32, cudaMemcpyDeviceToDevice, db->stream));
-    ORB_CUDA_TRY(cudaStreamSynchronize(db->stream));
+    cudaError_t ce = db->n ? cudaMemcpyAsync(np, db->rows, (size_t)db->n * 32, cudaMemcpyDeviceToDevice, db->stream) : cudaSuccess;
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(db->stream);
+    if (ce != cudaSuccess) {  // the shard keeps its old rows
+      cudaFree(np);
+      return set_error(ORB_E_CUDA, "orbm_db_append: %s", cudaGetErrorString(ce));
+    }
     if (db->rows) cudaFree(db->rows);
     db->rows = np;
     db->cap = ncap;
