@@ -2,6 +2,7 @@
 // mbarrier / TMA bulk-copy wrappers for sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>  // header-only: ranges are no-ops unless a profiler injects the NVTX library
 
 #include <atomic>
 #include <cstdarg>
@@ -35,6 +36,15 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 
 // Selects the device; ORB_E_NO_DEVICE when there is none (no CPU fallback anywhere).
 int use_device(int device);
+
+// NVTX range around one stage / entry point on the calling host thread (tracing); kernels launched
+// inside show up under it in a timeline
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // Per-thread, per-device scratch of the small host-buffer entry points (SearchByBoW, stereo search,
 // pairwise distances): a grow-only device buffer, a page-locked host mirror of the same size and a

@@ -220,6 +220,7 @@ orient_describe_kernel(const __grid_constant__ ExtractParams P, int slots_per_fr
 }
 
 int launch_describe(const ExtractParams& P, cudaStream_t s, int* launches) {
+  NvtxRange nvtx_range("orbx:describe");
   const LevelGeom& last = P.lv[P.nlevels - 1];
   const int slots = last.kept_off + last.kept_cap;
   orient_describe_kernel<<<dim3(div_up(slots, kDescWarps * kKpPerWarp), P.n_frames), kDescWarps * 32, 0, s>>>(P, slots);

@@ -450,6 +450,7 @@ static int run_stages(orbx_handle* H, const ExtractParams& Q, cudaStream_t cs, i
 
 int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht, size_t stride, size_t frame_stride,
                        int memory) {
+  NvtxRange nvtx_range("orbx_extract_batch");
   if (!H || n < 0 || (memory != 0 && memory != 1)) return set_error(ORB_E_INVALID, "orbx_extract_batch: bad argument");
   H->counts_valid = false;
   if (n == 0 || !imgs || w <= 0 || ht <= 0) {  // empty image: nothing to do (ORBextractor.cc:1054-1055)
@@ -512,6 +513,7 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
 
 int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht, size_t stride, size_t frame_stride,
                             orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts, int chunk_frames) {
+  NvtxRange nvtx_range("orbx_extract_batch_host");
   if (!H || n < 0 || !counts || (n > 0 && (!kps || !desc))) return set_error(ORB_E_INVALID, "orbx_extract_batch_host: bad argument");
   H->counts_valid = false;
   if (n == 0 || !imgs || w <= 0 || ht <= 0) {

@@ -316,6 +316,7 @@ static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) 
 }
 
 int launch_fast(const ExtractParams& P, cudaStream_t s, int* launches) {
+  NvtxRange nvtx_range("orbx:fast");
   int max_w = 1, max_h = 1;
   for (int l = 0; l < P.nlevels; ++l) { max_w = std::max(max_w, P.lv[l].wCell); max_h = std::max(max_h, P.lv[l].hCell); }
   if (max_w >= kCellMax || max_h >= kCellMax) return set_error(ORB_E_INVALID, "FAST cell %dx%d exceeds %d", max_w, max_h, kCellMax - 1);

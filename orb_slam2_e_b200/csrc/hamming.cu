@@ -744,6 +744,7 @@ int orbm_db_destroy(orbm_db* db) {
 }
 
 int orbm_top2_search(orbm_db* db, const uint8_t* q, int nq, orbm_top2* out, int memory) {
+  NvtxRange nvtx_range("orbm_top2_search");
   if (!db || nq < 0 || (nq > 0 && (!q || !out))) return set_error(ORB_E_INVALID, "orbm_top2_search: bad argument");
   if (nq == 0) return ORB_OK;
   int rc = use_device(db->device);
@@ -1732,6 +1733,7 @@ int orbm_group_create_local(orbm_db* const* shards, int n_shards, orbm_group** o
 }
 
 int orbm_group_search(orbm_group* g, const uint8_t* q, int nq, float ratio, int th, orbm_top2* out, uint8_t* accept) {
+  NvtxRange nvtx_range("orbm_group_search");
   if (!g || nq < 0 || (nq > 0 && (!q || !out))) return set_error(ORB_E_INVALID, "orbm_group_search: bad argument");
   if (nq == 0) return ORB_OK;
   const NcclApi* N;

@@ -238,6 +238,7 @@ static int launch_levels(const ExtractParams& P, cudaStream_t s, int* launches) 
 }
 
 int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches) {
+  NvtxRange nvtx_range("orbx:pyramid");
   if (P.nlevels < 2) return ORB_OK;
   const LevelGeom& D = P.lv[1];
   // warps the largest level offers with long strips; below about one warp per scheduler slot the
@@ -376,6 +377,7 @@ blur_kernel(const __grid_constant__ ExtractParams P, const int* __restrict__ til
 }
 
 int launch_blur(const ExtractParams& P, cudaStream_t s, int* launches, bool after_quadtree) {
+  NvtxRange nvtx_range("orbx:blur");
   // blur_tiles (extractor.cu) is built for kBlurTH-row tiles; a few frames use kBlurTHFew-row tiles, whose
   // table is the second half of the same array
   const bool few = (long)P.n_frames * blur_warp_tiles(P.lv[0].w, P.lv[0].h, kBlurTH) < 2 * 148;

@@ -394,6 +394,7 @@ int quadtree_smem_bytes(int S, int NP) {
 }
 
 int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
+  NvtxRange nvtx_range("orbx:quadtree");
   int nmax = 1;
   for (int l = 0; l < P.nlevels; ++l) nmax = std::max(nmax, P.lv[l].kept_cap);
   // One or a few frames (at most two CTAs per SM in all): every (frame, level) CTA runs at once and the
