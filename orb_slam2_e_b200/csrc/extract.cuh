@@ -34,6 +34,8 @@ struct LevelGeom {
   uint32_t rcp_nCols;       // 2^32 / nCols + 1: x / nCols == __umulhi(x, rcp_nCols) while x * nCols < 2^32
   // quadtree (ORBextractor.cc:539-563)
   int boxW, boxH, nIni, quota, dmax;
+  int qt_d0;                // depth of the finest grid of the sort-free quadtree kernel (0: this level always takes the sorting kernel)
+  int qt_counts_global;     // its per-cell key counts live in the level's global scratch instead of shared memory (large quotas)
   float hX;
   // capacities / offsets (entries) inside one frame's cand / kept blocks
   int cand_cap, cand_off, kept_cap, kept_off;

@@ -178,6 +178,19 @@ int configure(orbx_handle* H, int w, int h, int n_frames, bool own_l0) {
       G.cand_cap = (int)align_up<size_t>((size_t)((vw + 1) / 2 + G.nCols) * ((vh + 1) / 2 + G.nRows), 4);  // NMS survivors: <= one per 2x2 block of a cell
       G.cand_off = cand_off;
       cand_off += G.cand_cap;
+      {  // sort-free quadtree (quadtree.cu): finest grid of about 6 x quota cells; the loop must be able to end one depth above it
+        int rb = 0;
+        while ((1 << rb) < G.nIni) ++rb;
+        const long long R = 1ll << rb, N = std::max(G.quota, 1);
+        int d0 = 2;
+        while (d0 < G.dmax && (R << (2 * d0)) < 6 * N) ++d0;
+        const long long cells = R << (2 * d0), total = cells * 4 / 3 + 8;
+        // scratch of the level: sequence numbers (u32 per pyramid cell) then, for large grids, the u16 counts; best keys (u64 per finest cell)
+        const bool fits = d0 >= 2 && d0 <= G.dmax && (R << (2 * (d0 - 1))) * 2 >= 3 * N && total * 6 + 64 <= (long long)G.cand_cap * 4 && cells <= G.cand_cap &&
+                          cells <= (1 << 18);
+        G.qt_d0 = fits ? d0 : 0;
+        G.qt_counts_global = fits && total > 12288 ? 1 : 0;  // up to 24 KB of shared-memory counters
+      }
       G.kept_cap = std::max(G.quota, 0) + 4 * G.nIni + 3;
       G.kept_off = kept_off;
       kept_off += G.kept_cap;

@@ -33,6 +33,7 @@ __device__ long long g_qt_prof[32];
 #else
 #define QT_STAMP(k) do { } while (0)
 #endif
+__device__ unsigned int g_qt_handed_back;  // (frame, level) pairs the sort-free kernel handed to the sorting kernel (orbx_debug_qt_handed_back)
 constexpr uint32_t kSeqMark = 0x8000u;  // "head of a child created by the final partial pass"
 
 struct QtCtl {  // control block in shared memory
@@ -161,7 +162,7 @@ __device__ __forceinline__ uint32_t bfs_creation_key(uint32_t code, int k, int d
 
 template <int T>
 __global__ void __launch_bounds__(T)
-quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
+quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP, int only_flagged) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
   const LevelGeom& G = P.lv[l];
@@ -181,6 +182,8 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
   long long qt_st[10];
 #endif
   QT_STAMP(0);
+  if (only_flagged && P.kept_count[f * P.nlevels + l] != -1) return;  // done by quadtree_pyramid_kernel
+  if (only_flagged && tid == 0) atomicAdd(&g_qt_handed_back, 1u);
   int n = P.cand_count[f * P.nlevels + l];
   n = min(n, G.cand_cap);
   uint32_t* kept = P.kept + (size_t)f * P.kept_frame + G.kept_off;
@@ -389,6 +392,229 @@ quadtree_select_kernel(const __grid_constant__ ExtractParams P, int S, int NP) {
 #endif
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Round 2: the same selection WITHOUT sorting the candidates, for the common case that the reference's loop ends at a
+// shallow depth.  Everything the replay, the ordered passes and the leaf selection need is a function of per-node key
+// counts and per-node best keys, and the nodes of depth d are the cells of a 2^d x 2^d grid per root (index = the path
+// code's prefix).  So: one pass of shared-memory atomics counts the candidates per cell of the depth-D0 grid and keeps
+// each cell's best key with a 64-bit atomicMax; the coarser grids are sums of four children; cnt[d] / nexp[d] are the
+// numbers of cells with >= 1 / >= 2 keys; an ordered pass enumerates the cells of depth d with >= 2 keys (children =
+// non-empty cells below them); a leaf's best key is the maximum over its depth-D0 descendants, and the depth at which a
+// single key became alone is found by walking up while the parent still holds one key.  D0 is chosen per level on the
+// host (about 6 x quota cells).  Whenever the loop would need depth D0 + 1 (sparse or clustered levels, very large
+// quotas), the CTA writes kept_count = -1 and the sorting kernel above redoes that (frame, level): results are
+// identical either way, only the time differs.  Replaces three radix passes, the boundary pass and two serial run
+// walks per candidate set: the level-0 CTA of a textured 640x480 frame took 205 k cycles with the sorting kernel.
+
+__host__ __device__ inline int qp_level_off(int R, int D0, int d) {  // first cell of depth d in the pyramid arrays: D0 first (word aligned), then D0-1 .. 0
+  int off = 0;
+  for (int k = D0; k > d; --k) off += R << (2 * k);
+  return off;
+}
+
+template <int T>
+__global__ void __launch_bounds__(T)
+quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int count_words, int split_words, int min_ratio4) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int l = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
+  const LevelGeom& G = P.lv[l];
+  const int N = G.quota, dmax = G.dmax, D0 = G.qt_d0;
+  int* const kc = &P.kept_count[f * P.nlevels + l];
+  int n = min(P.cand_count[f * P.nlevels + l], G.cand_cap);
+  if (n == 0) { if (tid == 0) *kc = 0; return; }
+  // sparse levels (few candidates per wanted keypoint) end deep in the tree: not worth trying here
+  if (D0 <= 0 || n >= 65535 || 4ll * n < (long long)min_ratio4 * N) { if (tid == 0) *kc = -1; return; }  // the sorting kernel takes this level
+
+  uint32_t* split = reinterpret_cast<uint32_t*>(smem) + count_words;   // bitmap over the cells of one depth: split by the final partial pass
+  unsigned long long* nkey = reinterpret_cast<unsigned long long*>(split + split_words);
+  uint32_t* nval = reinterpret_cast<uint32_t*>(nkey + NP);
+  uint32_t* nhead = nval + NP;
+  uint8_t* ngain = reinterpret_cast<uint8_t*>(nhead + NP);
+  QtCtl& C = *reinterpret_cast<QtCtl*>(smem + align_up<size_t>((size_t)count_words * 4 + (size_t)split_words * 4 + (size_t)NP * 17, 16));
+  int root_bits = 0;
+  while ((1 << root_bits) < G.nIni) ++root_bits;
+  const int R = 1 << root_bits;
+  const int cellsD0 = R << (2 * D0);
+  const int total_cells = qp_level_off(R, D0, 0) + R, my_words = (total_cells + 3) / 4 * 2;
+  const unsigned long long* gkeys = P.cand + (size_t)f * P.cand_frame + G.cand_off;
+  unsigned long long* best = P.qt_tmp + (size_t)f * P.cand_frame + G.cand_off;   // best key of every depth-D0 cell
+  uint32_t* seq = P.qt_seq + (size_t)f * P.cand_frame + G.cand_off;              // creation sequence per pyramid cell (written before read)
+  // key counts, u16 per cell, whole pyramid: shared memory, or (large grids) the level's global scratch behind the sequence numbers
+  uint32_t* cw = G.qt_counts_global ? seq + (total_cells + 3) / 4 * 4 : reinterpret_cast<uint32_t*>(smem);
+  uint16_t* c16 = reinterpret_cast<uint16_t*>(cw);
+  uint32_t* kept = P.kept + (size_t)f * P.kept_frame + G.kept_off;
+  const uint32_t mag_h = (1u << 20) / (uint32_t)G.hCell + 1u, mag_w = (1u << 20) / (uint32_t)G.wCell + 1u;
+
+  for (int i = tid; i < my_words; i += T) cw[i] = 0;
+  for (int i = tid; i < split_words; i += T) split[i] = 0;
+  for (int i = tid; i < cellsD0; i += T) best[i] = 0ull;
+  for (int i = tid; i < kMaxDepth + 3; i += T) { C.cnt[i] = 0; C.nexp[i] = 0; }
+  __syncthreads();
+  // one pass over the candidates: count and best key per depth-D0 cell
+  const int shD0 = 2 * (dmax - D0);
+  for (int i = tid; i < n; i += T) {
+    const uint32_t pay = (uint32_t)gkeys[i];
+    const int x = pay & 0xfff, y = (pay >> 12) & 0xfff;
+    const uint32_t code = __ldg(&P.qcode[G.qx + x]) | __ldg(&P.qcode[G.qy + y]);
+    const uint32_t c = code >> shD0;
+    atomicAdd(&cw[c >> 1], 1u << ((c & 1u) * 16));
+    // highest response, then earliest candidate in the reference's (cell row, cell col, y, x) detection order (:744-760)
+    const unsigned long long cell = (unsigned long long)((((uint32_t)(y - 3) * mag_h) >> 20) * (uint32_t)G.nCols + (((uint32_t)(x - 3) * mag_w) >> 20));
+    const unsigned long long order = (cell << 24) | (unsigned long long)(pay & 0xffffffu);
+    atomicMax(&best[c], ((unsigned long long)(pay >> 24) << 48) | (0xffffffffffffull - order));
+  }
+  __syncthreads();
+  // coarser grids (sums of four children) and, per depth, the number of nodes (cells with keys) and of divisible nodes
+  for (int d = D0; d >= 0; --d) {
+    const int cells = R << (2 * d), off = qp_level_off(R, D0, d), offc = d < D0 ? qp_level_off(R, D0, d + 1) : 0;
+    int nz = 0, ge2 = 0;
+    for (int c = tid; c < cells; c += T) {
+      int v;
+      if (d == D0) v = c16[off + c];
+      else {
+        const uint2 q = *reinterpret_cast<const uint2*>(&c16[offc + 4 * c]);  // four u16 children (offsets are multiples of 4 cells)
+        v = (int)(q.x & 0xffffu) + (int)(q.x >> 16) + (int)(q.y & 0xffffu) + (int)(q.y >> 16);
+        c16[off + c] = (uint16_t)v;
+      }
+      nz += v > 0;
+      ge2 += v > 1;
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { nz += __shfl_xor_sync(0xffffffffu, nz, s); ge2 += __shfl_xor_sync(0xffffffffu, ge2, s); }
+    if (lane == 0 && (nz | ge2)) { atomicAdd(&C.cnt[d], nz); atomicAdd(&C.nexp[d], ge2); }
+    __syncthreads();
+  }
+  // replay of the reference's pass loop (:593-739) on cnt[] / nexp[], depths 1 .. Dr; the loop must end there
+  const int Dr = min(D0 - 1, dmax);
+  if (tid < 32) {
+    const int dd = tid;
+    const int c = dd <= D0 ? C.cnt[dd] : 0, e = dd <= D0 ? C.nexp[dd] : 0;
+    const int prev = __shfl_up_sync(0xffffffffu, c, 1);
+    const bool stop = c >= N || c == prev, ordered = !stop && c + 3 * e > N;
+    const uint32_t m = __ballot_sync(0xffffffffu, dd >= 1 && dd <= Dr && (stop || ordered));
+    int d = -1, mode = kModeFull;
+    if (m) { d = __ffs(m) - 1; mode = __shfl_sync(0xffffffffu, (int)ordered, d) ? kModeOrdered : kModeFull; }
+    else if (Dr == dmax) d = dmax;  // the list stops growing at the last depth
+    const int size = __shfl_sync(0xffffffffu, c, max(d, 0));
+    if (tid == 0) { C.d = d; C.size = size; C.mode = mode; C.d_bfs = d; C.partial = 0; }
+  }
+  __syncthreads();
+  if (C.d < 0) { if (tid == 0) *kc = -1; return; }
+
+  // ordered passes: biggest nodes first, stop as soon as the list holds N nodes (:676-737)
+  bool first_ordered = true;
+  while (C.mode == kModeOrdered) {
+    const int d = C.d, size = C.size;
+    if (d + 1 > D0) { if (tid == 0) *kc = -1; return; }  // children below the pyramid (uniform: C.d is shared)
+    const int cells = R << (2 * d), off = qp_level_off(R, D0, d), offc = qp_level_off(R, D0, d + 1);
+    if (tid == 0) { C.counter = 0; C.mstar = 0x7fffffff; }
+    __syncthreads();
+    for (int c = tid; c < cells; c += T)
+      if (c16[off + c] > 1) nhead[atomicAdd(&C.counter, 1)] = (uint32_t)c;
+    __syncthreads();
+    const int M = C.counter;
+    int mp = 1;
+    while (mp < M) mp <<= 1;
+    for (int m = tid; m < mp; m += T) {
+      if (m >= M) { nkey[m] = ~0ull; nval[m] = 0; continue; }
+      const int c = (int)nhead[m];
+      int children = 0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) children += c16[offc + 4 * c + q] > 0;
+      ngain[m] = (uint8_t)(children - 1);
+      const uint32_t rank = first_ordered ? bfs_creation_key((uint32_t)c << (2 * (dmax - d)), d, dmax) : seq[off + c];
+      nkey[m] = ~(((unsigned long long)c16[off + c] << 32) | rank);  // ascending ~key == (count, rank) descending
+      nval[m] = (uint32_t)m;
+    }
+    __syncthreads();
+    bitonic_sort<T>(nkey, nval, mp);
+    int carried = 0;
+    for (int base = 0; base < M; base += T) {  // where does the running node count reach N?
+      const int j = base + tid;
+      const int g = j < M ? ngain[nval[j]] : 0;
+      const int incl = block_inclusive_scan<T>(g, C) + carried;
+      if (j < M && size + incl >= N) atomicMin(&C.mstar, j);
+      carried += C.scan_total;
+      __syncthreads();
+    }
+    const bool stops = C.mstar != 0x7fffffff;
+    const int n_split = stops ? C.mstar + 1 : M;
+    // the split nodes' children get their creation sequence (parent's place in the order, quadrant)
+    for (int j = tid; j < n_split; j += T) {
+      const int c = (int)nhead[nval[j]];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (c16[offc + 4 * c + q] > 0) seq[offc + 4 * c + q] = (uint32_t)j << 2 | (uint32_t)q;
+      if (stops) atomicOr(&split[c >> 5], 1u << (c & 31));
+    }
+    __syncthreads();
+    if (tid == 0) {
+      if (stops) { C.partial = 1; C.mode = kModeFull; }
+      else {
+        const int nsize = C.cnt[d + 1];
+        C.d = d + 1; C.size = nsize;
+        if (nsize >= N || nsize == size || d + 1 >= dmax) C.mode = kModeFull;  // :735
+      }
+    }
+    first_ordered = false;
+    __syncthreads();
+  }
+
+  // leaves: the nodes of depth dfin, and the children of those split by the final partial pass
+  const int dfin = C.d, partial = C.partial, d_bfs = C.d_bfs;
+  if (dfin + partial > D0 || 2 * (D0 - dfin) > 8) { if (tid == 0) *kc = -1; return; }  // (leaf scans cover at most 256 depth-D0 cells)
+  {
+    const int cells = R << (2 * dfin), off = qp_level_off(R, D0, dfin), offc = partial ? qp_level_off(R, D0, dfin + 1) : 0;
+    if (tid == 0) C.counter = 0;
+    __syncthreads();
+    for (int c = tid; c < cells; c += T) {
+      if (c16[off + c] == 0) continue;
+      if (partial && (split[c >> 5] >> (c & 31) & 1u)) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (c16[offc + 4 * c + q] > 0) nhead[min(atomicAdd(&C.counter, 1), NP - 1)] = (uint32_t)(4 * c + q) | 0x80000000u;
+      } else {
+        nhead[min(atomicAdd(&C.counter, 1), NP - 1)] = (uint32_t)c;
+      }
+    }
+    __syncthreads();
+  }
+  const int L = min(C.counter, G.kept_cap);
+  int lp = 1;
+  while (lp < L) lp <<= 1;
+  for (int m = tid; m < lp; m += T) {
+    if (m >= L) { nkey[m] = ~0ull; nval[m] = 0; continue; }
+    const uint32_t hd = nhead[m];
+    const int dl = dfin + (int)(hd >> 31);  // leaf depth
+    const int c = (int)(hd & 0x7fffffffu);
+    const int count = c16[qp_level_off(R, D0, dl) + c];
+    // best key of the leaf: maximum over its depth-D0 cells
+    unsigned long long bk = 0;
+    const int span = 1 << (2 * (D0 - dl));
+    for (int k = 0; k < span; ++k) bk = max(bk, best[(size_t)c * span + k]);
+    const uint32_t best_pay = (uint32_t)(bk >> 48) << 24 | (uint32_t)(0xffffffu - (uint32_t)(bk & 0xffffffull));
+    // depth at which this list node was created: a single key became alone where its ancestors stop holding one key
+    int created = dl;
+    if (count == 1)
+      while (created > 0 && c16[qp_level_off(R, D0, created - 1) + (c >> (2 * (dl - created + 1)))] == 1) --created;
+    const int ca = c >> (2 * (dl - created));  // ancestor cell at that depth
+    unsigned long long within;
+    if (created == 0) within = (unsigned long long)ca;  // single-key roots keep their push_back order
+    else if (created <= d_bfs) within = 0xffffffffull - bfs_creation_key((uint32_t)ca << (2 * (dmax - created)), created, dmax);
+    else within = 0xffffffffull - seq[qp_level_off(R, D0, created) + ca];
+    nkey[m] = ((unsigned long long)(31 - created) << 40) | within;
+    nval[m] = best_pay;
+  }
+  __syncthreads();
+  bitonic_sort<T>(nkey, nval, lp);
+  for (int m = tid; m < L; m += T) kept[m] = nval[m];
+  if (tid == 0) *kc = L;
+}
+
+int quadtree_pyramid_smem_bytes(int count_words, int split_words, int NP) {
+  return (int)(align_up<size_t>((size_t)count_words * 4 + (size_t)split_words * 4 + (size_t)NP * 17, 16) + sizeof(QtCtl));
+}
+
 int quadtree_smem_bytes(int S, int NP) {
   return (int)(align_up<size_t>((size_t)S * 10 + (size_t)NP * 17 + S + 1, 16) + sizeof(QtCtl));
 }
@@ -414,12 +640,40 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
   // (measured, round 2: a second launch with twice the shared-memory keys for the levels that overflow S -- the two
   // largest of a textured 640x480 frame -- makes those CTAs 30 % shorter but runs them at 4 per SM: 0.605 vs 0.613 ms
   // for the kernel and a worse overlap with the blur; not kept.  tools/exp_qt_profile2.py has the per-phase cycles.)
+  // the sort-free kernel first; the sorting kernel then redoes the (frame, level) pairs it handed back (kept_count == -1)
+  static const bool no_pyramid = getenv("ORBX_QT_NO_PYRAMID") != nullptr;
+  int cells_max = 0, split_words = 1;
+  bool any_level = false;
+  for (int l = 0; l < P.nlevels; ++l) {
+    int rb = 0;
+    while ((1 << rb) < P.lv[l].nIni) ++rb;
+    if (P.lv[l].qt_d0 > 0) {
+      any_level = true;
+      split_words = std::max(split_words, (((1 << rb) << (2 * P.lv[l].qt_d0)) / 4 + 31) / 32);
+      if (!P.lv[l].qt_counts_global) cells_max = std::max(cells_max, qp_level_off(1 << rb, P.lv[l].qt_d0, 0) + (1 << rb));
+    }
+  }
+  const int only_flagged = (!no_pyramid && any_level) ? 1 : 0;
+  static const int min_ratio4 = getenv("ORBX_QP_RATIO4") ? atoi(getenv("ORBX_QP_RATIO4")) : 12;  // candidates per wanted keypoint x 4 below which the sort-free kernel does not try
+  if (only_flagged) {
+    const int count_words = (cells_max + 3) / 4 * 2;
+    const int psmem = quadtree_pyramid_smem_bytes(count_words, split_words, NP);
+    if (wide) {
+      ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_pyramid_kernel<kQtThreadsWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem));
+      quadtree_pyramid_kernel<kQtThreadsWide><<<dim3(P.nlevels, P.n_frames), kQtThreadsWide, psmem, s>>>(P, NP, count_words, split_words, min_ratio4);
+    } else {
+      ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_pyramid_kernel<kQtThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem));
+      quadtree_pyramid_kernel<kQtThreads><<<dim3(P.nlevels, P.n_frames), kQtThreads, psmem, s>>>(P, NP, count_words, split_words, min_ratio4);
+    }
+    ORB_LAUNCH_CHECK();
+    ++*launches;
+  }
   if (wide) {
     ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel<kQtThreadsWide>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    quadtree_select_kernel<kQtThreadsWide><<<dim3(P.nlevels, P.n_frames), kQtThreadsWide, smem, s>>>(P, S, NP);
+    quadtree_select_kernel<kQtThreadsWide><<<dim3(P.nlevels, P.n_frames), kQtThreadsWide, smem, s>>>(P, S, NP, only_flagged);
   } else {
     ORB_CUDA_TRY(cudaFuncSetAttribute(quadtree_select_kernel<kQtThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    quadtree_select_kernel<kQtThreads><<<dim3(P.nlevels, P.n_frames), kQtThreads, smem, s>>>(P, S, NP);
+    quadtree_select_kernel<kQtThreads><<<dim3(P.nlevels, P.n_frames), kQtThreads, smem, s>>>(P, S, NP, only_flagged);
   }
   ORB_LAUNCH_CHECK();
   ++*launches;
@@ -427,6 +681,15 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
 }
 
 }  // namespace orbfront
+
+// developer counter: how many (frame, level) pairs needed the sorting kernel since the last call (resets)
+extern "C" int orbx_debug_qt_handed_back(unsigned int* out) {
+  cudaDeviceSynchronize();
+  unsigned int zero = 0;
+  if (cudaMemcpyFromSymbol(out, orbfront::g_qt_handed_back, sizeof(zero)) != cudaSuccess) return -1;
+  cudaMemcpyToSymbol(orbfront::g_qt_handed_back, &zero, sizeof(zero));
+  return 0;
+}
 
 #ifdef ORBX_QT_PROFILE2
 extern "C" int orbx_debug_qt_acc(unsigned long long* out) {

@@ -37,3 +37,14 @@ for _ in range(8):
 print("chunks=%s qt_keys=%s kind=%s n=%d stages(ms)=%s serial=%.3f batch(ms) min=%.3f med=%.3f -> %.0f frames/s" % (
     os.environ.get("ORBX_CHUNKS", "def"), os.environ.get("ORBX_QT_SMEM_KEYS", "def"), kind, n,
     {k: round(v, 3) for k, v in best.items()}, sum(best.values()), min(tot), sorted(tot)[len(tot) // 2], n / (min(tot) * 1e-3)))
+try:
+    import ctypes as C
+    from orb_slam2_e_b200 import _lib
+    lib = C.CDLL(os.path.join(os.path.dirname(_lib.__file__), "liborbfront.so"))
+    hb = C.c_uint(0)
+    lib.orbx_debug_qt_handed_back(C.byref(hb))
+    ext.extract_batch_device(dev.data_ptr(), n, h, w, w, w * h); ext.sync()
+    lib.orbx_debug_qt_handed_back(C.byref(hb))
+    print("quadtree: %d of %d (frame, level) pairs handed to the sorting kernel" % (hb.value, n * cfg[2]))
+except Exception as e:
+    print("no handed-back counter:", e)
