@@ -421,6 +421,10 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
   const int N = G.quota, dmax = G.dmax, D0 = G.qt_d0;
   int* const kc = &P.kept_count[f * P.nlevels + l];
   int n = min(P.cand_count[f * P.nlevels + l], G.cand_cap);
+#ifdef ORBX_QT_PROFILE2
+  long long qt_st[10];
+#endif
+  QT_STAMP(0);
   if (n == 0) { if (tid == 0) *kc = 0; return; }
   // sparse levels (few candidates per wanted keypoint) end deep in the tree: not worth trying here
   if (D0 <= 0 || n >= 65535 || 4ll * n < (long long)min_ratio4 * N) { if (tid == 0) *kc = -1; return; }  // the sorting kernel takes this level
@@ -450,6 +454,7 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
   for (int i = tid; i < cellsD0; i += T) best[i] = 0ull;
   for (int i = tid; i < kMaxDepth + 3; i += T) { C.cnt[i] = 0; C.nexp[i] = 0; }
   __syncthreads();
+  QT_STAMP(1);
   // one pass over the candidates: count and best key per depth-D0 cell
   const int shD0 = 2 * (dmax - D0);
   for (int i = tid; i < n; i += T) {
@@ -464,6 +469,7 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
     atomicMax(&best[c], ((unsigned long long)(pay >> 24) << 48) | (0xffffffffffffull - order));
   }
   __syncthreads();
+  QT_STAMP(2);
   // coarser grids (sums of four children) and, per depth, the number of nodes (cells with keys) and of divisible nodes
   for (int d = D0; d >= 0; --d) {
     const int cells = R << (2 * d), off = qp_level_off(R, D0, d), offc = d < D0 ? qp_level_off(R, D0, d + 1) : 0;
@@ -485,6 +491,7 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
     __syncthreads();
   }
   // replay of the reference's pass loop (:593-739) on cnt[] / nexp[], depths 1 .. Dr; the loop must end there
+  QT_STAMP(3);
   const int Dr = min(D0 - 1, dmax);
   if (tid < 32) {
     const int dd = tid;
@@ -500,6 +507,7 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
   }
   __syncthreads();
   if (C.d < 0) { if (tid == 0) *kc = -1; return; }
+  QT_STAMP(4);
 
   // ordered passes: biggest nodes first, stop as soon as the list holds N nodes (:676-737)
   bool first_ordered = true;
@@ -561,6 +569,7 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
   }
 
   // leaves: the nodes of depth dfin, and the children of those split by the final partial pass
+  QT_STAMP(5);
   const int dfin = C.d, partial = C.partial, d_bfs = C.d_bfs;
   if (dfin + partial > D0 || 2 * (D0 - dfin) > 8) { if (tid == 0) *kc = -1; return; }  // (leaf scans cover at most 256 depth-D0 cells)
   {
@@ -580,6 +589,7 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
     __syncthreads();
   }
   const int L = min(C.counter, G.kept_cap);
+  QT_STAMP(6);
   int lp = 1;
   while (lp < L) lp <<= 1;
   for (int m = tid; m < lp; m += T) {
@@ -606,9 +616,19 @@ quadtree_pyramid_kernel(const __grid_constant__ ExtractParams P, int NP, int cou
     nval[m] = best_pay;
   }
   __syncthreads();
+  QT_STAMP(7);
   bitonic_sort<T>(nkey, nval, lp);
+  QT_STAMP(8);
   for (int m = tid; m < L; m += T) kept[m] = nval[m];
   if (tid == 0) *kc = L;
+  QT_STAMP(9);
+#ifdef ORBX_QT_PROFILE2
+  if (tid == 0) {
+    for (int k = 0; k < 9; ++k) atomicAdd(&g_qt_acc[l][k], (unsigned long long)(qt_st[k + 1] - qt_st[k]));
+    atomicAdd(&g_qt_acc[l][9], 1ull);
+    atomicAdd(&g_qt_acc[l][10], (unsigned long long)n);
+  }
+#endif
 }
 
 int quadtree_pyramid_smem_bytes(int count_words, int split_words, int NP) {

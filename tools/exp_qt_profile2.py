@@ -7,6 +7,8 @@ from orb_slam2_e_b200 import synth, _lib
 from orb_slam2_e_b200.extractor import ORBextractor
 lib = C.CDLL(os.path.join(os.path.dirname(_lib.__file__), "liborbfront.so"))
 names = ["attach", "radix", "bounds", "replay", "ordered", "leaf heads", "leaf walk", "leaf sort", "emit", "ctas", "keys"]
+if os.environ.get("QP_NAMES"):  # the sort-free kernel's stamps
+    names = ["init", "count+best", "pyramid", "replay", "ordered", "leaf heads", "leaf build", "leaf sort", "emit", "ctas", "keys"]
 n, h, w = 1024, 480, 640
 host = synth.frame_batch("textured", n, h, w, 1000, distinct=32)
 dev = torch.from_numpy(host).cuda()
@@ -23,4 +25,4 @@ print("level  " + "  ".join("%9s" % x for x in names) + "   share")
 for l in range(8):
     print("%5d  " % l + "  ".join("%9.0f" % (a[l, k] / max(a[l, 9], 1)) for k in range(9)) + "  %9.0f  %9.0f   %.1f%%" % (a[l, 9], a[l, 10] / max(a[l, 9], 1), 100 * a[l, :9].sum() / tot))
 print("phase share: " + ", ".join("%s %.1f%%" % (names[k], 100 * a[:, k].sum() / tot) for k in range(9)))
-print("radix sub-phases (all CTAs, all passes): zero %.1f%%, histogram %.1f%%, scan %.1f%%, scatter %.1f%%" % tuple(100 * a[15, k] / a[15, :4].sum() for k in range(4)))
+if a[15, :4].sum() > 0: print("radix sub-phases (all CTAs, all passes): zero %.1f%%, histogram %.1f%%, scan %.1f%%, scatter %.1f%%" % tuple(100 * a[15, k] / a[15, :4].sum() for k in range(4)))
