@@ -584,13 +584,21 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
     const int k = div_up(n, size);
     if (k >= 8 && size >= 16) {
       // The pipeline is bound by the upload stream and ends one chunk's extraction after the last upload, so the chunks
-      // shrink linearly from 1.69x to 0.31x the mean size: the work still in flight when the last byte arrives is a
-      // third of a mean chunk's (1024 frames: 7.02 -> 6.86 ms per call against equal 64-frame chunks).
+      // shrink towards the end -- 1.5x the mean size for the first three eighths, then 1, 0.75, 0.5 and 0.25x (96 x 6,
+      // 64 x 4, 48 x 2, 32 x 2, 16 x 2 frames for 1024): large chunks where throughput counts, little work in flight when
+      // the last byte arrives (1024 frames: 6.72 -> 6.54 ms per call against equal 64-frame chunks).
+      std::vector<double> wgt(k);
+      double sum = 0;
+      for (int i = 0; i < k; ++i) {
+        const double p = (double)i / k;
+        wgt[i] = p < 0.375 ? 1.5 : p < 0.625 ? 1.0 : p < 0.75 ? 0.75 : p < 0.875 ? 0.5 : 0.25;
+        sum += wgt[i];
+      }
+      const int unit = size >= 64 ? 8 : 1;  // whole multiples of 8 frames where chunks are large
       double acc = 0;
       for (int i = 0; i < k; ++i) {
-        const int unit = size >= 64 ? 8 : 1;  // whole multiples of 8 frames where chunks are large
         chunk_begin.push_back((int)(acc / unit + 0.5) * unit);
-        acc += (double)n / k * (1.6875 - 1.375 * i / (k - 1));
+        acc += (double)n * wgt[i] / sum;
       }
     } else {
       for (int f0 = 0; f0 < n; f0 += size) chunk_begin.push_back(f0);

@@ -647,7 +647,9 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
   // level-0 CTA is the critical path, so CTAs are 1024 wide and keep up to 8192 keys in shared memory.
   // Batches: 256-thread CTAs with 2048 keys, many per SM (occupancy beats residency there).
   static const int wide_env = getenv("ORBX_QT_WIDE") ? atoi(getenv("ORBX_QT_WIDE")) : -1;
-  const bool wide = wide_env >= 0 ? wide_env != 0 : (long long)P.n_frames * P.nlevels <= 2 * 148;
+  // (a chunk of the host-batch pipeline -- no grid-barrier counter -- shares the GPU with the chunks around it: 1024-thread CTAs
+  // with 80 KB of shared memory would wait for half an SM to drain)
+  const bool wide = wide_env >= 0 ? wide_env != 0 : ((long long)P.n_frames * P.nlevels <= 2 * 148 && P.pyr_bar != nullptr);
   const int threads = wide ? kQtThreadsWide : kQtThreads;
   int NP = threads * 2;  // the radix counters ((threads / 32) x 256 x 4 B) alias the node tables (NP x 16 B)
   while (NP < nmax) NP <<= 1;
