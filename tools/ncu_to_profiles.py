@@ -67,8 +67,8 @@ def main():
         lines.append(k + "," + ",".join("%s %s" % d.get(x, ("", "")) for x in KEYS))
         t = (num(d, "dram__bytes_read.sum") or 0) + (num(d, "dram__bytes_write.sum") or 0)
         w = num(d, "smsp__inst_executed.sum") or 0
-        name = {"fast_cells_kernel": "fast", "blur_kernel": "blur", "orient_describe_kernel": "describe", "quadtree_select_kernel": "quadtree",
-                "top2_scan_kernel": "top2_scan"}.get(k)
+        name = {"fast_cells_kernel": "fast", "blur_kernel": "blur", "orient_describe_kernel": "describe", "quadtree_pyramid_kernel": "quadtree",
+                "quadtree_select_kernel": "quadtree_sorting", "top2_scan_kernel": "top2_scan"}.get(k)
         if k.startswith("resize_level"):
             n_resize += 1
             instr["per_step"]["pyramid"] = instr["per_step"].get("pyramid", 0) + w
@@ -80,8 +80,11 @@ def main():
         if name and name not in traffic:
             traffic[name] = t
             instr["per_launch"][name] = w
-            if name != "top2_scan":
-                instr["per_step"][name] = w
+            if name == "quadtree_sorting":  # the sorting kernel redoes the levels the sort-free kernel handed back: same stage
+                instr["per_step"]["quadtree"] = instr["per_step"].get("quadtree", 0) + w
+                traffic["quadtree"] = traffic.get("quadtree", 0) + t
+            elif name != "top2_scan":
+                instr["per_step"][name] = instr["per_step"].get(name, 0) + w
     instr["per_step"]["total"] = sum(v for k, v in instr["per_step"].items() if k != "total")
     instr["_note"] = "smsp__inst_executed.sum from profiles/%s_ncu_full.csv: executed warp instructions per launch, and per 1024-frame step (pyramid = its %d launches)" % (tag, n_resize)
     traffic["_note"] = "dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/%s_ncu_full.csv (ncu --set full, 1024-frame launches; pyramid_level1 = the level-1 launch)" % tag
