@@ -99,6 +99,14 @@ int orbx_batch_counts(orbx_handle* h, int* counts /* n */);
 int orbx_batch_read(orbx_handle* h, int frame, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
 /* Copies every frame's results in one transfer: frame f occupies rows [f*cap_per_frame, ...). */
 int orbx_batch_read_all(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts);
+/* Asynchronous form of orbx_batch_read_all (no reference counterpart: a Frame keeps its keypoints and descriptors on the
+ * host, Frame.cc:262-268, and a stereo Frame then matches them, :527-700 -- with the matching on the device
+ * (orbx_stereo_matches_batch) the download need not wait for it, nor it for the download).  _begin queues the
+ * copies behind the extraction on the handle's download stream and returns; other calls on the handle run beside the
+ * transfer; _end waits for it.  The host buffers must stay valid until _end and should be page-locked (pageable memory
+ * makes _begin itself wait).  The next extract call on the handle waits for an unfinished read. */
+int orbx_batch_read_begin(orbx_handle* h, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts);
+int orbx_batch_read_end(orbx_handle* h);
 /* Rows per frame that orbx_batch_read_all / orbx_extract_batch_host need for w x ht frames
  * (sum over levels of quota + 4 * quadtree roots + 3; the reference's DistributeOctTree may exceed
  * a level's quota by up to 3). */

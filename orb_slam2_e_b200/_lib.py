@@ -87,6 +87,8 @@ SIGNATURES = {
     "orbx_batch_counts": (_i, [_vp, _vp]),
     "orbx_batch_read": (_i, [_vp, _i, _vp, _vp, _i, _ip]),
     "orbx_batch_read_all": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "orbx_batch_read_begin": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "orbx_batch_read_end": (_i, [_vp]),
     "orbx_sync": (_i, [_vp]),
     "orbx_level_size": (_i, [_vp, _i, _ip, _ip]),
     "orbx_get_level": (_i, [_vp, _i, _i, _vp, _sz, _i]),

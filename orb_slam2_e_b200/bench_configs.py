@@ -198,12 +198,16 @@ def bench_stereo(B, args, rank, world, local, dist, with_cpu, n_pairs):
     ur_all = np.zeros((n_pairs, cap), np.float32)
     z_all = np.zeros((n_pairs, cap), np.float32)
 
+    pin_cnt = torch.zeros(n, dtype=torch.int32).pin_memory()
+    cnt = pin_cnt.numpy()
+
     def step():
         ext.extract_batch_device(dev.data_ptr(), n, h, w, pitch, pitch * h)
+        # the Frame keeps keypoints and descriptors on the host: their download runs beside the stereo kernels
+        ext.read_batch_begin(pin_kp.data_ptr(), pin_desc.data_ptr(), cap, pin_cnt.data_ptr())
         # mvuRight / mvDepth of every pair: three launches over the device-resident keypoints, one transfer
         _lib.check(L.orbx_stereo_matches_batch(ext._h, n_pairs, mb, KITTI_BF, _lib.ptr(ur_all), _lib.ptr(z_all), cap))
-        # the Frame keeps keypoints and descriptors on the host
-        ext.read_batch_into(pin_kp.data_ptr(), pin_desc.data_ptr(), cap, cnt)
+        ext.read_batch_end()
         return int((z_all > 0).sum())
 
     def step_per_pair():  # round-1 path: one orbx_stereo_matches call per pair on host keypoints

@@ -70,6 +70,8 @@ struct orbx_handle {
   Dev<uint8_t> border_tmp;
   // single-frame drop-in path: all bordered levels staged to page-locked memory on a side stream
   bool pyr_staging = false, pyr_pending = false;
+  bool read_pending = false;  // orbx_batch_read_begin queued copies on s_down that orbx_batch_read_end has not waited for
+  cudaEvent_t ev_read = nullptr;
   Dev<uint8_t> pyr_stage_dev;
   uint8_t* pyr_stage_host = nullptr;
   size_t pyr_stage_cap = 0, pyr_stage_off[kMaxLevels] = {};
@@ -371,6 +373,7 @@ int orbx_destroy(orbx_handle* H) {
   if (H->s_pyr) { cudaStreamSynchronize(H->s_pyr); cudaStreamDestroy(H->s_pyr); }
   if (H->ev_pyr_ready) cudaEventDestroy(H->ev_pyr_ready);
   if (H->ev_pyr_done) cudaEventDestroy(H->ev_pyr_done);
+  if (H->ev_read) cudaEventDestroy(H->ev_read);
   if (H->pyr_stage_host) cudaFreeHost(H->pyr_stage_host);
   if (H->out_stage_host) cudaFreeHost(H->out_stage_host);
   for (cudaEvent_t e : H->ev_up) cudaEventDestroy(e);
@@ -478,6 +481,10 @@ int orbx_extract_batch(orbx_handle* H, const uint8_t* imgs, int n, int w, int ht
     ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_pyr_done, 0));
     H->pyr_pending = false;
   }
+  if (H->read_pending) {  // so does an unfinished orbx_batch_read_begin
+    ORB_CUDA_TRY(cudaStreamSynchronize(H->s_down));
+    H->read_pending = false;
+  }
   if ((rc = check_limits(H, n, w, ht))) return rc;
   const bool alias = memory == 1 && ((uintptr_t)imgs % 16 == 0) && stride % 16 == 0 && (n == 1 || frame_stride % 16 == 0);
   // host frames with 16-byte-multiple strides are uploaded with one linear copy and read in place
@@ -541,6 +548,10 @@ int orbx_extract_batch_host(orbx_handle* H, const uint8_t* imgs, int n, int w, i
   if (H->pyr_pending) {  // the previous frame's staging copy reads the buffers this call rewrites
     ORB_CUDA_TRY(cudaStreamWaitEvent(H->stream, H->ev_pyr_done, 0));
     H->pyr_pending = false;
+  }
+  if (H->read_pending) {  // so does an unfinished orbx_batch_read_begin
+    ORB_CUDA_TRY(cudaStreamSynchronize(H->s_down));
+    H->read_pending = false;
   }
   if ((rc = check_limits(H, n, w, ht))) return rc;
   // frames whose rows and frame stride are 16-byte multiples are uploaded as they are (one linear
@@ -769,6 +780,38 @@ int orbx_batch_read_all(orbx_handle* H, orbx_keypoint* kps, uint8_t* desc, int c
   ORB_CUDA_TRY(cudaMemcpy2DAsync(desc, 32 * (size_t)cap_per_frame, H->out_desc.p, 32 * (size_t)oc, 32 * (size_t)oc,
                                  (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->stream));
   ORB_CUDA_TRY(cudaStreamSynchronize(H->stream));
+  return ORB_OK;
+}
+
+int orbx_batch_read_begin(orbx_handle* H, orbx_keypoint* kps, uint8_t* desc, int cap_per_frame, int* counts) {
+  if (!H || !kps || !desc || !counts) return set_error(ORB_E_INVALID, "orbx_batch_read_begin: bad argument");
+  if (H->n_frames == 0) return ORB_OK;
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  const int oc = H->P.out_cap;
+  if (cap_per_frame < oc)
+    return set_error(ORB_E_CAPACITY, "orbx_batch_read_begin: cap_per_frame %d < %d (per-frame output capacity)", cap_per_frame, oc);
+  if (!H->s_down) ORB_CUDA_TRY(cudaStreamCreateWithFlags(&H->s_down, cudaStreamNonBlocking));
+  if (!H->ev_read) ORB_CUDA_TRY(cudaEventCreateWithFlags(&H->ev_read, cudaEventDisableTiming));
+  // behind the extraction, beside whatever the handle's stream does next
+  ORB_CUDA_TRY(cudaEventRecord(H->ev_read, H->stream));
+  ORB_CUDA_TRY(cudaStreamWaitEvent(H->s_down, H->ev_read, 0));
+  ORB_CUDA_TRY(cudaMemcpyAsync(counts, H->out_count.p, sizeof(int) * (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->s_down));
+  ORB_CUDA_TRY(cudaMemcpy2DAsync(kps, sizeof(orbx_keypoint) * (size_t)cap_per_frame, H->out_kp.p, sizeof(orbx_keypoint) * (size_t)oc,
+                                 sizeof(orbx_keypoint) * (size_t)oc, (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->s_down));
+  ORB_CUDA_TRY(cudaMemcpy2DAsync(desc, 32 * (size_t)cap_per_frame, H->out_desc.p, 32 * (size_t)oc, 32 * (size_t)oc,
+                                 (size_t)H->n_frames, cudaMemcpyDeviceToHost, H->s_down));
+  H->read_pending = true;
+  return ORB_OK;
+}
+
+int orbx_batch_read_end(orbx_handle* H) {
+  if (!H) return set_error(ORB_E_INVALID, "orbx_batch_read_end: null");
+  if (!H->read_pending) return ORB_OK;
+  int rc = use_device(H->cfg.device);
+  if (rc) return rc;
+  ORB_CUDA_TRY(cudaStreamSynchronize(H->s_down));
+  H->read_pending = false;
   return ORB_OK;
 }
 

@@ -145,6 +145,13 @@ class ORBextractor:
             check(self._L.orbx_batch_read_all(self._h, ptr(kps), ptr(desc), cap, ptr(counts)))
         return [(kps[f, :counts[f]].copy(), desc[f, :counts[f]].copy()) for f in range(n)]
 
+    def read_batch_begin(self, kps_ptr: int, desc_ptr: int, cap: int, counts_ptr: int):
+        """orbx_batch_read_begin: queue the download of every frame's results (page-locked destinations) and return."""
+        check(self._L.orbx_batch_read_begin(self._h, C.c_void_p(kps_ptr), C.c_void_p(desc_ptr), cap, C.c_void_p(counts_ptr)))
+
+    def read_batch_end(self):
+        check(self._L.orbx_batch_read_end(self._h))
+
     def read_batch_into(self, kps_ptr: int, desc_ptr: int, cap: int, counts: np.ndarray):
         check(self._L.orbx_batch_read_all(self._h, C.c_void_p(kps_ptr), C.c_void_p(desc_ptr), cap, ptr(counts)))
 
