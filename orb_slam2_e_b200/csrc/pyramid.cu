@@ -142,17 +142,18 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
     w.w0 = __ldg(p); w.w1 = nw > 1 ? __ldg(p + 1) : 0u; w.w2 = nw > 2 ? __ldg(p + 2) : 0u;
   };
   int srow = t_cur.x;  // source row consumed next
-  Win wa, wb, wc;
+  Win wa, wb, wc, wd;
   request(srow, wa);
   request(srow + 1, wb);
   request(srow + 2, wc);
+  request(srow + 3, wd);
   uint32_t h0[4] = {0, 0, 0, 0}, h1[4] = {0, 0, 0, 0};
   // one source row: interpolate it horizontally (already >> 4) into hc, re-fill its window slot with row + 3, and emit
   // the destination row whose upper row is the previous source row (hp)
   auto step = [&](Win& w, const uint32_t (&hp)[4], uint32_t (&hc)[4]) {
     const uint32_t v0 = __funnelshift_r(w.w0, w.w1, sh), v1 = __funnelshift_r(w.w1, w.w2, sh);
     const uint32_t p01 = __byte_perm(v0, v1, sel01), p23 = __byte_perm(v0, v1, sel23);
-    request(srow + 3, w);
+    request(srow + 4, w);
     hc[0] = __dp2a_lo(coef[0], p01, 0u) >> 4;
     hc[1] = __dp2a_hi(coef[1], p01, 0u) >> 4;
     hc[2] = __dp2a_lo(coef[2], p23, 0u) >> 4;
@@ -171,13 +172,11 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
     }
     return ++srow > s_end;
   };
-  for (;;) {  // 6 = window ring (3) x interpolated-row ping-pong (2): no register moves between iterations
+  for (;;) {  // 4 = window ring (4) and interpolated-row ping-pong (2): no register moves between iterations
     if (step(wa, h0, h1)) break;
     if (step(wb, h1, h0)) break;
     if (step(wc, h0, h1)) break;
-    if (step(wa, h1, h0)) break;
-    if (step(wb, h0, h1)) break;
-    if (step(wc, h1, h0)) break;
+    if (step(wd, h1, h0)) break;
   }
 }
 
