@@ -308,7 +308,8 @@ template <int PITCH>
 static int launch_fast_pitch(const ExtractParams& P, cudaStream_t s, int max_h) {
   const int qk_entries = std::max(kQueue, (((PITCH - 8) / 2 + 1) * (max_h / 2 + 1) + 1) & ~1);  // as in the kernel
   const int warp_bytes = (int)align_up<size_t>((max_h + 6) * PITCH + (max_h + 2) * PITCH + 2 * qk_entries + 2 * ((max_h * ((PITCH - 8) / 4) + 1) & ~1), 16);  // tiles stay 16-byte aligned
-  const size_t smem = (size_t)warp_bytes * kFastWarps;  // <= 4 * ((65+61)*72 + 2 * 1024 + 2 * 944) < 48 KB
+  const size_t smem = (size_t)warp_bytes * kFastWarps;  // 59 x 56 cells (a level that is one cell): 49 392 bytes, just above the 48 KB default
+  if (smem > 48 * 1024) ORB_CUDA_TRY(cudaFuncSetAttribute(fast_cells_kernel<PITCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(div_up(P.total_cells, kFastWarps), P.n_frames);
   fast_cells_kernel<PITCH><<<grid, kFastWarps * 32, smem, s>>>(P, max_h, warp_bytes);
   ORB_LAUNCH_CHECK();

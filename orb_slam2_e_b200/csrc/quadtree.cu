@@ -675,6 +675,7 @@ int launch_quadtree(const ExtractParams& P, cudaStream_t s, int* launches) {
       if (!P.lv[l].qt_counts_global) cells_max = std::max(cells_max, qp_level_off(1 << rb, P.lv[l].qt_d0, 0) + (1 << rb));
     }
   }
+  split_words = (split_words + 3) & ~3;  // the 64-bit node keys follow the bitmap in shared memory
   const int only_flagged = (!no_pyramid && any_level) ? 1 : 0;
   static const int min_ratio4 = getenv("ORBX_QP_RATIO4") ? atoi(getenv("ORBX_QP_RATIO4")) : 12;  // candidates per wanted keypoint x 4 below which the sort-free kernel does not try
   if (only_flagged) {

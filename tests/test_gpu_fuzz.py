@@ -88,6 +88,14 @@ def test_random_case(seed):
     check(img, (nf, scale, nl, ini, mn))
 
 
+@pytest.mark.parametrize("seed", [131, 200, 257, 333])
+def test_random_case_found_by_extended_runs(seed):
+    """Seeds beyond the standard 36 that once failed: 131 (two quadtree roots and a 128-cell grid: the sort-free quadtree
+    kernel's shared-memory tables were misaligned), 200 (a level that is ONE 59 x 56 cell: the FAST tile needs a little more
+    than 48 KB of shared memory); two more as spot checks."""
+    test_random_case(seed)
+
+
 def test_wide_and_tall_aspect_ratios():
     rng = np.random.default_rng(5)
     check(rng.integers(0, 256, (100, 900), dtype=np.uint8), (1500, 1.2, 2, 20, 7))   # 13 quadtree roots
