@@ -134,3 +134,41 @@ def test_every_fast_tile_pitch_and_staging_shift(w, h, nlevels, scale, lo, hi):
     rng = np.random.default_rng(w * 1000 + h)
     for kind in ("noise", "blobs"):
         check(make_image(kind, h, w, rng), (400, scale, nlevels, 20, 7))
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_batch_takes_the_batch_kernels(seed):
+    """Batches of 40-90 frames select the batch variants of every stage (16-row resize strips, 112-row blur tiles,
+    256-thread quadtree CTAs of both selection kernels); a single frame selects the low-latency variants that the cases
+    above exercise.  Frames of a batch mix image kinds; a sample of them is compared with the oracle in full."""
+    rng = np.random.default_rng(7000 + seed)
+    h, w = int(rng.integers(120, 400)), int(rng.integers(160, 500))
+    scale = SCALES[int(rng.integers(0, len(SCALES)))]
+    nl = 1
+    while nl < 6 and min(h, w) / scale ** nl >= 70:
+        nl += 1
+    while any(round((round(w / scale ** l) - 32) / (round(h / scale ** l) - 32)) < 1 for l in range(nl)):
+        w += 16
+    nf = int(rng.integers(100, 2500))
+    ini, mn = THRESHOLDS[int(rng.integers(0, len(THRESHOLDS)))]
+    cfg = (nf, scale, nl, ini, mn)
+    # enough frames for every stage's batch variant (pyramid.cu launch_pyramid: >= 148 x 32 warps at level 1; quadtree.cu:
+    # more than 296 (frame, level) CTAs; blur: >= 296 warp tiles)
+    w1, h1 = round(w / scale), round(h / scale)
+    warps_l1 = -(-(-(-w1 // 32) * -(-h1 // 16)) // 4)
+    n = int(max(rng.integers(40, 90), -(-148 * 32 // warps_l1) + 4, 300 // nl + 2)) if nl > 1 else int(rng.integers(300, 400))
+    distinct = [make_image(KINDS[(seed + i) % len(KINDS)], h, w, rng) for i in range(6)]
+    frames = np.ascontiguousarray(np.stack([np.roll(distinct[i % 6], (i // 6) * 5, axis=1) for i in range(n)]))
+    g = ORBextractor(*cfg, max_width=w, max_height=h, max_batch=n)
+    res = g.extract_batch(frames)
+    port = PortExtractor(*cfg)
+    for f in sorted({0, 1, 5, n // 2, n - 7, n - 1}):
+        pk, pd = port.extract(frames[f])
+        gk, gd = res[f]
+        assert len(gk) == len(pk), (f, len(gk), len(pk))
+        for name in ("octave", "x", "y", "response", "size", "class_id"):
+            assert np.array_equal(gk[name], pk[name]), (f, name)
+        dang = np.abs(np.deg2rad(gk["angle"].astype(np.float64) - pk["angle"].astype(np.float64)))
+        assert np.minimum(dang, 2 * np.pi - dang).max(initial=0) <= 1e-3
+        if len(pk):
+            assert np.unpackbits(gd ^ pd).mean() <= 1e-4
