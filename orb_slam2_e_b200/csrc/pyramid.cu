@@ -20,7 +20,7 @@ namespace orbfront {
 // The strip length trades redundant work (each strip interpolates its first source rows again) for
 // parallelism: 16 rows for batches that fill the machine anyway, 4 rows when one or a few frames
 // would otherwise leave a handful of warps walking long dependent chains.
-constexpr int kStripBatch = 16, kStripFew = 4;
+constexpr int kStripLong = 32, kStripBatch = 16, kStripFew = 4;
 
 // Lane mapping (round 2): a warp owns four sub-tiles of 32 destination columns x kResizeStrip rows (8 lanes each),
 // consecutive in the level's row-major sub-tile order -- not one 128-column strip: level widths are rarely
@@ -242,6 +242,9 @@ int launch_pyramid(const ExtractParams& P, cudaStream_t s, int* launches) {
   const LevelGeom& D = P.lv[1];
   // warps the largest level offers with long strips; below about one warp per scheduler slot the
   // short strips win (measured: 640x480 x1 76 -> 49 us, 3840x2160 x1 121 -> 88 us)
+  // (32-row strips where even they fill the machine: the per-strip set-up -- tap table, first window loads -- is paid half as
+  // often: 1024 low-texture frames 0.804 -> 0.762 ms, textured 0.621 -> 0.614 ms)
+  if ((long)resize_warp_tiles(D.w, D.h, kStripLong) * P.n_frames >= 148 * 32) return launch_levels<kStripLong>(P, s, launches);
   const long warps_batch = (long)resize_warp_tiles(D.w, D.h, kStripBatch) * P.n_frames;
   if (warps_batch >= 148 * 32) return launch_levels<kStripBatch>(P, s, launches);
   const int blocks_few = div_up(resize_warp_tiles(D.w, D.h, kStripFew), 4) * P.n_frames;
