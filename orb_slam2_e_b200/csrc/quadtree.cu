@@ -1,4 +1,4 @@
-// Deterministic quadtree keypoint selection (sm_100a): one CTA per (frame, level).
+// Deterministic quadtree keypoint selection (sm_100a): one CTA per (frame, level) and kernel.
 //
 // Replaces ORBextractor::DistributeOctTree + ExtractorNode::DivideNode
 // (src/ORBextractor.cc:481-763), a sequential std::list algorithm, by an equivalent
@@ -17,6 +17,14 @@
 //     order inside a pass, single-key roots last in ascending order).
 // Integer/byte work, latency-bound inside a CTA; parallelism comes from the batch:
 // n_frames x n_levels independent CTAs.
+//
+// Two kernels implement this (launch_quadtree runs both, in this order):
+//   quadtree_pyramid_kernel  round 2, the common case: no sort at all -- per-cell key counts and best keys on a grid of
+//                            depth D0, the rules above replayed on the count pyramid (see its own comment below); it hands
+//                            a (frame, level) back (kept_count = -1) when the loop would need a deeper grid;
+//   quadtree_select_kernel   the sorted-path-code formulation described above, for the pairs handed back (and for
+//                            everything when ORBX_QT_NO_PYRAMID is set): every other CTA returns at once.
+// Both produce the same kept set in the same order (tests/test_gpu_quadtree_paths.py forces each of them).
 #include "extract.cuh"
 
 namespace orbfront {
