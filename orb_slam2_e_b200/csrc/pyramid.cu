@@ -18,7 +18,7 @@ namespace orbfront {
 // columns, keeps their horizontal taps in registers and reuses the horizontally interpolated
 // source row shared by consecutive destination rows.
 // The strip length trades redundant work (each strip interpolates its first source rows again) for
-// parallelism: 16 rows for batches that fill the machine anyway, 4 rows when one or a few frames
+// parallelism: 32 or 16 rows for batches that fill the machine anyway, 4 rows when one or a few frames
 // would otherwise leave a handful of warps walking long dependent chains.
 constexpr int kStripLong = 32, kStripBatch = 16, kStripFew = 4;
 
@@ -125,7 +125,7 @@ __device__ __forceinline__ void resize_words_block(const ExtractParams& P, int l
   // scale 1.2 (row i's lower row is row i+1's upper row), so every source row is loaded and interpolated
   // horizontally once, kept for one iteration, and a destination row is emitted whenever its upper row is the
   // previous source row (the table guarantees strictly increasing upper rows and lower = upper + 1, clamped at
-  // the last row -- checked on the host, extractor.cu).  Three source rows of loads are in flight.
+  // the last row -- checked on the host, extractor.cu).  Four source rows of loads are in flight.
   struct Win { uint32_t w0, w1, w2; };
   const int rows = min(kResizeStrip, D.h - y0);
   const ptrdiff_t dpitch = D.pitch;
